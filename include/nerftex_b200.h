@@ -1,0 +1,175 @@
+/* nerftex_b200.h — C ABI of libnerftex_b200.so (sm_100a).
+ *
+ * Drop-in boundary for the NeRF-Tex volume-rendering hot path.  The reference has no native
+ * FFI for this path (its arithmetic is TensorFlow eager ops); each entry point below therefore
+ * cites the reference *Python* call site it replaces (paths relative to hbaatz/nerf-tex).
+ * The Python host mirror in nerf_tex_b200/ binds these with ctypes; INTEGRATION.md shows the
+ * stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - every entry returns int: 0 = ok, <0 = error (NTX_E_*); ntx_last_error() gives the
+ *     message of the calling thread's last failure.
+ *   - all pointers are DEVICE pointers to contiguous row-major fp32 / int32 / int64 data unless
+ *     the comment says "host".  The caller owns every buffer (inputs, outputs, workspace).
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it and never
+ *     synchronise.  No entry allocates or frees device memory.
+ *   - there is no CPU fallback: on a machine without a CUDA device every compute entry fails
+ *     with NTX_E_CUDA.
+ */
+#ifndef NERFTEX_B200_H_
+#define NERFTEX_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NTX_VERSION 100 /* 0.1.0 */
+
+enum {
+    NTX_OK = 0,
+    NTX_E_INVALID = -1,     /* bad argument (null pointer, size out of range, unsupported config) */
+    NTX_E_CUDA = -2,        /* CUDA runtime error (message in ntx_last_error) */
+    NTX_E_UNSUPPORTED = -3, /* configuration outside what the sm_100a kernels implement */
+    NTX_E_NCCL = -4
+};
+
+int ntx_version(void);
+const char* ntx_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * K3 — sampling
+ * ---------------------------------------------------------------------------------------- */
+
+/* Stratified depths.  Replaces network/renderer.py:101-111 (Renderer.render_rays).
+ *   t[R,2] near/far, z_rand[R,S] uniform draws (required iff perturb), z[R,S] out.
+ * Bit-exact against the oracle's defined op order. */
+int ntx_stratified_z(const float* t, const float* z_rand, int R, int S, int perturb, float* z, void* stream);
+
+/* Inverse-CDF sampling.  Replaces network/renderer.py:589-618 (sample_pdf).
+ *   bins[R,C], weights[R,C-1]; u[R,N] uniform draws, or NULL when det (u = linspace(0,1,N));
+ *   samples[R,N] out; inds[R,N] out (searchsorted indices, may be NULL).  C <= 1025. */
+int ntx_sample_pdf(const float* bins, const float* weights, const float* u, int R, int C, int N, int det,
+                   float* samples, int32_t* inds, void* stream);
+
+/* Hierarchical resampling.  Replaces network/renderer.py:127-130: z_mid, sample_pdf(z_mid,
+ * weights[...,1:-1], N, det), sort(concat(z, z_samples)).
+ *   z[R,S], weights[R,S], u[R,N] or NULL; z_out[R,S+N]; z_samples[R,N], inds[R,N] optional.
+ *   S + N <= 1024. */
+int ntx_hierarchical_z(const float* z, const float* weights, const float* u, int R, int S, int N, int det,
+                       float* z_out, float* z_samples, int32_t* inds, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K2 — alpha compositing
+ * ---------------------------------------------------------------------------------------- */
+
+/* Replaces network/renderer.py:170-213 (Renderer.map_model_output).
+ *   packed != 0: `color` is rgbs[R,S,4] (raw r,g,b,sigma per sample; the layout ntx_mlp_forward
+ *                writes) and `sigma` is ignored.
+ *   packed == 0: color[R,S,3], sigma[R,S] (the reference's two model outputs).
+ *   z[R,S]; rays_d[R,3] (un-normalised; its norm scales dists); noise[R,S] already multiplied
+ *   by raw_noise_std, or NULL; bkgd_color: HOST pointer to 3 floats (used iff composite_bkgd).
+ *   Outputs: color_map[R,3], alpha_map[R], weights[R,S] (NULL to skip), depth[R] (NULL to
+ *   skip; the reference computes and discards it, :204). */
+int ntx_composite_forward(const float* color, const float* sigma, int packed, const float* z, const float* rays_d,
+                          const float* noise, int R, int S, int map_exr, int composite_bkgd,
+                          const float* bkgd_color, float* color_map, float* alpha_map, float* weights,
+                          float* depth, void* stream);
+
+/* Backward of ntx_composite_forward w.r.t. the raw model outputs (the reference obtains it from
+ * tf.GradientTape, network/train.py:62-66).  d_color_map[R,3], d_alpha_map[R] in;
+ * d_rgbs[R,S,4] out (packed raw r,g,b,sigma gradients).  Recomputes the forward per ray. */
+int ntx_composite_backward(const float* rgbs, const float* z, const float* rays_d, const float* noise, int R,
+                           int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                           const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream);
+
+/* Instanced compositing over CSR-packed in-shell samples.  Replaces network/renderer.py:300
+ * (density reweighting) and :318-354 (InstanceRenderer.map_model_output): the mesh hit
+ * (color_last, alpha_last) is appended as the final sample of every ray.
+ *   rgbs[T,4] raw model outputs of the T packed samples; dists[T]; alpha_weight[T] or NULL;
+ *   ray_ptr[H+1] int64 CSR offsets; color_last[H,3]; alpha_last[H];
+ *   ray_index[H] int32 destination row of each hit ray in the outputs, or NULL (identity);
+ *   instance_color[T,3] or NULL (false_color rendering, :306-307, :322-323);
+ *   color_map[n_out,3], alpha_map[n_out] are written only at hit rows (caller pre-zeroes, :313-314). */
+int ntx_composite_instanced_forward(const float* rgbs, const float* dists, const float* alpha_weight,
+                                    const int64_t* ray_ptr, const float* color_last, const float* alpha_last,
+                                    const int32_t* ray_index, const float* instance_color, int H,
+                                    float patch_scale, float density_scale, int map_exr, int composite_bkgd,
+                                    const float* bkgd_color, float* color_map, float* alpha_map, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K1 — fused positional encoding + conditioned MLP (bf16 tcgen05 / TMEM, fp32 accumulate)
+ * ---------------------------------------------------------------------------------------- */
+
+/* Architecture of network/model.py:58-125 (ParamNerf; Nerf :9-45 is n_geo = n_app = 0,
+ * color_depth = 0).  Supported by the sm_100a kernel: n_pos = 3, pos_freqs = 10, dir_freqs = 4,
+ * param_freqs = 4, width = 256, param_depth = 0, n_geo <= 3, n_app <= 7, depth <= 16. */
+typedef struct ntx_mlp_config {
+    int32_t n_pos;       /* 3 */
+    int32_t pos_freqs;   /* 10 */
+    int32_t dir_freqs;   /* 4 */
+    int32_t param_freqs; /* 4 */
+    int32_t n_geo;       /* n_parameters[0] */
+    int32_t n_app;       /* n_parameters[1] */
+    int32_t depth;       /* 8 */
+    int32_t width;       /* 256 */
+    int32_t skip_mask;   /* bit i set <=> i in skips (default 1<<4) */
+    int32_t color_depth; /* 1 */
+} ntx_mlp_config;
+
+typedef struct ntx_mlp ntx_mlp_t; /* opaque host-side handle: layer table only, owns no device memory */
+
+int ntx_mlp_create(const ntx_mlp_config* cfg, ntx_mlp_t** out);
+int ntx_mlp_destroy(ntx_mlp_t* mlp);
+
+/* Number of fp32 elements of the flat master weight buffer: for every Dense layer in graph
+ * order (trunk0..trunk{depth-1}, alpha, feature, colorhid0.., colorhalf, rgb) the Keras kernel
+ * W[in,out] row-major followed by the bias b[out].  Rows of W follow the reference's concat
+ * order ([pos_map, h] after a skip, [dir_map, feature]; network/model.py:108,115). */
+int64_t ntx_mlp_num_params(const ntx_mlp_t* mlp);
+/* Offset (in floats) of layer `i`'s kernel inside the flat buffer; fan_in/fan_out returned. */
+int ntx_mlp_num_layers(const ntx_mlp_t* mlp);
+int ntx_mlp_layer_info(const ntx_mlp_t* mlp, int i, int64_t* w_offset, int64_t* b_offset, int32_t* fan_in,
+                       int32_t* fan_out);
+/* Bytes of the packed bf16 weight image consumed by ntx_mlp_forward. */
+int64_t ntx_mlp_packed_bytes(const ntx_mlp_t* mlp);
+/* fp32 flat master (device) -> packed bf16 UMMA-canonical K-slices + fp32 head block (device). */
+int ntx_mlp_pack_weights(const ntx_mlp_t* mlp, const float* master, void* packed, void* stream);
+
+/* Model inputs.  Row r of the batch belongs to group g = r / rows_per_group (rows_per_group = S
+ * for the plain renderer where view dir and parameters are per ray, network/renderer.py:152-154;
+ * 1 for the instanced renderer where they are per sample, :278-280). */
+typedef struct ntx_mlp_inputs {
+    const float* pos;        /* [N,3] sample positions, or NULL to use rays_o + rays_d * z */
+    const float* rays_o;     /* [G,3] (used when pos == NULL; network/renderer.py:114) */
+    const float* rays_d;     /* [G,3] */
+    const float* z;          /* [N]   */
+    const float* dir;        /* [G,3] view direction fed to the network (already normalised) */
+    const float* params;     /* [G,n_geo+n_app] or NULL when the model has no parameters */
+    const float* row_scale;  /* [N] or NULL: blur multiplier per row (z, :156) */
+    const float* group_scale;/* [G] or NULL: blur multiplier per group (cone_scale, :156) */
+    int32_t blur_idx;        /* parameter index scaled by row_scale*group_scale, or -1 (:155-158) */
+    int32_t rows_per_group;
+    int64_t n_rows;          /* N */
+} ntx_mlp_inputs;
+
+/* Forward.  Replaces the Keras model call of network/renderer.py:160-161 / :290-291 including
+ * the FourierFeatures of network/layer.py:11-23.  rgbs[N,4] out: raw colour (pre-sigmoid) and
+ * raw density (pre-relu), network/model.py:111,123. */
+int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * tcgen05 self-test (used by tests/ to validate the UMMA shared-memory descriptors on a GPU)
+ * ---------------------------------------------------------------------------------------- */
+/* D[128,N] = A[128,K] * B[N,K]^T with bf16 inputs (given as fp32, rounded to bf16 on device),
+ * fp32 accumulate.  layout: 0 = SWIZZLE_64B K-slices of 32, 1 = SWIZZLE_128B K-slices of 64,
+ * 2 = no swizzle (interleaved core matrices). K multiple of 64, N in {128,256}. */
+int ntx_selftest_umma(const float* A, const float* B, int N, int K, int layout, float* D, void* stream);
+/* global -> shared through cp.async.bulk + mbarrier, then back out: dst[0:bytes] = src[0:bytes]. */
+int ntx_selftest_bulk_copy(const void* src, void* dst, int bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NERFTEX_B200_H_ */

@@ -1,0 +1,345 @@
+// K2 — alpha compositing (HBM-bound, one warp per ray).
+//
+// Per round a warp loads 32 consecutive samples of its ray (one 128-bit rgb-sigma load and one
+// depth per lane, fully coalesced), maps sigma to alpha, forms the transmittance with a
+// warp-level exclusive product scan (5 shuffles) chained across rounds by a carry, and keeps
+// per-lane partial sums of w*rgb, w*z and w that are reduced once per ray.
+//
+// Algorithmic HBM bytes: plain 24*S + 28 per ray (rgb 12 + sigma 4 + z 4 read,
+// weights 4 written per sample; rays_d 12 read, rgb 12 + acc 4 written per ray).
+#include "ntx_common.cuh"
+
+namespace {
+
+__device__ __forceinline__ float color_act(float c, int map_exr) {
+    // renderer.py:182-187
+    if (map_exr) return c > 0.0f ? c + 1.0f : expf(c);
+    return 1.0f / (1.0f + expf(-c));
+}
+
+__device__ __forceinline__ float color_act_grad(float c, float y, int map_exr) {
+    // derivative of color_act given its output y
+    if (map_exr) return c > 0.0f ? 1.0f : y;
+    return y * (1.0f - y);
+}
+
+// inclusive product scan across the warp
+__device__ __forceinline__ float warp_scan_mul(float v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v *= n;
+    }
+    return v;
+}
+
+__device__ __forceinline__ float warp_scan_add(float v, int lane) {
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        float n = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += n;
+    }
+    return v;
+}
+
+__device__ __forceinline__ float4 ldg_stream_f4(const float4* p) {
+    float4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+    return r;
+}
+
+struct Sample {
+    float r, g, b, s;
+};
+
+template <bool PACKED>
+__device__ __forceinline__ Sample load_sample(const float* color, const float* sigma, int64_t k) {
+    Sample o;
+    if (PACKED) {
+        float4 v = ldg_stream_f4(reinterpret_cast<const float4*>(color) + k);
+        o.r = v.x; o.g = v.y; o.b = v.z; o.s = v.w;
+    } else {
+        o.r = __ldg(color + 3 * k); o.g = __ldg(color + 3 * k + 1); o.b = __ldg(color + 3 * k + 2);
+        o.s = __ldg(sigma + k);
+    }
+    return o;
+}
+
+// distance of sample i to the next one; the last distance is duplicated (renderer.py:174-177)
+__device__ __forceinline__ float sample_dist(const float* zrow, int i, int S, float zi) {
+    if (S == 1) return 0.0f;
+    if (i < S - 1) return __ldg(zrow + i + 1) - zi;
+    return zi - __ldg(zrow + i - 1);
+}
+
+template <bool PACKED>
+__global__ void __launch_bounds__(256)
+composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ sigma, const float* __restrict__ z,
+                     const float* __restrict__ rays_d, const float* __restrict__ noise, int R, int S, int map_exr,
+                     int composite_bkgd, float bk0, float bk1, float bk2, float* __restrict__ color_map,
+                     float* __restrict__ alpha_map, float* __restrict__ weights, float* __restrict__ depth) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < R; ray += nwarps) {
+        const float d0 = __ldg(rays_d + 3 * ray), d1 = __ldg(rays_d + 3 * ray + 1), d2 = __ldg(rays_d + 3 * ray + 2);
+        const float norm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);                 // renderer.py:180
+        const float* zrow = z + ray * S;
+        float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f, dep = 0.0f;
+        for (int base = 0; base < S; base += 32) {
+            const int i = base + lane;
+            const bool valid = i < S;
+            float a = 0.0f, zi = 0.0f;
+            Sample sm = {0.f, 0.f, 0.f, 0.f};
+            if (valid) {
+                const int64_t k = ray * S + i;
+                sm = load_sample<PACKED>(color, sigma, k);
+                zi = __ldg(zrow + i);
+                float dist = sample_dist(zrow, i, S, zi) * norm;
+                float s = sm.s;
+                if (noise) s += __ldg(noise + k);                               // renderer.py:190-195
+                s = fmaxf(s, 0.0f);
+                a = 1.0f - expf(-s * dist);
+            }
+            const float om = (1.0f - a) + 1e-10f;                               // renderer.py:198
+            const float incl = warp_scan_mul(om, lane);
+            float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+            if (lane == 0) excl = 1.0f;
+            const float w = a * (carry * excl);
+            carry *= __shfl_sync(0xffffffffu, incl, 31);
+            if (valid) {
+                if (weights) weights[ray * S + i] = w;
+                c0 += w * color_act(sm.r, map_exr);                             // renderer.py:201
+                c1 += w * color_act(sm.g, map_exr);
+                c2 += w * color_act(sm.b, map_exr);
+                dep += w * zi;                                                  // renderer.py:204
+                acc += w;                                                       // renderer.py:207
+            }
+        }
+        c0 = ntx_warp_sum(c0); c1 = ntx_warp_sum(c1); c2 = ntx_warp_sum(c2);
+        acc = ntx_warp_sum(acc);
+        dep = ntx_warp_sum(dep);
+        if (lane == 0) {
+            if (composite_bkgd) {                                               // renderer.py:210-211
+                const float om = 1.0f - acc;
+                c0 += om * bk0; c1 += om * bk1; c2 += om * bk2;
+            }
+            color_map[3 * ray] = c0; color_map[3 * ray + 1] = c1; color_map[3 * ray + 2] = c2;
+            alpha_map[ray] = acc;
+            if (depth) depth[ray] = dep;
+        }
+    }
+}
+
+// Backward w.r.t. the packed raw outputs.  Pass 1 recomputes the forward and accumulates
+// G = sum_k gw_k * w_k; pass 2 recomputes again and emits
+//   d a_i   = gw_i * T_i - (G - prefix_incl_i) / om_i
+//   d sigma = d a_i * dist_i * (1 - a_i) * [sigma_i + noise_i > 0]
+//   d rgb   = w_i * dC * act'(raw)
+__global__ void __launch_bounds__(256)
+composite_bwd_kernel(const float* __restrict__ rgbs, const float* __restrict__ z, const float* __restrict__ rays_d,
+                     const float* __restrict__ noise, int R, int S, int map_exr, int composite_bkgd, float bk0,
+                     float bk1, float bk2, const float* __restrict__ d_color_map,
+                     const float* __restrict__ d_alpha_map, float* __restrict__ d_rgbs) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < R; ray += nwarps) {
+        const float d0 = __ldg(rays_d + 3 * ray), d1 = __ldg(rays_d + 3 * ray + 1), d2 = __ldg(rays_d + 3 * ray + 2);
+        const float norm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);
+        const float g0 = __ldg(d_color_map + 3 * ray), g1 = __ldg(d_color_map + 3 * ray + 1),
+                    g2 = __ldg(d_color_map + 3 * ray + 2);
+        float gA = __ldg(d_alpha_map + ray);
+        if (composite_bkgd) gA -= g0 * bk0 + g1 * bk1 + g2 * bk2;
+        const float* zrow = z + ray * S;
+        float G = 0.0f;
+        for (int pass = 0; pass < 2; ++pass) {
+            float carry = 1.0f, gcarry = 0.0f, gsum = 0.0f;
+            for (int base = 0; base < S; base += 32) {
+                const int i = base + lane;
+                const bool valid = i < S;
+                float a = 0.0f, dist = 0.0f, sraw = 0.0f;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (valid) {
+                    const int64_t k = ray * S + i;
+                    v = __ldg(reinterpret_cast<const float4*>(rgbs) + k);
+                    const float zi = __ldg(zrow + i);
+                    dist = sample_dist(zrow, i, S, zi) * norm;
+                    sraw = v.w;
+                    if (noise) sraw += __ldg(noise + k);
+                    a = 1.0f - expf(-fmaxf(sraw, 0.0f) * dist);
+                }
+                const float om = (1.0f - a) + 1e-10f;
+                const float incl = warp_scan_mul(om, lane);
+                float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+                if (lane == 0) excl = 1.0f;
+                const float T = carry * excl;
+                const float w = a * T;
+                carry *= __shfl_sync(0xffffffffu, incl, 31);
+                const float y0 = color_act(v.x, map_exr), y1 = color_act(v.y, map_exr), y2 = color_act(v.z, map_exr);
+                const float gw = valid ? (g0 * y0 + g1 * y1 + g2 * y2 + gA) : 0.0f;
+                const float gww = gw * w;
+                if (pass == 0) {
+                    gsum += gww;
+                } else {
+                    const float gscan = warp_scan_add(gww, lane);
+                    const float pre = gcarry + gscan;
+                    gcarry += __shfl_sync(0xffffffffu, gscan, 31);
+                    if (valid) {
+                        const float da = gw * T - (G - pre) / om;
+                        const float ds = (sraw > 0.0f) ? da * dist * (1.0f - a) : 0.0f;
+                        float4 o;
+                        o.x = w * g0 * color_act_grad(v.x, y0, map_exr);
+                        o.y = w * g1 * color_act_grad(v.y, y1, map_exr);
+                        o.z = w * g2 * color_act_grad(v.z, y2, map_exr);
+                        o.w = ds;
+                        reinterpret_cast<float4*>(d_rgbs)[ray * S + i] = o;
+                    }
+                }
+            }
+            if (pass == 0) G = ntx_warp_sum(gsum);
+        }
+    }
+}
+
+// Instanced variant over CSR-packed samples with the mesh hit appended (renderer.py:318-354).
+__global__ void __launch_bounds__(256)
+composite_inst_kernel(const float* __restrict__ rgbs, const float* __restrict__ dists,
+                      const float* __restrict__ alpha_weight, const int64_t* __restrict__ ray_ptr,
+                      const float* __restrict__ color_last, const float* __restrict__ alpha_last,
+                      const int32_t* __restrict__ ray_index, const float* __restrict__ instance_color, int H,
+                      float patch_scale, float density_scale, int map_exr, int composite_bkgd, float bk0, float bk1,
+                      float bk2, float* __restrict__ color_map, float* __restrict__ alpha_map) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t h = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; h < H; h += nwarps) {
+        const int64_t beg = __ldg(ray_ptr + h), end = __ldg(ray_ptr + h + 1);
+        float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f;
+        for (int64_t base = beg; base < end; base += 32) {
+            const int64_t k = base + lane;
+            const bool valid = k < end;
+            float a = 0.0f;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (valid) {
+                v = ldg_stream_f4(reinterpret_cast<const float4*>(rgbs) + k);
+                float s = v.w;
+                if (alpha_weight) s *= __ldg(alpha_weight + k) * density_scale;  // renderer.py:300
+                else s *= density_scale;
+                s = fmaxf(s, 0.0f);
+                a = 1.0f - expf(-(s * __ldg(dists + k)) / patch_scale);         // renderer.py:339
+            }
+            const float om = (1.0f - a) + 1e-10f;
+            const float incl = warp_scan_mul(om, lane);
+            float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+            if (lane == 0) excl = 1.0f;
+            const float w = a * (carry * excl);
+            carry *= __shfl_sync(0xffffffffu, incl, 31);
+            if (valid) {
+                float y0, y1, y2;
+                if (instance_color) {                                           // renderer.py:306-307,322-323
+                    y0 = __ldg(instance_color + 3 * k); y1 = __ldg(instance_color + 3 * k + 1);
+                    y2 = __ldg(instance_color + 3 * k + 2);
+                } else {
+                    y0 = color_act(v.x, map_exr); y1 = color_act(v.y, map_exr); y2 = color_act(v.z, map_exr);
+                }
+                c0 += w * y0; c1 += w * y1; c2 += w * y2;
+                acc += w;
+            }
+        }
+        c0 = ntx_warp_sum(c0); c1 = ntx_warp_sum(c1); c2 = ntx_warp_sum(c2);
+        acc = ntx_warp_sum(acc);
+        if (lane == 0) {
+            // appended sample S+1: the opaque mesh hit (renderer.py:331,339)
+            const float al = __ldg(alpha_last + h);
+            const float wl = al * carry;
+            c0 += wl * __ldg(color_last + 3 * h); c1 += wl * __ldg(color_last + 3 * h + 1);
+            c2 += wl * __ldg(color_last + 3 * h + 2);
+            acc += wl;
+            if (composite_bkgd) {
+                const float om = 1.0f - acc;
+                c0 += om * bk0; c1 += om * bk1; c2 += om * bk2;
+            }
+            const int64_t dst = ray_index ? (int64_t)__ldg(ray_index + h) : h;
+            color_map[3 * dst] = c0; color_map[3 * dst + 1] = c1; color_map[3 * dst + 2] = c2;
+            alpha_map[dst] = acc;
+        }
+    }
+}
+
+int grid_for_warps(int64_t n_warp_items, int threads) {
+    const int warps_per_block = threads / 32;
+    int64_t blocks = (n_warp_items + warps_per_block - 1) / warps_per_block;
+    const int64_t cap = (int64_t)ntx_sm_count() * 8 * 4;   // a few waves of 8 resident blocks per SM
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+}  // namespace
+
+NTX_API int ntx_composite_forward(const float* color, const float* sigma, int packed, const float* z,
+                                  const float* rays_d, const float* noise, int R, int S, int map_exr,
+                                  int composite_bkgd, const float* bkgd_color, float* color_map, float* alpha_map,
+                                  float* weights, float* depth, void* stream) {
+    NTX_REQUIRE(R >= 0 && S >= 1, "composite_forward: bad shape R=%d S=%d", R, S);
+    if (R == 0) return NTX_OK;
+    NTX_REQUIRE(color && z && rays_d && color_map && alpha_map, "composite_forward: null pointer");
+    NTX_REQUIRE(packed || sigma, "composite_forward: split layout requires sigma");
+    NTX_REQUIRE(!composite_bkgd || bkgd_color, "composite_forward: composite_bkgd requires bkgd_color");
+    NTX_REQUIRE(!packed || ((uintptr_t)color & 15) == 0, "composite_forward: packed rgbs must be 16-byte aligned");
+    const float b0 = composite_bkgd ? bkgd_color[0] : 0.f, b1 = composite_bkgd ? bkgd_color[1] : 0.f,
+                b2 = composite_bkgd ? bkgd_color[2] : 0.f;
+    const int threads = 256;
+    const int grid = grid_for_warps(R, threads);
+    cudaStream_t st = (cudaStream_t)stream;
+    if (packed)
+        composite_fwd_kernel<true><<<grid, threads, 0, st>>>(color, sigma, z, rays_d, noise, R, S, map_exr,
+                                                             composite_bkgd, b0, b1, b2, color_map, alpha_map,
+                                                             weights, depth);
+    else
+        composite_fwd_kernel<false><<<grid, threads, 0, st>>>(color, sigma, z, rays_d, noise, R, S, map_exr,
+                                                              composite_bkgd, b0, b1, b2, color_map, alpha_map,
+                                                              weights, depth);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}
+
+NTX_API int ntx_composite_backward(const float* rgbs, const float* z, const float* rays_d, const float* noise, int R,
+                                   int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                                   const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream) {
+    NTX_REQUIRE(R >= 0 && S >= 1, "composite_backward: bad shape R=%d S=%d", R, S);
+    if (R == 0) return NTX_OK;
+    NTX_REQUIRE(rgbs && z && rays_d && d_color_map && d_alpha_map && d_rgbs, "composite_backward: null pointer");
+    NTX_REQUIRE(!composite_bkgd || bkgd_color, "composite_backward: composite_bkgd requires bkgd_color");
+    NTX_REQUIRE((((uintptr_t)rgbs | (uintptr_t)d_rgbs) & 15) == 0, "composite_backward: rgbs must be 16-byte aligned");
+    const float b0 = composite_bkgd ? bkgd_color[0] : 0.f, b1 = composite_bkgd ? bkgd_color[1] : 0.f,
+                b2 = composite_bkgd ? bkgd_color[2] : 0.f;
+    const int threads = 256;
+    composite_bwd_kernel<<<grid_for_warps(R, threads), threads, 0, (cudaStream_t)stream>>>(
+        rgbs, z, rays_d, noise, R, S, map_exr, composite_bkgd, b0, b1, b2, d_color_map, d_alpha_map, d_rgbs);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}
+
+NTX_API int ntx_composite_instanced_forward(const float* rgbs, const float* dists, const float* alpha_weight,
+                                            const int64_t* ray_ptr, const float* color_last,
+                                            const float* alpha_last, const int32_t* ray_index,
+                                            const float* instance_color, int H, float patch_scale,
+                                            float density_scale, int map_exr, int composite_bkgd,
+                                            const float* bkgd_color, float* color_map, float* alpha_map,
+                                            void* stream) {
+    NTX_REQUIRE(H >= 0, "composite_instanced_forward: bad H=%d", H);
+    if (H == 0) return NTX_OK;
+    NTX_REQUIRE(ray_ptr && color_last && alpha_last && color_map && alpha_map,
+                "composite_instanced_forward: null pointer");
+    NTX_REQUIRE(patch_scale > 0.0f, "composite_instanced_forward: patch_scale must be positive");
+    NTX_REQUIRE(!composite_bkgd || bkgd_color, "composite_instanced_forward: composite_bkgd requires bkgd_color");
+    NTX_REQUIRE(((uintptr_t)rgbs & 15) == 0, "composite_instanced_forward: rgbs must be 16-byte aligned");
+    const float b0 = composite_bkgd ? bkgd_color[0] : 0.f, b1 = composite_bkgd ? bkgd_color[1] : 0.f,
+                b2 = composite_bkgd ? bkgd_color[2] : 0.f;
+    const int threads = 256;
+    composite_inst_kernel<<<grid_for_warps(H, threads), threads, 0, (cudaStream_t)stream>>>(
+        rgbs, dists, alpha_weight, ray_ptr, color_last, alpha_last, ray_index, instance_color, H, patch_scale,
+        density_scale, map_exr, composite_bkgd, b0, b1, b2, color_map, alpha_map);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}

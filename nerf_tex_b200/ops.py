@@ -1,0 +1,158 @@
+"""Tensor-level wrappers over the C ABI (one function per ``ntx_*`` entry point).
+
+Inputs are torch CUDA tensors (or any DLPack exporter, see ``_lib.as_cuda``); outputs are freshly
+allocated torch CUDA tensors.  All launches go to torch's current stream.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import as_cuda, check, ptr, stream_ptr
+
+
+def _bkgd(bkgd_color) -> "C.Array":
+    vals = [float(v) for v in (bkgd_color.tolist() if hasattr(bkgd_color, "tolist") else bkgd_color)]
+    return (C.c_float * 3)(*vals)
+
+
+# ------------------------------------------------------------------------------------------ K3
+
+def stratified_z(t: torch.Tensor, n_samples: int, perturb: bool, z_rand: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """network/renderer.py:101-111.  t[R,2] -> z[R,S]; z_rand[R,S] required iff perturb."""
+    t = as_cuda(t)
+    R = t.shape[0]
+    z = torch.empty((R, n_samples), dtype=torch.float32, device=t.device)
+    if perturb:
+        if z_rand is None:
+            raise _lib.NtxError("stratified_z: perturb=True needs explicit uniform draws z_rand[R,S]")
+        z_rand = as_cuda(z_rand)
+        assert z_rand.shape == (R, n_samples)
+    check(_lib.load().ntx_stratified_z(ptr(t), ptr(z_rand) if perturb else None, R, n_samples, int(perturb), ptr(z),
+                                       stream_ptr()))
+    return z
+
+
+def sample_pdf(bins: torch.Tensor, weights: torch.Tensor, n_samples: int, det: bool = False,
+               u: Optional[torch.Tensor] = None, return_inds: bool = False):
+    """network/renderer.py:589-618 on [R,C] bins / [R,C-1] weights."""
+    bins, weights = as_cuda(bins), as_cuda(weights)
+    R, Cb = bins.shape
+    assert weights.shape == (R, Cb - 1)
+    if not det:
+        if u is None:
+            u = torch.rand((R, n_samples), dtype=torch.float32, device=bins.device)
+        u = as_cuda(u)
+        assert u.shape == (R, n_samples)
+    samples = torch.empty((R, n_samples), dtype=torch.float32, device=bins.device)
+    inds = torch.empty((R, n_samples), dtype=torch.int32, device=bins.device) if return_inds else None
+    check(_lib.load().ntx_sample_pdf(ptr(bins), ptr(weights), None if det else ptr(u), R, Cb, n_samples, int(det),
+                                     ptr(samples), ptr(inds), stream_ptr()))
+    return (samples, inds) if return_inds else samples
+
+
+def hierarchical_z(z: torch.Tensor, weights: torch.Tensor, n_importance: int, det: bool,
+                   u: Optional[torch.Tensor] = None, return_aux: bool = False):
+    """network/renderer.py:127-130: merged, sorted depths [R,S+N]."""
+    z, weights = as_cuda(z), as_cuda(weights)
+    R, S = z.shape
+    assert weights.shape == (R, S)
+    if not det:
+        if u is None:
+            u = torch.rand((R, n_importance), dtype=torch.float32, device=z.device)
+        u = as_cuda(u)
+    z_out = torch.empty((R, S + n_importance), dtype=torch.float32, device=z.device)
+    zs = torch.empty((R, n_importance), dtype=torch.float32, device=z.device) if return_aux else None
+    inds = torch.empty((R, n_importance), dtype=torch.int32, device=z.device) if return_aux else None
+    check(_lib.load().ntx_hierarchical_z(ptr(z), ptr(weights), None if det else ptr(u), R, S, n_importance, int(det),
+                                         ptr(z_out), ptr(zs), ptr(inds), stream_ptr()))
+    return (z_out, zs, inds) if return_aux else z_out
+
+
+# ------------------------------------------------------------------------------------------ K2
+
+def composite_forward(rgbs: Optional[torch.Tensor], z: torch.Tensor, rays_d: torch.Tensor, *,
+                      color: Optional[torch.Tensor] = None, sigma: Optional[torch.Tensor] = None,
+                      noise: Optional[torch.Tensor] = None, map_exr: bool = False, composite_bkgd: bool = False,
+                      bkgd_color=(1., 1., 1.), want_weights: bool = True, want_depth: bool = False):
+    """network/renderer.py:170-213.  Either packed rgbs[R,S,4] or split color[R,S,3] + sigma[R,S]."""
+    z, rays_d = as_cuda(z), as_cuda(rays_d)
+    R, S = z.shape
+    packed = rgbs is not None
+    if packed:
+        rgbs = as_cuda(rgbs)
+        assert rgbs.shape == (R, S, 4)
+        cptr, sptr = ptr(rgbs), None
+    else:
+        color, sigma = as_cuda(color), as_cuda(sigma)
+        assert color.shape == (R, S, 3) and sigma.shape == (R, S)
+        cptr, sptr = ptr(color), ptr(sigma)
+    if noise is not None:
+        noise = as_cuda(noise)
+    dev = z.device
+    cmap = torch.empty((R, 3), dtype=torch.float32, device=dev)
+    amap = torch.empty((R,), dtype=torch.float32, device=dev)
+    w = torch.empty((R, S), dtype=torch.float32, device=dev) if want_weights else None
+    d = torch.empty((R,), dtype=torch.float32, device=dev) if want_depth else None
+    check(_lib.load().ntx_composite_forward(cptr, sptr, int(packed), ptr(z), ptr(rays_d), ptr(noise), R, S,
+                                            int(map_exr), int(composite_bkgd), _bkgd(bkgd_color), ptr(cmap),
+                                            ptr(amap), ptr(w), ptr(d), stream_ptr()))
+    return cmap, amap, w, d
+
+
+def composite_backward(rgbs, z, rays_d, d_color_map, d_alpha_map, *, noise=None, map_exr=False, composite_bkgd=False,
+                       bkgd_color=(1., 1., 1.)) -> torch.Tensor:
+    rgbs, z, rays_d = as_cuda(rgbs), as_cuda(z), as_cuda(rays_d)
+    d_color_map, d_alpha_map = as_cuda(d_color_map), as_cuda(d_alpha_map)
+    R, S = z.shape
+    if noise is not None:
+        noise = as_cuda(noise)
+    d_rgbs = torch.empty_like(rgbs)
+    check(_lib.load().ntx_composite_backward(ptr(rgbs), ptr(z), ptr(rays_d), ptr(noise), R, S, int(map_exr),
+                                             int(composite_bkgd), _bkgd(bkgd_color), ptr(d_color_map),
+                                             ptr(d_alpha_map), ptr(d_rgbs), stream_ptr()))
+    return d_rgbs
+
+
+def composite_instanced_forward(rgbs, dists, alpha_weight, ray_ptr, color_last, alpha_last, ray_index, n_out, *,
+                                patch_scale: float, density_scale: float = 1.0, map_exr: bool = False,
+                                composite_bkgd: bool = False, bkgd_color=(1., 1., 1.), instance_color=None):
+    """network/renderer.py:300,318-354 over CSR-packed samples; rows not hit stay zero (:313-314)."""
+    rgbs, dists = as_cuda(rgbs), as_cuda(dists)
+    ray_ptr = as_cuda(ray_ptr, torch.int64)
+    color_last, alpha_last = as_cuda(color_last), as_cuda(alpha_last)
+    H = ray_ptr.shape[0] - 1
+    if alpha_weight is not None:
+        alpha_weight = as_cuda(alpha_weight)
+    if ray_index is not None:
+        ray_index = as_cuda(ray_index, torch.int32)
+    if instance_color is not None:
+        instance_color = as_cuda(instance_color)
+    dev = rgbs.device
+    cmap = torch.zeros((n_out, 3), dtype=torch.float32, device=dev)
+    amap = torch.zeros((n_out,), dtype=torch.float32, device=dev)
+    check(_lib.load().ntx_composite_instanced_forward(
+        ptr(rgbs), ptr(dists), ptr(alpha_weight), ptr(ray_ptr), ptr(color_last), ptr(alpha_last), ptr(ray_index),
+        ptr(instance_color), H, float(patch_scale), float(density_scale), int(map_exr), int(composite_bkgd),
+        _bkgd(bkgd_color), ptr(cmap), ptr(amap), stream_ptr()))
+    return cmap, amap
+
+
+# ------------------------------------------------------------------------------------------ self-tests
+
+def selftest_umma(A: torch.Tensor, B: torch.Tensor, layout: int) -> torch.Tensor:
+    A, B = as_cuda(A), as_cuda(B)
+    assert A.shape[0] == 128 and A.shape[1] == B.shape[1]
+    D = torch.empty((128, B.shape[0]), dtype=torch.float32, device=A.device)
+    check(_lib.load().ntx_selftest_umma(ptr(A), ptr(B), B.shape[0], A.shape[1], layout, ptr(D), stream_ptr()))
+    return D
+
+
+def selftest_bulk_copy(src: torch.Tensor) -> torch.Tensor:
+    dst = torch.empty_like(src)
+    check(_lib.load().ntx_selftest_bulk_copy(ptr(src), ptr(dst), src.numel() * src.element_size(), stream_ptr()))
+    return dst
