@@ -1,0 +1,557 @@
+// K1 — fused Fourier-feature encoding + conditioned NeRF-Tex MLP forward for sm_100a.
+//
+// One persistent CTA per SM (320 threads) walks 256-row batches of samples:
+//
+//   warp 0      weight producer: streams the packed bf16 weight image, one [N x 32] K-slice per
+//               bulk-TMA copy (cp.async.bulk -> UBLKCP), into a 3-deep shared-memory ring.
+//   warp 1      MMA issuer: one elected thread issues tcgen05.mma (M=128, N=256|128, K=16, bf16 in,
+//               fp32 accumulate in TMEM) for BOTH 128-row tiles against every staged slice, so
+//               each weight byte fetched from L2 feeds 256 rows.
+//   warps 2-9   two epilogue warpgroups (one per tile, one thread per row): compute the encodings,
+//               and per layer pull the fp32 accumulator row out of TMEM (tcgen05.ld), apply ReLU,
+//               round to bf16 and write it back as next layer's A operand in the UMMA-canonical
+//               SWIZZLE_64B K-major layout.  Activations never leave the SM.
+//
+// Biases ride the tensor core: every encoding carries a constant-1 column, and the packer puts
+// the bias in the weight row that multiplies it.  Skip / direction concats are never
+// materialised: they are extra K-slices accumulated into the same TMEM tile.  The two tiny
+// heads (density 256->1, colour 128->3) run on CUDA cores in fp32 inside the epilogues.
+//
+// Reference: network/layer.py:11-23, network/model.py:58-125, network/renderer.py:145-168.
+#include <cuda_bf16.h>
+
+#include <new>
+
+#include "ntx_common.cuh"
+#include "ntx_mlp.cuh"
+#include "ntx_umma.cuh"
+
+namespace {
+
+using namespace umma;
+using namespace ntxmlp;
+
+// ----------------------------------------------------------------------------------------------
+// shared-memory map (bytes, from a 1024-aligned base)
+// ----------------------------------------------------------------------------------------------
+constexpr uint32_t kMainBytes = kMainBlocks * kBlockBytes;                 // 65536
+constexpr uint32_t kEncBytes = kEncBlocks * kBlockBytes;                   // 24576
+constexpr uint32_t kTileBytes = kMainBytes + kEncBytes;                    // 90112
+constexpr uint32_t kOffStages = kTilesPerCta * kTileBytes;                 // 180224
+constexpr uint32_t kOffHeads = kOffStages + kStages * kStageBytes;         // 229376
+constexpr uint32_t kOffBars = kOffHeads + kHeadFloats * 4;                 // +2592
+constexpr uint32_t kNumBars = 2 * kStages + 2;
+constexpr uint32_t kOffTmemSlot = kOffBars + kNumBars * 8;
+constexpr uint32_t kSmemBytes = kOffTmemSlot + 16;
+static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
+
+constexpr int kThreads = 320;
+constexpr int kEpiWarp0 = 2;
+
+struct KernelArgs {
+    ntx_mlp_inputs in;
+    const uint8_t* packed;
+    float* rgbs;
+};
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// 16-byte chunk `q` (8 bf16 columns) of row `row` inside a SW64 K-major region starting at `base`
+__device__ __forceinline__ uint32_t chunk_addr(uint32_t base, int q, int row) {
+    return base + (uint32_t)(q >> 2) * kBlockBytes + (uint32_t)row * 64 + (uint32_t)(((q & 3) ^ ((row >> 1) & 3)) << 4);
+}
+
+// [sin, cos](2^k x) for k = 0..3 as four bf16x2 words: one accurate sincosf + 3 angle doublings
+__device__ __forceinline__ void sincos4(float x, uint32_t (&w)[4]) {
+    float s, c;
+    sincosf(x, &s, &c);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        w[k] = pack_bf16(s, c);
+        const float s2 = 2.0f * s * c;
+        c = 1.0f - 2.0f * s * s;
+        s = s2;
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// the fused forward kernel
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1)
+mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__ KernelArgs args) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    if ((sbase & 1023u) != 0) __trap();
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar_full = sbase + kOffBars;                 // [kStages]
+    const uint32_t bar_empty = bar_full + 8 * kStages;          // [kStages]
+    const uint32_t bar_act = bar_empty + 8 * kStages;           // activations (A operand) ready
+    const uint32_t bar_acc = bar_act + 8;                       // accumulators ready
+    float* heads = reinterpret_cast<float*>(smem + kOffHeads);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffTmemSlot);
+
+    const int64_t n_rows = args.in.n_rows;
+    const int64_t n_batches = (n_rows + kRowsPerCta - 1) / kRowsPerCta;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kStages; ++i) {
+            mbar_init(bar_full + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, 1);
+        }
+        mbar_init(bar_act, kTilesPerCta * 4);   // one arrive per epilogue warp
+        mbar_init(bar_acc, 1);
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        tmem_alloc(sbase + kOffTmemSlot, 512);
+        tmem_relinquish();
+    }
+    // fp32 head weights -> shared (broadcast reads in the epilogues)
+    for (int i = threadIdx.x; i < kHeadFloats; i += kThreads)
+        heads[i] = reinterpret_cast<const float*>(args.packed)[i];
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================================================================== weight producer
+        if (lane == 0) {
+            uint32_t it = 0;
+            for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+                for (int s = 0; s < prog.n_slices; ++s, ++it) {
+                    const uint32_t stage = it % kStages, round = it / kStages;
+                    mbar_wait(bar_empty + 8 * stage, (round & 1) ^ 1);
+                    const uint32_t off = prog.slice_off[s], bytes = prog.slice_off[s + 1] - off;
+                    mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+                    tma_bulk_g2s(sbase + kOffStages + stage * kStageBytes, args.packed + off, bytes,
+                                 bar_full + 8 * stage);
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===================================================================== MMA issuer
+        if (lane == 0) {
+            uint32_t it = 0, act_phase = 0;
+            for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+                for (int st = 0; st < prog.n_steps; ++st) {
+                    const Step& step = prog.steps[st];
+                    const uint32_t idesc = idesc_bf16_f32(kTileRows, step.n_out);
+                    mbar_wait(bar_act, act_phase);
+                    act_phase ^= 1;
+                    tc_fence_after();
+                    uint32_t accumulate = 0;
+                    for (int s = step.slice_begin; s < step.slice_end; ++s, ++it) {
+                        const uint32_t sl = prog.slices[s];
+                        const uint32_t stage = it % kStages, round = it / kStages;
+                        mbar_wait(bar_full + 8 * stage, round & 1);
+                        tc_fence_after();
+                        const uint32_t a_off = (slice_is_enc(sl) ? kMainBytes : 0u) + slice_blk(sl) * kBlockBytes;
+                        const uint32_t b_addr = sbase + kOffStages + stage * kStageBytes;
+                        const int h0 = slice_half0(sl), nh = slice_nh(sl);
+                        for (int h = h0; h < h0 + nh; ++h) {
+                            const uint64_t bd = smem_desc(b_addr + h * 32, 16, 512, LAYOUT_SW64);
+#pragma unroll
+                            for (int t = 0; t < kTilesPerCta; ++t) {
+                                const uint64_t ad = smem_desc(sbase + t * kTileBytes + a_off + h * 32, 16, 512, LAYOUT_SW64);
+                                mma_bf16_ss(tmem_base + t * kWidth, ad, bd, idesc, accumulate);
+                            }
+                            accumulate = 1;
+                        }
+                        mma_commit(bar_empty + 8 * stage);     // slice free once these MMAs retire
+                    }
+                    mma_commit(bar_acc);                       // accumulators of both tiles complete
+                }
+            }
+        }
+    } else {
+        // ===================================================================== epilogue warpgroups
+        const int ew = warp - kEpiWarp0;            // 0..7
+        const int tile = ew >> 2;                   // 0: rows 0..127, 1: rows 128..255 of the batch
+        const int quarter = warp & 3;               // TMEM lane quarter this warp may access
+        const int row = quarter * 32 + lane;        // row inside the tile == TMEM lane
+        const uint32_t main_base = sbase + tile * kTileBytes;
+        const uint32_t enc_base = main_base + kMainBytes;
+        const uint32_t tmem_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + tile * kWidth;
+        const int g = prog.n_geo, a = prog.n_app;
+        const float* w_alpha = heads;               // [256], b at [256]
+        const float* w_rgb = heads + 260;           // [3][128], b at [260 + 384 ..]
+        uint32_t acc_phase = 0;
+
+        for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+            const int64_t grow = b * kRowsPerCta + tile * kTileRows + row;
+            const bool valid = grow < n_rows;
+            // ------------------------------------------------------------- load this row's inputs
+            float x[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 0.f}, pg[3] = {0.f, 0.f, 0.f};
+            float pa[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            if (valid) {
+                const int64_t grp = grow / args.in.rows_per_group;
+                if (args.in.pos) {
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) x[i] = __ldg(args.in.pos + 3 * grow + i);
+                } else {
+                    const float zz = __ldg(args.in.z + grow);                   // renderer.py:114
+#pragma unroll
+                    for (int i = 0; i < 3; ++i)
+                        x[i] = __ldg(args.in.rays_o + 3 * grp + i) + __ldg(args.in.rays_d + 3 * grp + i) * zz;
+                }
+#pragma unroll
+                for (int i = 0; i < 3; ++i) d[i] = __ldg(args.in.dir + 3 * grp + i);
+                if (args.in.params) {
+                    const float* pr = args.in.params + grp * (g + a);
+                    float blur = 1.0f;                                          // renderer.py:155-158
+                    if (args.in.blur_idx >= 0) {
+                        if (args.in.group_scale) blur = __ldg(args.in.group_scale + grp);
+                        if (args.in.row_scale) blur *= __ldg(args.in.row_scale + grow);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 3; ++j)
+                        if (j < g) pg[j] = __ldg(pr + j) * (j == args.in.blur_idx ? blur : 1.0f);
+#pragma unroll
+                    for (int j = 0; j < 7; ++j)
+                        if (j < a) pa[j] = __ldg(pr + g + j) * (g + j == args.in.blur_idx ? blur : 1.0f);
+                }
+            }
+            // ------------------------------------------------------------- pos-phase encoding
+            {
+                uint32_t w[32];
+#pragma unroll
+                for (int i = 0; i < 3; ++i) {
+                    float s, c;
+#pragma unroll
+                    for (int k = 0; k < 10; ++k) {
+                        if (k == 0) sincosf(x[i], &s, &c);
+                        else if (k == 5) sincosf(32.0f * x[i], &s, &c);     // restart: bounds the doubling error
+                        else { const float s2 = 2.0f * s * c; c = 1.0f - 2.0f * s * s; s = s2; }
+                        w[i * 10 + k] = pack_bf16(s, c);
+                    }
+                }
+                w[30] = pack_bf16(1.0f, x[0]);
+                w[31] = pack_bf16(x[1], x[2]);
+#pragma unroll
+                for (int q = 0; q < 8; ++q)
+                    st_shared_v4(chunk_addr(enc_base, q, row), w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+                if (g > 0) {
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        if (j < g) {
+                            uint32_t p4[4];
+                            sincos4(pg[j], p4);
+                            st_shared_v4(chunk_addr(enc_base, 8 + j, row), p4[0], p4[1], p4[2], p4[3]);
+                        }
+                    }
+                    st_shared_v4(chunk_addr(enc_base, 8 + g, row), pack_bf16(pg[0], pg[1]), pack_bf16(pg[2], 0.f), 0u, 0u);
+                    if ((g & 1) == 0) st_shared_v4(chunk_addr(enc_base, 9 + g, row), 0u, 0u, 0u, 0u);
+                }
+            }
+            fence_proxy_async_smem();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_act);
+
+            float alpha_raw = 0.0f;
+            // ------------------------------------------------------------- layer epilogues
+            for (int st = 0; st < prog.n_steps; ++st) {
+                const Step& step = prog.steps[st];
+                const uint32_t epi = step.epi;
+                mbar_wait(bar_acc, acc_phase);
+                acc_phase ^= 1;
+                tc_fence_after();
+                float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+                const int n_chunks = step.n_out >> 5;
+                for (int j = 0; j < n_chunks; ++j) {
+                    uint32_t v[32];
+                    tmem_ld_32x32b_x32(tmem_row + j * 32, v);
+                    tmem_ld_wait();
+                    float f[32];
+#pragma unroll
+                    for (int c = 0; c < 32; ++c) {
+                        f[c] = __uint_as_float(v[c]);
+                        if (epi & EPI_RELU) f[c] = fmaxf(f[c], 0.0f);
+                    }
+                    if (epi & EPI_ALPHA) {                                       // model.py:111
+                        const float4* wa = reinterpret_cast<const float4*>(w_alpha + j * 32);
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 ww = wa[c];
+                            alpha_raw += f[4 * c] * ww.x + f[4 * c + 1] * ww.y + f[4 * c + 2] * ww.z + f[4 * c + 3] * ww.w;
+                        }
+                    }
+                    if (epi & EPI_FINAL) {                                       // model.py:123
+                        const float4* w0 = reinterpret_cast<const float4*>(w_rgb + j * 32);
+                        const float4* w1 = reinterpret_cast<const float4*>(w_rgb + 128 + j * 32);
+                        const float4* w2 = reinterpret_cast<const float4*>(w_rgb + 256 + j * 32);
+#pragma unroll
+                        for (int c = 0; c < 8; ++c) {
+                            const float4 a0 = w0[c], a1 = w1[c], a2 = w2[c];
+                            o0 += f[4 * c] * a0.x + f[4 * c + 1] * a0.y + f[4 * c + 2] * a0.z + f[4 * c + 3] * a0.w;
+                            o1 += f[4 * c] * a1.x + f[4 * c + 1] * a1.y + f[4 * c + 2] * a1.z + f[4 * c + 3] * a1.w;
+                            o2 += f[4 * c] * a2.x + f[4 * c + 1] * a2.y + f[4 * c + 2] * a2.z + f[4 * c + 3] * a2.w;
+                        }
+                    } else {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c)
+                            st_shared_v4(chunk_addr(main_base, j * 4 + c, row),
+                                         pack_bf16(f[8 * c], f[8 * c + 1]), pack_bf16(f[8 * c + 2], f[8 * c + 3]),
+                                         pack_bf16(f[8 * c + 4], f[8 * c + 5]), pack_bf16(f[8 * c + 6], f[8 * c + 7]));
+                    }
+                }
+                if (epi & EPI_ALPHA) alpha_raw += w_alpha[256];
+                if (epi & EPI_SWITCH) {
+                    // ----------------------------------------------------- dir-phase encoding
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        uint32_t p4[4];
+                        sincos4(d[i], p4);
+                        st_shared_v4(chunk_addr(enc_base, i, row), p4[0], p4[1], p4[2], p4[3]);
+                    }
+#pragma unroll
+                    for (int j = 0; j < 7; ++j) {
+                        if (j < a) {
+                            uint32_t p4[4];
+                            sincos4(pa[j], p4);
+                            st_shared_v4(chunk_addr(enc_base, 3 + j, row), p4[0], p4[1], p4[2], p4[3]);
+                        }
+                    }
+                    st_shared_v4(chunk_addr(enc_base, 3 + a, row), pack_bf16(1.0f, d[0]), pack_bf16(d[1], d[2]),
+                                 pack_bf16(pa[0], pa[1]), pack_bf16(pa[2], pa[3]));
+                    if (a > 4)
+                        st_shared_v4(chunk_addr(enc_base, 4 + a, row), pack_bf16(pa[4], pa[5]), pack_bf16(pa[6], 0.f), 0u, 0u);
+                    if (dir_chunks(a) & 1) st_shared_v4(chunk_addr(enc_base, dir_chunks(a), row), 0u, 0u, 0u, 0u);
+                }
+                if (epi & EPI_FINAL) {
+                    if (valid) {
+                        const float* brgb = w_rgb + 384;
+                        reinterpret_cast<float4*>(args.rgbs)[grow] =
+                            make_float4(o0 + brgb[0], o1 + brgb[1], o2 + brgb[2], alpha_raw);
+                    }
+                    tc_fence_before();      // TMEM reads done before the next batch's MMAs overwrite it
+                } else {
+                    fence_proxy_async_smem();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_act);
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) {
+        __syncwarp();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// weight packer: flat fp32 master -> packed image (fp32 head block + bf16 SW64 K-slices)
+// ----------------------------------------------------------------------------------------------
+__global__ void mlp_pack_kernel(const __grid_constant__ Program prog, const float* __restrict__ master,
+                                uint8_t* __restrict__ packed) {
+    const int s = blockIdx.x;
+    if (s == prog.n_slices) {            // head block
+        float* h = reinterpret_cast<float*>(packed);
+        const Layer& la = prog.layers[prog.alpha_layer];
+        const Layer& lr = prog.layers[prog.rgb_layer];
+        for (int i = threadIdx.x; i < kHeadBytes / 4; i += blockDim.x) {
+            float v = 0.0f;
+            if (i < 256) v = master[la.w_off + i];                               // W_alpha[in=256, out=1]
+            else if (i == 256) v = master[la.b_off];
+            else if (i >= 260 && i < 260 + 384) { int c = (i - 260) / 128, k = (i - 260) % 128; v = master[lr.w_off + k * 3 + c]; }
+            else if (i >= 644 && i < 647) v = master[lr.b_off + (i - 644)];
+            h[i] = v;
+        }
+        return;
+    }
+    const uint32_t sl = prog.slices[s];
+    const Step& step = prog.steps[slice_step(sl)];
+    const Layer& L = prog.layers[step.layer];
+    const int N = step.n_out;
+    uint8_t* dst = packed + prog.slice_off[s];
+    const int h0 = slice_half0(sl), nh = slice_nh(sl);
+    for (int idx = threadIdx.x; idx < N * 32; idx += blockDim.x) {
+        const int n = idx >> 5, kk = idx & 31, half = kk >> 4;
+        float v = 0.0f;
+        if (half >= h0 && half < h0 + nh) {
+            if (slice_is_enc(sl)) {
+                const int col = slice_blk(sl) * 32 + kk;
+                const int ref = step.phase == 0 ? pos_col_to_ref(col, prog.n_geo) : dir_col_to_ref(col, prog.n_app);
+                if (ref == kRefOnes) v = master[L.b_off + n];
+                else if (ref >= 0 && step.enc_data) v = master[L.w_off + (int64_t)ref * L.fan_out + n];
+            } else {
+                const int c = slice_blk(sl) * 32 + kk;
+                v = master[L.w_off + (int64_t)(step.main_row0 + c) * L.fan_out + n];
+            }
+        }
+        *reinterpret_cast<__nv_bfloat16*>(dst + sw64_offset(n, kk, N)) = __float2bfloat16(v);
+    }
+}
+
+int build_program(ntx_mlp* m) {
+    const ntx_mlp_config& c = m->cfg;
+    Program& p = m->prog;
+    memset(&p, 0, sizeof(p));
+    const int g = c.n_geo, a = c.n_app, W = c.width;
+    p.n_geo = g; p.n_app = a;
+    p.P = c.n_pos * (1 + 2 * c.pos_freqs) + g * (1 + 2 * c.param_freqs);
+    p.D = 3 * (1 + 2 * c.dir_freqs) + a * (1 + 2 * c.param_freqs);
+
+    // ---- Dense layer table in graph order (model.py:104-123)
+    int64_t off = 0;
+    int nl = 0;
+    auto add_layer = [&](int fin, int fout) {
+        Layer& L = p.layers[nl];
+        L.fan_in = fin; L.fan_out = fout; L.w_off = off; off += (int64_t)fin * fout; L.b_off = off; off += fout;
+        return nl++;
+    };
+    int trunk[16];
+    int k = p.P;
+    for (int i = 0; i < c.depth; ++i) {
+        trunk[i] = add_layer(k, W);
+        k = ((c.skip_mask >> i) & 1) ? W + p.P : W;
+    }
+    p.alpha_layer = add_layer(k, 1);
+    const int feature = add_layer(k, W);
+    int colorhid[8];
+    k = W + p.D;
+    for (int i = 0; i < c.color_depth; ++i) { colorhid[i] = add_layer(k, W); k = W; }
+    const int colorhalf = add_layer(k, W / 2);
+    p.rgb_layer = add_layer(W / 2, 3);
+    p.n_layers = nl;
+    m->n_params = off;
+
+    // ---- MMA steps
+    int last_pos_step = 0;   // last step that consumes pos-encoding features
+    for (int i = 0; i < c.depth; ++i) if (i > 0 && ((c.skip_mask >> (i - 1)) & 1)) last_pos_step = i;
+    int ns = 0, nsl = 0;
+    uint32_t boff = kHeadBytes;
+    auto add_step = [&](int layer, int n_out, bool has_main, int enc_data, int phase, int main_row0, uint32_t epi) {
+        Step& s = p.steps[ns];
+        s.layer = layer; s.n_out = n_out; s.main_row0 = main_row0; s.enc_data = enc_data; s.phase = phase; s.epi = epi;
+        s.slice_begin = nsl;
+        if (has_main)
+            for (int b = 0; b < kMainBlocks; ++b) p.slices[nsl++] = make_slice(0, b, 0, 2, ns);
+        if (enc_data) {
+            const int halves = ((phase == 0 ? pos_chunks(g) : dir_chunks(a)) + 1) / 2;
+            for (int h = 0; h < halves; h += 2) p.slices[nsl++] = make_slice(1, h / 2, 0, halves - h >= 2 ? 2 : 1, ns);
+        } else {
+            const int oc = phase == 0 ? pos_ones_col() : dir_ones_col(a);
+            p.slices[nsl++] = make_slice(1, oc / 32, (oc % 32) / 16, 1, ns);
+        }
+        s.slice_end = nsl;
+        for (int q = s.slice_begin; q < s.slice_end; ++q) { p.slice_off[q] = boff; boff += (uint32_t)n_out * 64; }
+        return ns++;
+    };
+    for (int i = 0; i < c.depth; ++i) {
+        const bool skip_in = i > 0 && ((c.skip_mask >> (i - 1)) & 1);
+        uint32_t epi = EPI_RELU;
+        if (i == c.depth - 1) epi |= EPI_ALPHA;
+        if (i == last_pos_step) epi |= EPI_SWITCH;
+        add_step(trunk[i], W, i > 0, (i == 0 || skip_in) ? 1 : 0, i <= last_pos_step ? 0 : 1, skip_in ? p.P : 0, epi);
+    }
+    add_step(feature, W, true, 0, 1, 0, 0u);                                    // model.py:114 (linear)
+    for (int i = 0; i < c.color_depth; ++i)
+        add_step(colorhid[i], W, true, i == 0 ? 1 : 0, 1, i == 0 ? p.D : 0, EPI_RELU);
+    add_step(colorhalf, W / 2, true, c.color_depth == 0 ? 1 : 0, 1, c.color_depth == 0 ? p.D : 0, EPI_RELU | EPI_FINAL);
+    p.n_steps = ns;
+    p.n_slices = nsl;
+    p.slice_off[nsl] = boff;
+    m->packed_bytes = boff;
+    return NTX_OK;
+}
+
+}  // namespace
+
+NTX_API int ntx_mlp_create(const ntx_mlp_config* cfg, ntx_mlp_t** out) {
+    NTX_REQUIRE(cfg && out, "mlp_create: null pointer");
+    const ntx_mlp_config& c = *cfg;
+    if (!(c.n_pos == 3 && c.pos_freqs == 10 && c.dir_freqs == 4 && c.param_freqs == 4 && c.width == 256)) {
+        ntx_set_error("mlp_create: the sm_100a kernel implements n_pos=3, pos_freqs=10, dir_freqs=4, param_freqs=4, "
+                      "width=256 (got %d,%d,%d,%d,%d)", c.n_pos, c.pos_freqs, c.dir_freqs, c.param_freqs, c.width);
+        return NTX_E_UNSUPPORTED;
+    }
+    if (!(c.n_geo >= 0 && c.n_geo <= 3 && c.n_app >= 0 && c.n_app <= 7 && c.depth >= 1 && c.depth <= 16 &&
+          c.color_depth >= 0 && c.color_depth <= 2 && ((c.skip_mask >> (c.depth - 1)) == 0))) {
+        ntx_set_error("mlp_create: unsupported n_parameters=[%d,%d] depth=%d color_depth=%d skip_mask=0x%x "
+                      "(need n_geo<=3, n_app<=7, depth<=16, color_depth<=2, no skip on the last trunk layer)",
+                      c.n_geo, c.n_app, c.depth, c.color_depth, c.skip_mask);
+        return NTX_E_UNSUPPORTED;
+    }
+    ntx_mlp* m = new (std::nothrow) ntx_mlp();
+    NTX_REQUIRE(m, "mlp_create: out of host memory");
+    m->cfg = c;
+    build_program(m);
+    if (m->prog.n_steps > kMaxSteps || m->prog.n_slices > kMaxSlices) {
+        delete m;
+        ntx_set_error("mlp_create: network too deep for the step table");
+        return NTX_E_UNSUPPORTED;
+    }
+    *out = m;
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_destroy(ntx_mlp_t* mlp) {
+    delete mlp;
+    return NTX_OK;
+}
+
+NTX_API int64_t ntx_mlp_num_params(const ntx_mlp_t* mlp) { return mlp ? mlp->n_params : -1; }
+NTX_API int ntx_mlp_num_layers(const ntx_mlp_t* mlp) { return mlp ? mlp->prog.n_layers : -1; }
+NTX_API int64_t ntx_mlp_packed_bytes(const ntx_mlp_t* mlp) { return mlp ? mlp->packed_bytes : -1; }
+
+NTX_API int ntx_mlp_layer_info(const ntx_mlp_t* mlp, int i, int64_t* w_offset, int64_t* b_offset, int32_t* fan_in,
+                               int32_t* fan_out) {
+    NTX_REQUIRE(mlp && i >= 0 && i < mlp->prog.n_layers, "mlp_layer_info: bad layer index %d", i);
+    const Layer& L = mlp->prog.layers[i];
+    if (w_offset) *w_offset = L.w_off;
+    if (b_offset) *b_offset = L.b_off;
+    if (fan_in) *fan_in = L.fan_in;
+    if (fan_out) *fan_out = L.fan_out;
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_pack_weights(const ntx_mlp_t* mlp, const float* master, void* packed, void* stream) {
+    NTX_REQUIRE(mlp && master && packed, "mlp_pack_weights: null pointer");
+    NTX_REQUIRE(((uintptr_t)packed & 15) == 0, "mlp_pack_weights: packed image must be 16-byte aligned");
+    mlp_pack_kernel<<<mlp->prog.n_slices + 1, 256, 0, (cudaStream_t)stream>>>(mlp->prog, master, (uint8_t*)packed);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
+                            void* stream) {
+    NTX_REQUIRE(mlp && packed && in, "mlp_forward: null pointer");
+    NTX_REQUIRE(in->n_rows >= 0, "mlp_forward: negative row count");
+    if (in->n_rows == 0) return NTX_OK;
+    NTX_REQUIRE(rgbs && in->dir, "mlp_forward: null rgbs / dir");
+    NTX_REQUIRE(in->pos || (in->rays_o && in->rays_d && in->z), "mlp_forward: need pos, or rays_o + rays_d + z");
+    NTX_REQUIRE(in->rows_per_group >= 1, "mlp_forward: rows_per_group must be >= 1");
+    const int np = mlp->cfg.n_geo + mlp->cfg.n_app;
+    NTX_REQUIRE(np == 0 || in->params, "mlp_forward: the model takes %d parameters but params is NULL", np);
+    NTX_REQUIRE(in->blur_idx < np, "mlp_forward: blur_idx %d out of range", in->blur_idx);
+    NTX_REQUIRE((((uintptr_t)packed | (uintptr_t)rgbs) & 15) == 0, "mlp_forward: packed / rgbs must be 16-byte aligned");
+    static bool attr_set[64] = {};
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && !attr_set[dev]) {
+        NTX_CUDA(cudaFuncSetAttribute(mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+        attr_set[dev] = true;
+    }
+    KernelArgs ka;
+    ka.in = *in;
+    ka.packed = (const uint8_t*)packed;
+    ka.rgbs = rgbs;
+    const int64_t n_batches = (in->n_rows + kRowsPerCta - 1) / kRowsPerCta;
+    const int grid = (int)(n_batches < ntx_sm_count() ? n_batches : ntx_sm_count());
+    mlp_forward_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(mlp->prog, ka);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}

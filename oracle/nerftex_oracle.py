@@ -209,6 +209,43 @@ class ParamNerfOracle:
         return color.astype(F32), alpha.astype(F32)
 
 
+def _bf16(x: np.ndarray) -> np.ndarray:
+    """Round-to-nearest-even to bfloat16, returned as fp32."""
+    u = np.ascontiguousarray(x, dtype=np.float32).view(np.uint32)
+    r = ((u >> 16) & 1) + np.uint32(0x7FFF)
+    return ((u + r) & np.uint32(0xFFFF0000)).view(np.float32)
+
+
+def forward_bf16_emulated(model: "ParamNerfOracle", pos, dirs, params):
+    """The reference graph (model.py:58-125) evaluated with the CUDA kernel's quantisation points:
+    encodings, weights, biases of the tensor-core layers and stored activations rounded to bf16,
+    fp32 accumulation, fp32 density / colour heads fed by the un-rounded fp32 activations.
+    Separates logic errors (must match to ~1e-3) from bf16 rounding (looser north-star tolerance)."""
+    pos_map, dir_map = model.encode(pos, dirs, params)
+    pos_map, dir_map = _bf16(pos_map), _bf16(dir_map)
+    L = model.named_weights()
+    q = lambda n: (_bf16(L[n][0]).astype(np.float64), _bf16(L[n][1]).astype(np.float64))
+    h = pos_map.astype(np.float64)
+    h32 = None
+    for i in range(model.depth):
+        W, b = q(f"trunk{i}")
+        h32 = np.maximum(h @ W + b, 0).astype(F32)
+        h = _bf16(h32).astype(np.float64)
+        if i in model.skips:
+            h = np.concatenate([pos_map.astype(np.float64), h], -1)
+    alpha = (h32.astype(np.float64) @ L["alpha"][0].astype(np.float64) + L["alpha"][1]).astype(F32)
+    W, b = q("feature")
+    h = _bf16((h @ W + b).astype(F32)).astype(np.float64)
+    h = np.concatenate([dir_map.astype(np.float64), h], -1)
+    for i in range(model.color_depth):
+        W, b = q(f"colorhid{i}")
+        h = _bf16(np.maximum(h @ W + b, 0).astype(F32)).astype(np.float64)
+    W, b = q("colorhalf")
+    h32 = np.maximum(h @ W + b, 0).astype(F32)
+    color = (h32.astype(np.float64) @ L["rgb"][0].astype(np.float64) + L["rgb"][1]).astype(F32)
+    return color, alpha
+
+
 # ----------------------------------------------------------------------------------------
 # network/renderer.py — plain renderer
 # ----------------------------------------------------------------------------------------

@@ -77,4 +77,4 @@ def test_errors_are_loud():
     with pytest.raises(_lib.NtxError):
         ops.hierarchical_z(torch.zeros((4, 600), device="cuda"), torch.zeros((4, 600), device="cuda"), 600, True)
     with pytest.raises(_lib.NtxError):
-        ops.stratified_z(torch.zeros((4, 2)), 8, False)     # CPU tensor: no CPU path
+        _lib.ptr(torch.zeros((4, 2)))                        # CPU tensor at the ABI boundary: no CPU path
