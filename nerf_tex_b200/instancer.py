@@ -1,0 +1,122 @@
+"""Instancer boundary (instancer/instancer.pyx:6-54).
+
+The reference's native instancer (Embree scene of shell patches on a mesh) cannot be built or
+fed in this environment (Embree 3 is a system dependency, every mesh/texture is a git-LFS stub;
+SURVEY.md D8).  ``SyntheticInstancer`` keeps the exact constructor / ``n_instances`` /
+``get_model_input`` surface and produces seeded outputs with the statistics SURVEY.md section 8d
+prescribes, natively CSR-packed on the GPU (``get_model_input_csr``); ``get_model_input`` scatters
+the same data into the reference's dense 10-tuple for callers written against instancer.pyx:54.
+"""
+
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional
+
+import torch
+
+from ._lib import as_cuda
+
+
+class SyntheticInstancer:
+    def __init__(self, b_0: list, b_1: list, cast_shadow_rays=False, textures: list = [], transformations: list = [],
+                 mesh_path: str = None, patch_scale: float = 1., patch_origins_path='', min_shadow_samples: int = 4,
+                 n_shadow_samples: int = 512, min_texture_samples: int = 4, n_texture_samples: int = 512,
+                 jitter_amount: float = 0, instance_sampling_method: str = 'random', use_mean_distance: bool = False,
+                 auxiliary_meshes=[], transformation_export_path=None, *, seed: int = 0, hit_probability: float = 0.7,
+                 mean_valid: float = 120.0, sigma_valid: float = 0.6, num_instances: int = 10000) -> None:
+        assert instance_sampling_method in ('random', 'nearest', 'nearest_blend')      # instancer.pyx:12
+        self.b_0 = [float(v) for v in b_0]
+        self.b_1 = [float(v) for v in b_1]
+        self.patch_scale = float(patch_scale)
+        self.seed, self.hit_probability = int(seed), float(hit_probability)
+        self.mean_valid, self.sigma_valid = float(mean_valid), float(sigma_valid)
+        self._n_instances = int(num_instances)
+        self._calls = 0
+
+    def n_instances(self) -> int:
+        return self._n_instances
+
+    # ------------------------------------------------------------------------------------
+    def get_model_input_csr(self, rays_o, rays_d, parameters, n_samples: int, step_size: float) -> Dict[str, torch.Tensor]:
+        rays_o, rays_d, parameters = as_cuda(rays_o), as_cuda(rays_d), as_cuda(parameters)
+        dev = rays_o.device
+        R, p = rays_o.shape[0], parameters.shape[1]
+        gen = torch.Generator(device=dev).manual_seed(self.seed + 7919 * self._calls)
+        self._calls += 1
+        rnd = lambda *s: torch.rand(s, dtype=torch.float32, device=dev, generator=gen)
+        hit = rnd(R) < self.hit_probability
+        ray_index = torch.nonzero(hit).squeeze(1)
+        H = ray_index.shape[0]
+        logn = torch.randn(H, dtype=torch.float32, device=dev, generator=gen) * self.sigma_valid + math.log(self.mean_valid)
+        n_valid = torch.clamp(torch.round(torch.exp(logn)), 1, n_samples).to(torch.int64)
+        ray_ptr = torch.zeros(H + 1, dtype=torch.int64, device=dev)
+        ray_ptr[1:] = torch.cumsum(n_valid, 0)
+        T = int(ray_ptr[-1].item()) if H > 0 else 0
+        ray_of = torch.repeat_interleave(torch.arange(H, device=dev), n_valid)
+        pos_in_ray = torch.arange(T, device=dev) - ray_ptr[:-1][ray_of]
+        last = pos_in_ray == (n_valid[ray_of] - 1)
+        dists = torch.full((T,), float(step_size), dtype=torch.float32, device=dev)
+        dists = torch.where(last, dists + rnd(T) * float(step_size), dists)
+        b0 = torch.tensor(self.b_0, dtype=torch.float32, device=dev)
+        b1 = torch.tensor(self.b_1, dtype=torch.float32, device=dev)
+        pts = b0 + (b1 - b0) * rnd(T, 3)
+        # per-sample rotation of the (normalised) ray direction about z: each sample lives in its patch frame
+        d = rays_d[ray_index][ray_of]
+        d = d / torch.linalg.norm(d, dim=-1, keepdim=True)
+        ang = rnd(T) * (2 * math.pi)
+        ca, sa = torch.cos(ang), torch.sin(ang)
+        dirs = torch.stack([ca * d[:, 0] - sa * d[:, 1], sa * d[:, 0] + ca * d[:, 1], d[:, 2]], -1)
+        # parameters: per-ray values, the leading (texture-modulated) ones scaled per sample, light dir kept unit
+        params = parameters[ray_index][ray_of].clone()
+        n_tex = max(p - 3, 0)
+        if n_tex > 0:
+            params[:, :n_tex] = params[:, :n_tex] * rnd(T, n_tex)
+        t = pos_in_ray.to(torch.float32) * float(step_size) + 1.0
+        return {
+            "ray_ptr": ray_ptr, "ray_index": ray_index.to(torch.int32), "pts": pts.contiguous(), "dirs": dirs.contiguous(),
+            "params": params.contiguous(), "dists": dists.contiguous(), "t": t.contiguous(),
+            "alpha_weight": torch.ones(T, dtype=torch.float32, device=dev),
+            "instance_id": torch.randint(0, self._n_instances, (T,), device=dev, generator=gen, dtype=torch.int32),
+            "color_last": torch.zeros((H, 3), dtype=torch.float32, device=dev),
+            "alpha_last": (rnd(H) < 0.5).to(torch.float32),
+        }
+
+    def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float):
+        """Dense 10-tuple of instancer.pyx:54 (for small inputs / API parity)."""
+        csr = self.get_model_input_csr(rays_o, rays_d, parameters, n_samples, step_size)
+        return csr_to_dense(csr, as_cuda(rays_d), as_cuda(parameters), n_samples)
+
+
+def csr_to_dense(csr, rays_d, parameters, n_samples: int):
+    dev = rays_d.device
+    R, p = rays_d.shape[0], parameters.shape[1]
+    H = csr["ray_index"].shape[0]
+    counts = csr["ray_ptr"][1:] - csr["ray_ptr"][:-1]
+    ray_of = torch.repeat_interleave(csr["ray_index"].long(), counts)
+    pos_in_ray = torch.arange(csr["pts"].shape[0], device=dev) - torch.repeat_interleave(csr["ray_ptr"][:-1], counts)
+    rays_d_map = rays_d[:, None, :].repeat(1, n_samples, 1)                    # instancer.pyx:41
+    pts = torch.zeros((R, n_samples, 3), device=dev)
+    t = torch.zeros((R, n_samples), device=dev)
+    dists = torch.zeros((R, n_samples), device=dev)
+    alpha_weight = torch.ones((R, n_samples), device=dev)                      # instancer.pyx:47
+    instance_id = torch.zeros((R, n_samples), dtype=torch.int32, device=dev)
+    params_map = parameters[:, None, :].repeat(1, n_samples, 1)                # instancer.pyx:50
+    color_last = torch.zeros((R, 1, 3), device=dev)
+    alpha_last = torch.zeros((R, 1), device=dev)
+    rays_d_map[ray_of, pos_in_ray] = csr["dirs"]
+    pts[ray_of, pos_in_ray] = csr["pts"]
+    t[ray_of, pos_in_ray] = csr["t"]
+    dists[ray_of, pos_in_ray] = csr["dists"]
+    alpha_weight[ray_of, pos_in_ray] = csr["alpha_weight"]
+    instance_id[ray_of, pos_in_ray] = csr["instance_id"]
+    params_map[ray_of, pos_in_ray] = csr["params"]
+    color_last[csr["ray_index"].long(), 0] = csr["color_last"]
+    alpha_last[csr["ray_index"].long(), 0] = csr["alpha_last"]
+    idxs = csr["ray_index"].long()[:, None]                                    # tf.where(hit) -> [H,1]
+    return rays_d_map, pts, t, dists, color_last, alpha_last, alpha_weight, instance_id, idxs, params_map
+
+
+# The reference's configs name 'instancer.instancer.Instancer' (config_carpet_render.py:82).  The native
+# Embree instancer is unavailable here, so that path resolves to the synthetic generator.
+Instancer = SyntheticInstancer
