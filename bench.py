@@ -1,0 +1,386 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the NeRF-Tex hot path on B200.
+
+Workload (BASELINE.json configs[1], SURVEY.md section 8d "C2"): one 800x800 frame (640 000 rays) of the
+carpet-shape instanced render — model n_parameters [1,6], InstanceRenderer kwargs of
+configs/config_carpet_render.py:76-99 (n_samples 1024, step 0.002, patch_scale 0.09, render_chunk
+16384), random-init weights, seeded synthetic instancer output (hit ~ 0.7, in-shell samples per
+hit ray ~ LogNormal(ln 120, 0.6)).  A "step" is one frame: per render chunk one fused
+encoding+MLP launch (K1) and one compositing launch (K2).
+
+  value : rays/s, whole job, instancer records resident in HBM when the timed region starts.
+  e2e   : rays/s through the same plugin call (InstanceRenderer.__call__) with HOST buffers:
+          rays and per-chunk instancer records are copied from pinned host memory inside the timed
+          region and the rendered colour/alpha are read back.
+  --impl reference : the reference's CPU implementation of the same path.  The reference's
+          TensorFlow cannot be installed here, so this arm times the oracle port
+          (oracle/nerftex_oracle.py, NumPy + multithreaded BLAS) on a bounded ray subset.
+
+One process per GPU; for N > 1 launch with torch.distributed.run (weak scaling: every rank renders
+its own frame, no data-path collective).  Rank 0 prints ONE JSON line.
+"""
+
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+H = W = 800
+RENDER_CHUNK = 16384
+N_SAMPLES = 1024
+STEP_SIZE = 0.002
+PATCH_SCALE = 0.09
+NPAR = (1, 6)
+B0, B1 = [-1.4, -1.2, -.1], [1.2, 1.2, 1.8]
+DATASET_PARAMS = [1, 1, 1, .1, 0, 0, 1]          # config_carpet_render.py:40
+CPU_SAMPLE_RAYS = 2048
+MACS_PER_SAMPLE = {(1, 6): 680832, (1, 4): 676224, (2, 3): 678528}
+
+
+def peaks():
+    p = ROOT / "MEASURED_PEAKS.json"
+    if p.exists():
+        d = json.loads(p.read_text())
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_tflops": d["bf16_tflops"],
+                "bf16_tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "source": "measured"}
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+
+
+def frame_rays(seed: int):
+    """800x800 camera rays (ray_sampler.rays_from_camera semantics) with a constant near/far."""
+    rng = np.random.default_rng(seed)
+    focal = 0.5 * W / math.tan(0.5 * 0.63)
+    ii, jj = np.meshgrid(np.arange(H, dtype=np.float32), np.arange(W, dtype=np.float32), indexing="ij")
+    dirs = np.stack([(jj + .5 - .5 * W) / focal, -(ii + .5 - .5 * H) / focal, -np.ones_like(ii)], -1).reshape(-1, 3)
+    ang = rng.uniform(0, 2 * math.pi)
+    c2w = np.array([[math.cos(ang), 0, math.sin(ang)], [0, 1, 0], [-math.sin(ang), 0, math.cos(ang)]], np.float32)
+    rays_d = (dirs @ c2w.T).astype(np.float32)
+    rays_d /= np.linalg.norm(rays_d, axis=-1, keepdims=True)
+    rays_o = np.tile((c2w @ np.array([0, 0, 4.], np.float32))[None], (H * W, 1)).astype(np.float32)
+    t = np.tile(np.array([[2., 6.]], np.float32), (H * W, 1))
+    cone = (np.cos(np.arctan(np.linalg.norm(dirs[:, :2], axis=-1))) / np.linalg.norm(dirs, axis=-1) / focal)
+    return rays_o[None], rays_d[None], t[None], np.array([DATASET_PARAMS], np.float32), cone.astype(np.float32)[None, :, None]
+
+
+class ChunkReplayInstancer:
+    """Instancer boundary object for the bench: replays pre-generated per-chunk CSR records.
+    resident=True: records live in HBM.  resident=False: records live in pinned host memory and
+    every call copies its chunk to the device (the e2e arm)."""
+
+    patch_scale = PATCH_SCALE
+
+    def __init__(self, chunks, resident: bool):
+        import torch
+        self.resident = resident
+        self.i = 0
+        self.h2d_bytes = 0
+        if resident:
+            self.chunks = chunks
+        else:
+            self.chunks = [{k: v.cpu().pin_memory() for k, v in c.items()} for c in chunks]
+
+    def n_instances(self):
+        return 10000
+
+    def reset(self):
+        self.i = 0
+
+    def get_model_input_csr(self, rays_o, rays_d, parameters, n_samples, step_size):
+        c = self.chunks[self.i]
+        self.i = (self.i + 1) % len(self.chunks)
+        if self.resident:
+            return c
+        out = {}
+        for k, v in c.items():
+            out[k] = v.to(rays_o.device, non_blocking=True)
+            self.h2d_bytes += v.numel() * v.element_size()
+        return out
+
+
+def clocks_start():
+    path = Path(tempfile.gettempdir()) / f"ntx_clocks_{os.getpid()}.csv"
+    try:
+        proc = subprocess.Popen(
+            ["nvidia-smi", "-i", os.environ.get("LOCAL_RANK", "0"),
+             "--query-gpu=clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap", "--format=csv,noheader,nounits", "-lms", "100"],
+            stdout=open(path, "w"), stderr=subprocess.DEVNULL)
+        return proc, path
+    except Exception:
+        return None, path
+
+
+def clocks_stop(proc, path):
+    if proc is None:
+        return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+    proc.terminate()
+    try:
+        proc.wait(timeout=5)
+    except Exception:
+        proc.kill()
+    sm, mx, reasons = [], [], set()
+    names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    for line in Path(path).read_text().splitlines():
+        f = [x.strip() for x in line.split(",")]
+        if len(f) < 7:
+            continue
+        try:
+            sm.append(float(f[0])); mx.append(float(f[1]))
+        except ValueError:
+            continue
+        for n, v in zip(names, f[3:7]):
+            if v.lower().startswith("active"):
+                reasons.add(n)
+    # samples under load = the upper half of the observed clocks (idle samples bracket the region)
+    load = sorted(sm)[len(sm) // 2:] if sm else []
+    return {"sm_mhz": float(np.median(load)) if load else None, "sm_max_mhz": max(mx) if mx else None,
+            "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline_run(steps: int, warmup: int):
+    """Oracle port of InstanceRenderer.evaluate_model (renderer.py:247-354) on CPU_SAMPLE_RAYS rays."""
+    from oracle import nerftex_oracle as O
+    rng = np.random.default_rng(0)
+    R, S, p = CPU_SAMPLE_RAYS, N_SAMPLES, sum(NPAR)
+    hit = rng.uniform(size=R) < 0.7
+    idxs = np.nonzero(hit)[0]
+    n_valid = np.clip(np.round(np.exp(rng.normal(size=R) * 0.6 + math.log(120.))), 1, S).astype(np.int64)
+    n_valid[~hit] = 0
+    mask = np.arange(S)[None, :] < n_valid[:, None]
+    dists = np.where(mask, np.float32(STEP_SIZE), np.float32(0)).astype(np.float32)
+    pts = rng.uniform(B0, B1, (R, S, 3)).astype(np.float32)
+    d = rng.normal(size=(R, S, 3)).astype(np.float32)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    params = np.tile(np.array(DATASET_PARAMS, np.float32), (R, S, 1)) * rng.uniform(0.5, 1, (R, S, p)).astype(np.float32)
+    dense = (d, pts, np.zeros((R, S), np.float32), dists, np.zeros((R, 1, 3), np.float32),
+             (rng.uniform(size=(R, 1)) < .5).astype(np.float32), np.ones((R, S), np.float32),
+             np.zeros((R, S), np.int32), idxs, params)
+    model = O.ParamNerfOracle(n_parameters=NPAR, seed=1)
+    n_in_shell = int(mask.sum())
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        O.instance_evaluate_model(model, dense, R, patch_scale=PATCH_SCALE, net_chunk=32768)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    dt = float(np.mean(times))
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    return {"value": R / dt, "unit": "rays/s", "cores": cores, "kind": "port",
+            "sample": f"{R} rays of the frame ({n_in_shell} in-shell samples), oracle/nerftex_oracle.py "
+                      f"instance_evaluate_model (NumPy fp32 + multithreaded BLAS), mean of {steps} passes",
+            "samples_per_sec": n_in_shell / dt, "ms_per_pass": dt * 1e3}
+
+
+def config_dict(extra=None):
+    c = {"workload": "carpet-shape instanced render, 800x800 frame (640000 rays), n_parameters [1,6], "
+                     "n_samples<=1024, step 0.002, patch_scale 0.09, render_chunk 16384, random-init weights",
+         "rays_per_step": H * W, "cache": "per-step inputs (~4 GB of instancer records) exceed the 126 MB L2",
+         "instancer": "synthetic (seeded): hit~0.7, in-shell samples/ray~LogNormal(ln120,0.6)"}
+    if extra:
+        c.update(extra)
+    return c
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb = cpu_baseline_run(args.steps, max(args.warmup, 1))
+    line = {"impl": "reference", "metric": "rays/s (800x800 carpet-shape instanced render; samples/s alongside)",
+            "value": cb["value"], "unit": "rays/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": cb["ms_per_pass"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic", "config": config_dict({"reference_note":
+            "reference TensorFlow 2.4.1 is not installable in this image; oracle port timed on host cores"}),
+            "samples_per_sec": cb["samples_per_sec"], "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "rays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from nerf_tex_b200 import _lib, ops
+    from nerf_tex_b200.instancer import SyntheticInstancer
+    from nerf_tex_b200.model import ParamNerf
+    from nerf_tex_b200.renderer import InstanceRenderer
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    ff = lambda n: {"module": "network.model.FourierFeatures", "n_freq_bands": n}
+    model = ParamNerf(ff(10), ff(4), ff(4), n_parameters=list(NPAR), seed=1)["model"]
+    rays_o, rays_d, t, params, cone = frame_rays(seed=1000 + rank)
+    n_rays = H * W
+
+    # ---- pre-generate the instancer records of every render chunk (not part of the hot path)
+    synth = SyntheticInstancer(b_0=B0, b_1=B1, patch_scale=PATCH_SCALE, seed=rank)
+    d_o, d_d = torch.as_tensor(rays_o[0]).to(dev), torch.as_tensor(rays_d[0]).to(dev)
+    d_p = torch.as_tensor(params).to(dev).repeat_interleave(n_rays, dim=0)
+    chunks = []
+    for i in range(0, n_rays, RENDER_CHUNK):
+        chunks.append(synth.get_model_input_csr(d_o[i:i + RENDER_CHUNK], d_d[i:i + RENDER_CHUNK],
+                                                d_p[i:i + RENDER_CHUNK], N_SAMPLES, STEP_SIZE))
+    n_samples_total = int(sum(c["pts"].shape[0] for c in chunks))
+    n_hit = int(sum(c["ray_index"].shape[0] for c in chunks))
+    del d_p
+
+    resident = ChunkReplayInstancer(chunks, resident=True)
+    renderer = InstanceRenderer(instancer_config=resident, model=model, n_samples=N_SAMPLES, render_chunk=RENDER_CHUNK,
+                                net_chunk=32768, step_size=STEP_SIZE, density_reweighting=True)
+    dev_in = [torch.as_tensor(x).to(dev) for x in (rays_o, rays_d, t, params, cone)]
+
+    # K1 launch timing hooks (CUDA events on the launching stream)
+    k1_events = []
+    orig_forward = model.forward_rows
+
+    def timed_forward(**kw):
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        out = orig_forward(**kw)
+        e.record()
+        k1_events.append((s, e, kw["n_rows"]))
+        return out
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def one_step():
+        resident.reset()
+        return renderer(*dev_in, composite_bkgd=False, training=False)
+
+    for _ in range(max(args.warmup, 3)):
+        one_step()
+    model.forward_rows = timed_forward
+    sync_all()
+    proc, cpath = clocks_start()
+    time.sleep(0.3)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = one_step()
+    e1.record()
+    sync_all()
+    ms = e0.elapsed_time(e1)
+    model.forward_rows = orig_forward
+    time.sleep(0.2)
+    clocks = clocks_stop(proc, cpath)
+    k1_ms = sum(s.elapsed_time(e) for s, e, _ in k1_events)
+    k1_rows = sum(n for _, _, n in k1_events)
+    k1_launches = len(k1_events)
+
+    # ---- e2e arm: host buffers in, host result out, copies inside the timed region
+    host = ChunkReplayInstancer(chunks, resident=False)
+    renderer_h = InstanceRenderer(instancer_config=host, model=model, n_samples=N_SAMPLES, render_chunk=RENDER_CHUNK,
+                                  net_chunk=32768, step_size=STEP_SIZE, density_reweighting=True)
+    host_in = [torch.as_tensor(x).pin_memory() for x in (rays_o, rays_d, t, params, cone)]
+    res_c = torch.empty((1, n_rays, 3), dtype=torch.float32).pin_memory()
+    res_a = torch.empty((1, n_rays), dtype=torch.float32).pin_memory()
+
+    def one_step_e2e():
+        host.reset()
+        ins = [x.to(dev, non_blocking=True) for x in host_in]
+        o = renderer_h(*ins, composite_bkgd=False, training=False)
+        res_c.copy_(o["color_pred"], non_blocking=True)
+        res_a.copy_(o["alpha_pred"], non_blocking=True)
+
+    for _ in range(2):
+        one_step_e2e()
+    sync_all()
+    host.h2d_bytes = 0
+    e_steps = max(1, min(args.steps, 3))
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for _ in range(e_steps):
+        one_step_e2e()
+    e3.record()
+    sync_all()
+    ms_e2e = e2.elapsed_time(e3)
+    h2d = host.h2d_bytes // e_steps + sum(x.numel() * 4 for x in host_in)
+    d2h = res_c.numel() * 4 + res_a.numel() * 4
+
+    # ---- max over ranks
+    stats = torch.tensor([ms, ms_e2e, k1_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(n_samples_total), float(k1_rows)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms, ms_e2e, k1_ms = [float(x) for x in stats.tolist()]
+    samples_all, k1_rows_all = [float(x) for x in tot.tolist()]
+
+    if rank == 0:
+        pk = peaks()
+        sec = ms / 1e3
+        rays_per_s = world * n_rays * args.steps / sec
+        samples_per_s = samples_all * args.steps / sec
+        flops_per_row = 2.0 * MACS_PER_SAMPLE[NPAR]
+        k1_tflops = (k1_rows / max(k1_launches, 1)) * flops_per_row / ((k1_ms / max(k1_launches, 1)) / 1e3) / 1e12
+        line = {
+            "metric": "rays/s (800x800 carpet-shape instanced render; samples/s alongside)",
+            "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": config_dict({"hit_rays_per_frame": n_hit, "in_shell_samples_per_frame": n_samples_total,
+                                   "parallelism": f"rays: one frame per GPU x{world}, no collective"}),
+            "samples_per_sec": samples_per_s,
+            "roofline": {"kernel": "mlp_forward_kernel (K1 fused encoding + MLP, tcgen05)", "bound": "tensor",
+                         "achieved": k1_tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                         "frac": k1_tflops / pk["bf16_tflops_sustained"], "traffic": None,
+                         "peak_source": f"{pk['source']} bf16_tflops_sustained (kernel timed inside a long step)",
+                         "frac_of_burst_peak": k1_tflops / pk["bf16_tflops"],
+                         "flops_per_sample": flops_per_row, "rows_per_launch": k1_rows / max(k1_launches, 1),
+                         "launch_ms": k1_ms / max(k1_launches, 1), "k1_share_of_step": k1_ms / ms},
+            "e2e": {"value": world * n_rays * e_steps / (ms_e2e / 1e3), "unit": "rays/s",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / e_steps,
+                    "samples_per_sec": samples_all * e_steps / (ms_e2e / 1e3),
+                    "api": "InstanceRenderer.__call__ with pinned host rays + host instancer records"},
+            "gpu_launches": int(2 * len(chunks) * args.steps),
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_gpu(args)
+
+
+if __name__ == "__main__":
+    main()
