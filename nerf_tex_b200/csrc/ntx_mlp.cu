@@ -4,9 +4,10 @@
 //
 //   warp 0      weight producer: streams the packed bf16 weight image, one [N x 32] K-slice per
 //               bulk-TMA copy (cp.async.bulk -> UBLKCP), into a 3-deep shared-memory ring.
-//   warp 1      MMA issuer: one elected thread issues tcgen05.mma (M=128, N=256|128, K=16, bf16 in,
-//               fp32 accumulate in TMEM) for BOTH 128-row tiles against every staged slice, so
-//               each weight byte fetched from L2 feeds 256 rows.
+//   warp 1      MMA issuer: one elected lane issues tcgen05.mma (M=128, N=256|128, K=16, bf16 in,
+//               fp32 accumulate in TMEM).  The CTA's two 128-row tiles alternate layer by layer:
+//               while the tensor core runs tile 1's layer, tile 0's epilogue warps turn their
+//               accumulators into the next layer's operand, and vice versa.
 //   warps 2-9   two epilogue warpgroups (one per tile, one thread per row): compute the encodings,
 //               and per layer pull the fp32 accumulator row out of TMEM (tcgen05.ld), apply ReLU,
 //               round to bf16 and write it back as next layer's A operand in the UMMA-canonical
@@ -40,7 +41,7 @@ constexpr uint32_t kTileBytes = kMainBytes + kEncBytes;                    // 90
 constexpr uint32_t kOffStages = kTilesPerCta * kTileBytes;                 // 180224
 constexpr uint32_t kOffHeads = kOffStages + kStages * kStageBytes;         // 229376
 constexpr uint32_t kOffBars = kOffHeads + kHeadFloats * 4;                 // +2592
-constexpr uint32_t kNumBars = 2 * kStages + 2;
+constexpr uint32_t kNumBars = 2 * kStages + 2 * kTilesPerCta;
 constexpr uint32_t kOffTmemSlot = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemSlot + 16;
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
@@ -84,6 +85,45 @@ __device__ __forceinline__ void sincos4(float x, uint32_t (&w)[4]) {
 // ----------------------------------------------------------------------------------------------
 // the fused forward kernel
 // ----------------------------------------------------------------------------------------------
+
+// bf16x2 word {lo, hi} with ReLU folded into the conversion (one F2FP per two activations)
+__device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
+    uint32_t r;
+    asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+    return r;
+}
+
+// 32 fp32 accumulator columns (chunk j of this thread's row) -> bf16 -> next layer's A operand
+template <bool RELU>
+__device__ __forceinline__ void store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32]) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        uint32_t w[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float lo = __uint_as_float(v[8 * c + 2 * e]), hi = __uint_as_float(v[8 * c + 2 * e + 1]);
+            w[e] = RELU ? pack_bf16_relu(lo, hi) : pack_bf16(lo, hi);
+        }
+        st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
+    }
+}
+
+// plain hidden layer epilogue: TMEM loads software-pipelined against the convert + store
+template <bool RELU>
+__device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t main_base, int row, int n_chunks) {
+    uint32_t va[32], vb[32];
+    tmem_ld_32x32b_x32(tmem_row, va);
+    tmem_ld_wait();
+    for (int j = 0; j < n_chunks; j += 2) {
+        tmem_ld_32x32b_x32(tmem_row + (j + 1) * 32, vb);
+        store_chunk32<RELU>(main_base, j, row, va);
+        tmem_ld_wait();
+        if (j + 2 < n_chunks) tmem_ld_32x32b_x32(tmem_row + (j + 2) * 32, va);
+        store_chunk32<RELU>(main_base, j + 1, row, vb);
+        tmem_ld_wait();
+    }
+}
+
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__ KernelArgs args) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -91,10 +131,10 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
     if ((sbase & 1023u) != 0) __trap();
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t bar_full = sbase + kOffBars;                 // [kStages]
-    const uint32_t bar_empty = bar_full + 8 * kStages;          // [kStages]
-    const uint32_t bar_act = bar_empty + 8 * kStages;           // activations (A operand) ready
-    const uint32_t bar_acc = bar_act + 8;                       // accumulators ready
+    const uint32_t bar_full = sbase + kOffBars;                 // [kStages]  weight slice landed
+    const uint32_t bar_empty = bar_full + 8 * kStages;          // [kStages]  weight slice consumed
+    const uint32_t bar_act = bar_empty + 8 * kStages;           // [2] tile's A operand (activations) ready
+    const uint32_t bar_acc = bar_act + 8 * kTilesPerCta;        // [2] tile's accumulators ready
     float* heads = reinterpret_cast<float*>(smem + kOffHeads);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffTmemSlot);
 
@@ -106,8 +146,10 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
             mbar_init(bar_full + 8 * i, 1);
             mbar_init(bar_empty + 8 * i, 1);
         }
-        mbar_init(bar_act, kTilesPerCta * 4);   // one arrive per epilogue warp
-        mbar_init(bar_acc, 1);
+        for (int t = 0; t < kTilesPerCta; ++t) {
+            mbar_init(bar_act + 8 * t, 4);      // one arrive per epilogue warp of the tile
+            mbar_init(bar_acc + 8 * t, 1);
+        }
         fence_mbar_init();
     }
     if (warp == 1) {
@@ -124,51 +166,64 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
 
     if (warp == 0) {
         // ===================================================================== weight producer
+        // The two tiles run half a layer out of phase (tile 1's MMAs overlap tile 0's epilogue and
+        // vice versa), so every layer's slices are streamed once per tile, in MMA issue order.
         if (lane == 0) {
             uint32_t it = 0;
             for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
-                for (int s = 0; s < prog.n_slices; ++s, ++it) {
-                    const uint32_t stage = it % kStages, round = it / kStages;
-                    mbar_wait(bar_empty + 8 * stage, (round & 1) ^ 1);
-                    const uint32_t off = prog.slice_off[s], bytes = prog.slice_off[s + 1] - off;
-                    mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-                    tma_bulk_g2s(sbase + kOffStages + stage * kStageBytes, args.packed + off, bytes,
-                                 bar_full + 8 * stage);
+                for (int st = 0; st < prog.n_steps; ++st) {
+                    const int s0 = prog.steps[st].slice_begin, s1 = prog.steps[st].slice_end;
+                    for (int t = 0; t < kTilesPerCta; ++t) {
+                        for (int s = s0; s < s1; ++s, ++it) {
+                            const uint32_t stage = it % kStages, round = it / kStages;
+                            mbar_wait(bar_empty + 8 * stage, (round & 1) ^ 1);
+                            const uint32_t off = prog.slice_off[s], bytes = prog.slice_off[s + 1] - off;
+                            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+                            tma_bulk_g2s(sbase + kOffStages + stage * kStageBytes, args.packed + off, bytes,
+                                         bar_full + 8 * stage);
+                        }
+                    }
                 }
             }
         }
     } else if (warp == 1) {
         // ===================================================================== MMA issuer
-        if (lane == 0) {
-            uint32_t it = 0, act_phase = 0;
-            for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
-                for (int st = 0; st < prog.n_steps; ++st) {
-                    const Step& step = prog.steps[st];
-                    const uint32_t idesc = idesc_bf16_f32(kTileRows, step.n_out);
-                    mbar_wait(bar_act, act_phase);
-                    act_phase ^= 1;
+        // The whole warp walks the schedule (so every operand is warp-uniform); one elected lane
+        // issues tcgen05.mma / tcgen05.commit.
+        uint32_t it = 0, act_phase0 = 0, act_phase1 = 0;
+        for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+            for (int st = 0; st < prog.n_steps; ++st) {
+                const Step& step = prog.steps[st];
+                const uint32_t idesc = idesc_bf16_f32(kTileRows, step.n_out);
+#pragma unroll
+                for (int t = 0; t < kTilesPerCta; ++t) {
+                    if (t == 0) { mbar_wait(bar_act, act_phase0); act_phase0 ^= 1; }
+                    else { mbar_wait(bar_act + 8, act_phase1); act_phase1 ^= 1; }
                     tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + t * kWidth;
+                    const uint32_t a_tile = sbase + t * kTileBytes;
                     uint32_t accumulate = 0;
                     for (int s = step.slice_begin; s < step.slice_end; ++s, ++it) {
                         const uint32_t sl = prog.slices[s];
                         const uint32_t stage = it % kStages, round = it / kStages;
                         mbar_wait(bar_full + 8 * stage, round & 1);
                         tc_fence_after();
-                        const uint32_t a_off = (slice_is_enc(sl) ? kMainBytes : 0u) + slice_blk(sl) * kBlockBytes;
+                        const uint32_t a_addr = a_tile + (slice_is_enc(sl) ? kMainBytes : 0u) + slice_blk(sl) * kBlockBytes;
                         const uint32_t b_addr = sbase + kOffStages + stage * kStageBytes;
                         const int h0 = slice_half0(sl), nh = slice_nh(sl);
-                        for (int h = h0; h < h0 + nh; ++h) {
-                            const uint64_t bd = smem_desc(b_addr + h * 32, 16, 512, LAYOUT_SW64);
-#pragma unroll
-                            for (int t = 0; t < kTilesPerCta; ++t) {
-                                const uint64_t ad = smem_desc(sbase + t * kTileBytes + a_off + h * 32, 16, 512, LAYOUT_SW64);
-                                mma_bf16_ss(tmem_base + t * kWidth, ad, bd, idesc, accumulate);
-                            }
-                            accumulate = 1;
+                        if (elect_one_sync()) {
+                            mma_bf16_ss(d_tmem, smem_desc(a_addr + h0 * 32, 16, 512, LAYOUT_SW64),
+                                        smem_desc(b_addr + h0 * 32, 16, 512, LAYOUT_SW64), idesc, accumulate);
+                            if (nh == 2)
+                                mma_bf16_ss(d_tmem, smem_desc(a_addr + 32, 16, 512, LAYOUT_SW64),
+                                            smem_desc(b_addr + 32, 16, 512, LAYOUT_SW64), idesc, 1u);
+                            mma_commit(bar_empty + 8 * stage);      // slice free once these MMAs retire
                         }
-                        mma_commit(bar_empty + 8 * stage);     // slice free once these MMAs retire
+                        __syncwarp();
+                        accumulate = 1;
                     }
-                    mma_commit(bar_acc);                       // accumulators of both tiles complete
+                    if (elect_one_sync()) mma_commit(bar_acc + 8 * t);   // this tile's accumulators complete
+                    __syncwarp();
                 }
             }
         }
@@ -181,6 +236,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         const uint32_t main_base = sbase + tile * kTileBytes;
         const uint32_t enc_base = main_base + kMainBytes;
         const uint32_t tmem_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + tile * kWidth;
+        const uint32_t my_act = bar_act + 8 * tile, my_acc = bar_acc + 8 * tile;
         const int g = prog.n_geo, a = prog.n_app;
         const float* w_alpha = heads;               // [256], b at [256]
         const float* w_rgb = heads + 260;           // [3][128], b at [260 + 384 ..]
@@ -254,56 +310,60 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
             }
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(bar_act);
+            if (lane == 0) mbar_arrive(my_act);
 
             float alpha_raw = 0.0f;
             // ------------------------------------------------------------- layer epilogues
             for (int st = 0; st < prog.n_steps; ++st) {
                 const Step& step = prog.steps[st];
                 const uint32_t epi = step.epi;
-                mbar_wait(bar_acc, acc_phase);
+                const int n_chunks = step.n_out >> 5;
+                mbar_wait(my_acc, acc_phase);
                 acc_phase ^= 1;
                 tc_fence_after();
                 float o0 = 0.f, o1 = 0.f, o2 = 0.f;
-                const int n_chunks = step.n_out >> 5;
-                for (int j = 0; j < n_chunks; ++j) {
-                    uint32_t v[32];
-                    tmem_ld_32x32b_x32(tmem_row + j * 32, v);
-                    tmem_ld_wait();
-                    float f[32];
+                if ((epi & (EPI_ALPHA | EPI_FINAL)) == 0) {
+                    // hidden layer: (ReLU) -> bf16 -> A operand of the next layer
+                    if (epi & EPI_RELU) epilogue_store_layer<true>(tmem_row, main_base, row, n_chunks);
+                    else epilogue_store_layer<false>(tmem_row, main_base, row, n_chunks);
+                } else {
+                    // layers that also feed an fp32 head (density after the trunk, colour at the end)
+                    for (int j = 0; j < n_chunks; ++j) {
+                        uint32_t v[32];
+                        tmem_ld_32x32b_x32(tmem_row + j * 32, v);
+                        tmem_ld_wait();
+                        float f[32];
 #pragma unroll
-                    for (int c = 0; c < 32; ++c) {
-                        f[c] = __uint_as_float(v[c]);
-                        if (epi & EPI_RELU) f[c] = fmaxf(f[c], 0.0f);
-                    }
-                    if (epi & EPI_ALPHA) {                                       // model.py:111
-                        const float4* wa = reinterpret_cast<const float4*>(w_alpha + j * 32);
+                        for (int c = 0; c < 32; ++c) f[c] = fmaxf(__uint_as_float(v[c]), 0.0f);   // both are ReLU layers
+                        if (epi & EPI_ALPHA) {                                   // model.py:111
+                            const float4* wa = reinterpret_cast<const float4*>(w_alpha + j * 32);
 #pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            const float4 ww = wa[c];
-                            alpha_raw += f[4 * c] * ww.x + f[4 * c + 1] * ww.y + f[4 * c + 2] * ww.z + f[4 * c + 3] * ww.w;
+                            for (int c = 0; c < 8; ++c) {
+                                const float4 ww = wa[c];
+                                alpha_raw += f[4 * c] * ww.x + f[4 * c + 1] * ww.y + f[4 * c + 2] * ww.z + f[4 * c + 3] * ww.w;
+                            }
+                        }
+                        if (epi & EPI_FINAL) {                                   // model.py:123
+                            const float4* w0 = reinterpret_cast<const float4*>(w_rgb + j * 32);
+                            const float4* w1 = reinterpret_cast<const float4*>(w_rgb + 128 + j * 32);
+                            const float4* w2 = reinterpret_cast<const float4*>(w_rgb + 256 + j * 32);
+#pragma unroll
+                            for (int c = 0; c < 8; ++c) {
+                                const float4 a0 = w0[c], a1 = w1[c], a2 = w2[c];
+                                o0 += f[4 * c] * a0.x + f[4 * c + 1] * a0.y + f[4 * c + 2] * a0.z + f[4 * c + 3] * a0.w;
+                                o1 += f[4 * c] * a1.x + f[4 * c + 1] * a1.y + f[4 * c + 2] * a1.z + f[4 * c + 3] * a1.w;
+                                o2 += f[4 * c] * a2.x + f[4 * c + 1] * a2.y + f[4 * c + 2] * a2.z + f[4 * c + 3] * a2.w;
+                            }
+                        } else {
+#pragma unroll
+                            for (int c = 0; c < 4; ++c)
+                                st_shared_v4(chunk_addr(main_base, j * 4 + c, row),
+                                             pack_bf16(f[8 * c], f[8 * c + 1]), pack_bf16(f[8 * c + 2], f[8 * c + 3]),
+                                             pack_bf16(f[8 * c + 4], f[8 * c + 5]), pack_bf16(f[8 * c + 6], f[8 * c + 7]));
                         }
                     }
-                    if (epi & EPI_FINAL) {                                       // model.py:123
-                        const float4* w0 = reinterpret_cast<const float4*>(w_rgb + j * 32);
-                        const float4* w1 = reinterpret_cast<const float4*>(w_rgb + 128 + j * 32);
-                        const float4* w2 = reinterpret_cast<const float4*>(w_rgb + 256 + j * 32);
-#pragma unroll
-                        for (int c = 0; c < 8; ++c) {
-                            const float4 a0 = w0[c], a1 = w1[c], a2 = w2[c];
-                            o0 += f[4 * c] * a0.x + f[4 * c + 1] * a0.y + f[4 * c + 2] * a0.z + f[4 * c + 3] * a0.w;
-                            o1 += f[4 * c] * a1.x + f[4 * c + 1] * a1.y + f[4 * c + 2] * a1.z + f[4 * c + 3] * a1.w;
-                            o2 += f[4 * c] * a2.x + f[4 * c + 1] * a2.y + f[4 * c + 2] * a2.z + f[4 * c + 3] * a2.w;
-                        }
-                    } else {
-#pragma unroll
-                        for (int c = 0; c < 4; ++c)
-                            st_shared_v4(chunk_addr(main_base, j * 4 + c, row),
-                                         pack_bf16(f[8 * c], f[8 * c + 1]), pack_bf16(f[8 * c + 2], f[8 * c + 3]),
-                                         pack_bf16(f[8 * c + 4], f[8 * c + 5]), pack_bf16(f[8 * c + 6], f[8 * c + 7]));
-                    }
+                    if (epi & EPI_ALPHA) alpha_raw += w_alpha[256];
                 }
-                if (epi & EPI_ALPHA) alpha_raw += w_alpha[256];
                 if (epi & EPI_SWITCH) {
                     // ----------------------------------------------------- dir-phase encoding
 #pragma unroll
@@ -337,7 +397,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     fence_proxy_async_smem();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(bar_act);
+                    if (lane == 0) mbar_arrive(my_act);
                 }
             }
         }
