@@ -22,8 +22,8 @@ NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17",
     "-Xcompiler", "-fPIC,-fvisibility=hidden",
-    "--expt-relaxed-constexpr",
-]
+    "--expt-relaxed-constexpr", "--extended-lambda",
+] + os.environ.get("NTX_NVCC_EXTRA", "").split()
 
 
 def _nvcc() -> str:

@@ -47,6 +47,9 @@ constexpr uint32_t kSmemBytes = kOffTmemSlot + 16;
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 
 constexpr int kThreads = 320;
+#ifndef NTX_MMA_PREFETCH
+#define NTX_MMA_PREFETCH 0
+#endif
 constexpr int kEpiWarp0 = 2;
 
 struct KernelArgs {
@@ -169,18 +172,19 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         // The two tiles run half a layer out of phase (tile 1's MMAs overlap tile 0's epilogue and
         // vice versa), so every layer's slices are streamed once per tile, in MMA issue order.
         if (lane == 0) {
-            uint32_t it = 0;
+            uint32_t stage = 0, parity = 1;      // a fresh barrier passes a wait on parity 1
             for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
                 for (int st = 0; st < prog.n_steps; ++st) {
-                    const int s0 = prog.steps[st].slice_begin, s1 = prog.steps[st].slice_end;
+                    const int n_sl = prog.steps[st].slice_end - prog.steps[st].slice_begin;
+                    const uint32_t bytes = (uint32_t)prog.steps[st].n_out * 64u;
+                    const uint8_t* src0 = args.packed + prog.slice_off[prog.steps[st].slice_begin];
                     for (int t = 0; t < kTilesPerCta; ++t) {
-                        for (int s = s0; s < s1; ++s, ++it) {
-                            const uint32_t stage = it % kStages, round = it / kStages;
-                            mbar_wait(bar_empty + 8 * stage, (round & 1) ^ 1);
-                            const uint32_t off = prog.slice_off[s], bytes = prog.slice_off[s + 1] - off;
+                        const uint8_t* src = src0;
+                        for (int s = 0; s < n_sl; ++s, src += bytes) {
+                            mbar_wait(bar_empty + 8 * stage, parity);
                             mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-                            tma_bulk_g2s(sbase + kOffStages + stage * kStageBytes, args.packed + off, bytes,
-                                         bar_full + 8 * stage);
+                            tma_bulk_g2s(sbase + kOffStages + stage * kStageBytes, src, bytes, bar_full + 8 * stage);
+                            if (++stage == kStages) { stage = 0; parity ^= 1; }
                         }
                     }
                 }
@@ -190,38 +194,55 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         // ===================================================================== MMA issuer
         // The whole warp walks the schedule (so every operand is warp-uniform); one elected lane
         // issues tcgen05.mma / tcgen05.commit.
-        uint32_t it = 0, act_phase0 = 0, act_phase1 = 0;
+        uint32_t stage = 0, parity = 0, act_phase0 = 0, act_phase1 = 0;
+        uint32_t b16 = (sbase + kOffStages) >> 4;         // ring stage base >> 4
+        uint32_t full_bar = bar_full, empty_bar = bar_empty;
+#if NTX_MMA_PREFETCH
+        bool ready = false;      // result of the non-blocking probe of the next ring stage
+#endif
+        // one weight slice: wait until it landed, issue 1-2 MMAs (K=16 each), release the ring stage
+        auto issue_slice = [&](uint32_t d_tmem, uint32_t a16, uint32_t half0, uint32_t nh, uint32_t idesc, uint32_t accumulate) {
+#if NTX_MMA_PREFETCH
+            if (!ready) mbar_wait(full_bar, parity);
+#else
+            mbar_wait(full_bar, parity);
+#endif
+            tc_fence_after();
+            const uint32_t bb = b16 + half0 * 2, eb = empty_bar;
+            if (++stage == kStages) {
+                stage = 0; parity ^= 1; b16 = (sbase + kOffStages) >> 4; full_bar = bar_full; empty_bar = bar_empty;
+            } else {
+                b16 += kStageBytes >> 4; full_bar += 8; empty_bar += 8;
+            }
+#if NTX_MMA_PREFETCH
+            ready = mbar_test_wait(full_bar, parity);   // probe the next stage: latency hides behind the issue below
+#endif
+            if (elect_one_sync()) {
+                mma_bf16_ss(d_tmem, desc_sw64(a16), desc_sw64(bb), idesc, accumulate);
+                if (nh == 2) mma_bf16_ss(d_tmem, desc_sw64(a16 + 2), desc_sw64(bb + 2), idesc, 1u);
+                mma_commit(eb);                             // slice free once these MMAs retire
+            }
+            __syncwarp();
+        };
         for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
             for (int st = 0; st < prog.n_steps; ++st) {
-                const Step& step = prog.steps[st];
-                const uint32_t idesc = idesc_bf16_f32(kTileRows, step.n_out);
+                // copy the step into registers once (asm memory clobbers would otherwise reload it per slice)
+                const uint32_t idesc = idesc_bf16_f32(kTileRows, prog.steps[st].n_out);
+                const int n_main = prog.steps[st].n_main, enc_n = prog.steps[st].enc_n;
+                const uint32_t enc_half0 = prog.steps[st].enc_half0, enc_last_nh = prog.steps[st].enc_last_nh;
+                const uint32_t enc16 = ((uint32_t)kMainBytes + prog.steps[st].enc_blk0 * kBlockBytes + enc_half0 * 32u) >> 4;
 #pragma unroll
                 for (int t = 0; t < kTilesPerCta; ++t) {
                     if (t == 0) { mbar_wait(bar_act, act_phase0); act_phase0 ^= 1; }
                     else { mbar_wait(bar_act + 8, act_phase1); act_phase1 ^= 1; }
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + t * kWidth;
-                    const uint32_t a_tile = sbase + t * kTileBytes;
-                    uint32_t accumulate = 0;
-                    for (int s = step.slice_begin; s < step.slice_end; ++s, ++it) {
-                        const uint32_t sl = prog.slices[s];
-                        const uint32_t stage = it % kStages, round = it / kStages;
-                        mbar_wait(bar_full + 8 * stage, round & 1);
-                        tc_fence_after();
-                        const uint32_t a_addr = a_tile + (slice_is_enc(sl) ? kMainBytes : 0u) + slice_blk(sl) * kBlockBytes;
-                        const uint32_t b_addr = sbase + kOffStages + stage * kStageBytes;
-                        const int h0 = slice_half0(sl), nh = slice_nh(sl);
-                        if (elect_one_sync()) {
-                            mma_bf16_ss(d_tmem, smem_desc(a_addr + h0 * 32, 16, 512, LAYOUT_SW64),
-                                        smem_desc(b_addr + h0 * 32, 16, 512, LAYOUT_SW64), idesc, accumulate);
-                            if (nh == 2)
-                                mma_bf16_ss(d_tmem, smem_desc(a_addr + 32, 16, 512, LAYOUT_SW64),
-                                            smem_desc(b_addr + 32, 16, 512, LAYOUT_SW64), idesc, 1u);
-                            mma_commit(bar_empty + 8 * stage);      // slice free once these MMAs retire
-                        }
-                        __syncwarp();
-                        accumulate = 1;
-                    }
+                    const uint32_t a16_tile = (sbase + t * kTileBytes) >> 4;
+                    for (int i = 0; i < n_main; ++i)
+                        issue_slice(d_tmem, a16_tile + i * (kBlockBytes >> 4), 0u, 2u, idesc, i > 0 ? 1u : 0u);
+                    for (int e = 0; e < enc_n; ++e)
+                        issue_slice(d_tmem, a16_tile + enc16 + e * (kBlockBytes >> 4), enc_half0,
+                                    e == enc_n - 1 ? enc_last_nh : 2u, idesc, (n_main > 0 || e > 0) ? 1u : 0u);
                     if (elect_one_sync()) mma_commit(bar_acc + 8 * t);   // this tile's accumulators complete
                     __syncwarp();
                 }
@@ -497,14 +518,17 @@ int build_program(ntx_mlp* m) {
         Step& s = p.steps[ns];
         s.layer = layer; s.n_out = n_out; s.main_row0 = main_row0; s.enc_data = enc_data; s.phase = phase; s.epi = epi;
         s.slice_begin = nsl;
+        s.n_main = has_main ? kMainBlocks : 0;
         if (has_main)
             for (int b = 0; b < kMainBlocks; ++b) p.slices[nsl++] = make_slice(0, b, 0, 2, ns);
         if (enc_data) {
             const int halves = ((phase == 0 ? pos_chunks(g) : dir_chunks(a)) + 1) / 2;
             for (int h = 0; h < halves; h += 2) p.slices[nsl++] = make_slice(1, h / 2, 0, halves - h >= 2 ? 2 : 1, ns);
+            s.enc_n = (halves + 1) / 2; s.enc_blk0 = 0; s.enc_half0 = 0; s.enc_last_nh = (halves & 1) ? 1 : 2;
         } else {
             const int oc = phase == 0 ? pos_ones_col() : dir_ones_col(a);
             p.slices[nsl++] = make_slice(1, oc / 32, (oc % 32) / 16, 1, ns);
+            s.enc_n = 1; s.enc_blk0 = oc / 32; s.enc_half0 = (oc % 32) / 16; s.enc_last_nh = 1;
         }
         s.slice_end = nsl;
         for (int q = s.slice_begin; q < s.slice_end; ++q) { p.slice_off[q] = boff; boff += (uint32_t)n_out * 64; }

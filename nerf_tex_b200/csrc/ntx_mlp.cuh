@@ -17,8 +17,8 @@
 
 namespace ntxmlp {
 
-constexpr int kMaxSteps = 20;
-constexpr int kMaxSlices = 224;
+constexpr int kMaxSteps = 16;
+constexpr int kMaxSlices = 176;
 constexpr int kWidth = 256;
 constexpr int kTileRows = 128;        // rows per UMMA tile (M)
 constexpr int kTilesPerCta = 2;       // two tiles share every staged weight slice
@@ -47,12 +47,23 @@ struct Step {
     int32_t enc_data;       // 1: this layer consumes the resident encoding's features, 0: bias column only
     int32_t phase;          // 0: pos encoding resident, 1: dir encoding resident
     uint32_t epi;           // EPI_* flags
+    // compact form of the slice list for the MMA issuer (no per-slice table lookups)
+    int32_t n_main;         // leading slices that read main-buffer blocks 0..n_main-1 (two K=16 halves each)
+    int32_t enc_n;          // trailing slices that read encoding blocks enc_blk0..enc_blk0+enc_n-1
+    int32_t enc_blk0;
+    int32_t enc_half0;      // first K=16 half used inside the encoding block(s)
+    int32_t enc_last_nh;    // halves issued for the last encoding slice (the others use 2)
+    int32_t pad_[3];
 };
 
 // slice word: bit0 a_is_enc | bits1-4 a_blk | bit5 first half | bits6-7 n_halves | bits8-15 step
+//             | bits16-29 (byte offset of the A operand inside its tile) >> 4, ready for the descriptor
 __host__ __device__ inline uint32_t make_slice(int is_enc, int blk, int half0, int nh, int step) {
-    return (uint32_t)is_enc | ((uint32_t)blk << 1) | ((uint32_t)half0 << 5) | ((uint32_t)nh << 6) | ((uint32_t)step << 8);
+    const uint32_t a_rel = (is_enc ? (uint32_t)(kMainBlocks * kBlockBytes) : 0u) + (uint32_t)blk * kBlockBytes + (uint32_t)half0 * 32u;
+    return (uint32_t)is_enc | ((uint32_t)blk << 1) | ((uint32_t)half0 << 5) | ((uint32_t)nh << 6) | ((uint32_t)step << 8) |
+           ((a_rel >> 4) << 16);
 }
+__host__ __device__ inline uint32_t slice_a16(uint32_t s) { return (s >> 16) & 0x3FFFu; }
 __host__ __device__ inline int slice_is_enc(uint32_t s) { return s & 1; }
 __host__ __device__ inline int slice_blk(uint32_t s) { return (s >> 1) & 15; }
 __host__ __device__ inline int slice_half0(uint32_t s) { return (s >> 5) & 1; }

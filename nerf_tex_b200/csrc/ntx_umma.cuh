@@ -44,6 +44,16 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
         : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     return ok != 0;
 }
+// non-blocking probe (never suspends the thread)
+__device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
 // A protocol bug must fault, not hang the GPU: after ~2 s of waiting the kernel traps.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
@@ -108,6 +118,12 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo, uint
     d |= (uint64_t)1 << 46;            // descriptor version = 1 (Blackwell)
     d |= (uint64_t)(layout & 7) << 61;
     return d;
+}
+
+// SWIZZLE_64B K-major descriptor split into a constant high word and an address-bearing low word
+constexpr uint32_t kDescHiSw64 = (512u >> 4) | (1u << 14) | ((uint32_t)LAYOUT_SW64 << 29);
+__device__ __forceinline__ uint64_t desc_sw64(uint32_t addr16) {      // addr16 = shared address >> 4
+    return ((uint64_t)kDescHiSw64 << 32) | (uint64_t)((addr16 & 0x3FFFu) | (1u << 16));
 }
 
 // kind::f16, A = B = bf16 (K-major), D = fp32, dense.
