@@ -104,7 +104,7 @@ int ntx_composite_instanced_forward(const float* rgbs, const float* dists, const
 
 /* Architecture of network/model.py:58-125 (ParamNerf; Nerf :9-45 is n_geo = n_app = 0,
  * color_depth = 0).  Supported by the sm_100a kernel: n_pos = 3, pos_freqs = 10, dir_freqs = 4,
- * param_freqs = 4, width = 256, param_depth = 0, n_geo <= 3, n_app <= 7, depth <= 16. */
+ * param_freqs = 4, width = 256, param_depth = 0, n_geo <= 3, n_app <= 7, depth <= 12. */
 typedef struct ntx_mlp_config {
     int32_t n_pos;       /* 3 */
     int32_t pos_freqs;   /* 10 */
@@ -158,6 +158,25 @@ typedef struct ntx_mlp_inputs {
  * the FourierFeatures of network/layer.py:11-23.  rgbs[N,4] out: raw colour (pre-sigmoid) and
  * raw density (pre-relu), network/model.py:111,123. */
 int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs, void* stream);
+
+/* Training forward: ntx_mlp_forward that also saves, in bf16, every tensor-core operand the
+ * backward pass needs (the reference keeps them on the tf.GradientTape, network/train.py:62-64):
+ *   enc_pos[N,96], enc_dir[N,96]  encoded inputs in the kernel's column order (see
+ *                                 ntx_mlp_enc_columns), constant-1 bias column included;
+ *   acts[n_steps][N,256]          stored output of every step (post-activation; the 128-wide
+ *                                 last step fills columns 0..127). */
+int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
+                          void* enc_pos, void* enc_dir, void* acts, void* stream);
+
+/* Schedule introspection for the host-side backward (nerf_tex_b200/autograd.py).  A "step" is one
+ * tensor-core layer: trunk0..trunk{depth-1}, feature, colorhid*, colorhalf. */
+int ntx_mlp_num_steps(const ntx_mlp_t* mlp);
+int ntx_mlp_step_info(const ntx_mlp_t* mlp, int step, int32_t* layer, int32_t* n_out, int32_t* main_row0,
+                      int32_t* enc_data, int32_t* phase, int32_t* relu);
+/* ref_index[96] (host): for encoding column c of `phase` (0 pos, 1 dir) the row of the reference's
+ * pos_inputs_map / dir_inputs_map it holds (network/model.py:77-101), -1 for the constant-1
+ * column, -2 for zero padding. */
+int ntx_mlp_enc_columns(const ntx_mlp_t* mlp, int phase, int32_t* ref_index);
 
 /* ------------------------------------------------------------------------------------------
  * tcgen05 self-test (used by tests/ to validate the UMMA shared-memory descriptors on a GPU)

@@ -55,6 +55,10 @@ SIGNATURES = {
     "ntx_mlp_packed_bytes": (_I64, [_P]),
     "ntx_mlp_pack_weights": (_I, [_P, _P, _P, _P]),
     "ntx_mlp_forward": (_I, [_P, _P, C.POINTER(MlpInputs), _P, _P]),
+    "ntx_mlp_forward_train": (_I, [_P, _P, C.POINTER(MlpInputs), _P, _P, _P, _P, _P]),
+    "ntx_mlp_num_steps": (_I, [_P]),
+    "ntx_mlp_step_info": (_I, [_P, _I] + [C.POINTER(C.c_int32)] * 6),
+    "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),
     "ntx_selftest_umma": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ntx_selftest_bulk_copy": (_I, [_P, _P, _I, _P]),
 }

@@ -1,0 +1,155 @@
+"""Backward pass of one network pass (K1 + K2) as a torch.autograd.Function.
+
+Forward: ``ntx_mlp_forward_train`` (fused encoding + MLP that also saves every tensor-core operand
+in bf16) followed by ``ntx_composite_forward``.  Backward: ``ntx_composite_backward`` (hand-written,
+warp per ray) gives d(raw rgb, sigma); the MLP's dgrad / wgrad chain then runs layer by layer on
+the saved bf16 operands as plain library GEMMs (torch.mm -> cuBLAS, bf16 in / fp32 accumulate) —
+round 1 keeps the backward GEMMs in the library; a fused tcgen05 backward is the next step (see
+DESIGN.md).  No gradient flows into the encodings, the sampled depths or the compositing weights
+that drive resampling (network/renderer.py:129 stop_gradient).
+
+The result is ``d loss / d master`` on the model's flat fp32 weight buffer, in the reference's
+Dense order, so any torch optimizer (or the NCCL all-reduce of train.py) works on one tensor.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import torch
+
+from . import _lib, ops
+from ._lib import MlpInputs, check, ptr, stream_ptr
+
+ENC_COLS = 96
+
+
+class MlpSchedule:
+    """Host mirror of the kernel's layer schedule (ntx_mlp_step_info / ntx_mlp_enc_columns)."""
+
+    def __init__(self, model) -> None:
+        lib = _lib.load()
+        h = model._h
+        self.n_steps = lib.ntx_mlp_num_steps(h)
+        self.steps: List[Dict[str, int]] = []
+        for st in range(self.n_steps):
+            v = [C.c_int32() for _ in range(6)]
+            check(lib.ntx_mlp_step_info(h, st, *[C.byref(x) for x in v]))
+            self.steps.append(dict(zip(("layer", "n_out", "main_row0", "enc_data", "phase", "relu"), [x.value for x in v])))
+        self.enc_maps = []
+        for phase in (0, 1):
+            arr = (C.c_int32 * ENC_COLS)()
+            check(lib.ntx_mlp_enc_columns(h, phase, arr))
+            ref = torch.tensor(list(arr), dtype=torch.int64)
+            cols = torch.nonzero(ref >= 0).squeeze(1)
+            self.enc_maps.append((cols.to(model.device), ref[cols].to(model.device)))
+        self.depth = model.cfg.depth
+        self.alpha_layer = self.depth                       # Dense order: trunk0..trunk{d-1}, alpha, feature, ...
+        self.rgb_layer = len(model.layers) - 1
+
+
+def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, rays_o=None, rays_d=None, z=None,
+                      row_scale=None, group_scale=None, blur_idx=None):
+    """Raw rgbs[N,4] plus the saved bf16 operands (enc_pos, enc_dir, acts)."""
+    packed = model.ensure_packed()
+    sched = model.schedule()
+    dev = model.device
+    rgbs = torch.empty((n_rows, 4), dtype=torch.float32, device=dev)
+    enc_pos = torch.empty((n_rows, ENC_COLS), dtype=torch.bfloat16, device=dev)
+    enc_dir = torch.empty((n_rows, ENC_COLS), dtype=torch.bfloat16, device=dev)
+    acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev)
+    inp = MlpInputs(ptr(pos), ptr(rays_o), ptr(rays_d), ptr(z), ptr(dir), ptr(params), ptr(row_scale), ptr(group_scale),
+                    -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows))
+    check(_lib.load().ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
+                                            ptr(acts), stream_ptr()))
+    return rgbs, (enc_pos, enc_dir, acts)
+
+
+def mlp_backward(model, saved, d_rgbs: torch.Tensor) -> torch.Tensor:
+    """d loss / d master given d loss / d rgbs[N,4]  (model.py:104-123 in reverse).
+
+    All GEMMs take bf16 operands with fp32 accumulation; weight gradients come out in fp32.  (An
+    fp32 / TF32 gradient chain was measured to give the same agreement with the float64 reference —
+    the residual is the bf16 forward itself — so the cheaper bf16 chain is kept.)"""
+    enc_pos, enc_dir, acts = saved
+    sched = model.schedule()
+    master = model.master.detach()
+    grad = torch.zeros_like(master)
+    bf = torch.bfloat16
+
+    def wview(layer):
+        wo, bo, fi, fo = model.layers[layer]
+        return master[wo:wo + fi * fo].view(fi, fo), grad[wo:wo + fi * fo].view(fi, fo), grad[bo:bo + fo]
+
+    d_rgb = d_rgbs[:, :3].contiguous()
+    d_sigma = d_rgbs[:, 3:4].contiguous()
+
+    # colour head: rgb = h_half @ W_rgb + b   (model.py:123)
+    last = sched.n_steps - 1
+    h_half = acts[last][:, :128]
+    W, gW, gb = wview(sched.rgb_layer)
+    gW.copy_(torch.mm(h_half.t(), d_rgb.to(bf), out_dtype=torch.float32))
+    gb.copy_(d_rgb.sum(0))
+    d_out = torch.mm(d_rgb.to(bf), W.t().to(bf))                        # [N,128] bf16
+
+    # density head: sigma = h_trunk @ w_alpha + b   (model.py:111)
+    Wa, gWa, gba = wview(sched.alpha_layer)
+    h_trunk = acts[sched.depth - 1]
+    gWa.copy_(torch.mm(h_trunk.t(), d_sigma.to(bf), out_dtype=torch.float32))
+    gba.copy_(d_sigma.sum(0))
+
+    for st in range(last, -1, -1):
+        s = sched.steps[st]
+        n_out = s["n_out"]
+        if st == sched.depth - 1:                                        # alpha head branches off the trunk output
+            d_out = d_out + torch.mm(d_sigma.to(bf), Wa.t().to(bf))
+        act = acts[st][:, :n_out]
+        dY = torch.where(act > 0, d_out, torch.zeros_like(d_out)) if s["relu"] else d_out
+        dYb = dY
+        W, gW, gb = wview(s["layer"])
+        gb.copy_(dY.sum(0, dtype=torch.float32))
+        r0 = s["main_row0"]
+        if st > 0:                                                       # main operand = previous step's stored output
+            x = acts[st - 1]
+            gW[r0:r0 + 256].copy_(torch.mm(x.t(), dYb, out_dtype=torch.float32))
+        if s["enc_data"]:                                                # encoded inputs (pos at trunk0 / skip, dir at colour)
+            e = enc_pos if s["phase"] == 0 else enc_dir
+            cols, rows = sched.enc_maps[s["phase"]]
+            gE = torch.mm(e.t(), dYb, out_dtype=torch.float32)           # [96, n_out] in kernel column order
+            gW[rows] = gE[cols]
+        if st > 0:
+            d_out = torch.mm(dY, W[r0:r0 + 256].t().to(bf))              # dgrad into the previous step's output
+    return grad
+
+
+class NetworkPass(torch.autograd.Function):
+    """(master, inputs...) -> (color_map, alpha_map, weights) for one network over one ray chunk."""
+
+    @staticmethod
+    def forward(ctx, master, model, rays_o, rays_d, rays_d_n, z, parameters, cone_scale, blur_idx, noise, map_exr,
+                composite_bkgd, bkgd_color):
+        R, S = z.shape
+        npar = parameters.shape[1] if parameters is not None else 0
+        blur = blur_idx is not None
+        rgbs, saved = mlp_forward_train(model, n_rows=R * S, rays_o=rays_o, rays_d=rays_d, z=z, dir=rays_d_n,
+                                        params=parameters if npar > 0 else None, rows_per_group=S,
+                                        row_scale=z if blur else None,
+                                        group_scale=cone_scale.reshape(-1).contiguous() if blur else None,
+                                        blur_idx=blur_idx)
+        rgbs = rgbs.view(R, S, 4)
+        cmap, amap, w, _ = ops.composite_forward(rgbs, z, rays_d, noise=noise, map_exr=map_exr,
+                                                 composite_bkgd=composite_bkgd, bkgd_color=bkgd_color)
+        ctx.model, ctx.saved = model, saved
+        ctx.misc = (rgbs, z, rays_d, noise, map_exr, composite_bkgd, bkgd_color)
+        ctx.mark_non_differentiable(w)
+        return cmap, amap, w
+
+    @staticmethod
+    def backward(ctx, d_cmap, d_amap, d_w):
+        rgbs, z, rays_d, noise, map_exr, composite_bkgd, bkgd_color = ctx.misc
+        d_rgbs = ops.composite_backward(rgbs, z, rays_d, d_cmap.contiguous(), d_amap.contiguous(), noise=noise,
+                                        map_exr=map_exr, composite_bkgd=composite_bkgd, bkgd_color=bkgd_color)
+        grad = mlp_backward(ctx.model, ctx.saved, d_rgbs.view(-1, 4))
+        ctx.saved = None
+        return (grad,) + (None,) * 12

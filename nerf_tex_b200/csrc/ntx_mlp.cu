@@ -56,7 +56,17 @@ struct KernelArgs {
     ntx_mlp_inputs in;
     const uint8_t* packed;
     float* rgbs;
+    // training only: bf16 copies of every tensor-core operand the backward needs
+    uint4* dump_enc_pos;   // [N, 96] encoded pos-phase inputs (kernel column order, constant-1 column included)
+    uint4* dump_enc_dir;   // [N, 96]
+    uint4* dump_acts;      // [n_steps][N, 256] stored outputs of every step (the 128-wide last step uses cols 0..127)
 };
+
+constexpr int kEncCols = kEncBlocks * 32;   // 96
+
+__device__ __forceinline__ void st_global_v4(uint4* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+    asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
 
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -97,8 +107,8 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 }
 
 // 32 fp32 accumulator columns (chunk j of this thread's row) -> bf16 -> next layer's A operand
-template <bool RELU>
-__device__ __forceinline__ void store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32]) {
+template <bool RELU, bool DUMP>
+__device__ __forceinline__ void store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32], uint4* grow_ptr) {
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         uint32_t w[4];
@@ -108,25 +118,28 @@ __device__ __forceinline__ void store_chunk32(uint32_t main_base, int j, int row
             w[e] = RELU ? pack_bf16_relu(lo, hi) : pack_bf16(lo, hi);
         }
         st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
+        if (DUMP && grow_ptr) st_global_v4(grow_ptr + j * 4 + c, w[0], w[1], w[2], w[3]);
     }
 }
 
 // plain hidden layer epilogue: TMEM loads software-pipelined against the convert + store
-template <bool RELU>
-__device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t main_base, int row, int n_chunks) {
+template <bool RELU, bool DUMP>
+__device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t main_base, int row, int n_chunks,
+                                                     uint4* grow_ptr) {
     uint32_t va[32], vb[32];
     tmem_ld_32x32b_x32(tmem_row, va);
     tmem_ld_wait();
     for (int j = 0; j < n_chunks; j += 2) {
         tmem_ld_32x32b_x32(tmem_row + (j + 1) * 32, vb);
-        store_chunk32<RELU>(main_base, j, row, va);
+        store_chunk32<RELU, DUMP>(main_base, j, row, va, grow_ptr);
         tmem_ld_wait();
         if (j + 2 < n_chunks) tmem_ld_32x32b_x32(tmem_row + (j + 2) * 32, va);
-        store_chunk32<RELU>(main_base, j + 1, row, vb);
+        store_chunk32<RELU, DUMP>(main_base, j + 1, row, vb, grow_ptr);
         tmem_ld_wait();
     }
 }
 
+template <bool DUMP>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__ KernelArgs args) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -313,21 +326,27 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 }
                 w[30] = pack_bf16(1.0f, x[0]);
                 w[31] = pack_bf16(x[1], x[2]);
+                uint4* dp = (DUMP && valid) ? args.dump_enc_pos + grow * (kEncCols / 8) : nullptr;
+                auto put = [&](int q, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+                    st_shared_v4(chunk_addr(enc_base, q, row), w0, w1, w2, w3);
+                    if (DUMP && dp) st_global_v4(dp + q, w0, w1, w2, w3);
+                };
 #pragma unroll
-                for (int q = 0; q < 8; ++q)
-                    st_shared_v4(chunk_addr(enc_base, q, row), w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+                for (int q = 0; q < 8; ++q) put(q, w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
                 if (g > 0) {
 #pragma unroll
                     for (int j = 0; j < 3; ++j) {
                         if (j < g) {
                             uint32_t p4[4];
                             sincos4(pg[j], p4);
-                            st_shared_v4(chunk_addr(enc_base, 8 + j, row), p4[0], p4[1], p4[2], p4[3]);
+                            put(8 + j, p4[0], p4[1], p4[2], p4[3]);
                         }
                     }
-                    st_shared_v4(chunk_addr(enc_base, 8 + g, row), pack_bf16(pg[0], pg[1]), pack_bf16(pg[2], 0.f), 0u, 0u);
-                    if ((g & 1) == 0) st_shared_v4(chunk_addr(enc_base, 9 + g, row), 0u, 0u, 0u, 0u);
+                    put(8 + g, pack_bf16(pg[0], pg[1]), pack_bf16(pg[2], 0.f), 0u, 0u);
+                    if ((g & 1) == 0) put(9 + g, 0u, 0u, 0u, 0u);
                 }
+                if (DUMP && dp)
+                    for (int q = pos_chunks(g) + (pos_chunks(g) & 1); q < kEncCols / 8; ++q) st_global_v4(dp + q, 0u, 0u, 0u, 0u);
             }
             fence_proxy_async_smem();
             __syncwarp();
@@ -343,10 +362,11 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 acc_phase ^= 1;
                 tc_fence_after();
                 float o0 = 0.f, o1 = 0.f, o2 = 0.f;
+                uint4* gp = (DUMP && valid) ? args.dump_acts + ((int64_t)st * n_rows + grow) * (kWidth / 8) : nullptr;
                 if ((epi & (EPI_ALPHA | EPI_FINAL)) == 0) {
                     // hidden layer: (ReLU) -> bf16 -> A operand of the next layer
-                    if (epi & EPI_RELU) epilogue_store_layer<true>(tmem_row, main_base, row, n_chunks);
-                    else epilogue_store_layer<false>(tmem_row, main_base, row, n_chunks);
+                    if (epi & EPI_RELU) epilogue_store_layer<true, DUMP>(tmem_row, main_base, row, n_chunks, gp);
+                    else epilogue_store_layer<false, DUMP>(tmem_row, main_base, row, n_chunks, gp);
                 } else {
                     // layers that also feed an fp32 head (density after the trunk, colour at the end)
                     for (int j = 0; j < n_chunks; ++j) {
@@ -375,37 +395,45 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                                 o1 += f[4 * c] * a1.x + f[4 * c + 1] * a1.y + f[4 * c + 2] * a1.z + f[4 * c + 3] * a1.w;
                                 o2 += f[4 * c] * a2.x + f[4 * c + 1] * a2.y + f[4 * c + 2] * a2.z + f[4 * c + 3] * a2.w;
                             }
-                        } else {
+                        }
+                        if (!(epi & EPI_FINAL) || DUMP) {
 #pragma unroll
-                            for (int c = 0; c < 4; ++c)
-                                st_shared_v4(chunk_addr(main_base, j * 4 + c, row),
-                                             pack_bf16(f[8 * c], f[8 * c + 1]), pack_bf16(f[8 * c + 2], f[8 * c + 3]),
-                                             pack_bf16(f[8 * c + 4], f[8 * c + 5]), pack_bf16(f[8 * c + 6], f[8 * c + 7]));
+                            for (int c = 0; c < 4; ++c) {
+                                const uint32_t w0 = pack_bf16(f[8 * c], f[8 * c + 1]), w1 = pack_bf16(f[8 * c + 2], f[8 * c + 3]),
+                                               w2 = pack_bf16(f[8 * c + 4], f[8 * c + 5]), w3 = pack_bf16(f[8 * c + 6], f[8 * c + 7]);
+                                if (!(epi & EPI_FINAL)) st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w0, w1, w2, w3);
+                                if (DUMP && gp) st_global_v4(gp + j * 4 + c, w0, w1, w2, w3);
+                            }
                         }
                     }
                     if (epi & EPI_ALPHA) alpha_raw += w_alpha[256];
                 }
                 if (epi & EPI_SWITCH) {
                     // ----------------------------------------------------- dir-phase encoding
+                    uint4* dp = (DUMP && valid) ? args.dump_enc_dir + grow * (kEncCols / 8) : nullptr;
+                    auto put = [&](int q, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
+                        st_shared_v4(chunk_addr(enc_base, q, row), w0, w1, w2, w3);
+                        if (DUMP && dp) st_global_v4(dp + q, w0, w1, w2, w3);
+                    };
 #pragma unroll
                     for (int i = 0; i < 3; ++i) {
                         uint32_t p4[4];
                         sincos4(d[i], p4);
-                        st_shared_v4(chunk_addr(enc_base, i, row), p4[0], p4[1], p4[2], p4[3]);
+                        put(i, p4[0], p4[1], p4[2], p4[3]);
                     }
 #pragma unroll
                     for (int j = 0; j < 7; ++j) {
                         if (j < a) {
                             uint32_t p4[4];
                             sincos4(pa[j], p4);
-                            st_shared_v4(chunk_addr(enc_base, 3 + j, row), p4[0], p4[1], p4[2], p4[3]);
+                            put(3 + j, p4[0], p4[1], p4[2], p4[3]);
                         }
                     }
-                    st_shared_v4(chunk_addr(enc_base, 3 + a, row), pack_bf16(1.0f, d[0]), pack_bf16(d[1], d[2]),
-                                 pack_bf16(pa[0], pa[1]), pack_bf16(pa[2], pa[3]));
-                    if (a > 4)
-                        st_shared_v4(chunk_addr(enc_base, 4 + a, row), pack_bf16(pa[4], pa[5]), pack_bf16(pa[6], 0.f), 0u, 0u);
-                    if (dir_chunks(a) & 1) st_shared_v4(chunk_addr(enc_base, dir_chunks(a), row), 0u, 0u, 0u, 0u);
+                    put(3 + a, pack_bf16(1.0f, d[0]), pack_bf16(d[1], d[2]), pack_bf16(pa[0], pa[1]), pack_bf16(pa[2], pa[3]));
+                    if (a > 4) put(4 + a, pack_bf16(pa[4], pa[5]), pack_bf16(pa[6], 0.f), 0u, 0u);
+                    if (dir_chunks(a) & 1) put(dir_chunks(a), 0u, 0u, 0u, 0u);
+                    if (DUMP && dp)
+                        for (int q = dir_chunks(a) + (dir_chunks(a) & 1); q < kEncCols / 8; ++q) st_global_v4(dp + q, 0u, 0u, 0u, 0u);
                 }
                 if (epi & EPI_FINAL) {
                     if (valid) {
@@ -562,10 +590,10 @@ NTX_API int ntx_mlp_create(const ntx_mlp_config* cfg, ntx_mlp_t** out) {
                       "width=256 (got %d,%d,%d,%d,%d)", c.n_pos, c.pos_freqs, c.dir_freqs, c.param_freqs, c.width);
         return NTX_E_UNSUPPORTED;
     }
-    if (!(c.n_geo >= 0 && c.n_geo <= 3 && c.n_app >= 0 && c.n_app <= 7 && c.depth >= 1 && c.depth <= 16 &&
+    if (!(c.n_geo >= 0 && c.n_geo <= 3 && c.n_app >= 0 && c.n_app <= 7 && c.depth >= 1 && c.depth <= 12 &&
           c.color_depth >= 0 && c.color_depth <= 2 && ((c.skip_mask >> (c.depth - 1)) == 0))) {
         ntx_set_error("mlp_create: unsupported n_parameters=[%d,%d] depth=%d color_depth=%d skip_mask=0x%x "
-                      "(need n_geo<=3, n_app<=7, depth<=16, color_depth<=2, no skip on the last trunk layer)",
+                      "(need n_geo<=3, n_app<=7, depth<=12, color_depth<=2, no skip on the last trunk layer)",
                       c.n_geo, c.n_app, c.depth, c.color_depth, c.skip_mask);
         return NTX_E_UNSUPPORTED;
     }
@@ -610,8 +638,8 @@ NTX_API int ntx_mlp_pack_weights(const ntx_mlp_t* mlp, const float* master, void
     return NTX_OK;
 }
 
-NTX_API int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
-                            void* stream) {
+static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
+                          void* enc_pos, void* enc_dir, void* acts, bool dump, void* stream) {
     NTX_REQUIRE(mlp && packed && in, "mlp_forward: null pointer");
     NTX_REQUIRE(in->n_rows >= 0, "mlp_forward: negative row count");
     if (in->n_rows == 0) return NTX_OK;
@@ -622,20 +650,64 @@ NTX_API int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_
     NTX_REQUIRE(np == 0 || in->params, "mlp_forward: the model takes %d parameters but params is NULL", np);
     NTX_REQUIRE(in->blur_idx < np, "mlp_forward: blur_idx %d out of range", in->blur_idx);
     NTX_REQUIRE((((uintptr_t)packed | (uintptr_t)rgbs) & 15) == 0, "mlp_forward: packed / rgbs must be 16-byte aligned");
-    static bool attr_set[64] = {};
+    if (dump) {
+        NTX_REQUIRE(enc_pos && enc_dir && acts, "mlp_forward_train: null save buffer");
+        NTX_REQUIRE((((uintptr_t)enc_pos | (uintptr_t)enc_dir | (uintptr_t)acts) & 15) == 0,
+                    "mlp_forward_train: save buffers must be 16-byte aligned");
+    }
+    static bool attr_set[64][2] = {};
     int dev = 0;
     NTX_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev]) {
-        NTX_CUDA(cudaFuncSetAttribute(mlp_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-        attr_set[dev] = true;
+    if (dev < 64 && !attr_set[dev][dump]) {
+        if (dump)
+            NTX_CUDA(cudaFuncSetAttribute(mlp_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+        else
+            NTX_CUDA(cudaFuncSetAttribute(mlp_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+        attr_set[dev][dump] = true;
     }
     KernelArgs ka;
     ka.in = *in;
     ka.packed = (const uint8_t*)packed;
     ka.rgbs = rgbs;
+    ka.dump_enc_pos = (uint4*)enc_pos;
+    ka.dump_enc_dir = (uint4*)enc_dir;
+    ka.dump_acts = (uint4*)acts;
     const int64_t n_batches = (in->n_rows + kRowsPerCta - 1) / kRowsPerCta;
     const int grid = (int)(n_batches < ntx_sm_count() ? n_batches : ntx_sm_count());
-    mlp_forward_kernel<<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(mlp->prog, ka);
+    if (dump) mlp_forward_kernel<true><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(mlp->prog, ka);
+    else mlp_forward_kernel<false><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(mlp->prog, ka);
     NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
+                            void* stream) {
+    return launch_forward(mlp, packed, in, rgbs, nullptr, nullptr, nullptr, false, stream);
+}
+
+NTX_API int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
+                                  void* enc_pos, void* enc_dir, void* acts, void* stream) {
+    return launch_forward(mlp, packed, in, rgbs, enc_pos, enc_dir, acts, true, stream);
+}
+
+NTX_API int ntx_mlp_num_steps(const ntx_mlp_t* mlp) { return mlp ? mlp->prog.n_steps : -1; }
+
+NTX_API int ntx_mlp_step_info(const ntx_mlp_t* mlp, int st, int32_t* layer, int32_t* n_out, int32_t* main_row0,
+                              int32_t* enc_data, int32_t* phase, int32_t* relu) {
+    NTX_REQUIRE(mlp && st >= 0 && st < mlp->prog.n_steps, "mlp_step_info: bad step %d", st);
+    const Step& s = mlp->prog.steps[st];
+    if (layer) *layer = s.layer;
+    if (n_out) *n_out = s.n_out;
+    if (main_row0) *main_row0 = s.main_row0;
+    if (enc_data) *enc_data = s.enc_data;
+    if (phase) *phase = s.phase;
+    if (relu) *relu = (s.epi & EPI_RELU) ? 1 : 0;
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_enc_columns(const ntx_mlp_t* mlp, int phase, int32_t* ref_index) {
+    NTX_REQUIRE(mlp && ref_index && (phase == 0 || phase == 1), "mlp_enc_columns: bad argument");
+    for (int c = 0; c < kEncCols; ++c)
+        ref_index[c] = phase == 0 ? pos_col_to_ref(c, mlp->prog.n_geo) : dir_col_to_ref(c, mlp->prog.n_app);
     return NTX_OK;
 }

@@ -92,13 +92,25 @@ class FusedNerfTexMLP:
             out.append(self.master[bo:bo + fo])
         return out
 
+    def schedule(self):
+        """Host mirror of the kernel's layer schedule (used by the backward pass)."""
+        if getattr(self, "_schedule", None) is None:
+            from .autograd import MlpSchedule
+            self._schedule = MlpSchedule(self)
+        return self._schedule
+
+    def requires_grad_(self, flag: bool = True):
+        """Make the flat master buffer a trainable leaf (its .grad is filled by loss.backward())."""
+        self.master.requires_grad_(flag)
+        return self
+
     def mark_dirty(self) -> None:
         """Call after changing ``master`` in place (optimizer step, checkpoint load)."""
         self._packed_version = -1
 
     def ensure_packed(self) -> torch.Tensor:
         if self._packed_version != self.master._version:
-            check(_lib.load().ntx_mlp_pack_weights(self._h, ptr(self.master), ptr(self.packed), stream_ptr()))
+            check(_lib.load().ntx_mlp_pack_weights(self._h, ptr(self.master.detach()), ptr(self.packed), stream_ptr()))
             self._packed_version = self.master._version
         return self.packed
 

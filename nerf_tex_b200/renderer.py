@@ -142,6 +142,13 @@ class Renderer:
         R, S = z.shape
         if self.raw_noise_std > 0 and noise is None:                             # :190-192
             noise = self._rand((R, S), z.device, normal=True) * self.raw_noise_std
+        if torch.is_grad_enabled() and model.master.requires_grad:
+            # training: same kernels, plus saved operands and a backward (train.py:62-66 tape)
+            from .autograd import NetworkPass
+            cmap, amap, w = NetworkPass.apply(model.master, model, rays_o, rays_d, rays_d_n.contiguous(), z, parameters,
+                                              cone_scale, self.blur_idx, noise, self.map_exr, composite_bkgd,
+                                              tuple(float(c) for c in bkgd_color))
+            return cmap, amap, w, None
         rgbs = self.evaluate_model_packed(rays_o, rays_d, rays_d_n, parameters, cone_scale, z, model)
         cmap, amap, w, _ = ops.composite_forward(rgbs, z, rays_d, noise=noise, map_exr=self.map_exr,
                                                  composite_bkgd=composite_bkgd, bkgd_color=bkgd_color,

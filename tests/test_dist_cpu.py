@@ -1,0 +1,62 @@
+"""Host-side multi-process logic on CPU (gloo, world_size 2): gradient all-reduce averaging and
+ray sharding.  The kernels are not involved; this covers the N > 1 plumbing of train.py."""
+
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+class _FakeModel:
+    def __init__(self, n, rank):
+        self.master = torch.zeros(n, requires_grad=True)
+        self.master.grad = torch.full((n,), float(rank + 1))
+
+
+def _worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from nerf_tex_b200.train import Trainer, shard_rays
+    tr = Trainer.__new__(Trainer)
+    tr.models, tr.pg = {"model": _FakeModel(1000, rank), "model_fine": _FakeModel(10, rank)}, None
+    tr.allreduce_gradients()
+    g = tr.models["model"].master.grad
+    sl = shard_rays(640000, rank, world, block=16)
+    q.put((rank, float(g[0]), float(g[-1]), sl.start, sl.stop))
+    dist.destroy_process_group()
+
+
+def test_allreduce_mean_and_ray_shards_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert all(abs(r[1] - 1.5) < 1e-6 and abs(r[2] - 1.5) < 1e-6 for r in res)      # mean of 1 and 2
+    assert res[0][3] == 0 and res[0][4] == res[1][3] and res[1][4] == 640000          # shards tile the frame
+
+
+def test_shard_rays_covers_everything():
+    from nerf_tex_b200.train import shard_rays
+    for n, w in [(640000, 8), (4096, 3), (10, 4), (1, 8)]:
+        covered = []
+        for r in range(w):
+            s = shard_rays(n, r, w, block=16)
+            covered += list(range(s.start, s.stop))
+        assert covered == list(range(n))
