@@ -179,6 +179,42 @@ int ntx_mlp_step_info(const ntx_mlp_t* mlp, int step, int32_t* layer, int32_t* n
 int ntx_mlp_enc_columns(const ntx_mlp_t* mlp, int phase, int32_t* ref_index);
 
 /* ------------------------------------------------------------------------------------------
+ * Whole ray chunk: K3 -> K1 -> K2 [-> K3 -> K1 -> K2]
+ * ---------------------------------------------------------------------------------------- */
+
+/* View directions fed to the network: out[R,3] = rays_d / |rays_d| (network/renderer.py:98). */
+int ntx_normalize_dirs(const float* rays_d, int R, float* out, void* stream);
+
+/* Options of network/renderer.py:34-45 that shape one chunk. */
+typedef struct ntx_render_config {
+    int32_t n_samples;       /* S */
+    int32_t n_importance;    /* N (0: single pass) */
+    int32_t perturb;         /* stratified jitter; also sample_pdf's det flag (renderer.py:128) */
+    int32_t map_exr;
+    int32_t composite_bkgd;
+    int32_t blur_idx;        /* -1: none */
+    float bkgd_color[3];
+} ntx_render_config;
+
+/* Device scratch (bytes) ntx_render_rays needs for R rays: view dirs, depths, raw network outputs
+ * and weights of the coarse pass, merged depths and raw outputs of the fine pass. */
+int64_t ntx_render_rays_workspace_bytes(int R, int n_samples, int n_importance);
+
+/* Replaces Renderer.render_rays (network/renderer.py:92-143) for one chunk of R rays that all hit
+ * the proxy.  rays_o, rays_d[R,3]; t[R,2]; parameters[R,p] or NULL; cone_scale[R] (used iff
+ * blur_idx >= 0); z_rand[R,S] iff perturb; u[R,N] iff n_importance > 0 and !perturb; noise[R,S],
+ * noise_fine[R,S+N] (already scaled by raw_noise_std) or NULL.  mlp_fine / packed_fine may be NULL
+ * (the coarse model is reused, :134).  Outputs: color_pred[R,3], alpha_pred[R]; with
+ * n_importance > 0 also color_pred_coarse[R,3], alpha_pred_coarse[R] (:138).
+ * workspace: 256-byte aligned device scratch of at least ntx_render_rays_workspace_bytes(). */
+int ntx_render_rays(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_t* mlp_fine, const void* packed_fine,
+                    const ntx_render_config* cfg, const float* rays_o, const float* rays_d, const float* t,
+                    const float* parameters, const float* cone_scale, const float* z_rand, const float* u,
+                    const float* noise, const float* noise_fine, int R, float* color_pred, float* alpha_pred,
+                    float* color_pred_coarse, float* alpha_pred_coarse, void* workspace, int64_t workspace_bytes,
+                    void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * tcgen05 self-test (used by tests/ to validate the UMMA shared-memory descriptors on a GPU)
  * ---------------------------------------------------------------------------------------- */
 /* D[128,N] = A[128,K] * B[N,K]^T with bf16 inputs (given as fp32, rounded to bf16 on device),

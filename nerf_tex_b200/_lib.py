@@ -30,6 +30,11 @@ class MlpConfig(C.Structure):
                                           "width", "skip_mask", "color_depth")]
 
 
+class RenderConfig(C.Structure):
+    _fields_ = [("n_samples", C.c_int32), ("n_importance", C.c_int32), ("perturb", C.c_int32), ("map_exr", C.c_int32),
+                ("composite_bkgd", C.c_int32), ("blur_idx", C.c_int32), ("bkgd_color", C.c_float * 3)]
+
+
 class MlpInputs(C.Structure):
     _fields_ = [("pos", C.c_void_p), ("rays_o", C.c_void_p), ("rays_d", C.c_void_p), ("z", C.c_void_p),
                 ("dir", C.c_void_p), ("params", C.c_void_p), ("row_scale", C.c_void_p), ("group_scale", C.c_void_p),
@@ -59,6 +64,9 @@ SIGNATURES = {
     "ntx_mlp_num_steps": (_I, [_P]),
     "ntx_mlp_step_info": (_I, [_P, _I] + [C.POINTER(C.c_int32)] * 6),
     "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),
+    "ntx_normalize_dirs": (_I, [_P, _I, _P, _P]),
+    "ntx_render_rays_workspace_bytes": (_I64, [_I, _I, _I]),
+    "ntx_render_rays": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P, _I64, _P]),
     "ntx_selftest_umma": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ntx_selftest_bulk_copy": (_I, [_P, _P, _I, _P]),
 }

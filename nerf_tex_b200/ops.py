@@ -142,6 +142,57 @@ def composite_instanced_forward(rgbs, dists, alpha_weight, ray_ptr, color_last, 
     return cmap, amap
 
 
+# ------------------------------------------------------------------------------------------ whole chunk
+
+def render_config(n_samples, n_importance, perturb, map_exr, composite_bkgd, blur_idx, bkgd_color) -> "_lib.RenderConfig":
+    vals = [float(v) for v in (bkgd_color.tolist() if hasattr(bkgd_color, "tolist") else bkgd_color)]
+    return _lib.RenderConfig(int(n_samples), int(n_importance), int(bool(perturb)), int(bool(map_exr)),
+                             int(bool(composite_bkgd)), -1 if blur_idx is None else int(blur_idx), (C.c_float * 3)(*vals))
+
+
+def normalize_dirs(rays_d: torch.Tensor) -> torch.Tensor:
+    """network/renderer.py:98."""
+    rays_d = as_cuda(rays_d)
+    out = torch.empty_like(rays_d)
+    check(_lib.load().ntx_normalize_dirs(ptr(rays_d), rays_d.shape[0], ptr(out), stream_ptr()))
+    return out
+
+
+def render_rays_workspace_bytes(R: int, n_samples: int, n_importance: int) -> int:
+    return int(_lib.load().ntx_render_rays_workspace_bytes(int(R), int(n_samples), int(n_importance)))
+
+
+def render_rays(model, model_fine, cfg, rays_o, rays_d, t, parameters, cone_scale, z_rand=None, u=None, noise=None,
+                noise_fine=None, workspace: Optional[torch.Tensor] = None, entry: str = "ntx_render_rays"):
+    """One chunk of Renderer.render_rays (network/renderer.py:92-143) in a single C call."""
+    lib = _lib.load()
+    R = rays_o.shape[0]
+    dev = rays_o.device
+    fine = cfg.n_importance > 0
+    color = torch.empty((R, 3), dtype=torch.float32, device=dev)
+    alpha = torch.empty((R,), dtype=torch.float32, device=dev)
+    color_c = torch.empty((R, 3), dtype=torch.float32, device=dev) if fine else None
+    alpha_c = torch.empty((R,), dtype=torch.float32, device=dev) if fine else None
+    npar = parameters.shape[1] if parameters is not None else 0
+    packed = model.ensure_packed()
+    packed_f = model_fine.ensure_packed() if model_fine is not None else None
+    args = [model._h, ptr(packed), model_fine._h if model_fine is not None else None, ptr(packed_f), C.byref(cfg),
+            ptr(rays_o), ptr(rays_d), ptr(t), ptr(parameters) if npar > 0 else None,
+            ptr(cone_scale.reshape(-1).contiguous()) if cone_scale is not None else None, ptr(z_rand), ptr(u), ptr(noise),
+            ptr(noise_fine), R, ptr(color), ptr(alpha), ptr(color_c), ptr(alpha_c)]
+    if entry == "ntx_render_rays":
+        need = lib.ntx_render_rays_workspace_bytes(R, cfg.n_samples, cfg.n_importance)
+        if workspace is None:
+            workspace = torch.empty(max(need, 256), dtype=torch.uint8, device=dev)
+        check(lib.ntx_render_rays(*args, ptr(workspace), workspace.numel(), stream_ptr()))
+    else:
+        check(getattr(lib, entry)(*args, stream_ptr()))
+    out = {"color_pred": color, "alpha_pred": alpha}
+    if fine:
+        out.update({"color_pred_coarse": color_c, "alpha_pred_coarse": alpha_c})
+    return out, workspace
+
+
 # ------------------------------------------------------------------------------------------ self-tests
 
 def selftest_umma(A: torch.Tensor, B: torch.Tensor, layout: int) -> torch.Tensor:

@@ -114,9 +114,29 @@ class Renderer:
         R = rays_o.shape[0]
         dev = rays_o.device
         S = self.n_samples
-        rays_d_n = rays_d / torch.linalg.norm(rays_d, dim=-1, keepdim=True)     # :98
         if self.perturb and z_rand is None:
             z_rand = self._rand((R, S), dev)                                     # :110
+        grad = torch.is_grad_enabled() and (self.model.master.requires_grad or
+                                            (self.model_fine is not None and self.model_fine.master.requires_grad))
+        if not return_aux and not grad and S >= 3:
+            # inference: the whole chunk is one C call (ntx_render_rays)
+            if self.n_importance > 0 and not self.perturb and u is None:
+                u = self._rand((R, self.n_importance), dev)
+            if self.raw_noise_std > 0:
+                if noise is None:
+                    noise = self._rand((R, S), dev, normal=True) * self.raw_noise_std
+                if self.n_importance > 0 and noise_fine is None:
+                    noise_fine = self._rand((R, S + self.n_importance), dev, normal=True) * self.raw_noise_std
+            cfg = ops.render_config(S, self.n_importance, self.perturb, self.map_exr, composite_bkgd, self.blur_idx,
+                                    bkgd_color)
+            need = ops.render_rays_workspace_bytes(R, S, self.n_importance)
+            ws = getattr(self, "_workspace", None)
+            if ws is None or ws.numel() < need or ws.device != dev:
+                ws = None                      # (re)allocated by ops.render_rays and kept for the next chunk
+            out, self._workspace = ops.render_rays(self.model, self.model_fine, cfg, rays_o, rays_d, t, parameters,
+                                                   cone_scale, z_rand, u, noise, noise_fine, ws)
+            return out
+        rays_d_n = ops.normalize_dirs(rays_d)                                    # :98
         z = ops.stratified_z(t, S, bool(self.perturb), z_rand)                   # :101-111
         color_map, alpha_map, weights, rgbs = self._eval_and_composite(
             self.model, rays_o, rays_d, rays_d_n, z, parameters, cone_scale, composite_bkgd, bkgd_color, noise,
