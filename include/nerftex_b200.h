@@ -214,6 +214,38 @@ int ntx_render_rays(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_t* m
                     float* color_pred_coarse, float* alpha_pred_coarse, void* workspace, int64_t workspace_bytes,
                     void* stream);
 
+/* Allocation-free twin of ntx_render_rays.  (No counterpart in the reference: it exists for the
+ * way this library gets embedded, not for anything the reference computes.)
+ *
+ * Who needs it: a host that cannot hand the library a device workspace.  The typical case is this
+ * library loaded into the reference's own TensorFlow process — TF's allocator claims almost all
+ * GPU memory at start-up, so a cudaMalloc made on the side fails, and TF's tensors cannot be sized
+ * from C.  The same holds for a render loop that may not tolerate the device-wide stall an
+ * allocation causes, and for plug-in hosts that forbid allocation after initialisation.
+ *
+ * How: the scratch is a fixed array of NTX_STATIC_SCRATCH_BYTES inside the library's device image
+ * (every GPU that loads the library holds those bytes until the process exits).  This call never
+ * allocates or frees device memory and calls no routine that does.  Inputs and outputs are still
+ * the caller's buffers, exactly as for ntx_render_rays (same arguments minus the workspace).
+ *
+ * Limits and rules:
+ *   - a chunk whose ntx_render_rays_workspace_bytes() exceeds NTX_STATIC_SCRATCH_BYTES is refused
+ *     with NTX_E_INVALID and a message naming both sizes (4096 rays of 64 + 128 samples fit);
+ *     split the chunk, or use ntx_render_rays;
+ *   - the first call on each device looks up the array's device address (with that device
+ *     current).  Make that first call during set-up, before any stream capture begins;
+ *   - all calls share the one array and it keeps whatever the last call wrote.  Nothing in it
+ *     needs clearing — each call overwrites every region before reading it — but two calls that
+ *     can overlap on the GPU (different streams, or host threads on the same device) race on
+ *     it: keep calls to this entry on one stream, or order them yourself. */
+#define NTX_STATIC_SCRATCH_BYTES (24u << 20)
+int ntx_render_rays_static(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_t* mlp_fine,
+                           const void* packed_fine, const ntx_render_config* cfg, const float* rays_o,
+                           const float* rays_d, const float* t, const float* parameters, const float* cone_scale,
+                           const float* z_rand, const float* u, const float* noise, const float* noise_fine, int R,
+                           float* color_pred, float* alpha_pred, float* color_pred_coarse, float* alpha_pred_coarse,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * tcgen05 self-test (used by tests/ to validate the UMMA shared-memory descriptors on a GPU)
  * ---------------------------------------------------------------------------------------- */

@@ -67,6 +67,7 @@ SIGNATURES = {
     "ntx_normalize_dirs": (_I, [_P, _I, _P, _P]),
     "ntx_render_rays_workspace_bytes": (_I64, [_I, _I, _I]),
     "ntx_render_rays": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P, _I64, _P]),
+    "ntx_render_rays_static": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P]),
     "ntx_selftest_umma": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ntx_selftest_bulk_copy": (_I, [_P, _P, _I, _P]),
 }

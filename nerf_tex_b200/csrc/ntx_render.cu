@@ -2,7 +2,14 @@
 // normalise view directions -> stratified depths (K3) -> fused MLP (K1) -> compositing (K2)
 // [-> hierarchical resampling (K3) -> fine MLP (K1) -> compositing (K2)].
 // Intermediates (depths, raw network outputs, weights) live in a caller-provided scratch buffer.
+#include <mutex>
+
 #include "ntx_common.cuh"
+
+// Scratch of ntx_render_rays_static: lives in the library image, so every GPU that loads the
+// library carries NTX_STATIC_SCRATCH_BYTES of it until the process exits.  In host code this name
+// is only a handle for cudaGetSymbolAddress — never a pointer a kernel may be given.
+static __device__ __align__(256) unsigned char g_render_scratch[NTX_STATIC_SCRATCH_BYTES];
 
 namespace {
 
@@ -136,4 +143,48 @@ NTX_API int ntx_render_rays(const ntx_mlp_t* mlp, const void* packed, const ntx_
     return ntx_render_rays_impl(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, parameters, cone_scale,
                                 z_rand, u, noise, noise_fine, R, color_pred, alpha_pred, color_pred_coarse,
                                 alpha_pred_coarse, (uint8_t*)workspace, stream);
+}
+
+// Device address of g_render_scratch on the current device, looked up once per device.
+static int static_scratch_address(uint8_t** out) {
+    static std::mutex mu;
+    static uint8_t* per_device[64] = {};
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    NTX_REQUIRE(dev >= 0 && dev < 64, "render_rays_static: device ordinal %d not supported", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    if (!per_device[dev]) {
+        void* p = nullptr;
+        NTX_CUDA(cudaGetSymbolAddress(&p, g_render_scratch));
+        NTX_REQUIRE(p != nullptr, "render_rays_static: the scratch symbol has no address on device %d", dev);
+        per_device[dev] = (uint8_t*)p;
+    }
+    *out = per_device[dev];
+    return NTX_OK;
+}
+
+// ntx_render_rays for hosts that must not (or cannot) allocate device memory; see nerftex_b200.h.
+NTX_API int ntx_render_rays_static(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_t* mlp_fine,
+                                   const void* packed_fine, const ntx_render_config* cfg, const float* rays_o,
+                                   const float* rays_d, const float* t, const float* parameters,
+                                   const float* cone_scale, const float* z_rand, const float* u, const float* noise,
+                                   const float* noise_fine, int R, float* color_pred, float* alpha_pred,
+                                   float* color_pred_coarse, float* alpha_pred_coarse, void* stream) {
+    int rc = ntx_render_rays_check(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, z_rand, u, R, color_pred,
+                                   alpha_pred, color_pred_coarse, alpha_pred_coarse);
+    if (rc || R == 0) return rc;
+    const int64_t need = ntx_render_rays_workspace_bytes(R, cfg->n_samples, cfg->n_importance);
+    NTX_REQUIRE(need <= (int64_t)NTX_STATIC_SCRATCH_BYTES,
+                "render_rays_static: %d rays x (%d + %d) samples need %lld B of scratch but the built-in buffer holds "
+                "%lld B; split the chunk or use ntx_render_rays with your own workspace",
+                R, cfg->n_samples, cfg->n_importance, (long long)need, (long long)NTX_STATIC_SCRATCH_BYTES);
+    uint8_t* ws = nullptr;
+    rc = static_scratch_address(&ws);
+    if (rc) return rc;
+    // Nothing in the scratch has to start at zero: every region (view dirs, depths, raw outputs,
+    // weights, merged depths) is written in full by an earlier kernel of this call before a later
+    // one reads it, so whatever the previous call left behind is never observed.
+    return ntx_render_rays_impl(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, parameters, cone_scale,
+                                z_rand, u, noise, noise_fine, R, color_pred, alpha_pred, color_pred_coarse,
+                                alpha_pred_coarse, ws, stream);
 }
