@@ -13,8 +13,9 @@ namespace {
 
 __device__ __forceinline__ float color_act(float c, int map_exr) {
     // renderer.py:182-187
-    if (map_exr) return c > 0.0f ? c + 1.0f : expf(c);
-    return 1.0f / (1.0f + expf(-c));
+    // ex2.approx-based exp and an approximate divide: ~1e-6 relative, inside the 1e-5 parity bar
+    if (map_exr) return c > 0.0f ? c + 1.0f : __expf(c);
+    return __fdividef(1.0f, 1.0f + __expf(-c));
 }
 
 __device__ __forceinline__ float color_act_grad(float c, float y, int map_exr) {
@@ -73,6 +74,26 @@ __device__ __forceinline__ float sample_dist(const float* zrow, int i, int S, fl
     return zi - __ldg(zrow + i - 1);
 }
 
+// one round of inputs of a lane: raw sample, depth, optional noise
+struct RoundIn {
+    Sample sm;
+    float z, nz;
+};
+
+template <bool PACKED>
+__device__ __forceinline__ RoundIn load_round(const float* color, const float* sigma, const float* zrow,
+                                              const float* noise, int64_t row0, int i, int S) {
+    RoundIn r;
+    r.sm = {0.f, 0.f, 0.f, 0.f};
+    r.z = 0.0f; r.nz = 0.0f;
+    if (i < S) {
+        r.sm = load_sample<PACKED>(color, sigma, row0 + i);
+        r.z = __ldg(zrow + i);
+        if (noise) r.nz = __ldg(noise + row0 + i);
+    }
+    return r;
+}
+
 template <bool PACKED>
 __global__ void __launch_bounds__(256)
 composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ sigma, const float* __restrict__ z,
@@ -82,24 +103,32 @@ composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ 
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < R; ray += nwarps) {
+        const int64_t row0 = ray * S;
+        const float* zrow = z + row0;
+        // software pipeline: the loads of round r+1 are in flight while round r is scanned
+        RoundIn cur = load_round<PACKED>(color, sigma, zrow, noise, row0, lane, S);
         const float d0 = __ldg(rays_d + 3 * ray), d1 = __ldg(rays_d + 3 * ray + 1), d2 = __ldg(rays_d + 3 * ray + 2);
         const float norm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);                 // renderer.py:180
-        const float* zrow = z + ray * S;
-        float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f, dep = 0.0f;
+        float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f, dep = 0.0f, prev_z31 = 0.0f;
         for (int base = 0; base < S; base += 32) {
             const int i = base + lane;
             const bool valid = i < S;
-            float a = 0.0f, zi = 0.0f;
-            Sample sm = {0.f, 0.f, 0.f, 0.f};
+            const RoundIn nxt = load_round<PACKED>(color, sigma, zrow, noise, row0, i + 32, S);
+            // neighbours' depths by shuffle: z[i+1] from lane+1 (lane 31: next round's lane 0),
+            // z[i-1] from lane-1 (lane 0: previous round's lane 31)
+            float z_up = __shfl_down_sync(0xffffffffu, cur.z, 1);
+            const float z_next0 = __shfl_sync(0xffffffffu, nxt.z, 0);
+            if (lane == 31) z_up = z_next0;
+            float z_dn = __shfl_up_sync(0xffffffffu, cur.z, 1);
+            if (lane == 0) z_dn = prev_z31;
+            prev_z31 = __shfl_sync(0xffffffffu, cur.z, 31);
+            float a = 0.0f;
             if (valid) {
-                const int64_t k = ray * S + i;
-                sm = load_sample<PACKED>(color, sigma, k);
-                zi = __ldg(zrow + i);
-                float dist = sample_dist(zrow, i, S, zi) * norm;
-                float s = sm.s;
-                if (noise) s += __ldg(noise + k);                               // renderer.py:190-195
-                s = fmaxf(s, 0.0f);
-                a = 1.0f - expf(-s * dist);
+                // last distance duplicated (renderer.py:174-177)
+                float dist = (S == 1) ? 0.0f : (i < S - 1 ? z_up - cur.z : cur.z - z_dn);
+                dist *= norm;
+                const float s = fmaxf(cur.sm.s + cur.nz, 0.0f);                 // renderer.py:190-195
+                a = 1.0f - __expf(-s * dist);
             }
             const float om = (1.0f - a) + 1e-10f;                               // renderer.py:198
             const float incl = warp_scan_mul(om, lane);
@@ -108,13 +137,14 @@ composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ 
             const float w = a * (carry * excl);
             carry *= __shfl_sync(0xffffffffu, incl, 31);
             if (valid) {
-                if (weights) weights[ray * S + i] = w;
-                c0 += w * color_act(sm.r, map_exr);                             // renderer.py:201
-                c1 += w * color_act(sm.g, map_exr);
-                c2 += w * color_act(sm.b, map_exr);
-                dep += w * zi;                                                  // renderer.py:204
+                if (weights) weights[row0 + i] = w;
+                c0 += w * color_act(cur.sm.r, map_exr);                         // renderer.py:201
+                c1 += w * color_act(cur.sm.g, map_exr);
+                c2 += w * color_act(cur.sm.b, map_exr);
+                dep += w * cur.z;                                               // renderer.py:204
                 acc += w;                                                       // renderer.py:207
             }
+            cur = nxt;
         }
         c0 = ntx_warp_sum(c0); c1 = ntx_warp_sum(c1); c2 = ntx_warp_sum(c2);
         acc = ntx_warp_sum(acc);
