@@ -21,6 +21,8 @@
 // Reference: network/layer.py:11-23, network/model.py:58-125, network/renderer.py:145-168.
 #include <cuda_bf16.h>
 
+#include <stdlib.h>
+
 #include <new>
 
 #include "ntx_common.cuh"
@@ -39,9 +41,11 @@ constexpr uint32_t kMainBytes = kMainBlocks * kBlockBytes;                 // 65
 constexpr uint32_t kEncBytes = kEncBlocks * kBlockBytes;                   // 24576
 constexpr uint32_t kTileBytes = kMainBytes + kEncBytes;                    // 90112
 constexpr uint32_t kOffStages = kTilesPerCta * kTileBytes;                 // 180224
-constexpr uint32_t kOffHeads = kOffStages + kStages * kStageBytes;         // 229376
+constexpr uint32_t kRingBytes = kStages * kStageBytes;                     // 49152: 3 x 16 KB, or 6 x 8 KB per CTA of a pair
+constexpr uint32_t kOffHeads = kOffStages + kRingBytes;                    // 229376
 constexpr uint32_t kOffBars = kOffHeads + kHeadFloats * 4;                 // +2592
-constexpr uint32_t kNumBars = 2 * kStages + 2 * kTilesPerCta;
+constexpr uint32_t kMaxStages = 2 * kStages;
+constexpr uint32_t kNumBars = 2 * kMaxStages + 2 * kTilesPerCta;
 constexpr uint32_t kOffTmemSlot = kOffBars + kNumBars * 8;
 constexpr uint32_t kSmemBytes = kOffTmemSlot + 16;
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
@@ -139,44 +143,55 @@ __device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t
     }
 }
 
-template <bool DUMP>
+// CTAS == 1: every CTA is on its own (cta_group::1, M = 128 per instruction).
+// CTAS == 2: CTA pairs (cluster of 2, cta_group::2): one tcgen05.mma issued by the even CTA drives
+//            both SMs (M = 256), each CTA stages only its half of every weight slice (N/2 rows), so
+//            the L2->SM weight traffic per SM halves and the 48 KB ring holds 6 slices instead of 3.
+template <bool DUMP, int CTAS>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__ KernelArgs args) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     if ((sbase & 1023u) != 0) __trap();
 
+    constexpr uint32_t NSTAGE = kStages * CTAS;                 // ring stages
+    constexpr uint32_t STAGE_BYTES = kStageBytes / CTAS;        // bytes of one ring stage
+    const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;   // 0: issues the MMAs
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const uint32_t bar_full = sbase + kOffBars;                 // [kStages]  weight slice landed
-    const uint32_t bar_empty = bar_full + 8 * kStages;          // [kStages]  weight slice consumed
-    const uint32_t bar_act = bar_empty + 8 * kStages;           // [2] tile's A operand (activations) ready
+    const uint32_t bar_full = sbase + kOffBars;                 // [NSTAGE]  weight slice landed
+    const uint32_t bar_empty = bar_full + 8 * kMaxStages;       // [NSTAGE]  weight slice consumed
+    const uint32_t bar_act = bar_empty + 8 * kMaxStages;        // [2] tile's A operand (activations) ready
     const uint32_t bar_acc = bar_act + 8 * kTilesPerCta;        // [2] tile's accumulators ready
     float* heads = reinterpret_cast<float*>(smem + kOffHeads);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kOffTmemSlot);
 
     const int64_t n_rows = args.in.n_rows;
-    const int64_t n_batches = (n_rows + kRowsPerCta - 1) / kRowsPerCta;
+    // a "batch" is what one CTA (or CTA pair) processes per trip: 256 rows per CTA
+    const int64_t n_batches = (n_rows + kRowsPerCta * CTAS - 1) / (kRowsPerCta * CTAS);
+    const int64_t batch0 = blockIdx.x / CTAS, batch_stride = gridDim.x / CTAS;
 
     if (threadIdx.x == 0) {
-        for (int i = 0; i < kStages; ++i) {
-            mbar_init(bar_full + 8 * i, 1);
+        for (uint32_t i = 0; i < NSTAGE; ++i) {
+            // pair: the issuing CTA's "landed" barrier also collects the peer's relay arrive
+            mbar_init(bar_full + 8 * i, (CTAS == 2 && rank == 0) ? 2 : 1);
             mbar_init(bar_empty + 8 * i, 1);
         }
         for (int t = 0; t < kTilesPerCta; ++t) {
-            mbar_init(bar_act + 8 * t, 4);      // one arrive per epilogue warp of the tile
+            mbar_init(bar_act + 8 * t, 4 * CTAS);   // one arrive per epilogue warp of the tile (both CTAs)
             mbar_init(bar_acc + 8 * t, 1);
         }
         fence_mbar_init();
     }
     if (warp == 1) {
-        tmem_alloc(sbase + kOffTmemSlot, 512);
-        tmem_relinquish();
+        if (CTAS == 2) { tmem_alloc2(sbase + kOffTmemSlot, 512); tmem_relinquish2(); }
+        else { tmem_alloc(sbase + kOffTmemSlot, 512); tmem_relinquish(); }
     }
     // fp32 head weights -> shared (broadcast reads in the epilogues)
     for (int i = threadIdx.x; i < kHeadFloats; i += kThreads)
         heads[i] = reinterpret_cast<const float*>(args.packed)[i];
     tc_fence_before();
     __syncthreads();
+    if (CTAS == 2) cluster_sync_all();          // peer barriers initialised before any remote arrive / multicast
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -186,18 +201,19 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         // vice versa), so every layer's slices are streamed once per tile, in MMA issue order.
         if (lane == 0) {
             uint32_t stage = 0, parity = 1;      // a fresh barrier passes a wait on parity 1
-            for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+            for (int64_t b = batch0; b < n_batches; b += batch_stride) {
                 for (int st = 0; st < prog.n_steps; ++st) {
                     const int n_sl = prog.steps[st].slice_end - prog.steps[st].slice_begin;
-                    const uint32_t bytes = (uint32_t)prog.steps[st].n_out * 64u;
-                    const uint8_t* src0 = args.packed + prog.slice_off[prog.steps[st].slice_begin];
+                    const uint32_t slice_bytes = (uint32_t)prog.steps[st].n_out * 64u;
+                    const uint32_t bytes = slice_bytes / CTAS;               // pair: this CTA's N/2 rows of the slice
+                    const uint8_t* src0 = args.packed + prog.slice_off[prog.steps[st].slice_begin] + rank * bytes;
                     for (int t = 0; t < kTilesPerCta; ++t) {
                         const uint8_t* src = src0;
-                        for (int s = 0; s < n_sl; ++s, src += bytes) {
+                        for (int s = 0; s < n_sl; ++s, src += slice_bytes) {
                             mbar_wait(bar_empty + 8 * stage, parity);
                             mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-                            tma_bulk_g2s(sbase + kOffStages + stage * kStageBytes, src, bytes, bar_full + 8 * stage);
-                            if (++stage == kStages) { stage = 0; parity ^= 1; }
+                            tma_bulk_g2s(sbase + kOffStages + stage * STAGE_BYTES, src, bytes, bar_full + 8 * stage);
+                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
                         }
                     }
                 }
@@ -207,40 +223,54 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         // ===================================================================== MMA issuer
         // The whole warp walks the schedule (so every operand is warp-uniform); one elected lane
         // issues tcgen05.mma / tcgen05.commit.
+        if (CTAS == 2 && rank != 0) {
+            // peer CTA of a pair: this warp only relays "my half of the slice has landed" to the
+            // issuing CTA (bulk copies can only signal a barrier in their own CTA)
+            if (lane == 0) {
+                uint32_t stage = 0, parity = 0;
+                const uint32_t remote_full = mapa_shared(bar_full, 0);
+                for (int64_t b = batch0; b < n_batches; b += batch_stride) {
+                    for (int st = 0; st < prog.n_steps; ++st) {
+                        const int n_sl = (prog.steps[st].slice_end - prog.steps[st].slice_begin) * kTilesPerCta;
+                        for (int s = 0; s < n_sl; ++s) {
+                            mbar_wait(bar_full + 8 * stage, parity);
+                            mbar_arrive_remote(remote_full + 8 * stage);
+                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
+                        }
+                    }
+                }
+            }
+        } else {
         uint32_t stage = 0, parity = 0, act_phase0 = 0, act_phase1 = 0;
         uint32_t b16 = (sbase + kOffStages) >> 4;         // ring stage base >> 4
         uint32_t full_bar = bar_full, empty_bar = bar_empty;
-#if NTX_MMA_PREFETCH
-        bool ready = false;      // result of the non-blocking probe of the next ring stage
-#endif
         // one weight slice: wait until it landed, issue 1-2 MMAs (K=16 each), release the ring stage
         auto issue_slice = [&](uint32_t d_tmem, uint32_t a16, uint32_t half0, uint32_t nh, uint32_t idesc, uint32_t accumulate) {
-#if NTX_MMA_PREFETCH
-            if (!ready) mbar_wait(full_bar, parity);
-#else
             mbar_wait(full_bar, parity);
-#endif
             tc_fence_after();
             const uint32_t bb = b16 + half0 * 2, eb = empty_bar;
-            if (++stage == kStages) {
+            if (++stage == NSTAGE) {
                 stage = 0; parity ^= 1; b16 = (sbase + kOffStages) >> 4; full_bar = bar_full; empty_bar = bar_empty;
             } else {
-                b16 += kStageBytes >> 4; full_bar += 8; empty_bar += 8;
+                b16 += STAGE_BYTES >> 4; full_bar += 8; empty_bar += 8;
             }
-#if NTX_MMA_PREFETCH
-            ready = mbar_test_wait(full_bar, parity);   // probe the next stage: latency hides behind the issue below
-#endif
             if (elect_one_sync()) {
-                mma_bf16_ss(d_tmem, desc_sw64(a16), desc_sw64(bb), idesc, accumulate);
-                if (nh == 2) mma_bf16_ss(d_tmem, desc_sw64(a16 + 2), desc_sw64(bb + 2), idesc, 1u);
-                mma_commit(eb);                             // slice free once these MMAs retire
+                if (CTAS == 2) {
+                    mma_bf16_ss_2cta(d_tmem, desc_sw64(a16), desc_sw64(bb), idesc, accumulate);
+                    if (nh == 2) mma_bf16_ss_2cta(d_tmem, desc_sw64(a16 + 2), desc_sw64(bb + 2), idesc, 1u);
+                    mma_commit_2cta(eb);                    // slice free (in both CTAs) once these MMAs retire
+                } else {
+                    mma_bf16_ss(d_tmem, desc_sw64(a16), desc_sw64(bb), idesc, accumulate);
+                    if (nh == 2) mma_bf16_ss(d_tmem, desc_sw64(a16 + 2), desc_sw64(bb + 2), idesc, 1u);
+                    mma_commit(eb);                         // slice free once these MMAs retire
+                }
             }
             __syncwarp();
         };
-        for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
+        for (int64_t b = batch0; b < n_batches; b += batch_stride) {
             for (int st = 0; st < prog.n_steps; ++st) {
                 // copy the step into registers once (asm memory clobbers would otherwise reload it per slice)
-                const uint32_t idesc = idesc_bf16_f32(kTileRows, prog.steps[st].n_out);
+                const uint32_t idesc = idesc_bf16_f32(kTileRows * CTAS, prog.steps[st].n_out);
                 const int n_main = prog.steps[st].n_main, enc_n = prog.steps[st].enc_n;
                 const uint32_t enc_half0 = prog.steps[st].enc_half0, enc_last_nh = prog.steps[st].enc_last_nh;
                 const uint32_t enc16 = ((uint32_t)kMainBytes + prog.steps[st].enc_blk0 * kBlockBytes + enc_half0 * 32u) >> 4;
@@ -256,10 +286,14 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     for (int e = 0; e < enc_n; ++e)
                         issue_slice(d_tmem, a16_tile + enc16 + e * (kBlockBytes >> 4), enc_half0,
                                     e == enc_n - 1 ? enc_last_nh : 2u, idesc, (n_main > 0 || e > 0) ? 1u : 0u);
-                    if (elect_one_sync()) mma_commit(bar_acc + 8 * t);   // this tile's accumulators complete
+                    if (elect_one_sync()) {                 // this tile's accumulators complete
+                        if (CTAS == 2) mma_commit_2cta(bar_acc + 8 * t);
+                        else mma_commit(bar_acc + 8 * t);
+                    }
                     __syncwarp();
                 }
             }
+        }
         }
     } else {
         // ===================================================================== epilogue warpgroups
@@ -275,9 +309,15 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         const float* w_alpha = heads;               // [256], b at [256]
         const float* w_rgb = heads + 260;           // [3][128], b at [260 + 384 ..]
         uint32_t acc_phase = 0;
+        // pair: the tile's "operand ready" barrier lives in the issuing CTA
+        const uint32_t act_remote = (CTAS == 2 && rank != 0) ? mapa_shared(my_act, 0) : 0u;
+        auto arrive_act = [&]() {
+            if (CTAS == 2 && rank != 0) mbar_arrive_remote(act_remote);
+            else mbar_arrive(my_act);
+        };
 
-        for (int64_t b = blockIdx.x; b < n_batches; b += gridDim.x) {
-            const int64_t grow = b * kRowsPerCta + tile * kTileRows + row;
+        for (int64_t b = batch0; b < n_batches; b += batch_stride) {
+            const int64_t grow = (b * CTAS + rank) * kRowsPerCta + tile * kTileRows + row;
             const bool valid = grow < n_rows;
             // ------------------------------------------------------------- load this row's inputs
             float x[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 0.f}, pg[3] = {0.f, 0.f, 0.f};
@@ -350,7 +390,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
             }
             fence_proxy_async_smem();
             __syncwarp();
-            if (lane == 0) mbar_arrive(my_act);
+            if (lane == 0) arrive_act();
 
             float alpha_raw = 0.0f;
             // ------------------------------------------------------------- layer epilogues
@@ -446,7 +486,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     fence_proxy_async_smem();
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive(my_act);
+                    if (lane == 0) arrive_act();
                 }
             }
         }
@@ -454,9 +494,11 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
 
     tc_fence_before();
     __syncthreads();
+    if (CTAS == 2) cluster_sync_all();          // no CTA leaves while its peer may still signal it
     if (warp == 1) {
         __syncwarp();
-        tmem_dealloc(tmem_base, 512);
+        if (CTAS == 2) tmem_dealloc2(tmem_base, 512);
+        else tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -655,15 +697,17 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
         NTX_REQUIRE((((uintptr_t)enc_pos | (uintptr_t)enc_dir | (uintptr_t)acts) & 15) == 0,
                     "mlp_forward_train: save buffers must be 16-byte aligned");
     }
-    static bool attr_set[64][2] = {};
+    // NTX_MLP_CTAS=1 selects the single-CTA kernel (cta_group::1); default is CTA pairs (cta_group::2)
+    static const int ctas = [] { const char* e = getenv("NTX_MLP_CTAS"); return (e && e[0] == '1') ? 1 : 2; }();
+    using KernelFn = void (*)(const Program, const KernelArgs);
+    KernelFn fn = ctas == 2 ? (dump ? mlp_forward_kernel<true, 2> : mlp_forward_kernel<false, 2>)
+                            : (dump ? mlp_forward_kernel<true, 1> : mlp_forward_kernel<false, 1>);
+    static bool attr_set[64][2][2] = {};
     int dev = 0;
     NTX_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev][dump]) {
-        if (dump)
-            NTX_CUDA(cudaFuncSetAttribute(mlp_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-        else
-            NTX_CUDA(cudaFuncSetAttribute(mlp_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-        attr_set[dev][dump] = true;
+    if (dev < 64 && !attr_set[dev][dump][ctas - 1]) {
+        NTX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+        attr_set[dev][dump][ctas - 1] = true;
     }
     KernelArgs ka;
     ka.in = *in;
@@ -672,11 +716,21 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     ka.dump_enc_pos = (uint4*)enc_pos;
     ka.dump_enc_dir = (uint4*)enc_dir;
     ka.dump_acts = (uint4*)acts;
-    const int64_t n_batches = (in->n_rows + kRowsPerCta - 1) / kRowsPerCta;
-    const int grid = (int)(n_batches < ntx_sm_count() ? n_batches : ntx_sm_count());
-    if (dump) mlp_forward_kernel<true><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(mlp->prog, ka);
-    else mlp_forward_kernel<false><<<grid, kThreads, kSmemBytes, (cudaStream_t)stream>>>(mlp->prog, ka);
-    NTX_LAUNCH_CHECK();
+    const int64_t rows_per_unit = (int64_t)kRowsPerCta * ctas;
+    const int64_t n_units = (in->n_rows + rows_per_unit - 1) / rows_per_unit;
+    const int64_t max_units = ntx_sm_count() / ctas;
+    const int grid = (int)(n_units < max_units ? n_units : max_units) * ctas;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmemBytes;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ctas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    NTX_CUDA(cudaLaunchKernelEx(&cfg, fn, mlp->prog, ka));
     return NTX_OK;
 }
 
