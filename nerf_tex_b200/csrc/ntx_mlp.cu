@@ -154,8 +154,11 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
     const uint32_t sbase = smem_u32(smem);
     if ((sbase & 1023u) != 0) __trap();
 
-    constexpr uint32_t NSTAGE = kStages * CTAS;                 // ring stages
-    constexpr uint32_t STAGE_BYTES = kStageBytes / CTAS;        // bytes of one ring stage
+    // A ring stage is 16 KB: one whole [N x 32] slice for a lone CTA; for a pair, this CTA's halves
+    // ([N/2 x 32], 8 KB) of TWO consecutive slices, so that one barrier round trip feeds four MMAs.
+    constexpr uint32_t NSTAGE = kStages;                        // ring stages
+    constexpr uint32_t STAGE_BYTES = kStageBytes;               // bytes of one ring stage
+    constexpr int SPS = CTAS;                                   // slices per stage
     const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;   // 0: issues the MMAs
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bar_full = sbase + kOffBars;                 // [NSTAGE]  weight slice landed
@@ -203,17 +206,25 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
             uint32_t stage = 0, parity = 1;      // a fresh barrier passes a wait on parity 1
             for (int64_t b = batch0; b < n_batches; b += batch_stride) {
                 for (int st = 0; st < prog.n_steps; ++st) {
-                    const int n_sl = prog.steps[st].slice_end - prog.steps[st].slice_begin;
+                    const int n_main = prog.steps[st].n_main, enc_n = prog.steps[st].enc_n;
                     const uint32_t slice_bytes = (uint32_t)prog.steps[st].n_out * 64u;
-                    const uint32_t bytes = slice_bytes / CTAS;               // pair: this CTA's N/2 rows of the slice
+                    const uint32_t bytes = slice_bytes / CTAS;               // pair: this CTA's N/2 rows of a slice
                     const uint8_t* src0 = args.packed + prog.slice_off[prog.steps[st].slice_begin] + rank * bytes;
                     for (int t = 0; t < kTilesPerCta; ++t) {
                         const uint8_t* src = src0;
-                        for (int s = 0; s < n_sl; ++s, src += slice_bytes) {
-                            mbar_wait(bar_empty + 8 * stage, parity);
-                            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-                            tma_bulk_g2s(sbase + kOffStages + stage * STAGE_BYTES, src, bytes, bar_full + 8 * stage);
-                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
+                        // stage groups: main slices first, then encoding slices, SPS slices per stage
+                        for (int part = 0; part < 2; ++part) {
+                            int left = part == 0 ? n_main : enc_n;
+                            while (left > 0) {
+                                const int n = left < SPS ? left : SPS;
+                                mbar_wait(bar_empty + 8 * stage, parity);
+                                mbar_arrive_expect_tx(bar_full + 8 * stage, bytes * n);
+                                for (int j = 0; j < n; ++j, src += slice_bytes)
+                                    tma_bulk_g2s(sbase + kOffStages + stage * STAGE_BYTES + j * bytes, src, bytes,
+                                                 bar_full + 8 * stage);
+                                if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
+                                left -= n;
+                            }
                         }
                     }
                 }
@@ -231,7 +242,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 const uint32_t remote_full = mapa_shared(bar_full, 0);
                 for (int64_t b = batch0; b < n_batches; b += batch_stride) {
                     for (int st = 0; st < prog.n_steps; ++st) {
-                        const int n_sl = (prog.steps[st].slice_end - prog.steps[st].slice_begin) * kTilesPerCta;
+                        const int n_sl = ((prog.steps[st].n_main + SPS - 1) / SPS + (prog.steps[st].enc_n + SPS - 1) / SPS) *
+                                         kTilesPerCta;
                         for (int s = 0; s < n_sl; ++s) {
                             mbar_wait(bar_full + 8 * stage, parity);
                             mbar_arrive_remote(remote_full + 8 * stage);
@@ -244,8 +256,11 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         uint32_t stage = 0, parity = 0, act_phase0 = 0, act_phase1 = 0;
         uint32_t b16 = (sbase + kOffStages) >> 4;         // ring stage base >> 4
         uint32_t full_bar = bar_full, empty_bar = bar_empty;
-        // one weight slice: wait until it landed, issue 1-2 MMAs (K=16 each), release the ring stage
-        auto issue_slice = [&](uint32_t d_tmem, uint32_t a16, uint32_t half0, uint32_t nh, uint32_t idesc, uint32_t accumulate) {
+        // one ring stage: wait until it landed, issue its MMAs (K=16 each; up to 2 per slice, SPS slices),
+        // release the stage.  a16: A operand of the first slice (>>4); consecutive slices read consecutive
+        // 32-column A blocks.  nh_last: K=16 halves of the stage's last slice (the others use 2).
+        auto issue_stage = [&](uint32_t d_tmem, uint32_t a16, uint32_t half0, int n_slices, uint32_t nh_last,
+                               uint32_t b_slice16, uint32_t idesc, uint32_t accumulate) {
             mbar_wait(full_bar, parity);
             tc_fence_after();
             const uint32_t bb = b16 + half0 * 2, eb = empty_bar;
@@ -255,15 +270,22 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 b16 += STAGE_BYTES >> 4; full_bar += 8; empty_bar += 8;
             }
             if (elect_one_sync()) {
-                if (CTAS == 2) {
-                    mma_bf16_ss_2cta(d_tmem, desc_sw64(a16), desc_sw64(bb), idesc, accumulate);
-                    if (nh == 2) mma_bf16_ss_2cta(d_tmem, desc_sw64(a16 + 2), desc_sw64(bb + 2), idesc, 1u);
-                    mma_commit_2cta(eb);                    // slice free (in both CTAs) once these MMAs retire
-                } else {
-                    mma_bf16_ss(d_tmem, desc_sw64(a16), desc_sw64(bb), idesc, accumulate);
-                    if (nh == 2) mma_bf16_ss(d_tmem, desc_sw64(a16 + 2), desc_sw64(bb + 2), idesc, 1u);
-                    mma_commit(eb);                         // slice free once these MMAs retire
+#pragma unroll
+                for (int j = 0; j < SPS; ++j) {
+                    if (j < n_slices) {
+                        const uint32_t aj = a16 + j * (kBlockBytes >> 4), bj = bb + j * b_slice16;
+                        const uint32_t nh = (j == n_slices - 1) ? nh_last : 2u;
+                        if (CTAS == 2) {
+                            mma_bf16_ss_2cta(d_tmem, desc_sw64(aj), desc_sw64(bj), idesc, (j > 0) ? 1u : accumulate);
+                            if (nh == 2) mma_bf16_ss_2cta(d_tmem, desc_sw64(aj + 2), desc_sw64(bj + 2), idesc, 1u);
+                        } else {
+                            mma_bf16_ss(d_tmem, desc_sw64(aj), desc_sw64(bj), idesc, (j > 0) ? 1u : accumulate);
+                            if (nh == 2) mma_bf16_ss(d_tmem, desc_sw64(aj + 2), desc_sw64(bj + 2), idesc, 1u);
+                        }
+                    }
                 }
+                if (CTAS == 2) mma_commit_2cta(eb);         // stage free (in both CTAs) once these MMAs retire
+                else mma_commit(eb);
             }
             __syncwarp();
         };
@@ -274,6 +296,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 const int n_main = prog.steps[st].n_main, enc_n = prog.steps[st].enc_n;
                 const uint32_t enc_half0 = prog.steps[st].enc_half0, enc_last_nh = prog.steps[st].enc_last_nh;
                 const uint32_t enc16 = ((uint32_t)kMainBytes + prog.steps[st].enc_blk0 * kBlockBytes + enc_half0 * 32u) >> 4;
+                const uint32_t b_slice16 = ((uint32_t)prog.steps[st].n_out * 64u / CTAS) >> 4;   // this CTA's bytes of one slice
 #pragma unroll
                 for (int t = 0; t < kTilesPerCta; ++t) {
                     if (t == 0) { mbar_wait(bar_act, act_phase0); act_phase0 ^= 1; }
@@ -281,11 +304,13 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     tc_fence_after();
                     const uint32_t d_tmem = tmem_base + t * kWidth;
                     const uint32_t a16_tile = (sbase + t * kTileBytes) >> 4;
-                    for (int i = 0; i < n_main; ++i)
-                        issue_slice(d_tmem, a16_tile + i * (kBlockBytes >> 4), 0u, 2u, idesc, i > 0 ? 1u : 0u);
-                    for (int e = 0; e < enc_n; ++e)
-                        issue_slice(d_tmem, a16_tile + enc16 + e * (kBlockBytes >> 4), enc_half0,
-                                    e == enc_n - 1 ? enc_last_nh : 2u, idesc, (n_main > 0 || e > 0) ? 1u : 0u);
+                    for (int i = 0; i < n_main; i += SPS)
+                        issue_stage(d_tmem, a16_tile + i * (kBlockBytes >> 4), 0u, SPS, 2u, b_slice16, idesc, i > 0 ? 1u : 0u);
+                    for (int e = 0; e < enc_n; e += SPS) {
+                        const int n = enc_n - e < SPS ? enc_n - e : SPS;
+                        issue_stage(d_tmem, a16_tile + enc16 + e * (kBlockBytes >> 4), enc_half0, n,
+                                    e + n == enc_n ? enc_last_nh : 2u, b_slice16, idesc, (n_main > 0 || e > 0) ? 1u : 0u);
+                    }
                     if (elect_one_sync()) {                 // this tile's accumulators complete
                         if (CTAS == 2) mma_commit_2cta(bar_acc + 8 * t);
                         else mma_commit(bar_acc + 8 * t);
