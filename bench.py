@@ -81,8 +81,10 @@ class ChunkReplayInstancer:
 
     patch_scale = PATCH_SCALE
 
-    def __init__(self, chunks, resident: bool):
+    def __init__(self, chunks, resident: bool, fields=None):
         import torch
+        if fields is not None:           # host side: ship only the records this renderer configuration consumes
+            chunks = [{k: v for k, v in c.items() if k in fields} for c in chunks]
         self.resident = resident
         self.i = 0
         self.h2d_bytes = 0
@@ -249,6 +251,47 @@ def hbm_kernels_bench(dev, pk):
     return out
 
 
+def train_step_bench(dev, steps=5):
+    """SURVEY.md C3 (grass_filtered shape): 4096 rays, model [2,3], blur_idx 0, raw_noise_std 0.1,
+    AlphaLoss(smape, mse); variant (i) single net x 256 samples and (ii) CoarseFine 64 + 128.
+    Whole step: forward (K3/K1/K2), loss, backward (K2-bwd + MLP dgrad/wgrad), Adam."""
+    import torch
+    from nerf_tex_b200.loss import AlphaLoss
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.renderer import Renderer
+    from nerf_tex_b200.train import Trainer
+    g = torch.Generator(device=dev).manual_seed(0)
+    R = 4096
+    ro = torch.tensor([[0., 0.5, 5.]], device=dev).repeat(R, 1)
+    rd = torch.rand((R, 3), device=dev, generator=g) * 2 - 1 - ro
+    rd = rd / rd.norm(dim=-1, keepdim=True)
+    data = {"rays_o": ro[None], "rays_d": rd[None],
+            "t": torch.stack([3 + torch.rand(R, device=dev, generator=g), 6 + torch.rand(R, device=dev, generator=g)], -1)[None],
+            "parameters": torch.rand((1, 5), device=dev, generator=g), "cone_scale": torch.rand((1, R, 1), device=dev, generator=g) * .01,
+            "color": torch.rand((1, R, 3), device=dev, generator=g), "alpha": torch.rand((1, R), device=dev, generator=g)}
+    out = {}
+    for name, (S, N) in (("single_256", (256, 0)), ("coarse_fine_64_128", (64, 128))):
+        models = {"model": FusedNerfTexMLP(2, 3, seed=1)}
+        if N:
+            models["model_fine"] = FusedNerfTexMLP(2, 3, seed=2, name="model_fine")
+        r = Renderer(n_samples=S, n_importance=N, perturb=True, blur_idx=0, raw_noise_std=0.1, seed=0, **models)
+        tr = Trainer(models, r, AlphaLoss("network.loss.smape", "network.loss.mse"))
+        for _ in range(3):
+            tr.train_step(data)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            loss = tr.train_step(data)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / steps
+        rows = R * 256
+        out[name] = {"ms_per_step": ms, "rays_per_sec": R / ms * 1e3, "mlp_rows_per_step": rows,
+                     "fwd_bwd_tflops": rows * 2.92 * 2 * 678528 / (ms / 1e3) / 1e12, "loss": float(loss)}
+    return out
+
+
 def config_dict(extra=None):
     c = {"workload": "carpet-shape instanced render, 800x800 frame (640000 rays), n_parameters [1,6], "
                      "n_samples<=1024, step 0.002, patch_scale 0.09, render_chunk 16384, random-init weights",
@@ -358,7 +401,10 @@ def run_gpu(args):
     k1_launches = len(k1_events)
 
     # ---- e2e arm: host buffers in, host result out, copies inside the timed region
-    host = ChunkReplayInstancer(chunks, resident=False)
+    # `t` feeds only the blur_idx scaling (renderer.py:260-263) and `instance_id` only false-colour
+    # rendering (:306-307); neither is enabled in the carpet config, so the host does not send them
+    needed = {"ray_ptr", "ray_index", "pts", "dirs", "params", "dists", "alpha_weight", "color_last", "alpha_last"}
+    host = ChunkReplayInstancer(chunks, resident=False, fields=needed)
     renderer_h = InstanceRenderer(instancer_config=host, model=model, n_samples=N_SAMPLES, render_chunk=RENDER_CHUNK,
                                   net_chunk=32768, step_size=STEP_SIZE, density_reweighting=True)
     host_in = [torch.as_tensor(x).pin_memory() for x in (rays_o, rays_d, t, params, cone)]
@@ -429,6 +475,7 @@ def run_gpu(args):
             del chunks, resident, host
             torch.cuda.empty_cache()
             line["hbm_kernels"] = hbm_kernels_bench(dev, pk)
+            line["train_step"] = train_step_bench(dev)
             line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
         print(json.dumps(line), flush=True)
     if world > 1:
