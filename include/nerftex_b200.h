@@ -163,10 +163,39 @@ int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inpu
  * backward pass needs (the reference keeps them on the tf.GradientTape, network/train.py:62-64):
  *   enc_pos[N,96], enc_dir[N,96]  encoded inputs in the kernel's column order (see
  *                                 ntx_mlp_enc_columns), constant-1 bias column included;
- *   acts[n_steps][N,256]          stored output of every step (post-activation; the 128-wide
- *                                 last step fills columns 0..127). */
+ *   acts[n_steps][N,256]          (optional, may be NULL) stored output of every step, row-major
+ *                                 (post-activation; the 128-wide last step fills columns 0..127);
+ *   acts_img[n_steps][n_tiles][64 KB]  (optional) the same outputs as 128-row tile images: exactly the
+ *                                 SWIZZLE_64B operand layout the kernels keep in shared memory
+ *                                 (32-column blocks of [128 rows x 64 B], 16-byte chunk index XOR
+ *                                 (row >> 1) & 3), written with bulk stores; consumed as-is by
+ *                                 ntx_mlp_backward_*; ntx_untile converts to row-major;
+ *   masks[n_steps][n_tiles*128][8] (with acts_img) u32 words: bit c of word j set <=> output column
+ *                                 32 j + c of that row is > 0 (the ReLU derivative).
+ * n_tiles >= ntx_mlp_train_tiles(N) (rows are processed in whole 512-row CTA-pair batches). */
+int64_t ntx_mlp_train_tiles(int64_t n_rows);
 int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
-                          void* enc_pos, void* enc_dir, void* acts, void* stream);
+                          void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks, int64_t n_tiles,
+                          void* stream);
+/* Tile images -> row-major bf16: out[n_rows, cols] from img[n_tiles][64 KB] (cols <= 256, multiple of 32). */
+int ntx_untile(const void* img, int64_t n_rows, int cols, void* out, void* stream);
+
+/* Backward of the MLP on the saved operands (the reference gets it from tape.gradient,
+ * network/train.py:66).  Two kernels:
+ *   ntx_mlp_backward_data    fused data-gradient chain: from d_rgbs[N,4] (gradient w.r.t. the raw outputs)
+ *                            and the ReLU masks it produces dy_img[n_steps][n_tiles][64 KB], the gradient
+ *                            w.r.t. every step's pre-activation output, as tile images.  packed_t is the
+ *                            transposed packed weight image (ntx_mlp_packed_t_bytes / ntx_mlp_pack_weights_t).
+ *   ntx_mlp_backward_weights for every step >= 1 adds X^T dY (rows main_row0.. of that layer's kernel) and the
+ *                            bias gradient 1^T dY into the flat fp32 gradient buffer `grad` (layout of the master
+ *                            buffer; the caller zeroes it).  The encoded-input rows, step 0 and the two small heads
+ *                            are left to the host (nerf_tex_b200/autograd.py). */
+int64_t ntx_mlp_packed_t_bytes(const ntx_mlp_t* mlp);
+int ntx_mlp_pack_weights_t(const ntx_mlp_t* mlp, const float* master, void* packed_t, void* stream);
+int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
+                          void* dy_img, int64_t n_rows, int64_t n_tiles, void* stream);
+int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, float* grad,
+                             int64_t n_rows, int64_t n_tiles, void* stream);
 
 /* Schedule introspection for the host-side backward (nerf_tex_b200/autograd.py).  A "step" is one
  * tensor-core layer: trunk0..trunk{depth-1}, feature, colorhid*, colorhalf. */
@@ -253,6 +282,9 @@ int ntx_render_rays_static(const ntx_mlp_t* mlp, const void* packed, const ntx_m
  * fp32 accumulate.  layout: 0 = SWIZZLE_64B K-slices of 32, 1 = SWIZZLE_128B K-slices of 64,
  * 2 = no swizzle (interleaved core matrices). K multiple of 64, N in {128,256}. */
 int ntx_selftest_umma(const float* A, const float* B, int N, int K, int layout, float* D, void* stream);
+/* D[128,N] = At^T * Bt, At[K,128] and Bt[K,N] row-major: both operands MN-major, SWIZZLE_64B row images
+ * (the operand form of the weight-gradient GEMM, K = sample rows).  K in {64,128}, N in {128,256}. */
+int ntx_selftest_umma_mn(const float* At, const float* Bt, int N, int K, float* D, void* stream);
 /* global -> shared through cp.async.bulk + mbarrier, then back out: dst[0:bytes] = src[0:bytes]. */
 int ntx_selftest_bulk_copy(const void* src, void* dst, int bytes, void* stream);
 

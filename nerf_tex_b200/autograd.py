@@ -50,20 +50,81 @@ class MlpSchedule:
 
 
 def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, rays_o=None, rays_d=None, z=None,
-                      row_scale=None, group_scale=None, blur_idx=None):
-    """Raw rgbs[N,4] plus the saved bf16 operands (enc_pos, enc_dir, acts)."""
+                      row_scale=None, group_scale=None, blur_idx=None, row_major_acts: bool = False):
+    """Raw rgbs[N,4] plus the saved operands: (enc_pos, enc_dir, acts_img, masks[, acts])."""
     packed = model.ensure_packed()
     sched = model.schedule()
     dev = model.device
+    lib = _lib.load()
+    n_tiles = int(lib.ntx_mlp_train_tiles(int(n_rows)))
     rgbs = torch.empty((n_rows, 4), dtype=torch.float32, device=dev)
     enc_pos = torch.empty((n_rows, ENC_COLS), dtype=torch.bfloat16, device=dev)
     enc_dir = torch.empty((n_rows, ENC_COLS), dtype=torch.bfloat16, device=dev)
-    acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev)
+    acts_img = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=dev)
+    masks = torch.empty((sched.n_steps, n_tiles * 128, 8), dtype=torch.int32, device=dev)
+    acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev) if row_major_acts else None
     inp = MlpInputs(ptr(pos), ptr(rays_o), ptr(rays_d), ptr(z), ptr(dir), ptr(params), ptr(row_scale), ptr(group_scale),
                     -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows))
-    check(_lib.load().ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
-                                            ptr(acts), stream_ptr()))
-    return rgbs, (enc_pos, enc_dir, acts)
+    check(lib.ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
+                                    ptr(acts), ptr(acts_img), ptr(masks), n_tiles, stream_ptr()))
+    return rgbs, (enc_pos, enc_dir, acts_img, masks, acts)
+
+
+def untile(img: torch.Tensor, n_rows: int, cols: int = 256) -> torch.Tensor:
+    """[n_tiles, 128*256] tile images -> row-major bf16 [n_rows, cols]."""
+    out = torch.empty((n_rows, cols), dtype=torch.bfloat16, device=img.device)
+    check(_lib.load().ntx_untile(ptr(img), int(n_rows), int(cols), ptr(out), stream_ptr()))
+    return out
+
+
+def mlp_backward_native(model, saved, d_rgbs: torch.Tensor, return_dy: bool = False):
+    """d loss / d master with the hand-written kernels: ntx_mlp_backward_data (fused dgrad chain) and
+    ntx_mlp_backward_weights (X^T dY and 1^T dY on the saved tile images).  What stays on the host, as small
+    torch GEMMs on un-tiled copies: the encoded-input rows of the three layers that read an encoding
+    (K = 96), everything of step 0, and the two heads (N = 1 and N = 3)."""
+    enc_pos, enc_dir, acts_img, masks, _ = saved
+    lib = _lib.load()
+    sched = model.schedule()
+    n_rows, n_tiles = enc_pos.shape[0], acts_img.shape[1]
+    master = model.master.detach()
+    bf = torch.bfloat16
+    if getattr(model, "_packed_t_version", None) != model.master._version:
+        if getattr(model, "_packed_t", None) is None:
+            model._packed_t = torch.empty(int(lib.ntx_mlp_packed_t_bytes(model._h)), dtype=torch.uint8, device=model.device)
+        check(lib.ntx_mlp_pack_weights_t(model._h, ptr(master), ptr(model._packed_t), stream_ptr()))
+        model._packed_t_version = model.master._version
+    d_rgbs = d_rgbs.contiguous()
+    dy_img = torch.empty_like(acts_img)
+    check(lib.ntx_mlp_backward_data(model._h, ptr(model._packed_t), ptr(d_rgbs), ptr(masks), ptr(dy_img), n_rows, n_tiles,
+                                    stream_ptr()))
+    grad = torch.zeros_like(master)
+    check(lib.ntx_mlp_backward_weights(model._h, ptr(acts_img), ptr(dy_img), ptr(grad), n_rows, n_tiles, stream_ptr()))
+
+    def gview(layer):
+        wo, bo, fi, fo = model.layers[layer]
+        return grad[wo:wo + fi * fo].view(fi, fo), grad[bo:bo + fo]
+
+    for st, s in enumerate(sched.steps):
+        if st > 0 and not s["enc_data"]:
+            continue
+        dY = untile(dy_img[st], n_rows, s["n_out"])
+        gW, gb = gview(s["layer"])
+        if st == 0:
+            gb.copy_(dY.sum(0, dtype=torch.float32))
+        if s["enc_data"]:
+            e = enc_pos if s["phase"] == 0 else enc_dir
+            cols, rows = sched.enc_maps[s["phase"]]
+            gE = torch.mm(e.t(), dY, out_dtype=torch.float32)
+            gW[rows] = gE[cols]
+    d_rgb, d_sigma = d_rgbs[:, :3].contiguous(), d_rgbs[:, 3:4].contiguous()
+    last = sched.n_steps - 1
+    gW, gb = gview(sched.rgb_layer)                                       # model.py:123
+    gW.copy_(torch.mm(untile(acts_img[last], n_rows, 128).t(), d_rgb.to(bf), out_dtype=torch.float32))
+    gb.copy_(d_rgb.sum(0))
+    gWa, gba = gview(sched.alpha_layer)                                   # model.py:111
+    gWa.copy_(torch.mm(untile(acts_img[sched.depth - 1], n_rows).t(), d_sigma.to(bf), out_dtype=torch.float32))
+    gba.copy_(d_sigma.sum(0))
+    return (grad, dy_img) if return_dy else grad
 
 
 def mlp_backward(model, saved, d_rgbs: torch.Tensor) -> torch.Tensor:
@@ -72,7 +133,10 @@ def mlp_backward(model, saved, d_rgbs: torch.Tensor) -> torch.Tensor:
     All GEMMs take bf16 operands with fp32 accumulation; weight gradients come out in fp32.  (An
     fp32 / TF32 gradient chain was measured to give the same agreement with the float64 reference —
     the residual is the bf16 forward itself — so the cheaper bf16 chain is kept.)"""
-    enc_pos, enc_dir, acts = saved
+    enc_pos, enc_dir, acts_img, masks, acts = saved
+    n_rows = enc_pos.shape[0]
+    if acts is None:
+        acts = [untile(acts_img[st], n_rows) for st in range(acts_img.shape[0])]
     sched = model.schedule()
     master = model.master.detach()
     grad = torch.zeros_like(master)
@@ -150,6 +214,6 @@ class NetworkPass(torch.autograd.Function):
         rgbs, z, rays_d, noise, map_exr, composite_bkgd, bkgd_color = ctx.misc
         d_rgbs = ops.composite_backward(rgbs, z, rays_d, d_cmap.contiguous(), d_amap.contiguous(), noise=noise,
                                         map_exr=map_exr, composite_bkgd=composite_bkgd, bkgd_color=bkgd_color)
-        grad = mlp_backward(ctx.model, ctx.saved, d_rgbs.view(-1, 4))
+        grad = mlp_backward_native(ctx.model, ctx.saved, d_rgbs.view(-1, 4))
         ctx.saved = None
         return (grad,) + (None,) * 12

@@ -28,6 +28,7 @@
 #include "ntx_common.cuh"
 #include "ntx_mlp.cuh"
 #include "ntx_umma.cuh"
+#include "ntx_mlp_dev.cuh"
 
 namespace {
 
@@ -37,7 +38,6 @@ using namespace ntxmlp;
 // ----------------------------------------------------------------------------------------------
 // shared-memory map (bytes, from a 1024-aligned base)
 // ----------------------------------------------------------------------------------------------
-constexpr uint32_t kMainBytes = kMainBlocks * kBlockBytes;                 // 65536
 constexpr uint32_t kEncBytes = kEncBlocks * kBlockBytes;                   // 24576
 constexpr uint32_t kTileBytes = kMainBytes + kEncBytes;                    // 90112
 constexpr uint32_t kOffStages = kTilesPerCta * kTileBytes;                 // 180224
@@ -63,41 +63,12 @@ struct KernelArgs {
     // training only: bf16 copies of every tensor-core operand the backward needs
     uint4* dump_enc_pos;   // [N, 96] encoded pos-phase inputs (kernel column order, constant-1 column included)
     uint4* dump_enc_dir;   // [N, 96]
-    uint4* dump_acts;      // [n_steps][N, 256] stored outputs of every step (the 128-wide last step uses cols 0..127)
+    uint4* dump_acts;      // [n_steps][N, 256] stored outputs of every step (the 128-wide last step uses cols 0..127); may be NULL
+    uint8_t* dump_img;     // [n_steps][n_tiles][64 KB]: the same outputs as 128-row SWIZZLE_64B tile images (the A
+                           // operand buffer as it sits in shared memory), written by bulk stores; may be NULL
+    uint4* dump_masks;     // [n_steps][n_tiles*128][8 x u32]: bit c of word j = output column 32 j + c is > 0
+    int64_t n_tiles;       // tiles allocated per step in dump_img / dump_masks
 };
-
-constexpr int kEncCols = kEncBlocks * 32;   // 96
-
-__device__ __forceinline__ void st_global_v4(uint4* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.global.v4.b32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-
-__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
-    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
-}
-
-__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-
-// 16-byte chunk `q` (8 bf16 columns) of row `row` inside a SW64 K-major region starting at `base`
-__device__ __forceinline__ uint32_t chunk_addr(uint32_t base, int q, int row) {
-    return base + (uint32_t)(q >> 2) * kBlockBytes + (uint32_t)row * 64 + (uint32_t)(((q & 3) ^ ((row >> 1) & 3)) << 4);
-}
-
-// [sin, cos](2^k x) for k = 0..3 as four bf16x2 words: one accurate sincosf + 3 angle doublings
-__device__ __forceinline__ void sincos4(float x, uint32_t (&w)[4]) {
-    float s, c;
-    sincosf(x, &s, &c);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        w[k] = pack_bf16(s, c);
-        const float s2 = 2.0f * s * c;
-        c = 1.0f - 2.0f * s * s;
-        s = s2;
-    }
-}
 
 // ----------------------------------------------------------------------------------------------
 // the fused forward kernel
@@ -111,8 +82,20 @@ __device__ __forceinline__ uint32_t pack_bf16_relu(float lo, float hi) {
 }
 
 // 32 fp32 accumulator columns (chunk j of this thread's row) -> bf16 -> next layer's A operand
+// bits {2e, 2e+1} of the result: the two bf16 halves of packed word e are non-zero (i.e. > 0 after ReLU)
+__device__ __forceinline__ uint32_t nonzero_bits4(const uint32_t (&w)[4]) {
+    uint32_t m = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        m |= ((w[e] & 0xFFFFu) != 0u ? 1u : 0u) << (2 * e);
+        m |= ((w[e] >> 16) != 0u ? 1u : 0u) << (2 * e + 1);
+    }
+    return m;
+}
+
 template <bool RELU, bool DUMP>
-__device__ __forceinline__ void store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32], uint4* grow_ptr) {
+__device__ __forceinline__ uint32_t store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32], uint4* grow_ptr) {
+    uint32_t mask = 0;
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         uint32_t w[4];
@@ -123,23 +106,28 @@ __device__ __forceinline__ void store_chunk32(uint32_t main_base, int j, int row
         }
         st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
         if (DUMP && grow_ptr) st_global_v4(grow_ptr + j * 4 + c, w[0], w[1], w[2], w[3]);
+        if (DUMP) mask |= nonzero_bits4(w) << (8 * c);
     }
+    return mask;
 }
 
 // plain hidden layer epilogue: TMEM loads software-pipelined against the convert + store
 template <bool RELU, bool DUMP>
 __device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t main_base, int row, int n_chunks,
-                                                     uint4* grow_ptr) {
+                                                     uint4* grow_ptr, uint32_t (&masks)[8]) {
     uint32_t va[32], vb[32];
     tmem_ld_32x32b_x32(tmem_row, va);
     tmem_ld_wait();
-    for (int j = 0; j < n_chunks; j += 2) {
-        tmem_ld_32x32b_x32(tmem_row + (j + 1) * 32, vb);
-        store_chunk32<RELU, DUMP>(main_base, j, row, va, grow_ptr);
-        tmem_ld_wait();
-        if (j + 2 < n_chunks) tmem_ld_32x32b_x32(tmem_row + (j + 2) * 32, va);
-        store_chunk32<RELU, DUMP>(main_base, j + 1, row, vb, grow_ptr);
-        tmem_ld_wait();
+#pragma unroll
+    for (int j = 0; j < 8; j += 2) {
+        if (j < n_chunks) {
+            tmem_ld_32x32b_x32(tmem_row + (j + 1) * 32, vb);
+            masks[j] = store_chunk32<RELU, DUMP>(main_base, j, row, va, grow_ptr);
+            tmem_ld_wait();
+            if (j + 2 < n_chunks) tmem_ld_32x32b_x32(tmem_row + (j + 2) * 32, va);
+            masks[j + 1] = store_chunk32<RELU, DUMP>(main_base, j + 1, row, vb, grow_ptr);
+            tmem_ld_wait();
+        }
     }
 }
 
@@ -427,11 +415,17 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 acc_phase ^= 1;
                 tc_fence_after();
                 float o0 = 0.f, o1 = 0.f, o2 = 0.f;
-                uint4* gp = (DUMP && valid) ? args.dump_acts + ((int64_t)st * n_rows + grow) * (kWidth / 8) : nullptr;
+                uint4* gp = (DUMP && valid && args.dump_acts) ? args.dump_acts + ((int64_t)st * n_rows + grow) * (kWidth / 8) : nullptr;
+                uint32_t masks[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                if (DUMP && args.dump_img) {
+                    // the previous step's image store must have finished reading this tile's buffer
+                    if (row == 0) tma_store_wait_read();
+                    named_bar_sync(1 + tile, kTileRows);
+                }
                 if ((epi & (EPI_ALPHA | EPI_FINAL)) == 0) {
                     // hidden layer: (ReLU) -> bf16 -> A operand of the next layer
-                    if (epi & EPI_RELU) epilogue_store_layer<true, DUMP>(tmem_row, main_base, row, n_chunks, gp);
-                    else epilogue_store_layer<false, DUMP>(tmem_row, main_base, row, n_chunks, gp);
+                    if (epi & EPI_RELU) epilogue_store_layer<true, DUMP>(tmem_row, main_base, row, n_chunks, gp, masks);
+                    else epilogue_store_layer<false, DUMP>(tmem_row, main_base, row, n_chunks, gp, masks);
                 } else {
                     // layers that also feed an fp32 head (density after the trunk, colour at the end)
                     for (int j = 0; j < n_chunks; ++j) {
@@ -462,12 +456,19 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                             }
                         }
                         if (!(epi & EPI_FINAL) || DUMP) {
+                            uint32_t mj = 0;
 #pragma unroll
                             for (int c = 0; c < 4; ++c) {
-                                const uint32_t w0 = pack_bf16(f[8 * c], f[8 * c + 1]), w1 = pack_bf16(f[8 * c + 2], f[8 * c + 3]),
-                                               w2 = pack_bf16(f[8 * c + 4], f[8 * c + 5]), w3 = pack_bf16(f[8 * c + 6], f[8 * c + 7]);
-                                if (!(epi & EPI_FINAL)) st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w0, w1, w2, w3);
-                                if (DUMP && gp) st_global_v4(gp + j * 4 + c, w0, w1, w2, w3);
+                                uint32_t w[4] = {pack_bf16(f[8 * c], f[8 * c + 1]), pack_bf16(f[8 * c + 2], f[8 * c + 3]),
+                                                 pack_bf16(f[8 * c + 4], f[8 * c + 5]), pack_bf16(f[8 * c + 6], f[8 * c + 7])};
+                                // (the last layer's output only enters shared memory to be dumped as an image)
+                                if (!(epi & EPI_FINAL) || DUMP) st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
+                                if (DUMP && gp) st_global_v4(gp + j * 4 + c, w[0], w[1], w[2], w[3]);
+                                if (DUMP) mj |= nonzero_bits4(w) << (8 * c);
+                            }
+                            if (DUMP) {
+#pragma unroll
+                                for (int q = 0; q < 8; ++q) if (q == j) masks[q] = mj;
                             }
                         }
                     }
@@ -500,6 +501,20 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     if (DUMP && dp)
                         for (int q = dir_chunks(a) + (dir_chunks(a) & 1); q < kEncCols / 8; ++q) st_global_v4(dp + q, 0u, 0u, 0u, 0u);
                 }
+                if (DUMP && args.dump_img) {
+                    // relu sign bits (for the backward's masks) and the tile image of this step's stored output
+                    const int64_t tile_g = (b * CTAS + rank) * kTilesPerCta + tile;
+                    uint4* mp = args.dump_masks + (((int64_t)st * args.n_tiles + tile_g) * kTileRows + row) * 2;
+                    st_global_v4(mp, masks[0], masks[1], masks[2], masks[3]);
+                    st_global_v4(mp + 1, masks[4], masks[5], masks[6], masks[7]);
+                    fence_proxy_async_smem();
+                    named_bar_sync(1 + tile, kTileRows);
+                    if (row == 0) {
+                        tma_bulk_s2g(args.dump_img + ((int64_t)st * args.n_tiles + tile_g) * (int64_t)kMainBytes, main_base,
+                                     (uint32_t)step.n_out * kTileRows * 2);
+                        tma_store_commit();
+                    }
+                }
                 if (epi & EPI_FINAL) {
                     if (valid) {
                         const float* brgb = w_rgb + 384;
@@ -517,6 +532,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         }
     }
 
+    if (DUMP) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // image stores fully written
     tc_fence_before();
     __syncthreads();
     if (CTAS == 2) cluster_sync_all();          // no CTA leaves while its peer may still signal it
@@ -525,6 +541,19 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         if (CTAS == 2) tmem_dealloc2(tmem_base, 512);
         else tmem_dealloc(tmem_base, 512);
     }
+}
+
+// tile images -> row-major (test / host-side helper)
+__global__ void untile_kernel(const uint8_t* __restrict__ img, int64_t n_rows, int cols, uint4* __restrict__ out) {
+    const int chunks_per_row = cols / 8;
+    const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n_rows * chunks_per_row) return;
+    const int64_t r = idx / chunks_per_row;
+    const int q = (int)(idx % chunks_per_row);
+    const int64_t tile = r / kTileRows;
+    const int row = (int)(r % kTileRows);
+    const uint32_t off = (uint32_t)(q >> 2) * kBlockBytes + (uint32_t)row * 64 + (uint32_t)(((q & 3) ^ ((row >> 1) & 3)) << 4);
+    out[idx] = *reinterpret_cast<const uint4*>(img + tile * (int64_t)kMainBytes + off);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -705,8 +734,14 @@ NTX_API int ntx_mlp_pack_weights(const ntx_mlp_t* mlp, const float* master, void
     return NTX_OK;
 }
 
+// 128-row tiles the training kernels touch for n_rows rows (whole 512-row CTA-pair batches)
+NTX_API int64_t ntx_mlp_train_tiles(int64_t n_rows) {
+    return ((n_rows + 511) / 512) * 4;
+}
+
 static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
-                          void* enc_pos, void* enc_dir, void* acts, bool dump, void* stream) {
+                          void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks, int64_t n_tiles,
+                          bool dump, void* stream) {
     NTX_REQUIRE(mlp && packed && in, "mlp_forward: null pointer");
     NTX_REQUIRE(in->n_rows >= 0, "mlp_forward: negative row count");
     if (in->n_rows == 0) return NTX_OK;
@@ -718,9 +753,14 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     NTX_REQUIRE(in->blur_idx < np, "mlp_forward: blur_idx %d out of range", in->blur_idx);
     NTX_REQUIRE((((uintptr_t)packed | (uintptr_t)rgbs) & 15) == 0, "mlp_forward: packed / rgbs must be 16-byte aligned");
     if (dump) {
-        NTX_REQUIRE(enc_pos && enc_dir && acts, "mlp_forward_train: null save buffer");
-        NTX_REQUIRE((((uintptr_t)enc_pos | (uintptr_t)enc_dir | (uintptr_t)acts) & 15) == 0,
+        NTX_REQUIRE(enc_pos && enc_dir && (acts || acts_img), "mlp_forward_train: null save buffer");
+        NTX_REQUIRE((((uintptr_t)enc_pos | (uintptr_t)enc_dir | (uintptr_t)acts | (uintptr_t)acts_img | (uintptr_t)masks) & 15) == 0,
                     "mlp_forward_train: save buffers must be 16-byte aligned");
+        if (acts_img) {
+            NTX_REQUIRE(masks, "mlp_forward_train: tile images need the mask buffer too");
+            NTX_REQUIRE(n_tiles >= ntx_mlp_train_tiles(in->n_rows), "mlp_forward_train: %lld tiles given, %lld needed",
+                        (long long)n_tiles, (long long)ntx_mlp_train_tiles(in->n_rows));
+        }
     }
     // NTX_MLP_CTAS=1 selects the single-CTA kernel (cta_group::1); default is CTA pairs (cta_group::2)
     static const int ctas = [] { const char* e = getenv("NTX_MLP_CTAS"); return (e && e[0] == '1') ? 1 : 2; }();
@@ -741,6 +781,9 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     ka.dump_enc_pos = (uint4*)enc_pos;
     ka.dump_enc_dir = (uint4*)enc_dir;
     ka.dump_acts = (uint4*)acts;
+    ka.dump_img = (uint8_t*)acts_img;
+    ka.dump_masks = (uint4*)masks;
+    ka.n_tiles = n_tiles;
     const int64_t rows_per_unit = (int64_t)kRowsPerCta * ctas;
     const int64_t n_units = (in->n_rows + rows_per_unit - 1) / rows_per_unit;
     const int64_t max_units = ntx_sm_count() / ctas;
@@ -761,12 +804,23 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
 
 NTX_API int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
                             void* stream) {
-    return launch_forward(mlp, packed, in, rgbs, nullptr, nullptr, nullptr, false, stream);
+    return launch_forward(mlp, packed, in, rgbs, nullptr, nullptr, nullptr, nullptr, nullptr, 0, false, stream);
 }
 
 NTX_API int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
-                                  void* enc_pos, void* enc_dir, void* acts, void* stream) {
-    return launch_forward(mlp, packed, in, rgbs, enc_pos, enc_dir, acts, true, stream);
+                                  void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks,
+                                  int64_t n_tiles, void* stream) {
+    return launch_forward(mlp, packed, in, rgbs, enc_pos, enc_dir, acts, acts_img, masks, n_tiles, true, stream);
+}
+
+NTX_API int ntx_untile(const void* img, int64_t n_rows, int cols, void* out, void* stream) {
+    NTX_REQUIRE(n_rows >= 0 && cols >= 32 && cols <= 256 && cols % 32 == 0, "untile: bad shape");
+    if (n_rows == 0) return NTX_OK;
+    NTX_REQUIRE(img && out, "untile: null pointer");
+    const int64_t total = n_rows * (cols / 8);
+    untile_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const uint8_t*)img, n_rows, cols, (uint4*)out);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
 }
 
 NTX_API int ntx_mlp_num_steps(const ntx_mlp_t* mlp) { return mlp ? mlp->prog.n_steps : -1; }

@@ -1,0 +1,641 @@
+// K1-bwd — backward of the fused MLP on the operands saved by ntx_mlp_forward_train.
+//
+//   mlp_dgrad_kernel  the data-gradient chain, fused like the forward: for every 128-row tile the
+//                     gradient w.r.t. each layer's pre-activation output is produced layer by layer
+//                     in reverse, dY_{s-1} = relu'(act_{s-1}) * (dY_s W_s^T [+ d sigma w_alpha^T]),
+//                     with tcgen05.mma (bf16 in, fp32 accumulate in TMEM), gradients staying in
+//                     shared memory between layers and each dY_s leaving once, as a tile image,
+//                     through a bulk store.  Same roles / CTA-pair protocol as the forward kernel.
+//   mlp_wgrad_kernel  dW_s = X_s^T dY_s and db_s = 1^T dY_s over all rows.  Both operands are the saved
+//                     tile images read as MN-major UMMA operands (K = sample rows): no transposes, no
+//                     re-layout.  One CTA per SM accumulates a full [256 x 256] fp32 dW in TMEM (all
+//                     512 columns) over its share of the tiles, then adds it to the flat gradient
+//                     buffer with red.global.add; idle warps sum dY columns for the bias gradient.
+//
+// No gradient flows into the encodings (nothing trainable upstream; network/renderer.py:129).
+// Reference: the tf.GradientTape of network/train.py:62-66 over network/model.py:104-123.
+#include <stdlib.h>
+
+#include "ntx_common.cuh"
+#include "ntx_mlp.cuh"
+#include "ntx_mlp_dev.cuh"
+#include "ntx_umma.cuh"
+
+namespace {
+
+using namespace umma;
+using namespace ntxmlp;
+
+constexpr int kThreadsBwd = 320;
+constexpr int kMaxBwdSteps = kMaxSteps;
+
+struct BwdStep {
+    int32_t fwd_step;      // forward step s whose weights are applied: dY_{s-1} = f(dY_s W_s^T)
+    int32_t n_k;           // K-slices of 32 = n_out(s) / 32
+    int32_t relu_prev;     // step s-1 ended in ReLU (mask its gradient)
+    int32_t add_alpha;     // step s-1 is the last trunk layer: the density head's gradient joins here
+    uint32_t slice_off;    // byte offset of this step's first slice in the packed transposed weights
+    int32_t pad_[3];
+};
+
+struct BwdProgram {
+    int32_t n_bwd;         // MMA steps of the chain = n_steps - 1
+    int32_t n_steps;
+    int32_t last_n_out;    // width of the last forward step (128)
+    int32_t pad_;
+    BwdStep steps[kMaxBwdSteps];
+};
+
+constexpr uint32_t kBwdHeadFloats = 256 + 3 * 128;      // w_alpha[256], W_rgb as [3][128]
+constexpr uint32_t kBwdHeadBytes = 4096;
+
+// shared-memory map of the data-gradient kernel
+constexpr uint32_t kDgOffStages = kTilesPerCta * kMainBytes;                  // 131072
+constexpr uint32_t kDgOffHeads = kDgOffStages + kStages * kStageBytes;        // +49152
+constexpr uint32_t kDgOffBars = kDgOffHeads + kBwdHeadFloats * 4;
+constexpr uint32_t kDgNumBars = 2 * kStages + 2 * kTilesPerCta;
+constexpr uint32_t kDgOffTmemSlot = kDgOffBars + kDgNumBars * 8;
+constexpr uint32_t kDgSmemBytes = kDgOffTmemSlot + 16;
+
+struct DgradArgs {
+    const uint8_t* packed_t;     // head block + transposed weight slices
+    const float* d_rgbs;         // [N,4]
+    const uint4* masks;          // [n_steps][n_tiles*128][2 x uint4]
+    uint8_t* dy_img;             // [n_steps][n_tiles][64 KB] out
+    int64_t n_rows, n_tiles;
+    int32_t depth;
+};
+
+template <int CTAS>
+__global__ void __launch_bounds__(kThreadsBwd, 1)
+mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant__ DgradArgs args) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    if ((sbase & 1023u) != 0) __trap();
+    constexpr uint32_t NSTAGE = kStages;
+    constexpr uint32_t STAGE_BYTES = kStageBytes;
+    constexpr int SPS = CTAS;
+    const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar_full = sbase + kDgOffBars;
+    const uint32_t bar_empty = bar_full + 8 * kStages;
+    const uint32_t bar_act = bar_empty + 8 * kStages;
+    const uint32_t bar_acc = bar_act + 8 * kTilesPerCta;
+    float* heads = reinterpret_cast<float*>(smem + kDgOffHeads);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kDgOffTmemSlot);
+
+    const int64_t n_rows = args.n_rows;
+    const int64_t n_batches = (n_rows + kRowsPerCta * CTAS - 1) / (kRowsPerCta * CTAS);
+    const int64_t batch0 = blockIdx.x / CTAS, batch_stride = gridDim.x / CTAS;
+
+    if (threadIdx.x == 0) {
+        for (uint32_t i = 0; i < NSTAGE; ++i) {
+            mbar_init(bar_full + 8 * i, (CTAS == 2 && rank == 0) ? 2 : 1);
+            mbar_init(bar_empty + 8 * i, 1);
+        }
+        for (int t = 0; t < kTilesPerCta; ++t) {
+            mbar_init(bar_act + 8 * t, 4 * CTAS);
+            mbar_init(bar_acc + 8 * t, 1);
+        }
+        fence_mbar_init();
+    }
+    if (warp == 1) {
+        if (CTAS == 2) { tmem_alloc2(sbase + kDgOffTmemSlot, 512); tmem_relinquish2(); }
+        else { tmem_alloc(sbase + kDgOffTmemSlot, 512); tmem_relinquish(); }
+    }
+    for (int i = threadIdx.x; i < (int)kBwdHeadFloats; i += kThreadsBwd)
+        heads[i] = reinterpret_cast<const float*>(args.packed_t)[i];
+    tc_fence_before();
+    __syncthreads();
+    if (CTAS == 2) cluster_sync_all();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===================================================================== weight producer
+        if (lane == 0) {
+            uint32_t stage = 0, parity = 1;
+            const uint32_t bytes = kStageBytes / CTAS;                         // this CTA's rows of one [256 x 32] slice
+            for (int64_t b = batch0; b < n_batches; b += batch_stride) {
+                for (int bs = 0; bs < prog.n_bwd; ++bs) {
+                    const int n_k = prog.steps[bs].n_k;
+                    const uint8_t* src0 = args.packed_t + prog.steps[bs].slice_off + rank * bytes;
+                    for (int t = 0; t < kTilesPerCta; ++t) {
+                        const uint8_t* src = src0;
+                        for (int left = n_k; left > 0;) {
+                            const int n = left < SPS ? left : SPS;
+                            mbar_wait(bar_empty + 8 * stage, parity);
+                            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes * n);
+                            for (int j = 0; j < n; ++j, src += kStageBytes)
+                                tma_bulk_g2s(sbase + kDgOffStages + stage * STAGE_BYTES + j * bytes, src, bytes,
+                                             bar_full + 8 * stage);
+                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
+                            left -= n;
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (CTAS == 2 && rank != 0) {
+            if (lane == 0) {                                                    // relay (see forward kernel)
+                uint32_t stage = 0, parity = 0;
+                const uint32_t remote_full = mapa_shared(bar_full, 0);
+                for (int64_t b = batch0; b < n_batches; b += batch_stride)
+                    for (int bs = 0; bs < prog.n_bwd; ++bs) {
+                        const int n_st = ((prog.steps[bs].n_k + SPS - 1) / SPS) * kTilesPerCta;
+                        for (int s = 0; s < n_st; ++s) {
+                            mbar_wait(bar_full + 8 * stage, parity);
+                            mbar_arrive_remote(remote_full + 8 * stage);
+                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
+                        }
+                    }
+            }
+        } else {
+            // ================================================================= MMA issuer
+            uint32_t stage = 0, parity = 0, act_phase0 = 0, act_phase1 = 0;
+            uint32_t b16 = (sbase + kDgOffStages) >> 4;
+            uint32_t full_bar = bar_full, empty_bar = bar_empty;
+            const uint32_t idesc = idesc_bf16_f32(kTileRows * CTAS, kWidth);
+            const uint32_t b_slice16 = (kStageBytes / CTAS) >> 4;
+            for (int64_t b = batch0; b < n_batches; b += batch_stride) {
+                for (int bs = 0; bs < prog.n_bwd; ++bs) {
+                    const int n_k = prog.steps[bs].n_k;
+#pragma unroll
+                    for (int t = 0; t < kTilesPerCta; ++t) {
+                        if (t == 0) { mbar_wait(bar_act, act_phase0); act_phase0 ^= 1; }
+                        else { mbar_wait(bar_act + 8, act_phase1); act_phase1 ^= 1; }
+                        tc_fence_after();
+                        const uint32_t d_tmem = tmem_base + t * kWidth;
+                        const uint32_t a16_tile = (sbase + t * kMainBytes) >> 4;
+                        for (int i = 0; i < n_k; i += SPS) {
+                            const int n = n_k - i < SPS ? n_k - i : SPS;
+                            mbar_wait(full_bar, parity);
+                            tc_fence_after();
+                            const uint32_t bb = b16, eb = empty_bar;
+                            if (++stage == NSTAGE) {
+                                stage = 0; parity ^= 1; b16 = (sbase + kDgOffStages) >> 4; full_bar = bar_full; empty_bar = bar_empty;
+                            } else {
+                                b16 += STAGE_BYTES >> 4; full_bar += 8; empty_bar += 8;
+                            }
+                            if (elect_one_sync()) {
+#pragma unroll
+                                for (int j = 0; j < SPS; ++j) {
+                                    if (j < n) {
+                                        const uint32_t aj = a16_tile + (i + j) * (kBlockBytes >> 4), bj = bb + j * b_slice16;
+                                        const uint32_t acc0 = (i + j) > 0 ? 1u : 0u;
+                                        if (CTAS == 2) {
+                                            mma_bf16_ss_2cta(d_tmem, desc_sw64(aj), desc_sw64(bj), idesc, acc0);
+                                            mma_bf16_ss_2cta(d_tmem, desc_sw64(aj + 2), desc_sw64(bj + 2), idesc, 1u);
+                                        } else {
+                                            mma_bf16_ss(d_tmem, desc_sw64(aj), desc_sw64(bj), idesc, acc0);
+                                            mma_bf16_ss(d_tmem, desc_sw64(aj + 2), desc_sw64(bj + 2), idesc, 1u);
+                                        }
+                                    }
+                                }
+                                if (CTAS == 2) mma_commit_2cta(eb); else mma_commit(eb);
+                            }
+                            __syncwarp();
+                        }
+                        if (elect_one_sync()) {
+                            if (CTAS == 2) mma_commit_2cta(bar_acc + 8 * t); else mma_commit(bar_acc + 8 * t);
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+    } else {
+        // ===================================================================== epilogue warpgroups
+        const int ew = warp - 2;
+        const int tile = ew >> 2;
+        const int quarter = warp & 3;
+        const int row = quarter * 32 + lane;
+        const uint32_t main_base = sbase + tile * kMainBytes;
+        const uint32_t tmem_row = tmem_base + ((uint32_t)(quarter * 32) << 16) + tile * kWidth;
+        const uint32_t my_act = bar_act + 8 * tile, my_acc = bar_acc + 8 * tile;
+        const float* w_alpha = heads;              // [256]
+        const float* w_rgb = heads + 256;          // [3][128]: w_rgb[j*128 + c] = W_rgb[c][j]
+        uint32_t acc_phase = 0;
+        const uint32_t act_remote = (CTAS == 2 && rank != 0) ? mapa_shared(my_act, 0) : 0u;
+        auto arrive_act = [&]() {
+            if (CTAS == 2 && rank != 0) mbar_arrive_remote(act_remote);
+            else mbar_arrive(my_act);
+        };
+        const int last = prog.n_steps - 1;
+
+        for (int64_t b = batch0; b < n_batches; b += batch_stride) {
+            const int64_t tile_g = (b * CTAS + rank) * kTilesPerCta + tile;
+            const int64_t grow = tile_g * kTileRows + row;
+            const bool valid = grow < n_rows;
+            float4 dr = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (valid) dr = __ldg(reinterpret_cast<const float4*>(args.d_rgbs) + grow);
+            auto mask_ptr = [&](int st) { return args.masks + (((int64_t)st * args.n_tiles + tile_g) * kTileRows + row) * 2; };
+            auto store_image = [&](int st, uint32_t bytes) {
+                fence_proxy_async_smem();
+                named_bar_sync(1 + tile, kTileRows);
+                if (row == 0) {
+                    tma_bulk_s2g(args.dy_img + ((int64_t)st * args.n_tiles + tile_g) * (int64_t)kMainBytes, main_base, bytes);
+                    tma_store_commit();
+                }
+            };
+            // ---- head of the chain: d(colour half output) = relu' * (d rgb W_rgb^T)   (model.py:122-123)
+            {
+                if (row == 0) tma_store_wait_read();
+                named_bar_sync(1 + tile, kTileRows);
+                const uint4 m4 = __ldg(mask_ptr(last));
+                const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t w[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int col = j * 32 + c * 8 + 2 * e;
+                            float v0 = dr.x * w_rgb[col] + dr.y * w_rgb[128 + col] + dr.z * w_rgb[256 + col];
+                            float v1 = dr.x * w_rgb[col + 1] + dr.y * w_rgb[128 + col + 1] + dr.z * w_rgb[256 + col + 1];
+                            if (!((mw[j] >> (c * 8 + 2 * e)) & 1u)) v0 = 0.0f;
+                            if (!((mw[j] >> (c * 8 + 2 * e + 1)) & 1u)) v1 = 0.0f;
+                            w[e] = pack_bf16(v0, v1);
+                        }
+                        st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
+                    }
+                }
+                store_image(last, (uint32_t)prog.last_n_out * kTileRows * 2);
+                fence_proxy_async_smem();
+                __syncwarp();
+                if (lane == 0) arrive_act();
+            }
+            // ---- the chain
+            for (int bs = 0; bs < prog.n_bwd; ++bs) {
+                const int st_prev = prog.steps[bs].fwd_step - 1;           // gradient produced for this forward step
+                const bool relu_prev = prog.steps[bs].relu_prev != 0, add_alpha = prog.steps[bs].add_alpha != 0;
+                uint32_t mw[8] = {~0u, ~0u, ~0u, ~0u, ~0u, ~0u, ~0u, ~0u};
+                if (relu_prev) {
+                    const uint4 a = __ldg(mask_ptr(st_prev)), c4 = __ldg(mask_ptr(st_prev) + 1);
+                    mw[0] = a.x; mw[1] = a.y; mw[2] = a.z; mw[3] = a.w; mw[4] = c4.x; mw[5] = c4.y; mw[6] = c4.z; mw[7] = c4.w;
+                }
+                mbar_wait(my_acc, acc_phase);
+                acc_phase ^= 1;
+                tc_fence_after();
+                if (row == 0) tma_store_wait_read();        // the previous image store has read this buffer
+                named_bar_sync(1 + tile, kTileRows);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    uint32_t v[32];
+                    tmem_ld_32x32b_x32(tmem_row + j * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) {
+                        uint32_t w[4];
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const int cc = c * 8 + 2 * e;
+                            float v0 = __uint_as_float(v[cc]), v1 = __uint_as_float(v[cc + 1]);
+                            if (add_alpha) {                                   // model.py:111: sigma = h w_alpha + b
+                                v0 += dr.w * w_alpha[j * 32 + cc];
+                                v1 += dr.w * w_alpha[j * 32 + cc + 1];
+                            }
+                            if (!((mw[j] >> cc) & 1u)) v0 = 0.0f;
+                            if (!((mw[j] >> (cc + 1)) & 1u)) v1 = 0.0f;
+                            w[e] = pack_bf16(v0, v1);
+                        }
+                        st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
+                    }
+                }
+                store_image(st_prev, kMainBytes);
+                if (bs + 1 < prog.n_bwd) {
+                    fence_proxy_async_smem();
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) arrive_act();
+                } else {
+                    tc_fence_before();
+                }
+            }
+        }
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (CTAS == 2) cluster_sync_all();
+    if (warp == 1) {
+        __syncwarp();
+        if (CTAS == 2) tmem_dealloc2(tmem_base, 512); else tmem_dealloc(tmem_base, 512);
+    }
+}
+
+// transposed weights for the chain: B[n = input feature (main rows), k = output feature] = W[main_row0 + n][k]
+__global__ void mlp_pack_bwd_kernel(const __grid_constant__ Program prog, const __grid_constant__ BwdProgram bprog,
+                                    const float* __restrict__ master, uint8_t* __restrict__ packed_t) {
+    const int bs = blockIdx.y;
+    if (bs == bprog.n_bwd) {             // head block
+        if (blockIdx.x != 0) return;
+        float* h = reinterpret_cast<float*>(packed_t);
+        const Layer& la = prog.layers[prog.alpha_layer];
+        const Layer& lr = prog.layers[prog.rgb_layer];
+        for (int i = threadIdx.x; i < (int)(kBwdHeadBytes / 4); i += blockDim.x) {
+            float v = 0.0f;
+            if (i < 256) v = master[la.w_off + i];
+            else if (i < 256 + 384) { const int j = (i - 256) / 128, c = (i - 256) % 128; v = master[lr.w_off + c * 3 + j]; }
+            h[i] = v;
+        }
+        return;
+    }
+    const BwdStep& B = bprog.steps[bs];
+    const int ks = blockIdx.x;
+    if (ks >= B.n_k) return;
+    const Step& step = prog.steps[B.fwd_step];
+    const Layer& L = prog.layers[step.layer];
+    uint8_t* dst = packed_t + B.slice_off + (size_t)ks * kStageBytes;
+    for (int idx = threadIdx.x; idx < 256 * 32; idx += blockDim.x) {
+        const int n = idx >> 5, kk = idx & 31;
+        const float v = master[L.w_off + (int64_t)(step.main_row0 + n) * L.fan_out + ks * 32 + kk];
+        *reinterpret_cast<__nv_bfloat16*>(dst + sw64_offset(n, kk, 256)) = __float2bfloat16(v);
+    }
+}
+
+int64_t build_bwd_program(const ntx_mlp* m, BwdProgram* bp) {
+    memset(bp, 0, sizeof(*bp));
+    const Program& p = m->prog;
+    bp->n_steps = p.n_steps;
+    bp->n_bwd = p.n_steps - 1;
+    bp->last_n_out = p.steps[p.n_steps - 1].n_out;
+    uint32_t off = kBwdHeadBytes;
+    for (int bs = 0; bs < bp->n_bwd; ++bs) {
+        const int st = p.n_steps - 1 - bs;
+        BwdStep& B = bp->steps[bs];
+        B.fwd_step = st;
+        B.n_k = p.steps[st].n_out / 32;
+        B.relu_prev = (p.steps[st - 1].epi & EPI_RELU) ? 1 : 0;
+        B.add_alpha = (st - 1 == m->cfg.depth - 1) ? 1 : 0;
+        B.slice_off = off;
+        off += (uint32_t)B.n_k * kStageBytes;
+    }
+    return off;
+}
+
+// ----------------------------------------------------------------------------------------------
+// weight gradient
+// ----------------------------------------------------------------------------------------------
+constexpr int kWgThreads = 192;                      // warp 0 producer, warp 1 MMA issuer, warps 2-5 bias sums + flush
+constexpr int kWgStages = 3;
+constexpr uint32_t kWgHalfRows = 64;                 // K rows per stage (half a tile)
+constexpr uint32_t kWgOperandBytes = 8 * kWgHalfRows * 64;      // 32 KB: 8 blocks of [64 rows x 64 B]
+constexpr uint32_t kWgStageBytes = 2 * kWgOperandBytes;         // X half + dY half
+constexpr uint32_t kWgOffBias = kWgStages * kWgStageBytes;      // 196608: [4][256] fp32 scratch for the bias reduction
+constexpr uint32_t kWgOffBars = kWgOffBias + 4 * 256 * 4;
+constexpr uint32_t kWgOffTmemSlot = kWgOffBars + (2 * kWgStages + 2) * 8;
+constexpr uint32_t kWgSmemBytes = kWgOffTmemSlot + 16;
+static_assert(kWgSmemBytes <= 232448, "weight-gradient kernel exceeds shared memory");
+
+struct WgradArgs {
+    const uint8_t* acts_img;     // [n_steps][n_tiles][64 KB]   X_s = acts_img[s-1]
+    const uint8_t* dy_img;       // [n_steps][n_tiles][64 KB]
+    float* grad;                 // flat fp32 gradient buffer (accumulated into)
+    int64_t n_tiles_alloc;       // tiles per step in the image buffers
+    int64_t n_tiles;             // tiles that hold real rows
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ WgradArgs args) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    const uint32_t sbase = smem_u32(smem);
+    if ((sbase & 1023u) != 0) __trap();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t bar_full = sbase + kWgOffBars;               // [3]
+    const uint32_t bar_empty = bar_full + 8 * kWgStages;        // [3]  1 commit + 4 bias warps
+    const uint32_t bar_acc = bar_empty + 8 * kWgStages;         // accumulators of a step complete
+    const uint32_t bar_free = bar_acc + 8;                      // accumulators flushed (4 warps)
+    float* bias_scratch = reinterpret_cast<float*>(smem + kWgOffBias);
+    volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kWgOffTmemSlot);
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < kWgStages; ++i) {
+            mbar_init(bar_full + 8 * i, 1);
+            mbar_init(bar_empty + 8 * i, 5);
+        }
+        mbar_init(bar_acc, 1);
+        mbar_init(bar_free, 4);
+        fence_mbar_init();
+    }
+    if (warp == 1) { tmem_alloc(sbase + kWgOffTmemSlot, 512); tmem_relinquish(); }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    // my tiles: blockIdx.x, += gridDim.x; each tile = 2 stages (rows 0..63, 64..127)
+    const int64_t my_tiles = args.n_tiles > blockIdx.x ? (args.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t stage = 0, parity = 1;
+            for (int st = 1; st < prog.n_steps; ++st) {
+                const int n_blk = prog.steps[st].n_out / 32;           // dY blocks (8, or 4 for the last step)
+                const uint8_t* xs = args.acts_img + (int64_t)(st - 1) * args.n_tiles_alloc * kMainBytes;
+                const uint8_t* ds = args.dy_img + (int64_t)st * args.n_tiles_alloc * kMainBytes;
+                for (int64_t i = 0; i < my_tiles; ++i) {
+                    const int64_t tile = blockIdx.x + i * gridDim.x;
+                    for (int half = 0; half < 2; ++half) {
+                        mbar_wait(bar_empty + 8 * stage, parity);
+                        mbar_arrive_expect_tx(bar_full + 8 * stage, (8 + n_blk) * kWgHalfRows * 64);
+                        const uint32_t dst = sbase + stage * kWgStageBytes;
+                        const uint8_t* xt = xs + tile * (int64_t)kMainBytes + half * (kWgHalfRows * 64);
+                        const uint8_t* dt = ds + tile * (int64_t)kMainBytes + half * (kWgHalfRows * 64);
+                        for (int blk = 0; blk < 8; ++blk)
+                            tma_bulk_g2s(dst + blk * (kWgHalfRows * 64), xt + blk * kBlockBytes, kWgHalfRows * 64, bar_full + 8 * stage);
+                        for (int blk = 0; blk < n_blk; ++blk)
+                            tma_bulk_g2s(dst + kWgOperandBytes + blk * (kWgHalfRows * 64), dt + blk * kBlockBytes, kWgHalfRows * 64,
+                                         bar_full + 8 * stage);
+                        if (++stage == kWgStages) { stage = 0; parity ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        uint32_t stage = 0, parity = 0, free_phase = 0;
+        const uint32_t lbo = kWgHalfRows * 64;                           // next 32 MN elements: next block
+        for (int st = 1; st < prog.n_steps; ++st) {
+            const uint32_t idesc = idesc_bf16_f32_mn(128, prog.steps[st].n_out);
+            if (st > 1) { mbar_wait(bar_free, free_phase); free_phase ^= 1; tc_fence_after(); }
+            uint32_t accumulate = 0;
+            for (int64_t i = 0; i < my_tiles * 2; ++i) {
+                mbar_wait(bar_full + 8 * stage, parity);
+                tc_fence_after();
+                const uint32_t xa = sbase + stage * kWgStageBytes, da = xa + kWgOperandBytes;
+                if (elect_one_sync()) {
+#pragma unroll
+                    for (int ks = 0; ks < 4; ++ks) {
+                        const uint64_t bd = smem_desc(da + ks * 1024, lbo, 512, LAYOUT_SW64);
+                        mma_bf16_ss(tmem_base, smem_desc(xa + ks * 1024, lbo, 512, LAYOUT_SW64), bd, idesc, accumulate);
+                        mma_bf16_ss(tmem_base + 256, smem_desc(xa + 4 * lbo + ks * 1024, lbo, 512, LAYOUT_SW64), bd, idesc, accumulate);
+                        accumulate = 1;
+                    }
+                    mma_commit(bar_empty + 8 * stage);
+                }
+                __syncwarp();
+                accumulate = 1;
+                if (++stage == kWgStages) { stage = 0; parity ^= 1; }
+            }
+            if (elect_one_sync()) mma_commit(bar_acc);
+            __syncwarp();
+        }
+    } else {
+        // bias sums from the staged dY halves, then flush of the accumulators
+        const int tid = threadIdx.x - 64;                 // 0..127
+        const int quarter = warp & 3;                      // TMEM lane quarter of this warp
+        const int cc = tid & 31, rg = tid >> 5;            // chunk column (8 cols), row group (16 rows)
+        uint32_t stage = 0, parity = 0, acc_phase = 0;
+        for (int st = 1; st < prog.n_steps; ++st) {
+            const Step& step = prog.steps[st];
+            const Layer& L = prog.layers[step.layer];
+            const int n_out = step.n_out;
+            float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            const bool has_col = cc * 8 < n_out;
+            for (int64_t i = 0; i < my_tiles * 2; ++i) {
+                mbar_wait(bar_full + 8 * stage, parity);
+                if (has_col) {
+                    const uint8_t* dy = smem + stage * kWgStageBytes + kWgOperandBytes + (cc >> 2) * (kWgHalfRows * 64);
+#pragma unroll 4
+                    for (int r = rg * 16; r < rg * 16 + 16; ++r) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(dy + r * 64 + (((cc & 3) ^ ((r >> 1) & 3)) << 4));
+                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            bsum[2 * e] += __uint_as_float(w[e] << 16);
+                            bsum[2 * e + 1] += __uint_as_float(w[e] & 0xFFFF0000u);
+                        }
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_empty + 8 * stage);
+                if (++stage == kWgStages) { stage = 0; parity ^= 1; }
+            }
+            // bias gradient: reduce the 4 row groups through shared memory, one atomic per column per CTA
+#pragma unroll
+            for (int e = 0; e < 8; ++e) bias_scratch[rg * 256 + cc * 8 + e] = bsum[e];
+            named_bar_sync(1, 128);
+            for (int c = tid; c < n_out; c += 128) {
+                const float s = bias_scratch[c] + bias_scratch[256 + c] + bias_scratch[512 + c] + bias_scratch[768 + c];
+                if (my_tiles > 0) atomicAdd(args.grad + L.b_off + c, s);
+            }
+            named_bar_sync(1, 128);
+            // weight gradient: thread = input feature row m (D0) and m + 128 (D1)
+            mbar_wait(bar_acc, acc_phase);
+            acc_phase ^= 1;
+            tc_fence_after();
+            if (my_tiles > 0) {
+                const int m = quarter * 32 + lane;
+#pragma unroll
+                for (int mh = 0; mh < 2; ++mh) {
+                    float* grow_ptr = args.grad + L.w_off + (int64_t)(step.main_row0 + mh * 128 + m) * L.fan_out;
+                    for (int j = 0; j < n_out / 32; ++j) {
+                        uint32_t v[32];
+                        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + mh * 256 + j * 32, v);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) atomicAdd(grow_ptr + j * 32 + c, __uint_as_float(v[c]));
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_free);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
+}
+
+}  // namespace
+
+NTX_API int64_t ntx_mlp_packed_t_bytes(const ntx_mlp_t* mlp) {
+    if (!mlp) return -1;
+    BwdProgram bp;
+    return build_bwd_program(mlp, &bp);
+}
+
+NTX_API int ntx_mlp_pack_weights_t(const ntx_mlp_t* mlp, const float* master, void* packed_t, void* stream) {
+    NTX_REQUIRE(mlp && master && packed_t, "mlp_pack_weights_t: null pointer");
+    NTX_REQUIRE(((uintptr_t)packed_t & 15) == 0, "mlp_pack_weights_t: buffer must be 16-byte aligned");
+    BwdProgram bp;
+    build_bwd_program(mlp, &bp);
+    dim3 grid(8, bp.n_bwd + 1);
+    mlp_pack_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(mlp->prog, bp, master, (uint8_t*)packed_t);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
+                                  void* dy_img, int64_t n_rows, int64_t n_tiles, void* stream) {
+    NTX_REQUIRE(mlp && packed_t && d_rgbs && masks && dy_img, "mlp_backward_data: null pointer");
+    NTX_REQUIRE(n_rows >= 0 && n_tiles >= ((n_rows + 511) / 512) * 4, "mlp_backward_data: %lld tiles for %lld rows",
+                (long long)n_tiles, (long long)n_rows);
+    if (n_rows == 0) return NTX_OK;
+    NTX_REQUIRE((((uintptr_t)packed_t | (uintptr_t)d_rgbs | (uintptr_t)masks | (uintptr_t)dy_img) & 15) == 0,
+                "mlp_backward_data: buffers must be 16-byte aligned");
+    static const int ctas = [] { const char* e = getenv("NTX_MLP_CTAS"); return (e && e[0] == '1') ? 1 : 2; }();
+    using KernelFn = void (*)(const BwdProgram, const DgradArgs);
+    KernelFn fn = ctas == 2 ? mlp_dgrad_kernel<2> : mlp_dgrad_kernel<1>;
+    static bool attr_set[64][2] = {};
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && !attr_set[dev][ctas - 1]) {
+        NTX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDgSmemBytes));
+        attr_set[dev][ctas - 1] = true;
+    }
+    BwdProgram bp;
+    build_bwd_program(mlp, &bp);
+    DgradArgs a;
+    a.packed_t = (const uint8_t*)packed_t;
+    a.d_rgbs = d_rgbs;
+    a.masks = (const uint4*)masks;
+    a.dy_img = (uint8_t*)dy_img;
+    a.n_rows = n_rows;
+    a.n_tiles = n_tiles;
+    a.depth = mlp->cfg.depth;
+    const int64_t rows_per_unit = (int64_t)kRowsPerCta * ctas;
+    const int64_t n_units = (n_rows + rows_per_unit - 1) / rows_per_unit;
+    const int64_t max_units = ntx_sm_count() / ctas;
+    const int grid = (int)(n_units < max_units ? n_units : max_units) * ctas;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreadsBwd);
+    cfg.dynamicSmemBytes = kDgSmemBytes;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = ctas; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    NTX_CUDA(cudaLaunchKernelEx(&cfg, fn, bp, a));
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, float* grad,
+                                     int64_t n_rows, int64_t n_tiles, void* stream) {
+    NTX_REQUIRE(mlp && acts_img && dy_img && grad, "mlp_backward_weights: null pointer");
+    NTX_REQUIRE(n_rows >= 0 && n_tiles >= (n_rows + 127) / 128, "mlp_backward_weights: bad tile count");
+    if (n_rows == 0) return NTX_OK;
+    static bool attr_set[64] = {};
+    int dev = 0;
+    NTX_CUDA(cudaGetDevice(&dev));
+    if (dev < 64 && !attr_set[dev]) {
+        NTX_CUDA(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWgSmemBytes));
+        attr_set[dev] = true;
+    }
+    WgradArgs a;
+    a.acts_img = (const uint8_t*)acts_img;
+    a.dy_img = (const uint8_t*)dy_img;
+    a.grad = grad;
+    a.n_tiles_alloc = n_tiles;
+    a.n_tiles = (n_rows + 127) / 128;
+    const int64_t g = a.n_tiles < ntx_sm_count() ? a.n_tiles : ntx_sm_count();
+    mlp_wgrad_kernel<<<(unsigned)g, kWgThreads, kWgSmemBytes, (cudaStream_t)stream>>>(mlp->prog, a);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}

@@ -78,6 +78,18 @@ __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst_smem, const void* src_
                  ::"r"(dst_smem), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
 }
 
+// shared -> global bulk store (TMA store), tracked by bulk async-groups of the issuing thread
+__device__ __forceinline__ void tma_bulk_s2g(void* dst_gmem, uint32_t src_smem, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(src_smem), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// wait until the sources of all committed bulk stores of this thread have been read
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // ---------------------------------------------------------------- TMEM
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {   // whole warp
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols)
@@ -124,6 +136,12 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t saddr, uint32_t lbo, uint
 constexpr uint32_t kDescHiSw64 = (512u >> 4) | (1u << 14) | ((uint32_t)LAYOUT_SW64 << 29);
 __device__ __forceinline__ uint64_t desc_sw64(uint32_t addr16) {      // addr16 = shared address >> 4
     return ((uint64_t)kDescHiSw64 << 32) | (uint64_t)((addr16 & 0x3FFFu) | (1u << 16));
+}
+
+// same bits with both operands MN-major (A stored [K][M], B stored [K][N]): used by the weight-gradient GEMM
+__host__ __device__ constexpr uint32_t idesc_bf16_f32_mn(int M, int N) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(N >> 3) << 17) |
+           ((uint32_t)(M >> 4) << 24);
 }
 
 // kind::f16, A = B = bf16 (K-major), D = fp32, dense.

@@ -31,3 +31,18 @@ def test_umma_gemm_layouts(layout, N, K):
     ref = _bf16(A).double() @ _bf16(B).double().T
     err = (D.cpu().double() - ref).abs().max().item()
     assert err < 1e-3, f"layout {layout} N={N} K={K}: max abs err {err}"
+
+
+@pytest.mark.parametrize("N,K", [(256, 128), (256, 64), (128, 128)])
+def test_umma_gemm_mn_major_operands(N, K):
+    """Both operands MN-major (stored [K][M], [K][N]) on the forward kernel's SWIZZLE_64B row images:
+    the operand form of the weight-gradient GEMM dW = X^T dY."""
+    from nerf_tex_b200 import ops
+    g = torch.Generator(device="cpu").manual_seed(N + K)
+    At = torch.randn((K, 128), generator=g)
+    Bt = torch.randn((K, N), generator=g)
+    D = ops.selftest_umma_mn(At.cuda(), Bt.cuda())
+    torch.cuda.synchronize()
+    ref = _bf16(At).double().T @ _bf16(Bt).double()
+    err = (D.cpu().double() - ref).abs().max().item()
+    assert err < 1e-3, f"MN-major N={N} K={K}: max abs err {err}"

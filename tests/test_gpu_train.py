@@ -137,3 +137,63 @@ def test_trainer_adam_step_matches_oracle_and_learns():
     assert tr.step == 1 and abs(tr.current_lr() - 5e-4 * 0.1 ** (1 / 5e5)) < 1e-12
     losses = [l0] + [float(tr.train_step(data, z_rand=z_rand)) for _ in range(25)]
     assert losses[-1] < 0.8 * losses[0], losses                    # it learns on a fixed batch
+
+
+@pytest.mark.parametrize("n", [100, 512, 1300])
+def test_training_forward_saves_tile_images_and_masks(n):
+    """The bulk-stored tile images (the kernels' SWIZZLE_64B shared-memory operand layout) hold the
+    same activations as the row-major dump, and the mask words are their sign bits."""
+    from nerf_tex_b200.autograd import mlp_forward_train, untile
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    m = FusedNerfTexMLP(n_geo=1, n_app=6, seed=5)
+    g = torch.Generator(device="cuda").manual_seed(n)
+    pos = torch.rand((n, 3), device="cuda", generator=g) * 2 - 1
+    d = torch.randn((n, 3), device="cuda", generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    prm = torch.rand((n, 7), device="cuda", generator=g)
+    rgbs, (enc_pos, enc_dir, acts_img, masks, acts) = mlp_forward_train(m, n_rows=n, pos=pos, dir=d, params=prm,
+                                                                        rows_per_group=1, row_major_acts=True)
+    ref = m.forward_rows(n_rows=n, pos=pos, dir=d, params=prm, rows_per_group=1)
+    torch.cuda.synchronize()
+    assert torch.equal(rgbs, ref)                                   # the training kernel computes the same outputs
+    sched = m.schedule()
+    for st, s in enumerate(sched.steps):
+        cols = s["n_out"]
+        got = untile(acts_img[st], n, cols)
+        assert torch.equal(got, acts[st][:, :cols]), st
+        if not s["relu"]:
+            continue                                                # the linear feature layer needs no mask
+        bits = (masks[st][:n].view(n, 8, 1) >> torch.arange(32, device="cuda", dtype=torch.int32).view(1, 1, 32)) & 1
+        want = (acts[st][:, :cols] > 0).view(n, cols // 32, 32).to(torch.int32)
+        assert torch.equal(bits[:, :cols // 32], want), st
+
+
+@pytest.mark.parametrize("npar,n", [((1, 4), 300), ((1, 6), 1500), ((0, 0), 700)])
+def test_native_backward_kernels_match_library_gemm_backward(npar, n):
+    """ntx_mlp_backward_data / _weights against the layer-wise torch.mm backward on the same saved
+    operands: both use bf16 operands with fp32 accumulation, so they agree far tighter than either
+    agrees with float64."""
+    from nerf_tex_b200.autograd import mlp_backward, mlp_backward_native, mlp_forward_train, untile
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    cd = 0 if npar == (0, 0) else 1
+    m = FusedNerfTexMLP(n_geo=npar[0], n_app=npar[1], color_depth=cd, seed=9)
+    g = torch.Generator(device="cuda").manual_seed(n)
+    pos = torch.rand((n, 3), device="cuda", generator=g) * 2 - 1
+    d = torch.randn((n, 3), device="cuda", generator=g)
+    d = d / d.norm(dim=-1, keepdim=True)
+    prm = torch.rand((n, sum(npar)), device="cuda", generator=g) if sum(npar) else None
+    rgbs, saved = mlp_forward_train(m, n_rows=n, pos=pos, dir=d, params=prm, rows_per_group=1)
+    d_rgbs = torch.randn((n, 4), device="cuda", generator=g) * 0.01
+    want = mlp_backward(m, saved, d_rgbs)
+    got, dy_img = mlp_backward_native(m, saved, d_rgbs, return_dy=True)
+    torch.cuda.synchronize()
+    rel = float((got - want).norm() / want.norm())
+    assert rel < 5e-3, rel
+    for (wo, bo, fi, fo), name in zip(m.layers, m.layer_names):
+        for a, b_ in ((wo, wo + fi * fo), (bo, bo + fo)):
+            w, g_ = want[a:b_], got[a:b_]
+            if float(w.norm()) > 0:
+                assert float((g_ - w).norm() / w.norm()) < 2e-2, (name, float((g_ - w).norm() / w.norm()))
+    # rows beyond n inside the last tile carry exactly zero gradient
+    tail = untile(dy_img[0], saved[2].shape[1] * 128)[n:]
+    assert float(tail.abs().max()) == 0.0 if tail.numel() else True
