@@ -161,8 +161,9 @@ int ntx_mlp_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inpu
 
 /* Training forward: ntx_mlp_forward that also saves, in bf16, every tensor-core operand the
  * backward pass needs (the reference keeps them on the tf.GradientTape, network/train.py:62-64):
- *   enc_pos[N,96], enc_dir[N,96]  encoded inputs in the kernel's column order (see
- *                                 ntx_mlp_enc_columns), constant-1 bias column included;
+ *   enc_pos[n_tiles][32 KB],      encoded inputs as tile images of 4 blocks (128 columns) in the kernel's
+ *   enc_dir[n_tiles][32 KB]       column order (ntx_mlp_enc_columns), constant-1 bias column included;
+ *                                 blocks 0..2 are written, block 3 must be zero-filled by the caller once;
  *   acts[n_steps][N,256]          (optional, may be NULL) stored output of every step, row-major
  *                                 (post-activation; the 128-wide last step fills columns 0..127);
  *   acts_img[n_steps][n_tiles][64 KB]  (optional) the same outputs as 128-row tile images: exactly the
@@ -177,8 +178,9 @@ int64_t ntx_mlp_train_tiles(int64_t n_rows);
 int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
                           void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks, int64_t n_tiles,
                           void* stream);
-/* Tile images -> row-major bf16: out[n_rows, cols] from img[n_tiles][64 KB] (cols <= 256, multiple of 32). */
-int ntx_untile(const void* img, int64_t n_rows, int cols, void* out, void* stream);
+/* Tile images -> row-major bf16: out[n_rows, cols] from img[n_tiles][tile_bytes] (cols <= 256, multiple of 32;
+ * tile_bytes = 65536 for activation / gradient images, 32768 for encoding images). */
+int ntx_untile(const void* img, int64_t n_rows, int cols, int64_t tile_bytes, void* out, void* stream);
 
 /* Backward of the MLP on the saved operands (the reference gets it from tape.gradient,
  * network/train.py:66).  Two kernels:
@@ -186,15 +188,20 @@ int ntx_untile(const void* img, int64_t n_rows, int cols, void* out, void* strea
  *                            and the ReLU masks it produces dy_img[n_steps][n_tiles][64 KB], the gradient
  *                            w.r.t. every step's pre-activation output, as tile images.  packed_t is the
  *                            transposed packed weight image (ntx_mlp_packed_t_bytes / ntx_mlp_pack_weights_t).
- *   ntx_mlp_backward_weights for every step >= 1 adds X^T dY (rows main_row0.. of that layer's kernel) and the
- *                            bias gradient 1^T dY into the flat fp32 gradient buffer `grad` (layout of the master
- *                            buffer; the caller zeroes it).  The encoded-input rows, step 0 and the two small heads
- *                            are left to the host (nerf_tex_b200/autograd.py). */
+ *   ntx_mlp_backward_weights adds into the flat fp32 gradient buffer `grad` (layout of the master buffer; the caller
+ *                            zeroes it): for every step >= 1 X^T dY (rows main_row0.. of that layer's kernel) and the
+ *                            bias gradient 1^T dY; the two heads' kernels (h^T d sigma, h^T d rgb).  For the steps that
+ *                            read an encoding it adds enc^T dY, in the kernel's column order, into
+ *                            enc_scratch[n_steps][128][256] fp32 (caller-zeroed): row c of enc_scratch[s] is the
+ *                            gradient of the weight row ntx_mlp_enc_columns maps column c to; the constant-1
+ *                            column's row is the bias gradient (needed for step 0).  The host scatters those 96
+ *                            rows and adds the heads' bias gradients (sum of d_rgbs). */
 int64_t ntx_mlp_packed_t_bytes(const ntx_mlp_t* mlp);
 int ntx_mlp_pack_weights_t(const ntx_mlp_t* mlp, const float* master, void* packed_t, void* stream);
 int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
                           void* dy_img, int64_t n_rows, int64_t n_tiles, void* stream);
-int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, float* grad,
+int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, const void* enc_pos,
+                             const void* enc_dir, const float* d_rgbs, float* grad, float* enc_scratch,
                              int64_t n_rows, int64_t n_tiles, void* stream);
 
 /* Schedule introspection for the host-side backward (nerf_tex_b200/autograd.py).  A "step" is one

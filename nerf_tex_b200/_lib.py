@@ -62,11 +62,11 @@ SIGNATURES = {
     "ntx_mlp_forward": (_I, [_P, _P, C.POINTER(MlpInputs), _P, _P]),
     "ntx_mlp_train_tiles": (_I64, [_I64]),
     "ntx_mlp_forward_train": (_I, [_P, _P, C.POINTER(MlpInputs), _P, _P, _P, _P, _P, _P, _I64, _P]),
-    "ntx_untile": (_I, [_P, _I64, _I, _P, _P]),
+    "ntx_untile": (_I, [_P, _I64, _I, _I64, _P, _P]),
     "ntx_mlp_packed_t_bytes": (_I64, [_P]),
     "ntx_mlp_pack_weights_t": (_I, [_P, _P, _P, _P]),
     "ntx_mlp_backward_data": (_I, [_P, _P, _P, _P, _P, _I64, _I64, _P]),
-    "ntx_mlp_backward_weights": (_I, [_P, _P, _P, _P, _I64, _I64, _P]),
+    "ntx_mlp_backward_weights": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _P]),
     "ntx_mlp_num_steps": (_I, [_P]),
     "ntx_mlp_step_info": (_I, [_P, _I] + [C.POINTER(C.c_int32)] * 6),
     "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),

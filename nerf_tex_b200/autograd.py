@@ -42,6 +42,7 @@ class MlpSchedule:
             arr = (C.c_int32 * ENC_COLS)()
             check(lib.ntx_mlp_enc_columns(h, phase, arr))
             ref = torch.tensor(list(arr), dtype=torch.int64)
+            self.ones_col = getattr(self, "ones_col", []) + [int(torch.nonzero(ref == -1).squeeze(1)[0])]
             cols = torch.nonzero(ref >= 0).squeeze(1)
             self.enc_maps.append((cols.to(model.device), ref[cols].to(model.device)))
         self.depth = model.cfg.depth
@@ -58,8 +59,21 @@ def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, r
     lib = _lib.load()
     n_tiles = int(lib.ntx_mlp_train_tiles(int(n_rows)))
     rgbs = torch.empty((n_rows, 4), dtype=torch.float32, device=dev)
-    enc_pos = torch.empty((n_rows, ENC_COLS), dtype=torch.bfloat16, device=dev)
-    enc_dir = torch.empty((n_rows, ENC_COLS), dtype=torch.bfloat16, device=dev)
+    # encoding tile images: 4 blocks of [128 x 32]; the kernel writes blocks 0..2, block 3 stays zero.
+    # Zero-filled once, then recycled through a small per-model pool (released by the backward).
+    pool = model.__dict__.setdefault("_enc_img_pool", {}).setdefault(n_tiles, [])
+    enc_pos = enc_dir = None
+    for ent in pool:
+        if not ent[2]:
+            ent[2] = True
+            enc_pos, enc_dir = ent[0], ent[1]
+            break
+    if enc_pos is None:
+        if len(pool) >= 4:
+            pool.clear()
+        enc_pos = torch.zeros((n_tiles, 128 * 128), dtype=torch.bfloat16, device=dev)
+        enc_dir = torch.zeros((n_tiles, 128 * 128), dtype=torch.bfloat16, device=dev)
+        pool.append([enc_pos, enc_dir, True])
     acts_img = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=dev)
     masks = torch.empty((sched.n_steps, n_tiles * 128, 8), dtype=torch.int32, device=dev)
     acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev) if row_major_acts else None
@@ -67,27 +81,34 @@ def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, r
                     -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows))
     check(lib.ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
                                     ptr(acts), ptr(acts_img), ptr(masks), n_tiles, stream_ptr()))
-    return rgbs, (enc_pos, enc_dir, acts_img, masks, acts)
+    return rgbs, (enc_pos, enc_dir, acts_img, masks, acts, n_rows)
+
+
+def release_saved(model, saved) -> None:
+    """Hand the encoding images of a finished pass back to the model's pool."""
+    for pool in model.__dict__.get("_enc_img_pool", {}).values():
+        for ent in pool:
+            if ent[0] is saved[0]:
+                ent[2] = False
 
 
 def untile(img: torch.Tensor, n_rows: int, cols: int = 256) -> torch.Tensor:
-    """[n_tiles, 128*256] tile images -> row-major bf16 [n_rows, cols]."""
+    """[n_tiles, 128*W] tile images (W = 256 activations / gradients, 128 encodings) -> row-major bf16 [n_rows, cols]."""
     out = torch.empty((n_rows, cols), dtype=torch.bfloat16, device=img.device)
-    check(_lib.load().ntx_untile(ptr(img), int(n_rows), int(cols), ptr(out), stream_ptr()))
+    check(_lib.load().ntx_untile(ptr(img), int(n_rows), int(cols), int(img.shape[1]) * 2, ptr(out), stream_ptr()))
     return out
 
 
 def mlp_backward_native(model, saved, d_rgbs: torch.Tensor, return_dy: bool = False):
     """d loss / d master with the hand-written kernels: ntx_mlp_backward_data (fused dgrad chain) and
-    ntx_mlp_backward_weights (X^T dY and 1^T dY on the saved tile images).  What stays on the host, as small
-    torch GEMMs on un-tiled copies: the encoded-input rows of the three layers that read an encoding
-    (K = 96), everything of step 0, and the two heads (N = 1 and N = 3)."""
-    enc_pos, enc_dir, acts_img, masks, _ = saved
+    ntx_mlp_backward_weights (X^T dY, 1^T dY, enc^T dY and the two heads on the saved tile images).  The host
+    only scatters the (at most 96) encoded-input rows of the three layers that read an encoding from the
+    kernel's column order to the reference's row order, and sums d_rgbs for the heads' biases."""
+    enc_pos, enc_dir, acts_img, masks, _, n_rows = saved
     lib = _lib.load()
     sched = model.schedule()
-    n_rows, n_tiles = enc_pos.shape[0], acts_img.shape[1]
+    n_tiles = acts_img.shape[1]
     master = model.master.detach()
-    bf = torch.bfloat16
     if getattr(model, "_packed_t_version", None) != model.master._version:
         if getattr(model, "_packed_t", None) is None:
             model._packed_t = torch.empty(int(lib.ntx_mlp_packed_t_bytes(model._h)), dtype=torch.uint8, device=model.device)
@@ -98,32 +119,25 @@ def mlp_backward_native(model, saved, d_rgbs: torch.Tensor, return_dy: bool = Fa
     check(lib.ntx_mlp_backward_data(model._h, ptr(model._packed_t), ptr(d_rgbs), ptr(masks), ptr(dy_img), n_rows, n_tiles,
                                     stream_ptr()))
     grad = torch.zeros_like(master)
-    check(lib.ntx_mlp_backward_weights(model._h, ptr(acts_img), ptr(dy_img), ptr(grad), n_rows, n_tiles, stream_ptr()))
+    enc_scratch = torch.zeros((sched.n_steps, 128, 256), dtype=torch.float32, device=master.device)
+    check(lib.ntx_mlp_backward_weights(model._h, ptr(acts_img), ptr(dy_img), ptr(enc_pos), ptr(enc_dir), ptr(d_rgbs),
+                                       ptr(grad), ptr(enc_scratch), n_rows, n_tiles, stream_ptr()))
 
     def gview(layer):
         wo, bo, fi, fo = model.layers[layer]
         return grad[wo:wo + fi * fo].view(fi, fo), grad[bo:bo + fo]
 
     for st, s in enumerate(sched.steps):
-        if st > 0 and not s["enc_data"]:
+        if not s["enc_data"]:
             continue
-        dY = untile(dy_img[st], n_rows, s["n_out"])
         gW, gb = gview(s["layer"])
-        if st == 0:
-            gb.copy_(dY.sum(0, dtype=torch.float32))
-        if s["enc_data"]:
-            e = enc_pos if s["phase"] == 0 else enc_dir
-            cols, rows = sched.enc_maps[s["phase"]]
-            gE = torch.mm(e.t(), dY, out_dtype=torch.float32)
-            gW[rows] = gE[cols]
-    d_rgb, d_sigma = d_rgbs[:, :3].contiguous(), d_rgbs[:, 3:4].contiguous()
-    last = sched.n_steps - 1
-    gW, gb = gview(sched.rgb_layer)                                       # model.py:123
-    gW.copy_(torch.mm(untile(acts_img[last], n_rows, 128).t(), d_rgb.to(bf), out_dtype=torch.float32))
-    gb.copy_(d_rgb.sum(0))
-    gWa, gba = gview(sched.alpha_layer)                                   # model.py:111
-    gWa.copy_(torch.mm(untile(acts_img[sched.depth - 1], n_rows).t(), d_sigma.to(bf), out_dtype=torch.float32))
-    gba.copy_(d_sigma.sum(0))
+        cols, rows = sched.enc_maps[s["phase"]]
+        gW[rows] = enc_scratch[st][cols, :s["n_out"]]
+        if st == 0:                                                       # no main operand: the bias gradient is the
+            gb.copy_(enc_scratch[st][sched.ones_col[s["phase"]], :s["n_out"]])    # constant-1 column's row
+    dsum = d_rgbs.sum(0)
+    gview(sched.rgb_layer)[1].copy_(dsum[:3])                             # model.py:123
+    gview(sched.alpha_layer)[1].copy_(dsum[3:4])                          # model.py:111
     return (grad, dy_img) if return_dy else grad
 
 
@@ -133,8 +147,8 @@ def mlp_backward(model, saved, d_rgbs: torch.Tensor) -> torch.Tensor:
     All GEMMs take bf16 operands with fp32 accumulation; weight gradients come out in fp32.  (An
     fp32 / TF32 gradient chain was measured to give the same agreement with the float64 reference —
     the residual is the bf16 forward itself — so the cheaper bf16 chain is kept.)"""
-    enc_pos, enc_dir, acts_img, masks, acts = saved
-    n_rows = enc_pos.shape[0]
+    enc_pos, enc_dir, acts_img, masks, acts, n_rows = saved
+    enc_pos, enc_dir = untile(enc_pos, n_rows, ENC_COLS), untile(enc_dir, n_rows, ENC_COLS)
     if acts is None:
         acts = [untile(acts_img[st], n_rows) for st in range(acts_img.shape[0])]
     sched = model.schedule()
@@ -215,5 +229,6 @@ class NetworkPass(torch.autograd.Function):
         d_rgbs = ops.composite_backward(rgbs, z, rays_d, d_cmap.contiguous(), d_amap.contiguous(), noise=noise,
                                         map_exr=map_exr, composite_bkgd=composite_bkgd, bkgd_color=bkgd_color)
         grad = mlp_backward_native(ctx.model, ctx.saved, d_rgbs.view(-1, 4))
+        release_saved(ctx.model, ctx.saved)
         ctx.saved = None
         return (grad,) + (None,) * 12

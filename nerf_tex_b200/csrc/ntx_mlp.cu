@@ -61,8 +61,9 @@ struct KernelArgs {
     const uint8_t* packed;
     float* rgbs;
     // training only: bf16 copies of every tensor-core operand the backward needs
-    uint4* dump_enc_pos;   // [N, 96] encoded pos-phase inputs (kernel column order, constant-1 column included)
-    uint4* dump_enc_dir;   // [N, 96]
+    uint8_t* dump_enc_pos; // [n_tiles][32 KB] tile images of the encoded pos-phase inputs (kernel column order,
+                           // constant-1 column included): blocks 0..2 = 96 columns are written, block 3 stays as allocated
+    uint8_t* dump_enc_dir; // [n_tiles][32 KB]
     uint4* dump_acts;      // [n_steps][N, 256] stored outputs of every step (the 128-wide last step uses cols 0..127); may be NULL
     uint8_t* dump_img;     // [n_steps][n_tiles][64 KB]: the same outputs as 128-row SWIZZLE_64B tile images (the A
                            // operand buffer as it sits in shared memory), written by bulk stores; may be NULL
@@ -364,6 +365,10 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 }
             }
             // ------------------------------------------------------------- pos-phase encoding
+            if (DUMP) {
+                if (row == 0) tma_store_wait_read();         // last batch's dir-encoding image has left the buffer
+                named_bar_sync(1 + tile, kTileRows);
+            }
             {
                 uint32_t w[32];
 #pragma unroll
@@ -379,10 +384,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 }
                 w[30] = pack_bf16(1.0f, x[0]);
                 w[31] = pack_bf16(x[1], x[2]);
-                uint4* dp = (DUMP && valid) ? args.dump_enc_pos + grow * (kEncCols / 8) : nullptr;
                 auto put = [&](int q, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
                     st_shared_v4(chunk_addr(enc_base, q, row), w0, w1, w2, w3);
-                    if (DUMP && dp) st_global_v4(dp + q, w0, w1, w2, w3);
                 };
 #pragma unroll
                 for (int q = 0; q < 8; ++q) put(q, w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
@@ -398,8 +401,16 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     put(8 + g, pack_bf16(pg[0], pg[1]), pack_bf16(pg[2], 0.f), 0u, 0u);
                     if ((g & 1) == 0) put(9 + g, 0u, 0u, 0u, 0u);
                 }
-                if (DUMP && dp)
-                    for (int q = pos_chunks(g) + (pos_chunks(g) & 1); q < kEncCols / 8; ++q) st_global_v4(dp + q, 0u, 0u, 0u, 0u);
+                if (DUMP) {
+                    for (int q = pos_chunks(g) + (pos_chunks(g) & 1); q < kEncCols / 8; ++q) put(q, 0u, 0u, 0u, 0u);
+                    fence_proxy_async_smem();
+                    named_bar_sync(1 + tile, kTileRows);
+                    if (row == 0) {
+                        const int64_t tile_g = (b * CTAS + rank) * kTilesPerCta + tile;
+                        tma_bulk_s2g(args.dump_enc_pos + tile_g * (int64_t)(4 * kBlockBytes), enc_base, kEncBytes);
+                        tma_store_commit();
+                    }
+                }
             }
             fence_proxy_async_smem();
             __syncwarp();
@@ -476,10 +487,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 }
                 if (epi & EPI_SWITCH) {
                     // ----------------------------------------------------- dir-phase encoding
-                    uint4* dp = (DUMP && valid) ? args.dump_enc_dir + grow * (kEncCols / 8) : nullptr;
                     auto put = [&](int q, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
                         st_shared_v4(chunk_addr(enc_base, q, row), w0, w1, w2, w3);
-                        if (DUMP && dp) st_global_v4(dp + q, w0, w1, w2, w3);
                     };
 #pragma unroll
                     for (int i = 0; i < 3; ++i) {
@@ -498,8 +507,16 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                     put(3 + a, pack_bf16(1.0f, d[0]), pack_bf16(d[1], d[2]), pack_bf16(pa[0], pa[1]), pack_bf16(pa[2], pa[3]));
                     if (a > 4) put(4 + a, pack_bf16(pa[4], pa[5]), pack_bf16(pa[6], 0.f), 0u, 0u);
                     if (dir_chunks(a) & 1) put(dir_chunks(a), 0u, 0u, 0u, 0u);
-                    if (DUMP && dp)
-                        for (int q = dir_chunks(a) + (dir_chunks(a) & 1); q < kEncCols / 8; ++q) st_global_v4(dp + q, 0u, 0u, 0u, 0u);
+                    if (DUMP) {
+                        for (int q = dir_chunks(a) + (dir_chunks(a) & 1); q < kEncCols / 8; ++q) put(q, 0u, 0u, 0u, 0u);
+                        fence_proxy_async_smem();
+                        named_bar_sync(1 + tile, kTileRows);
+                        if (row == 0) {
+                            const int64_t tile_g = (b * CTAS + rank) * kTilesPerCta + tile;
+                            tma_bulk_s2g(args.dump_enc_dir + tile_g * (int64_t)(4 * kBlockBytes), enc_base, kEncBytes);
+                            tma_store_commit();
+                        }
+                    }
                 }
                 if (DUMP && args.dump_img) {
                     // relu sign bits (for the backward's masks) and the tile image of this step's stored output
@@ -544,7 +561,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
 }
 
 // tile images -> row-major (test / host-side helper)
-__global__ void untile_kernel(const uint8_t* __restrict__ img, int64_t n_rows, int cols, uint4* __restrict__ out) {
+__global__ void untile_kernel(const uint8_t* __restrict__ img, int64_t n_rows, int cols, int64_t tile_bytes,
+                              uint4* __restrict__ out) {
     const int chunks_per_row = cols / 8;
     const int64_t idx = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= n_rows * chunks_per_row) return;
@@ -553,7 +571,7 @@ __global__ void untile_kernel(const uint8_t* __restrict__ img, int64_t n_rows, i
     const int64_t tile = r / kTileRows;
     const int row = (int)(r % kTileRows);
     const uint32_t off = (uint32_t)(q >> 2) * kBlockBytes + (uint32_t)row * 64 + (uint32_t)(((q & 3) ^ ((row >> 1) & 3)) << 4);
-    out[idx] = *reinterpret_cast<const uint4*>(img + tile * (int64_t)kMainBytes + off);
+    out[idx] = *reinterpret_cast<const uint4*>(img + tile * tile_bytes + off);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -753,10 +771,10 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     NTX_REQUIRE(in->blur_idx < np, "mlp_forward: blur_idx %d out of range", in->blur_idx);
     NTX_REQUIRE((((uintptr_t)packed | (uintptr_t)rgbs) & 15) == 0, "mlp_forward: packed / rgbs must be 16-byte aligned");
     if (dump) {
-        NTX_REQUIRE(enc_pos && enc_dir && (acts || acts_img), "mlp_forward_train: null save buffer");
+        NTX_REQUIRE(enc_pos && enc_dir && acts_img, "mlp_forward_train: null save buffer");
         NTX_REQUIRE((((uintptr_t)enc_pos | (uintptr_t)enc_dir | (uintptr_t)acts | (uintptr_t)acts_img | (uintptr_t)masks) & 15) == 0,
                     "mlp_forward_train: save buffers must be 16-byte aligned");
-        if (acts_img) {
+        {
             NTX_REQUIRE(masks, "mlp_forward_train: tile images need the mask buffer too");
             NTX_REQUIRE(n_tiles >= ntx_mlp_train_tiles(in->n_rows), "mlp_forward_train: %lld tiles given, %lld needed",
                         (long long)n_tiles, (long long)ntx_mlp_train_tiles(in->n_rows));
@@ -778,8 +796,8 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     ka.in = *in;
     ka.packed = (const uint8_t*)packed;
     ka.rgbs = rgbs;
-    ka.dump_enc_pos = (uint4*)enc_pos;
-    ka.dump_enc_dir = (uint4*)enc_dir;
+    ka.dump_enc_pos = (uint8_t*)enc_pos;
+    ka.dump_enc_dir = (uint8_t*)enc_dir;
     ka.dump_acts = (uint4*)acts;
     ka.dump_img = (uint8_t*)acts_img;
     ka.dump_masks = (uint4*)masks;
@@ -813,12 +831,13 @@ NTX_API int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, cons
     return launch_forward(mlp, packed, in, rgbs, enc_pos, enc_dir, acts, acts_img, masks, n_tiles, true, stream);
 }
 
-NTX_API int ntx_untile(const void* img, int64_t n_rows, int cols, void* out, void* stream) {
-    NTX_REQUIRE(n_rows >= 0 && cols >= 32 && cols <= 256 && cols % 32 == 0, "untile: bad shape");
+NTX_API int ntx_untile(const void* img, int64_t n_rows, int cols, int64_t tile_bytes, void* out, void* stream) {
+    NTX_REQUIRE(n_rows >= 0 && cols >= 32 && cols <= 256 && cols % 32 == 0 && tile_bytes >= (int64_t)cols * 256,
+                "untile: bad shape");
     if (n_rows == 0) return NTX_OK;
     NTX_REQUIRE(img && out, "untile: null pointer");
     const int64_t total = n_rows * (cols / 8);
-    untile_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const uint8_t*)img, n_rows, cols, (uint4*)out);
+    untile_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>((const uint8_t*)img, n_rows, cols, tile_bytes, (uint4*)out);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }

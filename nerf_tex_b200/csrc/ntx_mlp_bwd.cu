@@ -391,23 +391,35 @@ constexpr uint32_t kWgOffTmemSlot = kWgOffBars + (2 * kWgStages + 2) * 8;
 constexpr uint32_t kWgSmemBytes = kWgOffTmemSlot + 16;
 static_assert(kWgSmemBytes <= 232448, "weight-gradient kernel exceeds shared memory");
 
+// one GEMM of the weight-gradient kernel: out[m][n] += sum_rows X[row][m] * dY[row][n]
+struct WgJob {
+    const uint8_t* x;        // X tile images
+    const uint8_t* dy;       // dY tile images
+    float* out;              // row m of the result goes to out + m * out_ld
+    float* bias;             // 1^T dY goes here (NULL: skip)
+    int64_t x_tile_bytes;    // 65536 (activation images) or 32768 (encoding images)
+    int32_t x_blocks;        // 8: M = 256 (two accumulators), 4: M = 128
+    int32_t n_out;           // N (256 or 128) = dY blocks * 32
+    int32_t out_ld;
+    int32_t pad_;
+};
+
 struct WgradArgs {
-    const uint8_t* acts_img;     // [n_steps][n_tiles][64 KB]   X_s = acts_img[s-1]
-    const uint8_t* dy_img;       // [n_steps][n_tiles][64 KB]
-    float* grad;                 // flat fp32 gradient buffer (accumulated into)
-    int64_t n_tiles_alloc;       // tiles per step in the image buffers
+    WgJob jobs[kMaxSteps + 4];
+    int32_t n_jobs;
+    int32_t pad_;
     int64_t n_tiles;             // tiles that hold real rows
 };
 
 __global__ void __launch_bounds__(kWgThreads, 1)
-mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ WgradArgs args) {
+mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
     extern __shared__ __align__(1024) uint8_t smem[];
     const uint32_t sbase = smem_u32(smem);
     if ((sbase & 1023u) != 0) __trap();
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t bar_full = sbase + kWgOffBars;               // [3]
     const uint32_t bar_empty = bar_full + 8 * kWgStages;        // [3]  1 commit + 4 bias warps
-    const uint32_t bar_acc = bar_empty + 8 * kWgStages;         // accumulators of a step complete
+    const uint32_t bar_acc = bar_empty + 8 * kWgStages;         // accumulators of a job complete
     const uint32_t bar_free = bar_acc + 8;                      // accumulators flushed (4 warps)
     float* bias_scratch = reinterpret_cast<float*>(smem + kWgOffBias);
     volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(smem + kWgOffTmemSlot);
@@ -429,27 +441,26 @@ mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ W
 
     // my tiles: blockIdx.x, += gridDim.x; each tile = 2 stages (rows 0..63, 64..127)
     const int64_t my_tiles = args.n_tiles > blockIdx.x ? (args.n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    constexpr uint32_t kHalf = kWgHalfRows * 64;                         // bytes of one block's half (64 rows)
 
     if (warp == 0) {
         if (lane == 0) {
             uint32_t stage = 0, parity = 1;
-            for (int st = 1; st < prog.n_steps; ++st) {
-                const int n_blk = prog.steps[st].n_out / 32;           // dY blocks (8, or 4 for the last step)
-                const uint8_t* xs = args.acts_img + (int64_t)(st - 1) * args.n_tiles_alloc * kMainBytes;
-                const uint8_t* ds = args.dy_img + (int64_t)st * args.n_tiles_alloc * kMainBytes;
+            for (int jb = 0; jb < args.n_jobs; ++jb) {
+                const WgJob& J = args.jobs[jb];
+                const int xb = J.x_blocks, n_blk = J.n_out / 32;
                 for (int64_t i = 0; i < my_tiles; ++i) {
                     const int64_t tile = blockIdx.x + i * gridDim.x;
                     for (int half = 0; half < 2; ++half) {
                         mbar_wait(bar_empty + 8 * stage, parity);
-                        mbar_arrive_expect_tx(bar_full + 8 * stage, (8 + n_blk) * kWgHalfRows * 64);
+                        mbar_arrive_expect_tx(bar_full + 8 * stage, (xb + n_blk) * kHalf);
                         const uint32_t dst = sbase + stage * kWgStageBytes;
-                        const uint8_t* xt = xs + tile * (int64_t)kMainBytes + half * (kWgHalfRows * 64);
-                        const uint8_t* dt = ds + tile * (int64_t)kMainBytes + half * (kWgHalfRows * 64);
-                        for (int blk = 0; blk < 8; ++blk)
-                            tma_bulk_g2s(dst + blk * (kWgHalfRows * 64), xt + blk * kBlockBytes, kWgHalfRows * 64, bar_full + 8 * stage);
+                        const uint8_t* xt = J.x + tile * J.x_tile_bytes + half * kHalf;
+                        const uint8_t* dt = J.dy + tile * (int64_t)kMainBytes + half * kHalf;
+                        for (int blk = 0; blk < xb; ++blk)
+                            tma_bulk_g2s(dst + blk * kHalf, xt + blk * kBlockBytes, kHalf, bar_full + 8 * stage);
                         for (int blk = 0; blk < n_blk; ++blk)
-                            tma_bulk_g2s(dst + kWgOperandBytes + blk * (kWgHalfRows * 64), dt + blk * kBlockBytes, kWgHalfRows * 64,
-                                         bar_full + 8 * stage);
+                            tma_bulk_g2s(dst + kWgOperandBytes + blk * kHalf, dt + blk * kBlockBytes, kHalf, bar_full + 8 * stage);
                         if (++stage == kWgStages) { stage = 0; parity ^= 1; }
                     }
                 }
@@ -457,10 +468,10 @@ mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ W
         }
     } else if (warp == 1) {
         uint32_t stage = 0, parity = 0, free_phase = 0;
-        const uint32_t lbo = kWgHalfRows * 64;                           // next 32 MN elements: next block
-        for (int st = 1; st < prog.n_steps; ++st) {
-            const uint32_t idesc = idesc_bf16_f32_mn(128, prog.steps[st].n_out);
-            if (st > 1) { mbar_wait(bar_free, free_phase); free_phase ^= 1; tc_fence_after(); }
+        for (int jb = 0; jb < args.n_jobs; ++jb) {
+            const uint32_t idesc = idesc_bf16_f32_mn(128, args.jobs[jb].n_out);
+            const bool two = args.jobs[jb].x_blocks == 8;
+            if (jb > 0) { mbar_wait(bar_free, free_phase); free_phase ^= 1; tc_fence_after(); }
             uint32_t accumulate = 0;
             for (int64_t i = 0; i < my_tiles * 2; ++i) {
                 mbar_wait(bar_full + 8 * stage, parity);
@@ -468,10 +479,12 @@ mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ W
                 const uint32_t xa = sbase + stage * kWgStageBytes, da = xa + kWgOperandBytes;
                 if (elect_one_sync()) {
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {
-                        const uint64_t bd = smem_desc(da + ks * 1024, lbo, 512, LAYOUT_SW64);
-                        mma_bf16_ss(tmem_base, smem_desc(xa + ks * 1024, lbo, 512, LAYOUT_SW64), bd, idesc, accumulate);
-                        mma_bf16_ss(tmem_base + 256, smem_desc(xa + 4 * lbo + ks * 1024, lbo, 512, LAYOUT_SW64), bd, idesc, accumulate);
+                    for (int ks = 0; ks < 4; ++ks) {                     // 16 K rows per MMA
+                        const uint64_t bd = smem_desc(da + ks * 1024, kHalf, 512, LAYOUT_SW64);
+                        mma_bf16_ss(tmem_base, smem_desc(xa + ks * 1024, kHalf, 512, LAYOUT_SW64), bd, idesc, accumulate);
+                        if (two)
+                            mma_bf16_ss(tmem_base + 256, smem_desc(xa + 4 * kHalf + ks * 1024, kHalf, 512, LAYOUT_SW64), bd, idesc,
+                                        accumulate);
                         accumulate = 1;
                     }
                     mma_commit(bar_empty + 8 * stage);
@@ -484,21 +497,20 @@ mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ W
             __syncwarp();
         }
     } else {
-        // bias sums from the staged dY halves, then flush of the accumulators
+        // column sums of the staged dY halves (bias gradient), then the flush of the accumulators
         const int tid = threadIdx.x - 64;                 // 0..127
         const int quarter = warp & 3;                      // TMEM lane quarter of this warp
         const int cc = tid & 31, rg = tid >> 5;            // chunk column (8 cols), row group (16 rows)
         uint32_t stage = 0, parity = 0, acc_phase = 0;
-        for (int st = 1; st < prog.n_steps; ++st) {
-            const Step& step = prog.steps[st];
-            const Layer& L = prog.layers[step.layer];
-            const int n_out = step.n_out;
+        for (int jb = 0; jb < args.n_jobs; ++jb) {
+            const WgJob& J = args.jobs[jb];
+            const int n_out = J.n_out;
             float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            const bool has_col = cc * 8 < n_out;
+            const bool do_bias = J.bias != nullptr && cc * 8 < n_out;
             for (int64_t i = 0; i < my_tiles * 2; ++i) {
                 mbar_wait(bar_full + 8 * stage, parity);
-                if (has_col) {
-                    const uint8_t* dy = smem + stage * kWgStageBytes + kWgOperandBytes + (cc >> 2) * (kWgHalfRows * 64);
+                if (do_bias) {
+                    const uint8_t* dy = smem + stage * kWgStageBytes + kWgOperandBytes + (cc >> 2) * kHalf;
 #pragma unroll 4
                     for (int r = rg * 16; r < rg * 16 + 16; ++r) {
                         const uint4 v = *reinterpret_cast<const uint4*>(dy + r * 64 + (((cc & 3) ^ ((r >> 1) & 3)) << 4));
@@ -514,30 +526,30 @@ mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ W
                 if (lane == 0) mbar_arrive(bar_empty + 8 * stage);
                 if (++stage == kWgStages) { stage = 0; parity ^= 1; }
             }
-            // bias gradient: reduce the 4 row groups through shared memory, one atomic per column per CTA
+            if (J.bias != nullptr) {
 #pragma unroll
-            for (int e = 0; e < 8; ++e) bias_scratch[rg * 256 + cc * 8 + e] = bsum[e];
-            named_bar_sync(1, 128);
-            for (int c = tid; c < n_out; c += 128) {
-                const float s = bias_scratch[c] + bias_scratch[256 + c] + bias_scratch[512 + c] + bias_scratch[768 + c];
-                if (my_tiles > 0) atomicAdd(args.grad + L.b_off + c, s);
+                for (int e = 0; e < 8; ++e) bias_scratch[rg * 256 + cc * 8 + e] = bsum[e];
+                named_bar_sync(1, 128);
+                for (int c = tid; c < n_out; c += 128) {
+                    const float sm = bias_scratch[c] + bias_scratch[256 + c] + bias_scratch[512 + c] + bias_scratch[768 + c];
+                    if (my_tiles > 0) atomicAdd(J.bias + c, sm);
+                }
+                named_bar_sync(1, 128);
             }
-            named_bar_sync(1, 128);
-            // weight gradient: thread = input feature row m (D0) and m + 128 (D1)
+            // weight gradient: thread = result row m of accumulator 0 (and m + 128 of accumulator 1)
             mbar_wait(bar_acc, acc_phase);
             acc_phase ^= 1;
             tc_fence_after();
             if (my_tiles > 0) {
                 const int m = quarter * 32 + lane;
-#pragma unroll
-                for (int mh = 0; mh < 2; ++mh) {
-                    float* grow_ptr = args.grad + L.w_off + (int64_t)(step.main_row0 + mh * 128 + m) * L.fan_out;
+                for (int mh = 0; mh < J.x_blocks / 4; ++mh) {
+                    float* orow = J.out + (int64_t)(mh * 128 + m) * J.out_ld;
                     for (int j = 0; j < n_out / 32; ++j) {
                         uint32_t v[32];
                         tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + mh * 256 + j * 32, v);
                         tmem_ld_wait();
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) atomicAdd(grow_ptr + j * 32 + c, __uint_as_float(v[c]));
+                        for (int c = 0; c < 32; ++c) atomicAdd(orow + j * 32 + c, __uint_as_float(v[c]));
                     }
                 }
             }
@@ -549,6 +561,51 @@ mlp_wgrad_kernel(const __grid_constant__ Program prog, const __grid_constant__ W
     tc_fence_before();
     __syncthreads();
     if (warp == 1) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
+}
+
+// The two heads' kernels on CUDA cores, straight from the tile images (model.py:111,123):
+//   out[c * n_d + j] += sum_rows X[row][c] * d_rgbs[row][d0 + j]       (n_d = 1: density head, 3: colour head)
+// A warp reads 32 consecutive rows of one 32-column block (2 KB contiguous); partial sums stay in registers
+// over all tiles of the CTA and are reduced across the warp once at the end.
+template <int ND>
+__global__ void __launch_bounds__(256)
+mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_img, int x_blocks, const float* __restrict__ d_rgbs, int d0,
+                       float* __restrict__ out, int64_t n_rows, int64_t n_tiles) {
+    const int blk = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (blk >= x_blocks) return;
+    float acc[32 * ND];
+#pragma unroll
+    for (int i = 0; i < 32 * ND; ++i) acc[i] = 0.0f;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint8_t* tb = x_img + tile * (int64_t)kMainBytes + blk * kBlockBytes;
+#pragma unroll 1
+        for (int rgp = 0; rgp < 4; ++rgp) {
+            const int row = rgp * 32 + lane;
+            const int64_t grow = tile * kTileRows + row;
+            float d[ND];
+#pragma unroll
+            for (int j = 0; j < ND; ++j) d[j] = grow < n_rows ? __ldg(d_rgbs + 4 * grow + d0 + j) : 0.0f;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(tb + row * 64 + ((c ^ ((row >> 1) & 3)) << 4)));
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float x0 = __uint_as_float(w[e] << 16), x1 = __uint_as_float(w[e] & 0xFFFF0000u);
+#pragma unroll
+                    for (int j = 0; j < ND; ++j) {
+                        acc[(c * 8 + 2 * e) * ND + j] += x0 * d[j];
+                        acc[(c * 8 + 2 * e + 1) * ND + j] += x1 * d[j];
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < 32 * ND; ++i) {
+        const float v = ntx_warp_sum(acc[i]);
+        if (lane == 0) atomicAdd(out + (blk * 32 + i / ND) * ND + (i % ND), v);
+    }
 }
 
 }  // namespace
@@ -616,9 +673,11 @@ NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, co
     return NTX_OK;
 }
 
-NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, float* grad,
+NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, const void* enc_pos,
+                                     const void* enc_dir, const float* d_rgbs, float* grad, float* enc_scratch,
                                      int64_t n_rows, int64_t n_tiles, void* stream) {
-    NTX_REQUIRE(mlp && acts_img && dy_img && grad, "mlp_backward_weights: null pointer");
+    NTX_REQUIRE(mlp && acts_img && dy_img && enc_pos && enc_dir && d_rgbs && grad && enc_scratch,
+                "mlp_backward_weights: null pointer");
     NTX_REQUIRE(n_rows >= 0 && n_tiles >= (n_rows + 127) / 128, "mlp_backward_weights: bad tile count");
     if (n_rows == 0) return NTX_OK;
     static bool attr_set[64] = {};
@@ -628,14 +687,46 @@ NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img,
         NTX_CUDA(cudaFuncSetAttribute(mlp_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWgSmemBytes));
         attr_set[dev] = true;
     }
+    const Program& p = mlp->prog;
+    const int64_t step_bytes = n_tiles * (int64_t)kMainBytes;
     WgradArgs a;
-    a.acts_img = (const uint8_t*)acts_img;
-    a.dy_img = (const uint8_t*)dy_img;
-    a.grad = grad;
-    a.n_tiles_alloc = n_tiles;
+    memset(&a, 0, sizeof(a));
     a.n_tiles = (n_rows + 127) / 128;
+    int nj = 0;
+    for (int st = 0; st < p.n_steps; ++st) {
+        const Step& S = p.steps[st];
+        const Layer& L = p.layers[S.layer];
+        if (st > 0) {                                   // main operand: the previous step's stored output
+            WgJob& J = a.jobs[nj++];
+            J.x = (const uint8_t*)acts_img + (st - 1) * step_bytes;
+            J.dy = (const uint8_t*)dy_img + st * step_bytes;
+            J.out = grad + L.w_off + (int64_t)S.main_row0 * L.fan_out;
+            J.bias = grad + L.b_off;
+            J.x_tile_bytes = kMainBytes; J.x_blocks = 8; J.n_out = S.n_out; J.out_ld = L.fan_out;
+        }
+        if (S.enc_data) {                               // encoded inputs: rows in kernel column order -> scratch
+            WgJob& J = a.jobs[nj++];
+            J.x = (const uint8_t*)(S.phase == 0 ? enc_pos : enc_dir);
+            J.dy = (const uint8_t*)dy_img + st * step_bytes;
+            J.out = enc_scratch + (int64_t)st * 128 * 256;
+            J.bias = nullptr;
+            J.x_tile_bytes = 4 * kBlockBytes; J.x_blocks = 4; J.n_out = S.n_out; J.out_ld = 256;
+        }
+    }
+    a.n_jobs = nj;
+    cudaStream_t stc = (cudaStream_t)stream;
     const int64_t g = a.n_tiles < ntx_sm_count() ? a.n_tiles : ntx_sm_count();
-    mlp_wgrad_kernel<<<(unsigned)g, kWgThreads, kWgSmemBytes, (cudaStream_t)stream>>>(mlp->prog, a);
+    mlp_wgrad_kernel<<<(unsigned)g, kWgThreads, kWgSmemBytes, stc>>>(a);
+    NTX_LAUNCH_CHECK();
+    // heads: density (input = last trunk layer's output), colour (input = the 128-wide last step's output)
+    const Layer& la = p.layers[p.alpha_layer];
+    const Layer& lr = p.layers[p.rgb_layer];
+    const int64_t gh = a.n_tiles < 2 * ntx_sm_count() ? a.n_tiles : 2 * ntx_sm_count();
+    mlp_heads_wgrad_kernel<1><<<(unsigned)gh, 256, 0, stc>>>((const uint8_t*)acts_img + (int64_t)(mlp->cfg.depth - 1) * step_bytes,
+                                                              8, d_rgbs, 3, grad + la.w_off, n_rows, a.n_tiles);
+    NTX_LAUNCH_CHECK();
+    mlp_heads_wgrad_kernel<3><<<(unsigned)gh, 256, 0, stc>>>((const uint8_t*)acts_img + (int64_t)(p.n_steps - 1) * step_bytes,
+                                                              4, d_rgbs, 0, grad + lr.w_off, n_rows, a.n_tiles);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }

@@ -151,7 +151,7 @@ def test_training_forward_saves_tile_images_and_masks(n):
     d = torch.randn((n, 3), device="cuda", generator=g)
     d = d / d.norm(dim=-1, keepdim=True)
     prm = torch.rand((n, 7), device="cuda", generator=g)
-    rgbs, (enc_pos, enc_dir, acts_img, masks, acts) = mlp_forward_train(m, n_rows=n, pos=pos, dir=d, params=prm,
+    rgbs, (enc_pos, enc_dir, acts_img, masks, acts, _) = mlp_forward_train(m, n_rows=n, pos=pos, dir=d, params=prm,
                                                                         rows_per_group=1, row_major_acts=True)
     ref = m.forward_rows(n_rows=n, pos=pos, dir=d, params=prm, rows_per_group=1)
     torch.cuda.synchronize()
