@@ -292,6 +292,41 @@ def train_step_bench(dev, steps=5):
     return out
 
 
+def c1_forward_bench(dev, steps=20):
+    """BASELINE.json configs[0]: 4096 rays x (64 coarse + 128 fine), CoarseFine [1,4], forward only,
+    through Renderer.__call__ (K3 -> K1 -> K2 -> K3 -> K1 -> K2)."""
+    import torch
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.renderer import Renderer
+    g = torch.Generator(device=dev).manual_seed(0)
+    B, Nr = 16, 256
+    o = torch.randn((B, 3), device=dev, generator=g)
+    o[:, 2] = o[:, 2].abs()
+    o = 5 * o / o.norm(dim=-1, keepdim=True)
+    rays_o = o[:, None, :].repeat(1, Nr, 1)
+    rays_d = torch.rand((B, Nr, 3), device=dev, generator=g) * 2 - 1 - rays_o
+    rays_d = rays_d / rays_d.norm(dim=-1, keepdim=True)
+    t = torch.stack([3.5 + torch.rand((B, Nr), device=dev, generator=g) * .5, 5.5 + torch.rand((B, Nr), device=dev, generator=g)], -1)
+    params = torch.rand((B, 5), device=dev, generator=g)
+    cone = torch.full((B, Nr, 1), 2e-3, device=dev)
+    r = Renderer(model=FusedNerfTexMLP(1, 4, seed=1), model_fine=FusedNerfTexMLP(1, 4, seed=2, name="model_fine"),
+                 n_samples=64, n_importance=128, perturb=True, seed=0)
+    for _ in range(5):
+        r(rays_o, rays_d, t, params, cone, training=False)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        r(rays_o, rays_d, t, params, cone, training=False)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    rows = B * Nr * 256
+    return {"rays": B * Nr, "mlp_rows": rows, "ms_per_batch": ms, "rays_per_sec": B * Nr / ms * 1e3,
+            "samples_per_sec": rows / ms * 1e3, "mlp_tflops_incl_everything": rows * 2 * 676224 / (ms / 1e3) / 1e12,
+            "note": "4096-ray batch fills 148 SMs for only ~7 waves of 512-row CTA-pair batches; launch-latency sensitive"}
+
+
 def config_dict(extra=None):
     c = {"workload": "carpet-shape instanced render, 800x800 frame (640000 rays), n_parameters [1,6], "
                      "n_samples<=1024, step 0.002, patch_scale 0.09, render_chunk 16384, random-init weights",
@@ -476,6 +511,7 @@ def run_gpu(args):
             torch.cuda.empty_cache()
             line["hbm_kernels"] = hbm_kernels_bench(dev, pk)
             line["train_step"] = train_step_bench(dev)
+            line["c1_forward"] = c1_forward_bench(dev)
             line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
         print(json.dumps(line), flush=True)
     if world > 1:
