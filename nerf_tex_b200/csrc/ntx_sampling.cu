@@ -114,9 +114,35 @@ __global__ void sample_pdf_kernel(const float* __restrict__ src, const float* __
             if (HIER) sortbuf[S + n] = s;
         }
         if (HIER) {
-            // renderer.py:130: sort(concat([z_vals, z_samples])) — bitonic network in smem.
+            // renderer.py:130: sort(concat([z_vals, z_samples])).
             const float* zrow = src + ray * S;
+            float* orow = z_out + ray * (int64_t)(S + N);
             for (int i = lane; i < S; i += 32) sortbuf[i] = zrow[i];
+            __syncwarp();
+            // Fast path (the usual case: stratified depths are increasing, and so are the inverse-CDF samples of
+            // increasing u): both runs are already sorted, so every element's final position is its own index
+            // plus its rank in the other run (ties: depths first).  Any unsorted pair falls back to the network.
+            bool sorted = true;
+            for (int i = lane + 1; i < S; i += 32) sorted &= sortbuf[i] >= sortbuf[i - 1];
+            for (int n = lane + 1; n < N; n += 32) sorted &= sortbuf[S + n] >= sortbuf[S + n - 1];
+            if (__all_sync(0xffffffffu, sorted)) {
+                const float* zs = sortbuf;            // [S] sorted depths
+                const float* sm = sortbuf + S;        // [N] sorted samples
+                for (int i = lane; i < S; i += 32) {  // # samples strictly below z_i
+                    const float v = zs[i];
+                    int lo = 0, hi = N;
+                    while (lo < hi) { const int mid = (lo + hi) >> 1; if (sm[mid] < v) lo = mid + 1; else hi = mid; }
+                    orow[i + lo] = v;
+                }
+                for (int n = lane; n < N; n += 32) {  // # depths at or below s_n
+                    const float v = sm[n];
+                    int lo = 0, hi = S;
+                    while (lo < hi) { const int mid = (lo + hi) >> 1; if (zs[mid] <= v) lo = mid + 1; else hi = mid; }
+                    orow[n + lo] = v;
+                }
+                __syncwarp();
+                continue;
+            }
             for (int i = S + N + lane; i < p2; i += 32) sortbuf[i] = CUDART_INF_F;
             __syncwarp();
             for (int k = 2; k <= p2; k <<= 1) {
@@ -131,7 +157,6 @@ __global__ void sample_pdf_kernel(const float* __restrict__ src, const float* __
                     __syncwarp();
                 }
             }
-            float* orow = z_out + ray * (int64_t)(S + N);
             for (int i = lane; i < S + N; i += 32) orow[i] = sortbuf[i];
             __syncwarp();
         }
@@ -151,6 +176,8 @@ int launch_sample(const float* src, const float* weights, const float* u, int R,
     const int budget_floats = 46 * 1024 / 4 / warps;   // stay under the 48 KB default limit
     int rpw = 32;
     while (rpw > 1 && rpw * (cstride + bstride) + p2 > budget_floats) rpw >>= 1;
+    // small batches: fewer rays per warp so that every SM gets several warps (the per-ray work of a warp is serial)
+    while (rpw > 1 && (int64_t)R / (rpw * warps) < 4LL * ntx_sm_count()) rpw >>= 1;
     const size_t smem = (size_t)warps * (rpw * (cstride + bstride) + p2) * sizeof(float);
     NTX_REQUIRE(smem <= 46 * 1024, "sample_pdf: C=%d N=%d needs %zu B of shared memory", C, N, smem);
     const int64_t rays_per_block = (int64_t)rpw * warps;
