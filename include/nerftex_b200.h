@@ -215,6 +215,20 @@ int ntx_mlp_step_info(const ntx_mlp_t* mlp, int step, int32_t* layer, int32_t* n
 int ntx_mlp_enc_columns(const ntx_mlp_t* mlp, int phase, int32_t* ref_index);
 
 /* ------------------------------------------------------------------------------------------
+ * Camera rays
+ * ---------------------------------------------------------------------------------------- */
+
+/* Replaces network/ray_sampler.py:6-48 (rays_from_camera, Frustum, Proxy) and network/proxy.py:13-35 (AABB).
+ *   image_plane_loc[n,2] (row, column) pixel positions, or NULL for the first n pixels of the frame in
+ *   row-major order; c2w: HOST pointer to the 4x4 row-major camera-to-world matrix; normalize != 0 divides
+ *   rays_d by its norm (Proxy, :34); b0/b1: HOST pointers to the AABB corners (misses give t = inf, inf) or
+ *   both NULL for a constant [near, far] (Frustum, :19).
+ *   Outputs: rays_o[n,3], rays_d[n,3], t[n,2], cone_scale[n]. */
+int ntx_rays_from_camera(const float* image_plane_loc, int64_t n, int height, int width, float focal,
+                         const float* c2w, int normalize, const float* b0, const float* b1, float near_, float far_,
+                         float* rays_o, float* rays_d, float* t, float* cone_scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Whole ray chunk: K3 -> K1 -> K2 [-> K3 -> K1 -> K2]
  * ---------------------------------------------------------------------------------------- */
 

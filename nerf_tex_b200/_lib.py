@@ -70,6 +70,7 @@ SIGNATURES = {
     "ntx_mlp_num_steps": (_I, [_P]),
     "ntx_mlp_step_info": (_I, [_P, _I] + [C.POINTER(C.c_int32)] * 6),
     "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),
+    "ntx_rays_from_camera": (_I, [_P, _I64, _I, _I, _F, _P, _I, _P, _P, _F, _F, _P, _P, _P, _P, _P]),
     "ntx_normalize_dirs": (_I, [_P, _I, _P, _P]),
     "ntx_render_rays_workspace_bytes": (_I64, [_I, _I, _I]),
     "ntx_render_rays": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P, _I64, _P]),

@@ -142,6 +142,37 @@ def composite_instanced_forward(rgbs, dists, alpha_weight, ray_ptr, color_last, 
     return cmap, amap
 
 
+# ------------------------------------------------------------------------------------------ camera rays
+
+def rays_from_camera(image_plane_loc, height: int, width: int, focal: float, c2w, *, normalize: bool = False,
+                     aabb=None, near: float = 0.0, far: float = 0.0, n: Optional[int] = None, device=None):
+    """network/ray_sampler.py:6-48 + network/proxy.py:13-35 in one launch.  image_plane_loc[n,2] or None (first n
+    pixels of the frame, row-major).  aabb = (b_0, b_1) or None (constant near/far).  Returns rays_o, rays_d, t,
+    cone_scale[n,1]."""
+    if image_plane_loc is not None:
+        image_plane_loc = as_cuda(image_plane_loc, device=device)
+        n = image_plane_loc.shape[0]
+        dev = image_plane_loc.device
+    else:
+        n = height * width if n is None else int(n)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    m = [float(v) for v in (c2w.detach().cpu().reshape(-1).tolist() if isinstance(c2w, torch.Tensor) else
+                            [x for row in c2w for x in row])]
+    assert len(m) == 16, "c2w must be 4x4"
+    c2w_h = (C.c_float * 16)(*m)
+    b0 = (C.c_float * 3)(*[float(v) for v in aabb[0]]) if aabb is not None else None
+    b1 = (C.c_float * 3)(*[float(v) for v in aabb[1]]) if aabb is not None else None
+    rays_o = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    rays_d = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    t = torch.empty((n, 2), dtype=torch.float32, device=dev)
+    cone = torch.empty((n, 1), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().ntx_rays_from_camera(ptr(image_plane_loc), n, int(height), int(width), float(focal), c2w_h,
+                                               int(bool(normalize)), b0, b1, float(near), float(far), ptr(rays_o),
+                                               ptr(rays_d), ptr(t), ptr(cone), stream_ptr()))
+    return rays_o, rays_d, t, cone
+
+
 # ------------------------------------------------------------------------------------------ whole chunk
 
 def render_config(n_samples, n_importance, perturb, map_exr, composite_bkgd, blur_idx, bkgd_color) -> "_lib.RenderConfig":
