@@ -42,7 +42,7 @@ class MlpInputs(C.Structure):
 
 
 # name -> (restype, argtypes); must list every symbol include/nerftex_b200.h declares.
-_P, _I, _F, _I64 = C.c_void_p, C.c_int, C.c_float, C.c_int64
+_P, _I, _F, _I64, _U32 = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_uint32
 SIGNATURES = {
     "ntx_version": (_I, []),
     "ntx_last_error": (C.c_char_p, []),
@@ -72,6 +72,9 @@ SIGNATURES = {
     "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),
     "ntx_rays_from_camera": (_I, [_P, _I64, _I, _I, _F, _P, _I, _P, _P, _F, _F, _P, _P, _P, _P, _P]),
     "ntx_normalize_dirs": (_I, [_P, _I, _P, _P]),
+    "ntx_instancer_workspace_bytes": (_I64, [_I]),
+    "ntx_instancer_trace": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _F, _I, _U32, _I, _P, _P, _P, _P]),
+    "ntx_instancer_march": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _F, _I, _U32, _I, _I, _I, _P, _P] + [_P] * 7 + [_P]),
     "ntx_render_rays_workspace_bytes": (_I64, [_I, _I, _I]),
     "ntx_render_rays": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P, _I64, _P]),
     "ntx_render_rays_static": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P]),

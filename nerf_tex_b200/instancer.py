@@ -2,7 +2,8 @@
 
 The reference's native instancer (Embree scene of shell patches on a mesh) cannot be built or
 fed in this environment (Embree 3 is a system dependency, every mesh/texture is a git-LFS stub;
-SURVEY.md D8).  ``SyntheticInstancer`` keeps the exact constructor / ``n_instances`` /
+SURVEY.md D8).  ``Instancer`` is the device instancer for explicit patch transformations (no mesh);
+``SyntheticInstancer`` keeps the exact constructor / ``n_instances`` /
 ``get_model_input`` surface and produces seeded outputs with the statistics SURVEY.md section 8d
 prescribes, natively CSR-packed on the GPU (``get_model_input_csr``); ``get_model_input`` scatters
 the same data into the reference's dense 10-tuple for callers written against instancer.pyx:54.
@@ -117,6 +118,64 @@ def csr_to_dense(csr, rays_d, parameters, n_samples: int):
     return rays_d_map, pts, t, dists, color_last, alpha_last, alpha_weight, instance_id, idxs, params_map
 
 
-# The reference's configs name 'instancer.instancer.Instancer' (config_carpet_render.py:82).  The native
-# Embree instancer is unavailable here, so that path resolves to the synthetic generator.
-Instancer = SyntheticInstancer
+class Instancer:
+    """Device shell instancer behind the reference's constructor (instancer/instancer.pyx:6-36) for explicit patch
+    `transformations` (AddInstance, instancer.cpp:125-141).  What needs the Embree scene of a base mesh is refused:
+    `mesh_path`, shadow rays, parameter textures other than '' / 'light' / 'point', auxiliary meshes, and the
+    'nearest_blend' sampling method."""
+
+    def __init__(self, b_0: list, b_1: list, cast_shadow_rays=False, textures: list = [], transformations: list = [],
+                 mesh_path: str = None, patch_scale: float = 1., patch_origins_path='', min_shadow_samples: int = 4,
+                 n_shadow_samples: int = 512, min_texture_samples: int = 4, n_texture_samples: int = 512,
+                 jitter_amount: float = 0, instance_sampling_method: str = 'random', use_mean_distance: bool = False,
+                 auxiliary_meshes=[], transformation_export_path=None, *, seed: int = 0, device=None) -> None:
+        assert instance_sampling_method in ('random', 'nearest', 'nearest_blend')      # instancer.pyx:12
+        if mesh_path:
+            raise NotImplementedError("Instancer: placing patches on a mesh needs the reference's Embree scene and its "
+                                      "git-LFS meshes; pass explicit `transformations` (or use SyntheticInstancer)")
+        if cast_shadow_rays or auxiliary_meshes:
+            raise NotImplementedError("Instancer: shadow rays / auxiliary meshes need a mesh scene")
+        if instance_sampling_method == 'nearest_blend':
+            raise NotImplementedError("Instancer: 'nearest_blend' is not built; use 'random' or 'nearest'")
+        self.light_dir_idx = -1
+        for i, tex in enumerate(textures):                                             # instancer.pyx:20-28
+            if tex == 'light':
+                self.light_dir_idx = i
+            elif tex not in ('', None, 'point'):
+                raise NotImplementedError(f"Instancer: parameter texture {tex!r} needs a UV-mapped mesh")
+        import numpy as np
+        T = np.asarray(transformations, dtype=np.float64).reshape(-1, 4, 4)
+        if T.shape[0] == 0:
+            raise ValueError("Instancer: no instances (empty `transformations`)")
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        rt = np.transpose(T[:, :3, :3], (0, 2, 1))
+        as_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a.astype(np.float32))).to(dev)
+        self.minv = as_dev(np.linalg.inv(T)[:, :3, :])
+        self.dirt = as_dev(rt / np.linalg.norm(rt, axis=2, keepdims=True))
+        self.origins = as_dev(T[:, :3, 3])
+        self.transformations = T
+        self.b_0, self.b_1 = [float(v) for v in b_0], [float(v) for v in b_1]
+        self.patch_scale = float(patch_scale)
+        self.method = 0 if instance_sampling_method == 'random' else 1
+        self.use_mean_distance = bool(use_mean_distance)
+        self.seed = int(seed)
+        self._calls = 0
+        if transformation_export_path:
+            np.save(transformation_export_path, T)                                    # instancer.pyx:33-36
+
+    def n_instances(self) -> int:
+        return int(self.minv.shape[0])
+
+    def get_model_input_csr(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
+        from . import ops
+        if seed is None:                       # a fresh draw every call, like the reference's running mt19937
+            seed = self.seed + 7919 * self._calls
+            self._calls += 1
+        return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.minv, self.dirt, self.origins,
+                                             self.b_0, self.b_1, seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
+                                             use_mean_distance=self.use_mean_distance)
+
+    def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
+        """Dense 10-tuple of instancer.pyx:54."""
+        csr = self.get_model_input_csr(rays_o, rays_d, parameters, n_samples, step_size, seed)
+        return csr_to_dense(csr, as_cuda(rays_d), as_cuda(parameters), n_samples)

@@ -1,0 +1,166 @@
+"""Device shell instancer (ntx_instancer_trace / ntx_instancer_march) against oracle/instancer_oracle.py:
+bit-exact records, then end to end through InstanceRenderer."""
+
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import instancer_oracle as IO
+
+pytestmark = pytest.mark.gpu
+
+B0, B1 = [-0.5, -0.5, -0.1], [0.5, 0.5, 0.1]
+
+
+def patch_grid(n, seed, spacing=0.9, tilt=0.0):
+    """n x n patches on the z = 0 plane, randomly rotated about z (and tilted), randomly scaled: they overlap."""
+    rng = np.random.default_rng(seed)
+    Ts = []
+    for i in range(n):
+        for j in range(n):
+            a, b = rng.uniform(0, 2 * math.pi), rng.uniform(-tilt, tilt)
+            rz = np.array([[math.cos(a), -math.sin(a), 0], [math.sin(a), math.cos(a), 0], [0, 0, 1]])
+            rx = np.array([[1, 0, 0], [0, math.cos(b), -math.sin(b)], [0, math.sin(b), math.cos(b)]])
+            T = np.eye(4)
+            T[:3, :3] = (rz @ rx) * rng.uniform(0.8, 1.3)
+            T[:3, 3] = [i * spacing, j * spacing, 0.1 * rng.uniform()]
+            Ts.append(T)
+    return np.array(Ts)
+
+
+def rays_over(n, R, seed, spacing=0.9, grazing=False):
+    rng = np.random.default_rng(seed)
+    ext = n * spacing
+    o = np.stack([rng.uniform(-1, ext, R), rng.uniform(-1, ext, R), np.full(R, 3.0)], 1).astype(np.float32)
+    s = 3.0 if grazing else 0.3
+    d = np.stack([rng.uniform(-s, s, R), rng.uniform(-s, s, R), np.full(R, -1.0)], 1).astype(np.float32)
+    return o, d
+
+
+def check_records(got, want, R):
+    ns = got["n_samples_all"].cpu().numpy()
+    assert np.array_equal(ns, want["n_samples"])
+    assert np.array_equal(got["ray_index"].cpu().numpy(), np.nonzero(want["hit"])[0])
+    ptr_all = np.concatenate([[0], np.cumsum(want["n_samples"])])
+    assert np.array_equal(got["ray_ptr"].cpu().numpy(), np.concatenate([ptr_all[:-1][want["hit"]], ptr_all[-1:]]))
+    assert np.array_equal(got["instance_id"].cpu().numpy(), want["instance_id"])
+    for k in ("pts", "dirs", "params", "dists", "t", "alpha_weight"):
+        g = got[k].cpu().numpy()
+        assert g.shape == want[k].shape, k
+        assert np.array_equal(g.view(np.uint32), want[k].view(np.uint32)), (k, np.abs(g - want[k]).max())
+
+
+@pytest.mark.parametrize("method,mean_dist,light", [("random", False, 1), ("nearest", False, -1), ("random", True, 4),
+                                                    ("nearest", True, 0)])
+def test_records_bit_exact(method, mean_dist, light):
+    from nerf_tex_b200.instancer import Instancer
+    Ts = patch_grid(5, seed=1, tilt=0.3)
+    R = 700
+    o, d = rays_over(5, R, seed=2)
+    prm = np.random.default_rng(3).normal(size=(R, 7)).astype(np.float32)
+    textures = ["light" if i == light else "" for i in range(5)] if light >= 0 else []
+    inst = Instancer(B0, B1, textures=textures, transformations=Ts.tolist(), instance_sampling_method=method,
+                     use_mean_distance=mean_dist)
+    assert inst.n_instances() == 25 and inst.light_dir_idx == light
+    want = IO.get_model_input(o, d, prm, 48, 0.02, Ts, B0, B1, seed=11, light_dir_idx=light, method=method,
+                              use_mean_distance=mean_dist)
+    got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), 48, 0.02, seed=11)
+    torch.cuda.synchronize()
+    check_records(got, want, R)
+    assert want["n_samples"].sum() > 3000 and (want["alpha_weight"] > 1).any() == (method == "random")
+    assert 0 < want["hit"].sum() < R
+
+
+def test_grazing_rays_clip_and_many_instances():
+    """Rays nearly parallel to the patch plane cross many patches: the per-ray hit list saturates at 64 entries,
+    n_pts clips the sample count, and more instances than one shared-memory tile (128) are walked."""
+    from nerf_tex_b200.instancer import Instancer
+    Ts = patch_grid(14, seed=5, spacing=0.45)                      # 196 instances, heavy overlap
+    R = 300
+    o, d = rays_over(14, R, seed=6, spacing=0.45, grazing=True)
+    o[:, 2] = 0.3
+    d[:, 2] = -0.05
+    prm = np.zeros((R, 1), np.float32)
+    inst = Instancer(B0, B1, transformations=Ts.tolist())
+    for n_pts, step in ((16, 0.05), (256, 0.004)):
+        want = IO.get_model_input(o, d, prm, n_pts, step, Ts, B0, B1, seed=5)
+        got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), n_pts, step, seed=5)
+        check_records(got, want, R)
+        assert want["n_samples"].max() == n_pts
+    hits = [len(IO.ray_hits(o[i], d[i], IO.prepare_instances(Ts)[0], np.float32(B0), np.float32(B1))) for i in range(R)]
+    assert max(hits) == IO.MAX_HITS
+
+
+def test_edge_inputs():
+    from nerf_tex_b200 import ops
+    from nerf_tex_b200.instancer import Instancer
+    Ts = patch_grid(2, seed=0)
+    inst = Instancer(B0, B1, transformations=Ts.tolist())
+    # no ray at all
+    e = inst.get_model_input_csr(torch.zeros(0, 3), torch.zeros(0, 3), torch.zeros(0, 2), 8, 0.05)
+    assert e["pts"].shape == (0, 3) and e["ray_ptr"].tolist() == [0] and e["ray_index"].numel() == 0
+    # every ray misses; axis-parallel rays (division by zero inside the slab test) behave like the oracle
+    o = np.array([[10, 10, 3], [0.2, 0.1, 3], [0.2, 0.1, 0.05], [-3, 0.1, 0.0]], np.float32)
+    d = np.array([[0, 0, -1], [0, 0, -1], [1, 0, 0], [1, 0, 0]], np.float32)
+    prm = np.ones((4, 2), np.float32)
+    want = IO.get_model_input(o, d, prm, 8, 0.05, Ts, B0, B1, seed=1)
+    got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), 8, 0.05, seed=1)
+    check_records(got, want, 4)
+    assert not want["hit"][0] and want["hit"][1]
+    # refusals of what needs a mesh scene
+    with pytest.raises(NotImplementedError):
+        Instancer(B0, B1, mesh_path="meshes/carpet.obj")
+    with pytest.raises(NotImplementedError):
+        Instancer(B0, B1, transformations=Ts.tolist(), cast_shadow_rays=True)
+    with pytest.raises(NotImplementedError):
+        Instancer(B0, B1, transformations=Ts.tolist(), textures=["textures/height.png"])
+    with pytest.raises(ValueError):
+        Instancer(B0, B1)
+    with pytest.raises(RuntimeError):
+        ops.instancer_get_model_input(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 17), 8, 0.05, inst.minv, inst.dirt,
+                                      inst.origins, B0, B1)
+
+
+def test_dense_tuple_and_instance_renderer():
+    """instancer.pyx:54 dense tuple from the device records, and the whole InstanceRenderer on top of it against
+    the oracle instancer + oracle network + oracle compositor."""
+    from nerf_tex_b200.instancer import Instancer
+    from nerf_tex_b200.renderer import InstanceRenderer
+    from oracle import nerftex_oracle as O
+    from test_gpu_renderer import build_models, psnr
+    Ts = patch_grid(4, seed=9, tilt=0.2)
+    models, oracles = build_models((1, 6), False, seed=7)
+    kw = dict(b_0=B0, b_1=B1, textures=["", "", "", "", "light"], transformations=Ts.tolist())
+    r = InstanceRenderer(instancer_config=Instancer(seed=4, **kw), model=models["model"], n_samples=32, render_chunk=16384,
+                         step_size=0.01, density_scale=100.0)
+    R = 500
+    o, d = rays_over(4, R, seed=8)
+    params = np.array([[1, 1, 1, .1, .3, -.2, 1]], np.float32)
+    cone = np.random.default_rng(1).uniform(0.01, 0.05, (1, R, 1)).astype(np.float32)
+    t = np.tile(np.array([[[1., 3.]]], np.float32), (1, R, 1))
+    cu = lambda a: torch.as_tensor(a).cuda()
+    got = r(cu(o[None]), cu(d[None]), cu(t), cu(params), cu(cone), composite_bkgd=True, training=False)
+    pf = np.repeat(params, R, 0)
+    want = IO.get_model_input(o, d, pf, 32, 0.01, Ts, B0, B1, seed=4, light_dir_idx=4)
+    dense = Instancer(seed=4, **kw).get_model_input(cu(o), cu(d), cu(pf), 32, 0.01)
+    dense = [x.cpu().numpy() for x in dense]
+    # the dense tuple holds exactly the oracle records
+    ns = want["n_samples"]
+    assert np.array_equal(dense[8][:, 0], np.nonzero(want["hit"])[0])
+    k = 0
+    for ray in range(R):
+        n = ns[ray]
+        assert np.array_equal(dense[1][ray, :n], want["pts"][k:k + n]) and np.array_equal(dense[0][ray, :n], want["dirs"][k:k + n])
+        assert np.array_equal(dense[3][ray, :n], want["dists"][k:k + n]) and not dense[3][ray, n:].any()
+        assert np.array_equal(dense[9][ray, :n], want["params"][k:k + n])
+        k += n
+    wc, wa = O.instance_evaluate_model(oracles["model"], dense, R, cone_scale=cone[0], blur_idx=None, patch_scale=1.0,
+                                       density_scale=100.0, composite_bkgd=True, instance_color=None)
+    gc, ga = got["color_pred"].cpu().numpy()[0], got["alpha_pred"].cpu().numpy()[0]
+    assert (wa > 0.05).mean() > 0.05 and wa.max() > 0.4
+    # density_scale 100 x 0.2 path length amplifies the bf16 error of sigma 20-fold (tolerance section)
+    print("instancer e2e: max |d alpha|", np.abs(ga - wa).max(), "max |d color|", np.abs(gc - wc).max(), "psnr", psnr(gc, wc))
+    assert np.abs(ga - wa).max() < 1e-2 and np.abs(gc - wc).max() < 1e-2, (np.abs(ga - wa).max(), np.abs(gc - wc).max())
+    assert psnr(gc, wc) > 45
