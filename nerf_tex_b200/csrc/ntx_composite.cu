@@ -161,6 +161,133 @@ composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ 
     }
 }
 
+// ---- packed fast path: two samples per lane -------------------------------------------------------------------
+// The one-sample-per-lane kernel above is issue-bound (ncu: ~170 warp instructions per 32 samples).  Here a lane
+// owns two consecutive samples, so one warp round covers 64 samples: the product scan, the depth shuffles, the
+// pointer arithmetic and the loop overhead are paid once per 64 samples, exp / reciprocal are single MUFU ops, and the
+// per-ray reductions of (r, g, b, acc) share six shuffles.  Needs the packed layout and an even S.
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+template <bool MAP_EXR>
+__device__ __forceinline__ float color_act2(float c) {                         // renderer.py:182-187
+    constexpr float kLog2e = 1.4426950408889634f;
+    if (MAP_EXR) return c > 0.0f ? c + 1.0f : ex2_approx(c * kLog2e);
+    return rcp_approx(1.0f + ex2_approx(-c * kLog2e));
+}
+// v *= (value of lane - o), for lanes >= o (the shuffle's own range predicate guards the multiply)
+__device__ __forceinline__ void scan_mul_step(float& v, int o) {
+    asm("{\n\t.reg .pred p;\n\t.reg .f32 t;\n\tshfl.sync.up.b32 t|p, %0, %1, 0, 0xffffffff;\n\t@p mul.f32 %0, %0, t;\n\t}"
+        : "+f"(v) : "r"(o));
+}
+
+struct PairIn {
+    float4 a, b;      // raw rgb-sigma of the lane's two samples
+    float2 z, n;      // depths, sigma noise
+};
+
+__device__ __forceinline__ PairIn load_pair(const float4* prow, const float2* zrow, const float2* nrow, int pair, int npairs) {
+    PairIn r;
+    r.a = make_float4(0.f, 0.f, 0.f, 0.f);
+    r.b = r.a;
+    r.z = make_float2(0.f, 0.f);
+    r.n = r.z;
+    if (pair < npairs) {
+        r.a = ldg_stream_f4(prow + 2 * pair);
+        r.b = ldg_stream_f4(prow + 2 * pair + 1);
+        r.z = __ldg(zrow + pair);
+        if (nrow) r.n = __ldg(nrow + pair);
+    }
+    return r;
+}
+
+template <bool MAP_EXR>
+__global__ void __launch_bounds__(256)
+composite_fwd2_kernel(const float4* __restrict__ rgbs, const float* __restrict__ z, const float* __restrict__ rays_d,
+                      const float* __restrict__ noise, int R, int S, int composite_bkgd, float bk0, float bk1, float bk2,
+                      float* __restrict__ color_map, float* __restrict__ alpha_map, float* __restrict__ weights,
+                      float* __restrict__ depth) {
+    constexpr float kLog2e = 1.4426950408889634f;
+    const int lane = threadIdx.x & 31;
+    const int npairs = S >> 1;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < R; ray += nwarps) {
+        const int64_t row0 = ray * S;
+        const float4* prow = rgbs + row0;
+        const float2* zrow = reinterpret_cast<const float2*>(z + row0);
+        const float2* nrow = noise ? reinterpret_cast<const float2*>(noise + row0) : nullptr;
+        float2* wrow = weights ? reinterpret_cast<float2*>(weights + row0) : nullptr;
+        PairIn cur = load_pair(prow, zrow, nrow, lane, npairs);
+        const float d0 = __ldg(rays_d + 3 * ray), d1 = __ldg(rays_d + 3 * ray + 1), d2 = __ldg(rays_d + 3 * ray + 2);
+        const float scale = -kLog2e * sqrtf(d0 * d0 + d1 * d1 + d2 * d2);      // renderer.py:180, folded into the exp2
+        float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f, dep = 0.0f;
+        for (int pbase = 0; pbase < npairs; pbase += 32) {
+            const int pair = pbase + lane;
+            const PairIn nxt = load_pair(prow, zrow, nrow, pair + 32, npairs);
+            // z of the sample after the lane's second one: first depth of lane + 1 (lane 31: of the next round)
+            float z_up = __shfl_down_sync(0xffffffffu, cur.z.x, 1);
+            const float z_next0 = __shfl_sync(0xffffffffu, nxt.z.x, 0);
+            if (lane == 31) z_up = z_next0;
+            const float dist0 = cur.z.y - cur.z.x;
+            const float dist1 = (pair == npairs - 1) ? dist0 : z_up - cur.z.y;   // last distance duplicated (:174-177)
+            // lanes past the end hold zeros: sigma 0 -> alpha 0 -> factor 1 (1 + 1e-10 rounds to 1)
+            const float s0 = fmaxf(cur.a.w + cur.n.x, 0.0f), s1 = fmaxf(cur.b.w + cur.n.y, 0.0f);   // renderer.py:190-195
+            const float a0 = 1.0f - ex2_approx(s0 * dist0 * scale);
+            const float a1 = 1.0f - ex2_approx(s1 * dist1 * scale);
+            const float om0 = (1.0f - a0) + 1e-10f, om1 = (1.0f - a1) + 1e-10f;                    // renderer.py:198
+            float incl = om0 * om1;
+            scan_mul_step(incl, 1);
+            scan_mul_step(incl, 2);
+            scan_mul_step(incl, 4);
+            scan_mul_step(incl, 8);
+            scan_mul_step(incl, 16);
+            float excl = __shfl_up_sync(0xffffffffu, incl, 1);
+            if (lane == 0) excl = 1.0f;
+            const float t0 = carry * excl;
+            const float w0 = a0 * t0;
+            const float w1 = a1 * (t0 * om0);
+            carry *= __shfl_sync(0xffffffffu, incl, 31);
+            if (wrow && pair < npairs) wrow[pair] = make_float2(w0, w1);
+            c0 += w0 * color_act2<MAP_EXR>(cur.a.x) + w1 * color_act2<MAP_EXR>(cur.b.x);           // renderer.py:201
+            c1 += w0 * color_act2<MAP_EXR>(cur.a.y) + w1 * color_act2<MAP_EXR>(cur.b.y);
+            c2 += w0 * color_act2<MAP_EXR>(cur.a.z) + w1 * color_act2<MAP_EXR>(cur.b.z);
+            dep += w0 * cur.z.x + w1 * cur.z.y;                                                     // renderer.py:204
+            acc += w0 + w1;                                                                         // renderer.py:207
+            cur = nxt;
+        }
+        // four sums in six shuffles: halves of the warp trade what the other half keeps
+        const bool h16 = lane & 16, h8 = lane & 8;
+        float x = (h16 ? c1 : c0) + __shfl_xor_sync(0xffffffffu, h16 ? c0 : c1, 16);
+        float y = (h16 ? acc : c2) + __shfl_xor_sync(0xffffffffu, h16 ? c2 : acc, 16);
+        float u = (h8 ? y : x) + __shfl_xor_sync(0xffffffffu, h8 ? x : y, 8);
+        u += __shfl_xor_sync(0xffffffffu, u, 4);
+        u += __shfl_xor_sync(0xffffffffu, u, 2);
+        u += __shfl_xor_sync(0xffffffffu, u, 1);
+        // lane 0: r, lane 16: g, lane 8: b, lane 24: acc
+        const float acc_all = __shfl_sync(0xffffffffu, u, 24);
+        if (depth) {                                                             // warp-uniform
+            dep = ntx_warp_sum(dep);
+            if (lane == 0) depth[ray] = dep;
+        }
+        if ((lane & 7) == 0) {
+            const int comp = (lane >> 4) | ((lane >> 2) & 2);
+            if (comp == 3) {
+                alpha_map[ray] = u;
+            } else {
+                const float bk = comp == 0 ? bk0 : comp == 1 ? bk1 : bk2;
+                color_map[3 * ray + comp] = composite_bkgd ? u + (1.0f - acc_all) * bk : u;       // renderer.py:210-211
+            }
+        }
+    }
+}
+
 // Backward w.r.t. the packed raw outputs.  Pass 1 recomputes the forward and accumulates
 // G = sum_k gw_k * w_k; pass 2 recomputes again and emits
 //   d a_i   = gw_i * T_i - (G - prefix_incl_i) / om_i
@@ -321,7 +448,15 @@ NTX_API int ntx_composite_forward(const float* color, const float* sigma, int pa
     const int threads = 256;
     const int grid = grid_for_warps(R, threads);
     cudaStream_t st = (cudaStream_t)stream;
-    if (packed)
+    const bool pairs = packed && (S & 1) == 0 &&
+                       ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(noise) | reinterpret_cast<uintptr_t>(weights)) & 7) == 0;
+    if (pairs && map_exr)
+        composite_fwd2_kernel<true><<<grid, threads, 0, st>>>(reinterpret_cast<const float4*>(color), z, rays_d, noise, R, S,
+                                                              composite_bkgd, b0, b1, b2, color_map, alpha_map, weights, depth);
+    else if (pairs)
+        composite_fwd2_kernel<false><<<grid, threads, 0, st>>>(reinterpret_cast<const float4*>(color), z, rays_d, noise, R, S,
+                                                               composite_bkgd, b0, b1, b2, color_map, alpha_map, weights, depth);
+    else if (packed)
         composite_fwd_kernel<true><<<grid, threads, 0, st>>>(color, sigma, z, rays_d, noise, R, S, map_exr,
                                                              composite_bkgd, b0, b1, b2, color_map, alpha_map,
                                                              weights, depth);
