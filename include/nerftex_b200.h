@@ -103,10 +103,10 @@ int ntx_composite_instanced_forward(const float* rgbs, const float* dists, const
  * ---------------------------------------------------------------------------------------- */
 
 /* Architecture of network/model.py:58-125 (ParamNerf; Nerf :9-45 is n_geo = n_app = 0,
- * color_depth = 0).  Supported by the sm_100a kernel: n_pos = 3, pos_freqs = 10, dir_freqs = 4,
+ * color_depth = 0).  Supported by the sm_100a kernel: n_pos = 3 (or 6, see below), pos_freqs = 10, dir_freqs = 4,
  * param_freqs = 4, width = 256, param_depth = 0, n_geo <= 3, n_app <= 7, depth <= 12. */
 typedef struct ntx_mlp_config {
-    int32_t n_pos;       /* 3 */
+    int32_t n_pos;       /* 3; 6 = IntegratedPositionalEncoding of (mean, diagonal covariance), network/layer.py:25-41 */
     int32_t pos_freqs;   /* 10 */
     int32_t dir_freqs;   /* 4 */
     int32_t param_freqs; /* 4 */
@@ -152,6 +152,7 @@ typedef struct ntx_mlp_inputs {
     int32_t blur_idx;        /* parameter index scaled by row_scale*group_scale, or -1 (:155-158) */
     int32_t rows_per_group;
     int64_t n_rows;          /* N */
+    const float* pos_cov;    /* [N,3] diagonal covariance of pos: required by (and only read for) n_pos = 6 models */
 } ntx_mlp_inputs;
 
 /* Forward.  Replaces the Keras model call of network/renderer.py:160-161 / :290-291 including
@@ -227,6 +228,28 @@ int ntx_mlp_enc_columns(const ntx_mlp_t* mlp, int phase, int32_t* ref_index);
 int ntx_rays_from_camera(const float* image_plane_loc, int64_t n, int height, int width, float focal,
                          const float* c2w, int normalize, const float* b0, const float* b1, float near_, float far_,
                          float* rays_o, float* rays_d, float* t, float* cone_scale, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * mip variants (network/renderer.py:356-587): cone-segment gaussians + compositing over S + 1 depth edges.
+ * The integrated positional encoding itself (network/layer.py:25-41) is the n_pos = 6 mode of the fused MLP kernel.
+ * ---------------------------------------------------------------------------------------- */
+
+/* MipRenderer.get_cone_segment_gaussians (renderer.py:411-434): z_edges[R,S+1], radii[R] (blur parameter * cone
+ * scale, :384) -> mean[R,S,3], cov[R,S,3] (diagonal). */
+int ntx_mip_cone_gaussians(const float* rays_o, const float* rays_d, const float* z_edges, const float* radii, int R,
+                           int S, float* mean, float* cov, void* stream);
+/* MipInstanceRenderer.get_cone_segment_gaussians (renderer.py:570-587) on packed in-shell samples: dirs[T,3],
+ * t[T], radii[T] (blur * cone scale / patch scale, :511), dists[T] -> cov[T,3]. */
+int ntx_mip_cone_gaussians_instanced(const float* dirs, const float* t, const float* radii, const float* dists,
+                                     int64_t T, float* cov, void* stream);
+/* MipRenderer.map_model_output (renderer.py:436-473): like ntx_composite_forward / _backward on packed rgbs[R,S,4],
+ * but z_edges[R,S+1] delimits the S segments, so no distance is duplicated (:440). */
+int ntx_composite_edges_forward(const float* rgbs, const float* z_edges, const float* rays_d, const float* noise,
+                                int R, int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                                float* color_map, float* alpha_map, float* weights, void* stream);
+int ntx_composite_edges_backward(const float* rgbs, const float* z_edges, const float* rays_d, const float* noise,
+                                 int R, int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                                 const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Shell instancer (the caller in front of the hot path)

@@ -38,7 +38,7 @@ class RenderConfig(C.Structure):
 class MlpInputs(C.Structure):
     _fields_ = [("pos", C.c_void_p), ("rays_o", C.c_void_p), ("rays_d", C.c_void_p), ("z", C.c_void_p),
                 ("dir", C.c_void_p), ("params", C.c_void_p), ("row_scale", C.c_void_p), ("group_scale", C.c_void_p),
-                ("blur_idx", C.c_int32), ("rows_per_group", C.c_int32), ("n_rows", C.c_int64)]
+                ("blur_idx", C.c_int32), ("rows_per_group", C.c_int32), ("n_rows", C.c_int64), ("pos_cov", C.c_void_p)]
 
 
 # name -> (restype, argtypes); must list every symbol include/nerftex_b200.h declares.
@@ -72,6 +72,10 @@ SIGNATURES = {
     "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),
     "ntx_rays_from_camera": (_I, [_P, _I64, _I, _I, _F, _P, _I, _P, _P, _F, _F, _P, _P, _P, _P, _P]),
     "ntx_normalize_dirs": (_I, [_P, _I, _P, _P]),
+    "ntx_mip_cone_gaussians": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _P]),
+    "ntx_mip_cone_gaussians_instanced": (_I, [_P, _P, _P, _P, _I64, _P, _P]),
+    "ntx_composite_edges_forward": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
+    "ntx_composite_edges_backward": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
     "ntx_instancer_workspace_bytes": (_I64, [_I]),
     "ntx_instancer_trace": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _F, _I, _U32, _I, _P, _P, _P, _P]),
     "ntx_instancer_march": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _F, _I, _U32, _I, _I, _I, _P, _P] + [_P] * 7 + [_P]),

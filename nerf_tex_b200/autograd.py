@@ -51,7 +51,7 @@ class MlpSchedule:
 
 
 def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, rays_o=None, rays_d=None, z=None,
-                      row_scale=None, group_scale=None, blur_idx=None, row_major_acts: bool = False):
+                      row_scale=None, group_scale=None, blur_idx=None, row_major_acts: bool = False, pos_cov=None):
     """Raw rgbs[N,4] plus the saved operands: (enc_pos, enc_dir, acts_img, masks[, acts])."""
     packed = model.ensure_packed()
     sched = model.schedule()
@@ -78,7 +78,7 @@ def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, r
     masks = torch.empty((sched.n_steps, n_tiles * 128, 8), dtype=torch.int32, device=dev)
     acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev) if row_major_acts else None
     inp = MlpInputs(ptr(pos), ptr(rays_o), ptr(rays_d), ptr(z), ptr(dir), ptr(params), ptr(row_scale), ptr(group_scale),
-                    -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows))
+                    -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows), ptr(pos_cov))
     check(lib.ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
                                     ptr(acts), ptr(acts_img), ptr(masks), n_tiles, stream_ptr()))
     return rgbs, (enc_pos, enc_dir, acts_img, masks, acts, n_rows)
@@ -232,3 +232,33 @@ class NetworkPass(torch.autograd.Function):
         release_saved(ctx.model, ctx.saved)
         ctx.saved = None
         return (grad,) + (None,) * 12
+
+
+class MipNetworkPass(torch.autograd.Function):
+    """(master, mean, cov, ...) -> (color_map, alpha_map, weights): the mip renderer's network pass over one ray
+    chunk (network/renderer.py:388-396): integrated encoding of explicit cone gaussians, S + 1 depth edges."""
+
+    @staticmethod
+    def forward(ctx, master, model, mean, cov, rays_d, rays_d_n, z_edges, parameters, noise, map_exr, composite_bkgd,
+                bkgd_color):
+        R, S = z_edges.shape[0], z_edges.shape[1] - 1
+        npar = parameters.shape[1] if parameters is not None else 0
+        rgbs, saved = mlp_forward_train(model, n_rows=R * S, pos=mean.reshape(-1, 3), pos_cov=cov.reshape(-1, 3),
+                                        dir=rays_d_n, params=parameters if npar > 0 else None, rows_per_group=S)
+        rgbs = rgbs.view(R, S, 4)
+        cmap, amap, w = ops.composite_edges_forward(rgbs, z_edges, rays_d, noise=noise, map_exr=map_exr,
+                                                    composite_bkgd=composite_bkgd, bkgd_color=bkgd_color)
+        ctx.model, ctx.saved = model, saved
+        ctx.misc = (rgbs, z_edges, rays_d, noise, map_exr, composite_bkgd, bkgd_color)
+        ctx.mark_non_differentiable(w)
+        return cmap, amap, w
+
+    @staticmethod
+    def backward(ctx, d_cmap, d_amap, d_w):
+        rgbs, z_edges, rays_d, noise, map_exr, composite_bkgd, bkgd_color = ctx.misc
+        d_rgbs = ops.composite_edges_backward(rgbs, z_edges, rays_d, d_cmap.contiguous(), d_amap.contiguous(), noise=noise,
+                                              map_exr=map_exr, composite_bkgd=composite_bkgd, bkgd_color=bkgd_color)
+        grad = mlp_backward_native(ctx.model, ctx.saved, d_rgbs.view(-1, 4))
+        release_saved(ctx.model, ctx.saved)
+        ctx.saved = None
+        return (grad,) + (None,) * 11

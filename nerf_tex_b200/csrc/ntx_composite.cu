@@ -68,7 +68,8 @@ __device__ __forceinline__ Sample load_sample(const float* color, const float* s
 }
 
 // distance of sample i to the next one; the last distance is duplicated (renderer.py:174-177)
-__device__ __forceinline__ float sample_dist(const float* zrow, int i, int S, float zi) {
+__device__ __forceinline__ float sample_dist(const float* zrow, int i, int S, float zi, int edges) {
+    if (edges) return __ldg(zrow + i + 1) - zi;          // S + 1 segment edges (mip renderer, renderer.py:440)
     if (S == 1) return 0.0f;
     if (i < S - 1) return __ldg(zrow + i + 1) - zi;
     return zi - __ldg(zrow + i - 1);
@@ -82,15 +83,15 @@ struct RoundIn {
 
 template <bool PACKED>
 __device__ __forceinline__ RoundIn load_round(const float* color, const float* sigma, const float* zrow,
-                                              const float* noise, int64_t row0, int i, int S) {
+                                              const float* noise, int64_t row0, int i, int S, int edges) {
     RoundIn r;
     r.sm = {0.f, 0.f, 0.f, 0.f};
     r.z = 0.0f; r.nz = 0.0f;
     if (i < S) {
         r.sm = load_sample<PACKED>(color, sigma, row0 + i);
-        r.z = __ldg(zrow + i);
         if (noise) r.nz = __ldg(noise + row0 + i);
     }
+    if (i < S + edges) r.z = __ldg(zrow + i);            // edges: one more depth than samples
     return r;
 }
 
@@ -99,21 +100,21 @@ __global__ void __launch_bounds__(256)
 composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ sigma, const float* __restrict__ z,
                      const float* __restrict__ rays_d, const float* __restrict__ noise, int R, int S, int map_exr,
                      int composite_bkgd, float bk0, float bk1, float bk2, float* __restrict__ color_map,
-                     float* __restrict__ alpha_map, float* __restrict__ weights, float* __restrict__ depth) {
+                     float* __restrict__ alpha_map, float* __restrict__ weights, float* __restrict__ depth, int edges) {
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < R; ray += nwarps) {
         const int64_t row0 = ray * S;
-        const float* zrow = z + row0;
+        const float* zrow = z + ray * (S + edges);
         // software pipeline: the loads of round r+1 are in flight while round r is scanned
-        RoundIn cur = load_round<PACKED>(color, sigma, zrow, noise, row0, lane, S);
+        RoundIn cur = load_round<PACKED>(color, sigma, zrow, noise, row0, lane, S, edges);
         const float d0 = __ldg(rays_d + 3 * ray), d1 = __ldg(rays_d + 3 * ray + 1), d2 = __ldg(rays_d + 3 * ray + 2);
         const float norm = sqrtf(d0 * d0 + d1 * d1 + d2 * d2);                 // renderer.py:180
         float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f, dep = 0.0f, prev_z31 = 0.0f;
         for (int base = 0; base < S; base += 32) {
             const int i = base + lane;
             const bool valid = i < S;
-            const RoundIn nxt = load_round<PACKED>(color, sigma, zrow, noise, row0, i + 32, S);
+            const RoundIn nxt = load_round<PACKED>(color, sigma, zrow, noise, row0, i + 32, S, edges);
             // neighbours' depths by shuffle: z[i+1] from lane+1 (lane 31: next round's lane 0),
             // z[i-1] from lane-1 (lane 0: previous round's lane 31)
             float z_up = __shfl_down_sync(0xffffffffu, cur.z, 1);
@@ -125,7 +126,7 @@ composite_fwd_kernel(const float* __restrict__ color, const float* __restrict__ 
             float a = 0.0f;
             if (valid) {
                 // last distance duplicated (renderer.py:174-177)
-                float dist = (S == 1) ? 0.0f : (i < S - 1 ? z_up - cur.z : cur.z - z_dn);
+                float dist = edges ? z_up - cur.z : (S == 1) ? 0.0f : (i < S - 1 ? z_up - cur.z : cur.z - z_dn);
                 dist *= norm;
                 const float s = fmaxf(cur.sm.s + cur.nz, 0.0f);                 // renderer.py:190-195
                 a = 1.0f - __expf(-s * dist);
@@ -297,7 +298,7 @@ __global__ void __launch_bounds__(256)
 composite_bwd_kernel(const float* __restrict__ rgbs, const float* __restrict__ z, const float* __restrict__ rays_d,
                      const float* __restrict__ noise, int R, int S, int map_exr, int composite_bkgd, float bk0,
                      float bk1, float bk2, const float* __restrict__ d_color_map,
-                     const float* __restrict__ d_alpha_map, float* __restrict__ d_rgbs) {
+                     const float* __restrict__ d_alpha_map, float* __restrict__ d_rgbs, int edges) {
     const int lane = threadIdx.x & 31;
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t ray = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; ray < R; ray += nwarps) {
@@ -307,7 +308,7 @@ composite_bwd_kernel(const float* __restrict__ rgbs, const float* __restrict__ z
                     g2 = __ldg(d_color_map + 3 * ray + 2);
         float gA = __ldg(d_alpha_map + ray);
         if (composite_bkgd) gA -= g0 * bk0 + g1 * bk1 + g2 * bk2;
-        const float* zrow = z + ray * S;
+        const float* zrow = z + ray * (S + edges);
         float G = 0.0f;
         for (int pass = 0; pass < 2; ++pass) {
             float carry = 1.0f, gcarry = 0.0f, gsum = 0.0f;
@@ -320,7 +321,7 @@ composite_bwd_kernel(const float* __restrict__ rgbs, const float* __restrict__ z
                     const int64_t k = ray * S + i;
                     v = __ldg(reinterpret_cast<const float4*>(rgbs) + k);
                     const float zi = __ldg(zrow + i);
-                    dist = sample_dist(zrow, i, S, zi) * norm;
+                    dist = sample_dist(zrow, i, S, zi, edges) * norm;
                     sraw = v.w;
                     if (noise) sraw += __ldg(noise + k);
                     a = 1.0f - expf(-fmaxf(sraw, 0.0f) * dist);
@@ -433,10 +434,10 @@ int grid_for_warps(int64_t n_warp_items, int threads) {
 
 }  // namespace
 
-NTX_API int ntx_composite_forward(const float* color, const float* sigma, int packed, const float* z,
+static int composite_forward_impl(const float* color, const float* sigma, int packed, const float* z,
                                   const float* rays_d, const float* noise, int R, int S, int map_exr,
                                   int composite_bkgd, const float* bkgd_color, float* color_map, float* alpha_map,
-                                  float* weights, float* depth, void* stream) {
+                                  float* weights, float* depth, int edges, void* stream) {
     NTX_REQUIRE(R >= 0 && S >= 1, "composite_forward: bad shape R=%d S=%d", R, S);
     if (R == 0) return NTX_OK;
     NTX_REQUIRE(color && z && rays_d && color_map && alpha_map, "composite_forward: null pointer");
@@ -448,7 +449,7 @@ NTX_API int ntx_composite_forward(const float* color, const float* sigma, int pa
     const int threads = 256;
     const int grid = grid_for_warps(R, threads);
     cudaStream_t st = (cudaStream_t)stream;
-    const bool pairs = packed && (S & 1) == 0 &&
+    const bool pairs = !edges && packed && (S & 1) == 0 &&
                        ((reinterpret_cast<uintptr_t>(z) | reinterpret_cast<uintptr_t>(noise) | reinterpret_cast<uintptr_t>(weights)) & 7) == 0;
     if (pairs && map_exr)
         composite_fwd2_kernel<true><<<grid, threads, 0, st>>>(reinterpret_cast<const float4*>(color), z, rays_d, noise, R, S,
@@ -459,18 +460,33 @@ NTX_API int ntx_composite_forward(const float* color, const float* sigma, int pa
     else if (packed)
         composite_fwd_kernel<true><<<grid, threads, 0, st>>>(color, sigma, z, rays_d, noise, R, S, map_exr,
                                                              composite_bkgd, b0, b1, b2, color_map, alpha_map,
-                                                             weights, depth);
+                                                             weights, depth, edges);
     else
         composite_fwd_kernel<false><<<grid, threads, 0, st>>>(color, sigma, z, rays_d, noise, R, S, map_exr,
                                                               composite_bkgd, b0, b1, b2, color_map, alpha_map,
-                                                              weights, depth);
+                                                              weights, depth, edges);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
 
-NTX_API int ntx_composite_backward(const float* rgbs, const float* z, const float* rays_d, const float* noise, int R,
+NTX_API int ntx_composite_forward(const float* color, const float* sigma, int packed, const float* z,
+                                  const float* rays_d, const float* noise, int R, int S, int map_exr,
+                                  int composite_bkgd, const float* bkgd_color, float* color_map, float* alpha_map,
+                                  float* weights, float* depth, void* stream) {
+    return composite_forward_impl(color, sigma, packed, z, rays_d, noise, R, S, map_exr, composite_bkgd, bkgd_color,
+                                  color_map, alpha_map, weights, depth, 0, stream);
+}
+
+NTX_API int ntx_composite_edges_forward(const float* rgbs, const float* z_edges, const float* rays_d, const float* noise,
+                                        int R, int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                                        float* color_map, float* alpha_map, float* weights, void* stream) {
+    return composite_forward_impl(rgbs, nullptr, 1, z_edges, rays_d, noise, R, S, map_exr, composite_bkgd, bkgd_color,
+                                  color_map, alpha_map, weights, nullptr, 1, stream);
+}
+
+static int composite_backward_impl(const float* rgbs, const float* z, const float* rays_d, const float* noise, int R,
                                    int S, int map_exr, int composite_bkgd, const float* bkgd_color,
-                                   const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream) {
+                                   const float* d_color_map, const float* d_alpha_map, float* d_rgbs, int edges, void* stream) {
     NTX_REQUIRE(R >= 0 && S >= 1, "composite_backward: bad shape R=%d S=%d", R, S);
     if (R == 0) return NTX_OK;
     NTX_REQUIRE(rgbs && z && rays_d && d_color_map && d_alpha_map && d_rgbs, "composite_backward: null pointer");
@@ -480,9 +496,23 @@ NTX_API int ntx_composite_backward(const float* rgbs, const float* z, const floa
                 b2 = composite_bkgd ? bkgd_color[2] : 0.f;
     const int threads = 256;
     composite_bwd_kernel<<<grid_for_warps(R, threads), threads, 0, (cudaStream_t)stream>>>(
-        rgbs, z, rays_d, noise, R, S, map_exr, composite_bkgd, b0, b1, b2, d_color_map, d_alpha_map, d_rgbs);
+        rgbs, z, rays_d, noise, R, S, map_exr, composite_bkgd, b0, b1, b2, d_color_map, d_alpha_map, d_rgbs, edges);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
+}
+
+NTX_API int ntx_composite_backward(const float* rgbs, const float* z, const float* rays_d, const float* noise, int R,
+                                   int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                                   const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream) {
+    return composite_backward_impl(rgbs, z, rays_d, noise, R, S, map_exr, composite_bkgd, bkgd_color, d_color_map,
+                                   d_alpha_map, d_rgbs, 0, stream);
+}
+
+NTX_API int ntx_composite_edges_backward(const float* rgbs, const float* z_edges, const float* rays_d, const float* noise,
+                                         int R, int S, int map_exr, int composite_bkgd, const float* bkgd_color,
+                                         const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream) {
+    return composite_backward_impl(rgbs, z_edges, rays_d, noise, R, S, map_exr, composite_bkgd, bkgd_color, d_color_map,
+                                   d_alpha_map, d_rgbs, 1, stream);
 }
 
 NTX_API int ntx_composite_instanced_forward(const float* rgbs, const float* dists, const float* alpha_weight,

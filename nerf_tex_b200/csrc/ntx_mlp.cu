@@ -335,12 +335,17 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
             const bool valid = grow < n_rows;
             // ------------------------------------------------------------- load this row's inputs
             float x[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 0.f}, pg[3] = {0.f, 0.f, 0.f};
+            float xv[3] = {0.f, 0.f, 0.f};          // diagonal covariance of the position (integrated encoding only)
             float pa[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
             if (valid) {
                 const int64_t grp = grow / args.in.rows_per_group;
                 if (args.in.pos) {
 #pragma unroll
                     for (int i = 0; i < 3; ++i) x[i] = __ldg(args.in.pos + 3 * grow + i);
+                    if (prog.ipe) {
+#pragma unroll
+                        for (int i = 0; i < 3; ++i) xv[i] = __ldg(args.in.pos_cov + 3 * grow + i);
+                    }
                 } else {
                     const float zz = __ldg(args.in.z + grow);                   // renderer.py:114
 #pragma unroll
@@ -379,11 +384,17 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                         if (k == 0) sincosf(x[i], &s, &c);
                         else if (k == 5) sincosf(32.0f * x[i], &s, &c);     // restart: bounds the doubling error
                         else { const float s2 = 2.0f * s * c; c = 1.0f - 2.0f * s * s; s = s2; }
-                        w[i * 10 + k] = pack_bf16(s, c);
+                        if (prog.ipe) {
+                            // E[sin(2^k x)] for x ~ N(mean, var): sin(2^k mean) * exp(-var * 4^k / 2)   (layer.py:33-41)
+                            const float att = __expf(-0.5f * (float)(1 << (2 * k)) * xv[i]);
+                            w[i * 10 + k] = pack_bf16(s * att, c * att);
+                        } else {
+                            w[i * 10 + k] = pack_bf16(s, c);
+                        }
                     }
                 }
-                w[30] = pack_bf16(1.0f, x[0]);
-                w[31] = pack_bf16(x[1], x[2]);
+                w[30] = pack_bf16(1.0f, prog.ipe ? 0.0f : x[0]);            // no identity term in the integrated encoding
+                w[31] = prog.ipe ? 0u : pack_bf16(x[1], x[2]);
                 auto put = [&](int q, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t w3) {
                     st_shared_v4(chunk_addr(enc_base, q, row), w0, w1, w2, w3);
                 };
@@ -606,7 +617,7 @@ __global__ void mlp_pack_kernel(const __grid_constant__ Program prog, const floa
         if (half >= h0 && half < h0 + nh) {
             if (slice_is_enc(sl)) {
                 const int col = slice_blk(sl) * 32 + kk;
-                const int ref = step.phase == 0 ? pos_col_to_ref(col, prog.n_geo) : dir_col_to_ref(col, prog.n_app);
+                const int ref = step.phase == 0 ? pos_col_to_ref(col, prog.n_geo, prog.ipe) : dir_col_to_ref(col, prog.n_app);
                 if (ref == kRefOnes) v = master[L.b_off + n];
                 else if (ref >= 0 && step.enc_data) v = master[L.w_off + (int64_t)ref * L.fan_out + n];
             } else {
@@ -624,7 +635,8 @@ int build_program(ntx_mlp* m) {
     memset(&p, 0, sizeof(p));
     const int g = c.n_geo, a = c.n_app, W = c.width;
     p.n_geo = g; p.n_app = a;
-    p.P = c.n_pos * (1 + 2 * c.pos_freqs) + g * (1 + 2 * c.param_freqs);
+    p.ipe = c.n_pos == 6;
+    p.P = (p.ipe ? 6 * c.pos_freqs : 3 * (1 + 2 * c.pos_freqs)) + g * (1 + 2 * c.param_freqs);   // layer.py:21-23 / :33-37
     p.D = 3 * (1 + 2 * c.dir_freqs) + a * (1 + 2 * c.param_freqs);
 
     // ---- Dense layer table in graph order (model.py:104-123)
@@ -699,8 +711,8 @@ int build_program(ntx_mlp* m) {
 NTX_API int ntx_mlp_create(const ntx_mlp_config* cfg, ntx_mlp_t** out) {
     NTX_REQUIRE(cfg && out, "mlp_create: null pointer");
     const ntx_mlp_config& c = *cfg;
-    if (!(c.n_pos == 3 && c.pos_freqs == 10 && c.dir_freqs == 4 && c.param_freqs == 4 && c.width == 256)) {
-        ntx_set_error("mlp_create: the sm_100a kernel implements n_pos=3, pos_freqs=10, dir_freqs=4, param_freqs=4, "
+    if (!((c.n_pos == 3 || c.n_pos == 6) && c.pos_freqs == 10 && c.dir_freqs == 4 && c.param_freqs == 4 && c.width == 256)) {
+        ntx_set_error("mlp_create: the sm_100a kernel implements n_pos=3 (or 6: integrated encoding), pos_freqs=10, dir_freqs=4, param_freqs=4, "
                       "width=256 (got %d,%d,%d,%d,%d)", c.n_pos, c.pos_freqs, c.dir_freqs, c.param_freqs, c.width);
         return NTX_E_UNSUPPORTED;
     }
@@ -765,6 +777,7 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     if (in->n_rows == 0) return NTX_OK;
     NTX_REQUIRE(rgbs && in->dir, "mlp_forward: null rgbs / dir");
     NTX_REQUIRE(in->pos || (in->rays_o && in->rays_d && in->z), "mlp_forward: need pos, or rays_o + rays_d + z");
+    NTX_REQUIRE(!mlp->prog.ipe || (in->pos && in->pos_cov), "mlp_forward: an n_pos = 6 model needs pos (means) and pos_cov (variances)");
     NTX_REQUIRE(in->rows_per_group >= 1, "mlp_forward: rows_per_group must be >= 1");
     const int np = mlp->cfg.n_geo + mlp->cfg.n_app;
     NTX_REQUIRE(np == 0 || in->params, "mlp_forward: the model takes %d parameters but params is NULL", np);
@@ -860,6 +873,6 @@ NTX_API int ntx_mlp_step_info(const ntx_mlp_t* mlp, int st, int32_t* layer, int3
 NTX_API int ntx_mlp_enc_columns(const ntx_mlp_t* mlp, int phase, int32_t* ref_index) {
     NTX_REQUIRE(mlp && ref_index && (phase == 0 || phase == 1), "mlp_enc_columns: bad argument");
     for (int c = 0; c < kEncCols; ++c)
-        ref_index[c] = phase == 0 ? pos_col_to_ref(c, mlp->prog.n_geo) : dir_col_to_ref(c, mlp->prog.n_app);
+        ref_index[c] = phase == 0 ? pos_col_to_ref(c, mlp->prog.n_geo, mlp->prog.ipe) : dir_col_to_ref(c, mlp->prog.n_app);
     return NTX_OK;
 }

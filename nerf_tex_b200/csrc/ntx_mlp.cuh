@@ -78,6 +78,7 @@ struct Layer {
 struct Program {
     int32_t n_steps, n_slices;
     int32_t n_geo, n_app;
+    int32_t ipe;                  // 1: integrated positional encoding of (mean, variance) inputs (layer.py:25-41)
     int32_t P, D;                 // reference encoded widths (72 / 63 for n_parameters [1,4])
     int32_t alpha_layer, rgb_layer;
     Step steps[kMaxSteps];
@@ -89,14 +90,19 @@ struct Program {
 
 constexpr int kRefOnes = -1, kRefZero = -2;
 
-// our pos-phase column -> index into the reference's pos_inputs_map (model.py:77,88-93)
-__host__ __device__ inline int pos_col_to_ref(int col, int g) {
-    if (col < 60) { int i = col / 20, r = col % 20, k = r >> 1, c = r & 1; return 3 + 6 * k + 3 * c + i; }
+// our pos-phase column -> index into the reference's pos_inputs_map (model.py:77,88-93).  With the integrated
+// encoding (layer.py:33-37) the map has no identity term and is ordered [sin block, cos block], each frequency-major.
+__host__ __device__ inline int pos_col_to_ref(int col, int g, int ipe = 0) {
+    const int base = ipe ? 60 : 63;
+    if (col < 60) {
+        int i = col / 20, r = col % 20, k = r >> 1, c = r & 1;
+        return ipe ? 30 * c + 3 * k + i : 3 + 6 * k + 3 * c + i;
+    }
     if (col == 60) return kRefOnes;
-    if (col < 64) return col - 61;
+    if (col < 64) return ipe ? kRefZero : col - 61;
     int q = (col - 64) >> 3, e = (col - 64) & 7;
-    if (q < g) { int k = e >> 1, c = e & 1; return 63 + g + 2 * g * k + g * c + q; }
-    if (q == g && e < g) return 63 + e;
+    if (q < g) { int k = e >> 1, c = e & 1; return base + g + 2 * g * k + g * c + q; }
+    if (q == g && e < g) return base + e;
     return kRefZero;
 }
 // our dir-phase column -> index into the reference's dir_inputs_map (model.py:78,96-101)

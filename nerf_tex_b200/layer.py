@@ -1,6 +1,6 @@
-"""Input encodings (network/layer.py).  In this package the Fourier features are computed inside
-the fused MLP kernel; the class below only carries the configuration, plus a standalone
-callable for users who want the features themselves."""
+"""Input encodings (network/layer.py).  In this package both encodings are computed inside the fused MLP
+kernel; the classes below only carry the configuration, plus a standalone callable for users who want the
+features themselves."""
 
 from __future__ import annotations
 
@@ -25,7 +25,19 @@ class FourierFeatures:
 
 
 class IntegratedPositionalEncoding:
-    """network/layer.py:25-41 — configuration holder; the mip renderers are not built yet."""
+    """network/layer.py:25-41: inputs [mean(3), diagonal covariance(3)] ->
+    concat([sin(y), sin(y + pi/2)]) * exp(-y_var / 2) with y = mean * 2^k, y_var = cov * 4^k, frequency-major."""
 
     def __init__(self, n_freq_bands: int) -> None:
         self.n_freq_bands = int(n_freq_bands)
+
+    def out_dim(self, d: int = 6) -> int:
+        return 6 * self.n_freq_bands
+
+    def __call__(self, inputs: torch.Tensor) -> torch.Tensor:
+        import math
+        freq = 2.0 ** torch.arange(self.n_freq_bands, dtype=torch.float32, device=inputs.device)
+        y = (inputs[..., None, :3] * freq[:, None]).reshape(-1, 3 * self.n_freq_bands)
+        y_var = (inputs[..., None, 3:] * freq[:, None] ** 2).reshape(-1, 3 * self.n_freq_bands)
+        x = torch.cat([y, y + 0.5 * math.pi], -1)
+        return torch.sin(x) * torch.exp(-0.5 * torch.cat([y_var, y_var], -1))

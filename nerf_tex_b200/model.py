@@ -16,7 +16,7 @@ import torch
 
 from . import _lib, util
 from ._lib import MlpConfig, MlpInputs, as_cuda, check, ptr, stream_ptr
-from .layer import FourierFeatures  # noqa: F401  (configs name network.model.FourierFeatures)
+from .layer import FourierFeatures, IntegratedPositionalEncoding  # noqa: F401  (configs name network.model.<layer>)
 
 
 class FusedNerfTexMLP:
@@ -117,13 +117,15 @@ class FusedNerfTexMLP:
     # -- forward ----------------------------------------------------------------------------
     def forward_rows(self, *, n_rows: int, dir: torch.Tensor, params: Optional[torch.Tensor], rows_per_group: int,
                      pos: Optional[torch.Tensor] = None, rays_o=None, rays_d=None, z=None, row_scale=None,
-                     group_scale=None, blur_idx: Optional[int] = None, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+                     group_scale=None, blur_idx: Optional[int] = None, out: Optional[torch.Tensor] = None,
+                     pos_cov: Optional[torch.Tensor] = None) -> torch.Tensor:
         """Raw rgbs[N,4] for N rows; see ``ntx_mlp_inputs`` in include/nerftex_b200.h."""
         packed = self.ensure_packed()
         if out is None:
             out = torch.empty((n_rows, 4), dtype=torch.float32, device=self.device)
         inp = MlpInputs(ptr(pos), ptr(rays_o), ptr(rays_d), ptr(z), ptr(dir), ptr(params), ptr(row_scale),
-                        ptr(group_scale), -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows))
+                        ptr(group_scale), -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows),
+                        ptr(pos_cov))
         check(_lib.load().ntx_mlp_forward(self._h, ptr(packed), C.byref(inp), ptr(out), stream_ptr()))
         return out
 
@@ -135,20 +137,26 @@ class FusedNerfTexMLP:
         params = as_cuda(params, device=self.device) if npar > 0 else None
         if params is not None:
             assert params.shape == (n, npar), f"params must be [N,{npar}]"
-        rgbs = self.forward_rows(n_rows=n, pos=pos, dir=dirs, params=params, rows_per_group=1)
+        cov = None
+        if self.cfg.n_pos == 6:                                  # [mean, diagonal covariance] (renderer.py:390)
+            assert pos.shape[1] == 6, "an n_pos = 6 model takes pos[N,6] = [mean, cov_diag]"
+            pos, cov = pos[:, :3].contiguous(), pos[:, 3:].contiguous()
+        rgbs = self.forward_rows(n_rows=n, pos=pos, pos_cov=cov, dir=dirs, params=params, rows_per_group=1)
         return rgbs[:, :3], rgbs[:, 3:4]
 
 
-def _freqs(cfg, default: int) -> int:
+def _freqs(cfg, default: int, kind: str = "FourierFeatures") -> int:
+    """n_freq_bands of an embedding config (dict naming network.layer.* or an instance); checks its class."""
     if cfg is None:
         return default
     if isinstance(cfg, dict):
-        mod = util.resolve_path(cfg.get("module", ""))
-        if not mod.endswith("FourierFeatures"):
-            raise NotImplementedError(f"embedding {cfg.get('module')} is not implemented on the sm_100a path "
-                                      f"(only FourierFeatures)")
-        return int(cfg["n_freq_bands"])
-    return int(cfg.n_freq_bands)
+        name = util.resolve_path(cfg.get("module", "")).split(".")[-1]
+        n = int(cfg["n_freq_bands"])
+    else:
+        name, n = type(cfg).__name__, int(cfg.n_freq_bands)
+    if name != kind:
+        raise NotImplementedError(f"embedding {name} is not implemented here on the sm_100a path (expected {kind})")
+    return n
 
 
 def ParamNerf(pos_embedding, dir_embedding, param_embedding, n_parameters: Union[int, list], n_pos: int = 3,
@@ -163,8 +171,11 @@ def ParamNerf(pos_embedding, dir_embedding, param_embedding, n_parameters: Union
                                   "shipped config and not implemented in the fused kernel")
     if embedding_config is not None:
         raise NotImplementedError("embedding_config names an embedding class that does not exist in the reference")
+    if n_pos not in (3, 6):
+        raise NotImplementedError("n_pos must be 3 (FourierFeatures) or 6 (IntegratedPositionalEncoding of mean + variance)")
+    pos_kind = "IntegratedPositionalEncoding" if n_pos == 6 else "FourierFeatures"     # layer.py:8-41
     m = FusedNerfTexMLP(n_geo=int(n_parameters[0]), n_app=int(n_parameters[1]), depth=depth, width=width, skips=skips,
-                        color_depth=color_depth, pos_freqs=_freqs(pos_embedding, 10), dir_freqs=_freqs(dir_embedding, 4),
+                        color_depth=color_depth, pos_freqs=_freqs(pos_embedding, 10, pos_kind), dir_freqs=_freqs(dir_embedding, 4),
                         param_freqs=_freqs(param_embedding, 4), n_pos=n_pos, name=name, seed=seed)
     return {name: m}
 

@@ -118,6 +118,59 @@ def composite_backward(rgbs, z, rays_d, d_color_map, d_alpha_map, *, noise=None,
     return d_rgbs
 
 
+def composite_edges_forward(rgbs, z_edges, rays_d, *, noise=None, map_exr=False, composite_bkgd=False,
+                            bkgd_color=(1., 1., 1.), want_weights: bool = True):
+    """MipRenderer.map_model_output (network/renderer.py:436-473): rgbs[R,S,4], z_edges[R,S+1]."""
+    rgbs, z_edges, rays_d = as_cuda(rgbs), as_cuda(z_edges), as_cuda(rays_d)
+    R, S = rgbs.shape[0], rgbs.shape[1]
+    assert z_edges.shape == (R, S + 1) and rgbs.shape == (R, S, 4)
+    if noise is not None:
+        noise = as_cuda(noise)
+    dev = rgbs.device
+    cmap = torch.empty((R, 3), dtype=torch.float32, device=dev)
+    amap = torch.empty((R,), dtype=torch.float32, device=dev)
+    w = torch.empty((R, S), dtype=torch.float32, device=dev) if want_weights else None
+    check(_lib.load().ntx_composite_edges_forward(ptr(rgbs), ptr(z_edges), ptr(rays_d), ptr(noise), R, S, int(map_exr),
+                                                  int(composite_bkgd), _bkgd(bkgd_color), ptr(cmap), ptr(amap), ptr(w),
+                                                  stream_ptr()))
+    return cmap, amap, w
+
+
+def composite_edges_backward(rgbs, z_edges, rays_d, d_color_map, d_alpha_map, *, noise=None, map_exr=False,
+                             composite_bkgd=False, bkgd_color=(1., 1., 1.)) -> torch.Tensor:
+    rgbs, z_edges, rays_d = as_cuda(rgbs), as_cuda(z_edges), as_cuda(rays_d)
+    d_color_map, d_alpha_map = as_cuda(d_color_map), as_cuda(d_alpha_map)
+    R, S = rgbs.shape[0], rgbs.shape[1]
+    if noise is not None:
+        noise = as_cuda(noise)
+    d_rgbs = torch.empty_like(rgbs)
+    check(_lib.load().ntx_composite_edges_backward(ptr(rgbs), ptr(z_edges), ptr(rays_d), ptr(noise), R, S, int(map_exr),
+                                                   int(composite_bkgd), _bkgd(bkgd_color), ptr(d_color_map),
+                                                   ptr(d_alpha_map), ptr(d_rgbs), stream_ptr()))
+    return d_rgbs
+
+
+def mip_cone_gaussians(rays_o, rays_d, z_edges, radii):
+    """MipRenderer.get_cone_segment_gaussians (network/renderer.py:411-434) -> mean[R,S,3], cov[R,S,3]."""
+    rays_o, rays_d, z_edges, radii = as_cuda(rays_o), as_cuda(rays_d), as_cuda(z_edges), as_cuda(radii).reshape(-1)
+    R, S = z_edges.shape[0], z_edges.shape[1] - 1
+    assert radii.shape[0] == R
+    mean = torch.empty((R, S, 3), dtype=torch.float32, device=z_edges.device)
+    cov = torch.empty_like(mean)
+    check(_lib.load().ntx_mip_cone_gaussians(ptr(rays_o), ptr(rays_d), ptr(z_edges), ptr(radii), R, S, ptr(mean), ptr(cov),
+                                             stream_ptr()))
+    return mean, cov
+
+
+def mip_cone_gaussians_instanced(dirs, t, radii, dists) -> torch.Tensor:
+    """MipInstanceRenderer.get_cone_segment_gaussians (network/renderer.py:570-587) on packed samples -> cov[T,3]."""
+    dirs, t, radii, dists = as_cuda(dirs), as_cuda(t), as_cuda(radii), as_cuda(dists)
+    T = t.shape[0]
+    cov = torch.empty((T, 3), dtype=torch.float32, device=t.device)
+    check(_lib.load().ntx_mip_cone_gaussians_instanced(ptr(dirs), ptr(t), ptr(radii), ptr(dists), T, ptr(cov), stream_ptr()))
+    return cov
+
+
 def composite_instanced_forward(rgbs, dists, alpha_weight, ray_ptr, color_last, alpha_last, ray_index, n_out, *,
                                 patch_scale: float, density_scale: float = 1.0, map_exr: bool = False,
                                 composite_bkgd: bool = False, bkgd_color=(1., 1., 1.), instance_color=None):

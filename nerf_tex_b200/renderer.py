@@ -296,14 +296,83 @@ def dense_to_csr(instancer_out) -> Dict[str, torch.Tensor]:
 
 
 class MipRenderer(Renderer):
-    """network/renderer.py:356-473 — not built yet (unused by every config)."""
+    """network/renderer.py:356-473: cone-segment gaussians + integrated positional encoding (the model is built with
+    ``n_pos=6`` and an ``IntegratedPositionalEncoding`` pos_embedding); the blur parameter is spliced out of the
+    parameter vector and becomes the cone radius (:384-386)."""
 
-    def __init__(self, *a, **k):
-        raise NotImplementedError("MipRenderer (integrated positional encoding) is not implemented on the sm_100a path")
+    def __init__(self, blur_idx: int = None, **kwargs):
+        super().__init__(**kwargs)
+        self.blur_idx_mip = blur_idx                                              # :362 hidden from the base class
+        if blur_idx is None:
+            raise ValueError("MipRenderer needs blur_idx (the parameter that scales the cone radius, renderer.py:384)")
+
+    def render_rays(self, rays_o, rays_d, t, parameters, cone_scale, composite_bkgd, bkgd_color, training,
+                    z_rand=None, noise=None, return_aux: bool = False, **kwargs):
+        if self.n_importance > 0:                                                 # :402-403
+            raise NotImplementedError("Importance sampling for mip-NeRF style rendering is not implemented "
+                                      "(nor is it in the reference, network/renderer.py:402-403)")
+        R, dev, S = rays_o.shape[0], rays_o.device, self.n_samples
+        rays_d_n = ops.normalize_dirs(rays_d)                                     # :371
+        if self.perturb and z_rand is None:
+            z_rand = self._rand((R, S + 1), dev)                                  # :380
+        z = ops.stratified_z(t, S + 1, bool(self.perturb), z_rand)                # :374-381  S + 1 segment edges
+        b = self.blur_idx_mip
+        blur = (parameters[:, b] * cone_scale.reshape(-1)).contiguous()           # :384
+        params = torch.cat([parameters[:, :b], parameters[:, b + 1:]], -1).contiguous()   # :385
+        mean, cov = ops.mip_cone_gaussians(rays_o, rays_d, z, blur)               # :388
+        if self.raw_noise_std > 0 and noise is None:                              # :456-458
+            noise = self._rand((R, S), dev, normal=True) * self.raw_noise_std
+        model = self.model
+        if torch.is_grad_enabled() and model.master.requires_grad:
+            from .autograd import MipNetworkPass
+            cmap, amap, w = MipNetworkPass.apply(model.master, model, mean, cov, rays_d, rays_d_n.contiguous(), z, params,
+                                                 noise, self.map_exr, composite_bkgd, tuple(float(c) for c in bkgd_color))
+        else:
+            rgbs = model.forward_rows(n_rows=R * S, pos=mean.view(-1, 3), pos_cov=cov.view(-1, 3), dir=rays_d_n.contiguous(),
+                                      params=params if params.shape[1] > 0 else None, rows_per_group=S).view(R, S, 4)   # :392
+            cmap, amap, w = ops.composite_edges_forward(rgbs, z, rays_d, noise=noise, map_exr=self.map_exr,
+                                                        composite_bkgd=composite_bkgd, bkgd_color=bkgd_color,
+                                                        want_weights=return_aux)   # :396
+        out = {"color_pred": cmap, "alpha_pred": amap}
+        return (out, {"z": z, "mean": mean, "cov": cov, "weights": w}) if return_aux else out
 
 
 class MipInstanceRenderer(InstanceRenderer):
-    """network/renderer.py:475-587 — not built yet (row f4)."""
+    """network/renderer.py:475-587: the instanced renderer with integrated positional encodings."""
 
-    def __init__(self, *a, **k):
-        raise NotImplementedError("MipInstanceRenderer is not implemented on the sm_100a path")
+    def __init__(self, blur_idx: int = None, **kwargs):
+        super().__init__(**kwargs)
+        self.blur_idx_mip = blur_idx                                              # :481
+        if blur_idx is None:
+            raise ValueError("MipInstanceRenderer needs blur_idx (renderer.py:511)")
+
+    def evaluate_model(self, rays_o, rays_d, parameters, cone_scale, model, composite_bkgd, bkgd_color, training):
+        n_rays, dev = rays_o.shape[0], rays_o.device
+        if hasattr(self.instancer, "get_model_input_csr"):
+            csr = self.instancer.get_model_input_csr(rays_o, rays_d, parameters, self.n_samples, self.step_size)
+        else:
+            csr = dense_to_csr(self.instancer.get_model_input(rays_o, rays_d, parameters, self.n_samples, self.step_size))
+        H = csr["ray_index"].shape[0]
+        if H == 0:                                                                # :494-495
+            return (torch.zeros((n_rays, 3), dtype=torch.float32, device=dev),
+                    torch.zeros((n_rays,), dtype=torch.float32, device=dev))
+        T = csr["pts"].shape[0]
+        if T > 0:
+            b = self.blur_idx_mip
+            counts = csr["ray_ptr"][1:] - csr["ray_ptr"][:-1]
+            cone_rows = cone_scale.reshape(-1)[csr["ray_index"].long()].repeat_interleave(counts)
+            blur = ((csr["params"][:, b] * cone_rows) / self.patch_scale).contiguous()           # :511
+            params = torch.cat([csr["params"][:, :b], csr["params"][:, b + 1:]], -1).contiguous()   # :512
+            cov = ops.mip_cone_gaussians_instanced(csr["dirs"], csr["t"], blur, csr["dists"])    # :536
+            rgbs = model.forward_rows(n_rows=T, pos=csr["pts"], pos_cov=cov, dir=csr["dirs"],
+                                      params=params if params.shape[1] > 0 else None, rows_per_group=1)   # :543
+        else:
+            rgbs = torch.zeros((0, 4), dtype=torch.float32, device=dev)
+        inst_col = None
+        if self.false_color:                                                      # :558-559
+            inst_col = self.instance_color[csr["instance_id"].long()].contiguous()
+        return ops.composite_instanced_forward(
+            rgbs, csr["dists"], csr["alpha_weight"] if self.density_reweighting else None, csr["ray_ptr"],
+            csr["color_last"], csr["alpha_last"], csr["ray_index"], n_rays, patch_scale=self.patch_scale,
+            density_scale=self.density_scale, map_exr=self.map_exr, composite_bkgd=composite_bkgd,
+            bkgd_color=bkgd_color, instance_color=inst_col)

@@ -102,7 +102,7 @@ def fourier_features(x: np.ndarray, n_freq_bands: int) -> np.ndarray:
 
 
 def integrated_positional_encoding(x: np.ndarray, n_freq_bands: int) -> np.ndarray:
-    """network/layer.py:25-41 (mip variant, rank f4; kept for completeness)."""
+    """network/layer.py:25-41: x = [mean(3), diagonal covariance(3)] -> [sin block, cos block] * exp(-var/2), no identity."""
     x = _f32(x)
     freq = (2.0 ** np.arange(n_freq_bands)).astype(F32)
     y = (x[..., None, :3] * freq[:, None]).reshape(-1, 3 * n_freq_bands)
@@ -132,7 +132,8 @@ class ParamNerfOracle:
         self.skips, self.color_depth = list(skips), color_depth
         self.pos_freqs, self.dir_freqs, self.param_freqs = pos_freqs, dir_freqs, param_freqs
         g, a = self.n_parameters
-        self.P = n_pos * (1 + 2 * pos_freqs) + g * (1 + 2 * param_freqs)
+        # n_pos = 6 is only ever used with IntegratedPositionalEncoding (layer.py:25-41): 2 * 3 * pos_freqs features
+        self.P = (6 * pos_freqs if n_pos == 6 else n_pos * (1 + 2 * pos_freqs)) + g * (1 + 2 * param_freqs)
         self.D = 3 * (1 + 2 * dir_freqs) + a * (1 + 2 * param_freqs)
         rng = np.random.default_rng(seed)
         self.layers: List[Tuple[str, np.ndarray, np.ndarray]] = []
@@ -173,7 +174,10 @@ class ParamNerfOracle:
     # -- forward ---------------------------------------------------------------------
     def encode(self, pos, dirs, params):
         g = self.n_parameters[0]
-        pos_map = fourier_features(pos, self.pos_freqs)                       # model.py:77
+        if self.n_pos == 6:
+            pos_map = integrated_positional_encoding(pos, self.pos_freqs)     # model.py:77 with layer.py:25-41
+        else:
+            pos_map = fourier_features(pos, self.pos_freqs)                   # model.py:77
         dir_map = fourier_features(dirs, self.dir_freqs)                      # model.py:78
         params = _f32(params)
         if g > 0:                                                             # model.py:88-93
@@ -279,7 +283,7 @@ def color_activation(color: np.ndarray, map_exr: bool) -> np.ndarray:
 
 
 def composite(color, alpha, z_vals, rays_d, composite_bkgd=False, bkgd_color=(1., 1., 1.), map_exr=False,
-              noise: Optional[np.ndarray] = None):
+              noise: Optional[np.ndarray] = None, edges: bool = False):
     """network/renderer.py:170-213 (Renderer.map_model_output).
 
     ``noise`` is the already-scaled ``N(0,1) * raw_noise_std`` tensor (explicit input).
@@ -287,7 +291,8 @@ def composite(color, alpha, z_vals, rays_d, composite_bkgd=False, bkgd_color=(1.
     computes depth (:204) and discards it."""
     color, alpha, z_vals, rays_d = _f32(color), _f32(alpha), _f32(z_vals), _f32(rays_d)
     dists = (z_vals[..., 1:] - z_vals[..., :-1]).astype(F32)
-    dists = np.concatenate([dists, dists[..., -1:]], -1)                       # :177 last dist duplicated
+    if not edges:
+        dists = np.concatenate([dists, dists[..., -1:]], -1)                   # :177 last dist duplicated
     norm = np.sqrt(seq_sum(rays_d * rays_d)).astype(F32)                       # :180
     dists = (dists * norm[..., None]).astype(F32)
     rgb = color_activation(color, map_exr)
@@ -297,7 +302,7 @@ def composite(color, alpha, z_vals, rays_d, composite_bkgd=False, bkgd_color=(1.
     trans = seq_cumprod_exclusive(((F32(1) - a).astype(F32) + F32(1e-10)).astype(F32))  # :198
     w = (a * trans).astype(F32)
     cmap = np.stack([seq_sum(w * rgb[..., c]) for c in range(3)], -1)          # :201
-    depth = seq_sum(w * z_vals)                                                # :204
+    depth = seq_sum(w * (z_vals[..., :-1] if edges else z_vals))               # :204
     amap = seq_sum(w)                                                          # :207
     if composite_bkgd:                                                         # :210-211
         cmap = (cmap + ((F32(1) - amap)[..., None] * _f32(bkgd_color)).astype(F32)).astype(F32)
@@ -490,6 +495,107 @@ def instance_evaluate_model(model, instancer_out, n_rays, cone_scale=None, blur_
     cm = np.zeros((n_rays, 3), F32)
     am = np.zeros((n_rays,), F32)
     cm[idxs], am[idxs] = cmap, amap                                            # :313-314
+    return cm, am
+
+
+# ----------------------------------------------------------------------------------------
+# network/renderer.py — mip variants (:356-587)
+# ----------------------------------------------------------------------------------------
+
+def mip_cone_gaussians(rays_o, rays_d, t_vals, radii):
+    """MipRenderer.get_cone_segment_gaussians (renderer.py:411-434): t_vals[R,S+1] edges, radii[R,1]."""
+    rays_o, rays_d, t_vals, radii = _f32(rays_o), _f32(rays_d), _f32(t_vals), _f32(radii)
+    t0, t1 = t_vals[..., :-1], t_vals[..., 1:]
+    mu = ((t0 + t1) / F32(2)).astype(F32)
+    hw = ((t1 - t0) / F32(2)).astype(F32)
+    den = (F32(3) * mu ** 2 + hw ** 2).astype(F32)
+    t_mean = (mu + (F32(2) * mu * hw ** 2) / den).astype(F32)
+    t_var = ((hw ** 2) / F32(3) - F32(4 / 15) * ((hw ** 4 * (F32(12) * mu ** 2 - hw ** 2)) / den ** 2)).astype(F32)
+    r_var = (radii ** 2 * ((mu ** 2) / F32(4) + F32(5 / 12) * hw ** 2 - F32(4 / 15) * (hw ** 4) / den)).astype(F32)
+    mean = (rays_o[..., None, :] + rays_d[..., None, :] * t_mean[..., None]).astype(F32)
+    d_mag_sq = np.maximum(F32(1e-10), (rays_d ** 2).sum(-1, keepdims=True)).astype(F32)
+    d_outer = (rays_d ** 2).astype(F32)
+    null_outer = (F32(1) - d_outer / d_mag_sq).astype(F32)
+    cov = (t_var[..., None] * d_outer[..., None, :] + r_var[..., None] * null_outer[..., None, :]).astype(F32)
+    return mean, cov
+
+
+def mip_cone_gaussians_instanced(rays_d, t_vals, radii, dists):
+    """MipInstanceRenderer.get_cone_segment_gaussians (renderer.py:570-587): flat per-sample arrays; mu = t, hw = dists."""
+    rays_d, mu, radii, hw = _f32(rays_d), _f32(t_vals), _f32(radii), _f32(dists)
+    den = (F32(3) * mu ** 2 + hw ** 2).astype(F32)
+    t_var = ((hw ** 2) / F32(3) - F32(4 / 15) * ((hw ** 4 * (F32(12) * mu ** 2 - hw ** 2)) / den ** 2)).astype(F32)
+    r_var = (radii ** 2 * ((mu ** 2) / F32(4) + F32(5 / 12) * hw ** 2 - F32(4 / 15) * (hw ** 4) / den)).astype(F32)
+    d_mag_sq = np.maximum(F32(1e-10), (rays_d ** 2).sum(-1, keepdims=True)).astype(F32)
+    d_outer = (rays_d ** 2).astype(F32)
+    null_outer = (F32(1) - d_outer / d_mag_sq).astype(F32)
+    return (t_var[:, None] * d_outer + r_var[:, None] * null_outer).astype(F32)
+
+
+def composite_edges(color, alpha, z_edges, rays_d, composite_bkgd=False, bkgd_color=(1., 1., 1.), map_exr=False, noise=None):
+    """MipRenderer.map_model_output (renderer.py:436-473): S + 1 depth edges, no duplicated last distance."""
+    cmap, amap, w, _ = composite(color, alpha, z_edges, rays_d, composite_bkgd, bkgd_color, map_exr, noise, edges=True)
+    return cmap, amap, w
+
+
+def mip_render_rays(model, rays_o, rays_d, t, parameters, cone_scale, n_samples, blur_idx, perturb=True, z_rand=None,
+                    noise=None, map_exr=False, composite_bkgd=False, bkgd_color=(1., 1., 1.), net_chunk=65536):
+    """MipRenderer.render_rays (renderer.py:365-409); `model` has n_pos = 6, and one parameter fewer than
+    `parameters` has columns (the blur parameter is spliced out, :385-386)."""
+    rays_o, rays_d, parameters = _f32(rays_o), _f32(rays_d), _f32(parameters)
+    norm = np.sqrt((rays_d * rays_d).sum(-1, keepdims=True)).astype(F32)
+    rays_d_n = (rays_d / norm).astype(F32)
+    z = stratified_z(t, n_samples + 1, perturb, z_rand)                        # :371-381 (S + 1 edges)
+    blur = (parameters[..., blur_idx, None] * _f32(cone_scale)).astype(F32)    # :384
+    params = np.concatenate([parameters[..., :blur_idx], parameters[..., blur_idx + 1:]], -1)
+    mean, cov = mip_cone_gaussians(rays_o, rays_d, z, blur)
+    pts = np.concatenate([mean, cov], -1)
+    color, alpha = evaluate_model(model, pts, rays_d_n, params, None, None, None, net_chunk)
+    cmap, amap, w = composite_edges(color, alpha, z, rays_d, composite_bkgd, bkgd_color, map_exr, noise)
+    return {"color_pred": cmap, "alpha_pred": amap}, {"z": z, "mean": mean, "cov": cov, "weights": w}
+
+
+def mip_instance_evaluate_model(model, instancer_out, n_rays, cone_scale, blur_idx, patch_scale=1.0, density_scale=1.0,
+                                density_reweighting=True, composite_bkgd=False, bkgd_color=(1., 1., 1.), map_exr=False,
+                                net_chunk=32768, instance_color=None):
+    """MipInstanceRenderer.evaluate_model (renderer.py:484-568)."""
+    rays_d_map, pts, t, dists, color_last, alpha_last, alpha_weight, instance_id, idxs, params_map = instancer_out
+    idxs = np.asarray(idxs).reshape(-1)
+    if idxs.shape[0] == 0:
+        return np.zeros((n_rays, 3), F32), np.zeros((n_rays,), F32)
+    g = lambda a: np.asarray(a)[idxs]
+    rays_d_map, pts, t, dists = g(rays_d_map), g(pts), g(t), g(dists)
+    color_last, alpha_last, alpha_weight = g(color_last), g(alpha_last), g(alpha_weight)
+    instance_id, params_map, cone = g(instance_id), _f32(g(params_map)), _f32(g(cone_scale))
+    blur = ((params_map[..., blur_idx] * cone[..., None, 0]).astype(F32) / F32(patch_scale)).astype(F32)   # :511
+    params_map = np.concatenate([params_map[..., :blur_idx], params_map[..., blur_idx + 1:]], -1)
+    H, S = dists.shape
+    pos_flat, dirs_flat = _f32(pts).reshape(-1, 3), _f32(rays_d_map).reshape(-1, 3)
+    params_flat = params_map.reshape(-1, params_map.shape[-1])
+    ip = np.nonzero(dists.reshape(-1) > 0)[0]                                  # :526
+    color = np.zeros((H * S, 3), F32)
+    alpha = np.zeros((H * S, 1), F32)
+    if ip.shape[0] > 0:
+        cov = mip_cone_gaussians_instanced(dirs_flat[ip], _f32(t).reshape(-1)[ip], blur.reshape(-1)[ip],
+                                           _f32(dists).reshape(-1)[ip])
+        pos6 = np.concatenate([pos_flat[ip], cov], -1)
+        for i in range(0, ip.shape[0], net_chunk):
+            c, a = model.forward(pos6[i:i + net_chunk], dirs_flat[ip[i:i + net_chunk]], params_flat[ip[i:i + net_chunk]])
+            color[ip[i:i + net_chunk]], alpha[ip[i:i + net_chunk]] = c, a
+        alpha = alpha.reshape(H, S)
+        mult = (_f32(alpha_weight) if density_reweighting else F32(1)) * F32(density_scale)
+        alpha = (alpha * mult).astype(F32)
+    else:
+        alpha = alpha.reshape(H, S)
+    color = color.reshape(H, S, 3)
+    false_color = instance_color is not None
+    if false_color:
+        color = _f32(instance_color)[instance_id.reshape(-1)].reshape(H, S, 3)
+    cmap, amap = composite_instanced(color, color_last, alpha, alpha_last, dists, patch_scale, composite_bkgd,
+                                     bkgd_color, map_exr, false_color)
+    cm = np.zeros((n_rays, 3), F32)
+    am = np.zeros((n_rays,), F32)
+    cm[idxs], am[idxs] = cmap, amap
     return cm, am
 
 

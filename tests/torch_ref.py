@@ -29,6 +29,11 @@ def mlp(om, P, pos, dirs, params):
         pos_map = torch.cat([pos_map, fourier(params[:, :g], om.param_freqs)], -1)
     if om.n_parameters[1] > 0:
         dir_map = torch.cat([dir_map, fourier(params[:, g:], om.param_freqs)], -1)
+    return mlp_from_maps(om, P, pos_map, dir_map)
+
+
+def mlp_from_maps(om, P, pos_map, dir_map):
+    """The Dense stack of model.py:104-123 on already-encoded inputs."""
     h = pos_map
     for i in range(om.depth):
         W, b = P[f"trunk{i}"]
