@@ -252,6 +252,19 @@ int ntx_composite_edges_backward(const float* rgbs, const float* z_edges, const 
                                  const float* d_color_map, const float* d_alpha_map, float* d_rgbs, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Image out (the step after a full-frame render)
+ * ---------------------------------------------------------------------------------------- */
+
+/* Replaces Logger.render_image's post-processing (network/logger.py:126-137) and the float -> uint8 conversion of
+ * write_image (:144): color[H*W,3] and alpha[H*W] (premultiplied) are low-pass filtered and downsampled by `factor`
+ * (util/interpolate.py:67-82: depthwise 'SAME' convolution with stride `factor`; taps_host = the n_taps normalised 1-D
+ * gaussian weights, HOST pointer, ignored for factor 1), then colour is divided by alpha + 1e-5 if straight_alpha.
+ * Outputs (either may be NULL): img[h,w,4] fp32 and img_u8[h,w,4] (values clamped to [0,1], times 255.5, truncated),
+ * h = ceil(H / factor), w = ceil(W / factor). */
+int ntx_image_finish(const float* color, const float* alpha, int H, int W, int factor, const float* taps_host, int n_taps,
+                     int straight_alpha, float* img, uint8_t* img_u8, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Shell instancer (the caller in front of the hot path)
  * ---------------------------------------------------------------------------------------- */
 

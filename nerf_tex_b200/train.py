@@ -109,10 +109,19 @@ def Train(target_path: str, train_dataset_config, val_dataset_config, model_conf
     renderer = util.instantiate(renderer_config)
     loss_fn = util.instantiate(loss_config)
     trainer = Trainer(models, renderer, loss_fn, lrate, lrate_decay)
+    logger = None
+    if logger_config is not None:                                                            # train.py:54-57
+        logger_config = util.EasyDict(logger_config)
+        val_dataset = util.instantiate(val_dataset_config) if isinstance(val_dataset_config, dict) else val_dataset_config
+        logger_config.update({"target_path": target_path, "checkpoint_variables": dict(models, step=0, optimizer=trainer),
+                              "dataset": val_dataset, "renderer": renderer, "n_iters": n_iters})
+        logger = util.instantiate(logger_config)                                             # restores the latest checkpoint
     losses = []
     for i, data in enumerate(train_dataset):
-        if i >= n_iters:
+        if trainer.step >= n_iters:                                                          # train.py:60
             break
         losses.append(trainer.train_step(data, getattr(train_dataset, "composite_bkgd", False),
                                          getattr(train_dataset, "bkgd_color", (1., 1., 1.))))
+        if logger is not None:
+            logger({"loss": losses[-1]})                                                     # train.py:69
     return trainer, losses

@@ -19,6 +19,9 @@ _ALIASES = {
     "network.proxy.": "nerf_tex_b200.proxy.",
     "network.loss.": "nerf_tex_b200.loss.",
     "network.render.": "nerf_tex_b200.render.",
+    "network.pixel_sampler.": "nerf_tex_b200.pixel_sampler.",
+    "network.dataset.": "nerf_tex_b200.dataset.",
+    "network.logger.": "nerf_tex_b200.logger.",
     "network.train.": "nerf_tex_b200.train.",
     "instancer.instancer.": "nerf_tex_b200.instancer.",
 }

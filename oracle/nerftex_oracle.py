@@ -686,3 +686,50 @@ def adam_step(p, g, m, v, step, lr, b1=0.9, b2=0.999, eps=1e-7):
     lr_t = lr * math.sqrt(1 - b2 ** step) / (1 - b1 ** step)
     p = p - lr_t * m / (np.sqrt(v) + eps)
     return p.astype(F32), m.astype(F32), v.astype(F32)
+
+
+# ----------------------------------------------------------------------------------------
+# network/logger.py:121-144 + util/interpolate.py:67-82 — image post-processing
+# ----------------------------------------------------------------------------------------
+
+def gaussian_kernel_2d(size: int, std: float) -> np.ndarray:
+    """util/interpolate.py:67-75."""
+    x = np.linspace(-(size - 1) / 2, (size - 1) / 2, size).astype(F32) + F32(.5 if size % 2 == 0 else 0)
+    k1 = np.exp(-.5 * (x / F32(std)) ** 2).astype(F32)
+    k2 = np.tensordot(k1, k1, axes=0).astype(F32)
+    return (k2 / k2.sum()).astype(F32)
+
+
+def filtered_downsample(img: np.ndarray, factor: int, std: float = .5) -> np.ndarray:
+    """util/interpolate.py:78-82: tf.nn.depthwise_conv2d(img, gaussian, strides=factor, padding='SAME')."""
+    img = _f32(img)
+    H, W, Cn = img.shape
+    k = int(factor * std * 6)
+    K = gaussian_kernel_2d(k, factor * std).astype(np.float64)
+    h, w = -(-H // factor), -(-W // factor)
+    pt = max((h - 1) * factor + k - H, 0) // 2
+    pl = max((w - 1) * factor + k - W, 0) // 2
+    pad = np.zeros((H + 2 * k, W + 2 * k, Cn), np.float64)
+    pad[k:k + H, k:k + W] = img
+    out = np.zeros((h, w, Cn), np.float64)
+    for i in range(k):
+        for j in range(k):
+            ys = k - pt + i + factor * np.arange(h)
+            xs = k - pl + j + factor * np.arange(w)
+            out += K[i, j] * pad[np.ix_(ys, xs)]
+    return out.astype(F32)
+
+
+def render_image_post(color_pred, alpha_pred, height, width, downsampling_factor=1, write_exr=False):
+    """Logger.render_image after the renderer call (logger.py:126-137)."""
+    img = np.concatenate([_f32(color_pred).reshape(-1, 3), _f32(alpha_pred).reshape(-1, 1)], -1).reshape(height, width, 4)
+    if downsampling_factor > 1:
+        img = filtered_downsample(img, downsampling_factor)
+    if not write_exr:
+        img = np.concatenate([img[..., :3] / (img[..., 3:] + F32(1e-5)), img[..., 3:]], -1).astype(F32)
+    return img
+
+
+def to_uint8(img):
+    """tf.image.convert_image_dtype(img, tf.uint8) for in-range values: floor(x * 255.5) (logger.py:144)."""
+    return (np.clip(_f32(img), 0, 1) * F32(255.5)).astype(np.uint8)
