@@ -3,7 +3,9 @@ full-frame rendering of a dataset into images (render_images / render_image / wr
 checkpoints of the flat weight buffers.  TensorBoard summaries are out of scope.
 
 Checkpoints are plain ``.npz`` files (``checkpoints/ckpt-<step>.npz``: one flat fp32 array per model, Adam
-moments if a trainer is attached, and the step) — the reference's TensorFlow checkpoint format is not read here."""
+moments if a trainer is attached, and the step).  If no such file exists but the directory holds a checkpoint
+written by the reference (TensorFlow tensor bundle), its Dense kernels / biases and step are read through
+``tf_checkpoint`` (see the status note there)."""
 
 from __future__ import annotations
 
@@ -43,6 +45,17 @@ class Logger:
         if latest:                                                                     # :38-40
             self.restore(latest)
             print("Restored model & optimizer from {}.".format(latest))
+        else:
+            from . import tf_checkpoint
+            tf_prefix = tf_checkpoint.latest_checkpoint(self.checkpoint_path)          # a checkpoint the reference wrote
+            if tf_prefix and os.path.exists(tf_prefix + ".index"):
+                for k, m in self.models.items():
+                    tf_checkpoint.load_model_weights(tf_prefix, m, k)
+                step = tf_checkpoint.read_step(tf_prefix)
+                self.step = self.step if step is None else step
+                if self.trainer is not None:
+                    self.trainer.step = self.step                                      # Adam moments restart from zero
+                print("Restored model weights from the TensorFlow checkpoint {}.".format(tf_prefix))
         self.imgs_path = os.path.join(self.target_path, "media/validation" if is_training else "media/test")   # :48,:52
         os.makedirs(self.imgs_path, exist_ok=True)
         if not is_training:
