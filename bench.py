@@ -49,6 +49,10 @@ CPU_SAMPLE_RAYS = 2048
 MACS_PER_SAMPLE = {(1, 6): 680832, (1, 4): 676224, (2, 3): 678528}
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of one mlp_forward_kernel chunk launch (profiles/r01_v6_k1_full_raw.csv)
+K1_NCU_DRAM_BYTES_PER_LAUNCH = 86104320 + 10907136
+
+
 def peaks():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -494,7 +498,9 @@ def run_gpu(args):
             "samples_per_sec": samples_per_s,
             "roofline": {"kernel": "mlp_forward_kernel (K1 fused encoding + MLP, tcgen05)", "bound": "tensor",
                          "achieved": k1_tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                         "frac": k1_tflops / pk["bf16_tflops_sustained"], "traffic": None,
+                         "frac": k1_tflops / pk["bf16_tflops_sustained"], "traffic": K1_NCU_DRAM_BYTES_PER_LAUNCH,
+                         "traffic_source": "ncu --set full capture of one chunk launch, dram__bytes_read.sum + dram__bytes_write.sum "
+                                           "(profiles/r01_v6_k1_full_raw.csv): inputs 52 B/row + weights; activations never leave the SM",
                          "peak_source": f"{pk['source']} bf16_tflops_sustained (kernel timed inside a long step)",
                          "frac_of_burst_peak": k1_tflops / pk["bf16_tflops"],
                          "flops_per_sample": flops_per_row, "rows_per_launch": k1_rows / max(k1_launches, 1),
