@@ -331,6 +331,101 @@ def c1_forward_bench(dev, steps=20):
             "note": "4096-ray batch fills 148 SMs for only ~7 waves of 512-row CTA-pair batches; launch-latency sensitive"}
 
 
+def carpet_patches(n: int, seed: int = 0, extent: float = 1.45, patch_scale: float = 0.09):
+    """Procedural stand-in for the reference's cloth mesh + anchor points (git-LFS stubs): `n` shell patches anchored
+    on the z = 0 plane inside [-extent, extent]^2, each rotated about z, tilted a little and scaled by patch_scale
+    (what AddInstance receives, instancer.cpp:125-141)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    T = np.tile(np.eye(4), (n, 1, 1))
+    a, bx, by = rng.uniform(0, 2 * math.pi, n), rng.normal(0, 0.15, n), rng.normal(0, 0.15, n)
+    ca, sa = np.cos(a), np.sin(a)
+    rz = np.stack([np.stack([ca, -sa, 0 * a], -1), np.stack([sa, ca, 0 * a], -1), np.stack([0 * a, 0 * a, 1 + 0 * a], -1)], 1)
+    rx = np.stack([np.stack([1 + 0 * a, 0 * a, 0 * a], -1), np.stack([0 * a, np.cos(bx), -np.sin(bx)], -1),
+                   np.stack([0 * a, np.sin(bx), np.cos(bx)], -1)], 1)
+    ry = np.stack([np.stack([np.cos(by), 0 * a, np.sin(by)], -1), np.stack([0 * a, 1 + 0 * a, 0 * a], -1),
+                   np.stack([-np.sin(by), 0 * a, np.cos(by)], -1)], 1)
+    T[:, :3, :3] = (rz @ rx @ ry) * (patch_scale * rng.uniform(0.9, 1.1, n))[:, None, None]
+    T[:, 0, 3], T[:, 1, 3] = rng.uniform(-extent, extent, n), rng.uniform(-extent, extent, n)
+    return T
+
+
+def device_instancer_bench(dev, steps=5):
+    """Rays in, image out with nothing per-sample crossing the host boundary: camera rays (ntx_rays_from_camera), the
+    device shell instancer (ntx_instancer_trace / _march over a procedural 1 500-patch carpet), K1, instanced K2 and the
+    image finishing kernel, for one 800x800 frame of the carpet render config (camera radius 6, angle 0.55, proxy box
+    [-1.5, 1.5]^3, step 0.002, patch box and scale of config_carpet_render.py:82-86)."""
+    import torch
+    from nerf_tex_b200.dataset import look_at
+    from nerf_tex_b200.image import finish_image
+    from nerf_tex_b200.instancer import Instancer
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.proxy import AABB
+    from nerf_tex_b200.ray_sampler import Proxy
+    from nerf_tex_b200.renderer import InstanceRenderer
+    n_inst = 1500
+    inst = Instancer(b_0=[-1.4, -1.2, -.1], b_1=[1.2, 1.2, 1.8], textures=["", "", "", "", "light"],
+                     transformations=carpet_patches(n_inst), patch_scale=0.09, instance_sampling_method="nearest", device=dev)
+    chunk = int(os.environ.get("NTX_BENCH_INST_CHUNK", "131072"))            # rays per instancer / K1 / K2 launch
+    r = InstanceRenderer(instancer_config=inst, model=FusedNerfTexMLP(*NPAR, seed=1, device=dev), n_samples=1024,
+                         render_chunk=chunk, step_size=0.002, density_reweighting=True)
+    focal = W / math.tan(0.55 / 2) / 2
+    sampler = Proxy(H, W, focal, AABB([-1.5, -1.5, -1.5], [1.5, 1.5, 1.5]))
+    z = 1 - 2 * 0.3                                                           # data.distribution.Sphere, u = 0.3
+    poses = [look_at([6 * math.cos(v) * math.sqrt(1 - z * z), 6 * math.sin(v) * math.sqrt(1 - z * z), 6 * z])
+             for v in (0.0, 1.3, 2.6, 3.9, 5.2)]
+    params = torch.tensor([[1, 1, 1, .1, 0, 0, 1.]], device=dev)
+    stats = {}
+
+    def frame(pose, count=False):
+        rays_o, rays_d, t, cone = sampler(None, pose)
+        if count:                                                             # workload statistics of this frame
+            hit = torch.isfinite(t[:, 0])
+            ro, rd = rays_o[hit].contiguous(), rays_d[hit].contiguous()
+            n_s = n_h = 0
+            for i in range(0, ro.shape[0], 16384):
+                csr = inst.get_model_input_csr(ro[i:i + 16384], rd[i:i + 16384], params.repeat(ro[i:i + 16384].shape[0], 1),
+                                               1024, 0.002, seed=0)
+                n_s, n_h = n_s + csr["pts"].shape[0], n_h + csr["ray_index"].shape[0]
+            stats.update({"proxy_hit_rays": int(ro.shape[0]), "shell_hit_rays": n_h, "in_shell_samples": n_s,
+                          "samples_per_shell_hit_ray": n_s / max(n_h, 1)})
+        out = r(rays_o[None], rays_d[None], t[None], params, cone[None], composite_bkgd=True, training=False)
+        _, u8 = finish_image(out["color_pred"], out["alpha_pred"], H, W, 1, straight_alpha=True, want_u8=True)
+        return u8
+
+    frame(poses[0], count=True)
+    frame(poses[1])
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        u8 = frame(poses[i % len(poses)])
+        host = u8.cpu()                                                       # the finished 8-bit frame lands on the host
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    # the instancer alone on one chunk
+    rays_o, rays_d, t, cone = sampler(None, poses[0])
+    hit = torch.isfinite(t[:, 0])
+    mid = int(hit.sum()) // 2                                                 # a chunk from the middle of the frame
+    ro, rd = rays_o[hit][mid - chunk // 2:mid + chunk // 2].contiguous(), rays_d[hit][mid - chunk // 2:mid + chunk // 2].contiguous()
+    pf = params.repeat(ro.shape[0], 1)
+    for _ in range(2):
+        inst.get_model_input_csr(ro, rd, pf, 1024, 0.002, seed=0)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(10):
+        inst.get_model_input_csr(ro, rd, pf, 1024, 0.002, seed=0)
+    e1.record()
+    torch.cuda.synchronize()
+    stats.update({"rays": H * W, "instances": n_inst, "ms_per_frame": ms, "rays_per_sec": H * W / ms * 1e3,
+                  "render_chunk": chunk, "instancer_ms_per_chunk": e0.elapsed_time(e1) / 10, "instancer_chunk_rays": int(ro.shape[0]), "h2d_bytes_per_frame": 64 + 28,
+                  "d2h_bytes_per_frame": int(host.numel()),
+                  "api": "Proxy ray sampler -> InstanceRenderer(Instancer(transformations=...)) -> finish_image; pose and "
+                         "parameter vector in, 8-bit RGBA frame out"})
+    return stats
+
+
 def config_dict(extra=None):
     c = {"workload": "carpet-shape instanced render, 800x800 frame (640000 rays), n_parameters [1,6], "
                      "n_samples<=1024, step 0.002, patch_scale 0.09, render_chunk 16384, random-init weights",
@@ -518,6 +613,7 @@ def run_gpu(args):
             line["hbm_kernels"] = hbm_kernels_bench(dev, pk)
             line["train_step"] = train_step_bench(dev)
             line["c1_forward"] = c1_forward_bench(dev)
+            line["device_instancer_frame"] = device_instancer_bench(dev)
             line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
         print(json.dumps(line), flush=True)
     if world > 1:

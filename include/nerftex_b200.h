@@ -272,24 +272,27 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
  * for explicit patch instances: no mesh, no parameter textures, no shadow rays, no auxiliary meshes.
  *   minv[I,3,4]  rows 0..2 of the inverse instance transform (world -> patch), dirt[I,3,3] the row-normalised
  *   transposed rotation, origins[I,3] the instance translation (AddInstance, instancer.cpp:125-141);
- *   b_0/b_1: HOST pointers to the patch box corners.  Box hits are kept for t in [0, 100]; at most 64 hits per ray
- *   (the smallest t win).  Random draws are a counter hash of (seed, ray[, step]), not the reference's mt19937.
+ *   spheres[I,4] (optional, 16-byte aligned): world-space bounding sphere of every instanced box as (centre, radius^2),
+ *   radius inflated by >= 1 %: a cheap first test that never changes the result;
+ *   b_0/b_1: HOST pointers to the patch box corners.  Box hits are kept for t in [0, 100]; at most 200 hits per ray
+ *   (MAX_TOTAL_HITS, instancer.cpp:22; the smallest t win).  Random draws are a counter hash of (seed, ray[, step]), not the reference's mt19937.
  * Pass 1 (trace) fills workspace (ntx_instancer_workspace_bytes(R) bytes), n_samples[R] (marching samples of every
  * ray, <= n_pts) and hit[R] (ray touched any patch box).  The caller turns n_samples into ray_ptr[R+1] (exclusive
- * prefix sum, int64) and sizes the outputs; pass 2 (march) writes the samples of ray r at ray_ptr[r]...:
+ * prefix sum, int64; T = ray_ptr[R] samples in total) and sizes the outputs; pass 2 (march) writes the samples of ray r
+ * at ray_ptr[r]...:
  *   pts[T,3] patch-local position, dirs[T,3] patch-local unit view direction, params_out[T,n_param] (the ray's
  *   parameters; entries light_dir_idx..+2, if light_dir_idx >= 0, are the normalised light direction mapped into the
  *   patch frame, instancer.cpp:943-960), dists[T], t[T], alpha_weight[T] (number of overlapping patches for method 0
  *   'random', 1 for method 1 'nearest'), instance_id[T].  n_param <= 16. */
 int64_t ntx_instancer_workspace_bytes(int R);
 int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R, const float* minv, const float* dirt,
-                        const float* origins, int n_inst, const float* b_0, const float* b_1, float step_size, int n_pts,
+                        const float* origins, const float* spheres, int n_inst, const float* b_0, const float* b_1, float step_size, int n_pts,
                         uint32_t seed, int use_mean_distance, void* workspace, int32_t* n_samples, int32_t* hit,
                         void* stream);
 int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
                         const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
                         uint32_t seed, int light_dir_idx, int method, int use_mean_distance, const void* workspace,
-                        const int64_t* ray_ptr, float* pts, float* dirs, float* params_out, float* dists, float* t,
+                        const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists, float* t,
                         float* alpha_weight, int32_t* instance_id, void* stream);
 
 /* ------------------------------------------------------------------------------------------

@@ -1,12 +1,13 @@
 // Shell instancer on the device (row f1 of the scope table): what C_Instancer::GetModelInput
 // (instancer/src/instancer.cpp:751-1037) does on the host with Embree, for the subset that needs no mesh —
 // explicit patch instances, no parameter textures, no shadow rays:
-//   pass 1 (ntx_instancer_trace): one thread per ray tests every instanced patch box (slab test in the patch
-//          frame, instance matrices staged through shared memory), keeps the sorted hit list, walks the
-//          in-shell intervals and counts the marching samples;
-//   pass 2 (ntx_instancer_march): after a prefix sum over the counts, the same walk emits the samples
-//          CSR-packed: patch-local point / view direction / parameters (light direction mapped into the patch
-//          frame), step length, ray parameter, overlap weight, instance id.
+//   pass 1 (ntx_instancer_trace): one thread per ray tests every instanced patch box — a conservative bounding-sphere
+//          test on tiles staged through shared memory, then for the survivors the slab test in the patch frame —
+//          keeps the sorted hit list, walks the in-shell intervals and counts the marching samples;
+//   pass 2 (ntx_instancer_march): after a prefix sum over the counts, one thread per SAMPLE (so every store is
+//          coalesced) finds its ray and hit interval by binary search, replays the hits before it to get the patches it
+//          is inside, and emits the record CSR-packed: patch-local point / view direction / parameters (light
+//          direction mapped into the patch frame), step length, ray parameter, overlap weight, instance id.
 // Arithmetic is fp32 with explicit round-to-nearest ops in the order of oracle/instancer_oracle.py (bit-exact);
 // random draws come from a counter hash of (seed, ray[, step]) instead of the reference's std::mt19937.
 #include <math_constants.h>
@@ -15,8 +16,10 @@
 
 namespace {
 
-constexpr int kMaxHits = 64;
+constexpr int kMaxHits = 200;        // MAX_TOTAL_HITS, instancer.cpp:22
 constexpr int kInstTile = 128;
+constexpr int kTraceThreads = 128;   // rays per block of the trace pass
+constexpr int kSmemHits = 56;        // hit-list entries per ray kept in shared memory; the rest lives in the ray's workspace row
 constexpr float kTFar = 100.0f;
 
 __host__ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
@@ -47,149 +50,186 @@ struct MarchOut {
     float* pts; float* dirs; float* params; float* dists; float* t; float* weight; int32_t* inst;
 };
 
-// The interval walk + march shared by both passes.  EMIT = false only counts.
-template <bool EMIT>
-__device__ int march_ray(const uint64_t* hits, int n_hits, const float* o, const float* d, const float* prm, int n_param,
-                         const float* __restrict__ minv, const float* __restrict__ dirt, const float* __restrict__ origins,
-                         int n_pts, float step_size, uint32_t seed, uint32_t ray, int light_idx, int method, int use_mean,
-                         int64_t out0, const MarchOut& out) {
-    uint32_t active[kMaxHits];
-    int n_act = 0;
-    auto toggle = [&](uint32_t inst) -> bool {          // returns true if inst was active (now removed)
-        for (int k = 0; k < n_act; ++k) {
-            if (active[k] == inst) {
-                for (int q = k; q + 1 < n_act; ++q) active[q] = active[q + 1];
-                --n_act;
-                return true;
+// What pass 1 leaves per ray for pass 2 (besides the sorted hit list): for every hit j the number of samples emitted
+// before the walk consumed it and the segment offset in force after it, plus the per-ray constants.
+struct RayInfo {
+    float t_offset, last_dist;
+    int32_t n_steps, single;
+};
+
+struct Workspace {
+    uint64_t* hits;      // [R][kMaxHits]
+    int32_t* step_at;    // [R][kMaxHits]
+    float* segoff;       // [R][kMaxHits]
+    RayInfo* info;       // [R]
+    int32_t* n_hits;     // [R]
+};
+__host__ __device__ inline Workspace carve_workspace(void* base, int64_t R) {
+    uint8_t* p = (uint8_t*)base;
+    Workspace w;
+    w.hits = (uint64_t*)p;   p += R * kMaxHits * 8;
+    w.step_at = (int32_t*)p; p += R * kMaxHits * 4;
+    w.segoff = (float*)p;    p += R * kMaxHits * 4;
+    w.info = (RayInfo*)p;    p += R * 16;
+    w.n_hits = (int32_t*)p;
+    return w;
+}
+
+// A hit is a 64-bit key: fp32 bits of t in the high word (t >= 0, so integer order is t order), then the instance id
+// (24 bits) — and, once the list is final, in the top byte of the low word the index of the instance's OTHER hit on this
+// ray (kNoPartner if it has none): a box is convex, so an instance contributes at most an entry and an exit.
+constexpr uint32_t kInstMask = 0x00FFFFFFu;
+constexpr uint32_t kNoPartner = 0xFFu;
+__device__ __forceinline__ uint32_t hit_inst(uint64_t h) { return (uint32_t)h & kInstMask; }
+__device__ __forceinline__ uint32_t hit_partner(uint64_t h) { return ((uint32_t)h) >> 24; }
+__device__ __forceinline__ float hit_t(uint64_t h) { return __uint_as_float((uint32_t)(h >> 32)); }
+
+// The instances a ray is currently inside (std::set<unsigned> active_instances, instancer.cpp:801), each with the
+// index of the hit that put it there.  Pass 1 only needs membership and the size, so the list is unordered
+// (append / swap-remove); the ascending-id order the reference's set has matters for the choice among overlapping
+// patches only, which pass 2 makes.
+struct OpenList {
+    uint32_t id[kMaxHits];
+    uint8_t from[kMaxHits];
+    int n = 0;
+    // returns the index of the hit that had inserted `inst` (now removed), or -1 if it was not a member (now inserted)
+    __device__ int toggle(uint32_t inst, int hit_index) {
+        for (int k = 0; k < n; ++k) {
+            if (id[k] == inst) {
+                const int f = from[k];
+                --n;
+                id[k] = id[n];
+                from[k] = from[n];
+                return f;
             }
         }
-        int k = n_act++;                                // sorted insert (ascending instance id, like std::set)
-        while (k > 0 && active[k - 1] > inst) { active[k] = active[k - 1]; --k; }
-        active[k] = inst;
-        return false;
-    };
+        id[n] = inst;
+        from[n++] = (uint8_t)hit_index;
+        return -1;
+    }
+};
+
+// Pass 1, per ray: total in-shell length, step count, then the walk along the concatenated segments
+// (instancer.cpp:801-1003) — counting only; what each sample needs later is recorded per hit.
+// `hits(j)` is a reference to the j-th key of the ray in ascending order; the first loop also pairs entries with exits.
+template <class Hits>
+__device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint32_t seed, uint32_t ray, int use_mean,
+                        int32_t* __restrict__ step_at, float* __restrict__ segoff, RayInfo* __restrict__ info) {
+    OpenList act;
     // :801-827 total in-shell length
     float total = 0.0f, t_entry = 0.0f;
     for (int j = 0; j < n_hits; ++j) {
-        const float tt = __uint_as_float((uint32_t)(hits[j] >> 32));
-        const bool was_empty = n_act == 0;
-        if (toggle((uint32_t)hits[j])) {
-            if (n_act == 0) total = __fadd_rn(total, __fsub_rn(tt, t_entry));
-        } else if (was_empty) {
-            t_entry = tt;
+        const uint64_t hj = hits(j);
+        const float tt = hit_t(hj);
+        const bool was_empty = act.n == 0;
+        const int f = act.toggle(hit_inst(hj), j);
+        if (f >= 0) {
+            hits(j) = hj | ((uint64_t)f << 24);
+            hits(f) = (hits(f) & ~((uint64_t)kNoPartner << 24)) | ((uint64_t)j << 24);
+            if (act.n == 0) total = __fadd_rn(total, __fsub_rn(tt, t_entry));
+        } else {
+            hits(j) = hj | ((uint64_t)kNoPartner << 24);
+            if (was_empty) t_entry = tt;
         }
     }
-    n_act = 0;
-    if (!(total > 0.0f)) return 0;
+    RayInfo ri = {0.f, 0.f, 0, 0};
+    if (!(total > 0.0f)) { *info = ri; return 0; }
     const uint32_t necessary = (uint32_t)__fdiv_rn(total, step_size);             // :845
     int n_steps = (int)min(necessary, (uint32_t)n_pts);
     const float u = ray_uniform(seed, ray);
-    float t_offset, last_dist;
-    bool single = false;
     if (n_steps == 0) {                                                           // :848-851
-        single = true; last_dist = total; t_offset = __fmul_rn(u, total); n_steps = 1;
+        ri.single = 1; ri.last_dist = total; ri.t_offset = __fmul_rn(u, total); n_steps = 1;
     } else {                                                                      // :852-861
-        last_dist = __fsub_rn(__fadd_rn(step_size, total), __fmul_rn((float)n_steps, step_size));
-        t_offset = __fmul_rn(u, step_size);
+        ri.last_dist = __fsub_rn(__fadd_rn(step_size, total), __fmul_rn((float)n_steps, step_size));
+        ri.t_offset = __fmul_rn(u, step_size);
     }
-    float dn[3], light[3] = {0.f, 0.f, 0.f};
-    if (EMIT) {
-        const float nn = norm3(d);
-        for (int a = 0; a < 3; ++a) dn[a] = __fdiv_rn(d[a], nn);
-        if (light_idx >= 0) {
-            const float ln = norm3(prm + light_idx);
-            for (int a = 0; a < 3; ++a) light[a] = __fdiv_rn(prm[light_idx + a], ln);
-        }
-    }
-    // :871-1003 march along the concatenated segments
+    ri.n_steps = n_steps;
+    *info = ri;
+    // One loop whose iteration either emits (here: counts) the next sample or consumes the next hit — the
+    // reference nests a sample loop inside the hit loop (:871-1003); same order of events.
     float segment_offset = 0.0f, cleared = 0.0f;
     t_entry = 0.0f;
-    int step = 0;
-    for (int j = 0; j < n_hits && step < n_steps; ++j) {
-        const float tt = __uint_as_float((uint32_t)(hits[j] >> 32));
-        float t_mu = __fadd_rn(__fadd_rn(__fmul_rn((float)step, step_size), t_offset), segment_offset);
-        float t_pt = use_mean ? mean_distance(t_mu, step_size) : t_mu;
-        while (n_act > 0 && t_pt < tt && step < n_steps) {
-            if (EMIT) {
-                float pt[3];
-                for (int a = 0; a < 3; ++a) pt[a] = __fadd_rn(o[a], __fmul_rn(t_pt, d[a]));
-                uint32_t sel = active[0];
-                float w = 1.0f;
-                if (n_act > 1) {
-                    if (method == 0) {                                            // random, :671-677
-                        sel = active[pick(seed, ray, (uint32_t)step, (uint32_t)n_act)];
-                        w = (float)n_act;
-                    } else {                                                      // nearest, :680-692
-                        float best = CUDART_INF_F;
-                        for (int k = 0; k < n_act; ++k) {
-                            const float* og = origins + 3 * active[k];
-                            const float df[3] = {__fsub_rn(pt[0], og[0]), __fsub_rn(pt[1], og[1]), __fsub_rn(pt[2], og[2])};
-                            const float dist = norm3(df);
-                            if (dist < best) { best = dist; sel = active[k]; }
-                        }
-                    }
-                }
-                const int64_t k = out0 + step;
-                const float* M = minv + 12 * sel;
-                const float* Dt = dirt + 9 * sel;
-                for (int a = 0; a < 3; ++a) {
-                    out.pts[3 * k + a] = __fadd_rn(dot3(M + 4 * a, pt), M[4 * a + 3]);      // getPt :556-558
-                    out.dirs[3 * k + a] = dot3(Dt + 3 * a, dn);                           // getDir :561-563
-                }
-                for (int q = 0; q < n_param; ++q) out.params[k * n_param + q] = prm[q];
-                if (light_idx >= 0)
-                    for (int a = 0; a < 3; ++a) out.params[k * n_param + light_idx + a] = dot3(Dt + 3 * a, light);
-                out.dists[k] = (step == n_steps - 1) ? last_dist : step_size;
-                if (single) out.dists[k] = last_dist;
-                out.t[k] = t_mu;
-                out.weight[k] = w;
-                out.inst[k] = (int32_t)sel;
-            }
+    int step = 0, j = 0, n_act = 0;
+    uint64_t hj = n_hits > 0 ? hits(0) : 0;
+    while (j < n_hits && step < n_steps) {
+        const float tt = hit_t(hj);
+        const float t_mu = __fadd_rn(__fadd_rn(__fmul_rn((float)step, step_size), ri.t_offset), segment_offset);
+        const float t_pt = use_mean ? mean_distance(t_mu, step_size) : t_mu;
+        if (n_act > 0 && t_pt < tt) {
             ++step;
-            t_mu = __fadd_rn(__fadd_rn(__fmul_rn((float)step, step_size), t_offset), segment_offset);
-            t_pt = use_mean ? mean_distance(t_mu, step_size) : t_mu;
-        }
-        const bool was_empty = n_act == 0;
-        if (toggle((uint32_t)hits[j])) {
-            if (n_act == 0) cleared = __fadd_rn(cleared, __fsub_rn(tt, t_entry));
-        } else if (was_empty) {
-            segment_offset = __fsub_rn(tt, cleared);
-            t_entry = tt;
+        } else {
+            // a hit whose partner came earlier closes that instance, any other hit opens one (the pairing above)
+            const uint32_t partner = hit_partner(hj);
+            if (partner != kNoPartner && (int)partner < j) {
+                if (--n_act == 0) cleared = __fadd_rn(cleared, __fsub_rn(tt, t_entry));
+            } else if (n_act++ == 0) {
+                segment_offset = __fsub_rn(tt, cleared);
+                t_entry = tt;
+            }
+            step_at[j] = step;
+            segoff[j] = segment_offset;
+            if (++j < n_hits) hj = hits(j);
         }
     }
+    for (; j < n_hits; ++j) step_at[j] = 0x7fffffff;     // never consumed: no sample lies behind these hits
     return step;
 }
 
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(kTraceThreads)
 instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, int R,
                        const float* __restrict__ minv, const float* __restrict__ dirt, const float* __restrict__ origins,
-                       int n_inst, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
-                       int n_pts, uint32_t seed, int use_mean, uint64_t* __restrict__ ws_hits, int32_t* __restrict__ ws_nhits,
-                       int32_t* __restrict__ n_samples, int32_t* __restrict__ hit_flag) {
+                       const float4* __restrict__ spheres, int n_inst, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
+                       int n_pts, uint32_t seed, int use_mean, Workspace ws, int32_t* __restrict__ n_samples,
+                       int32_t* __restrict__ hit_flag) {
     __shared__ float s_minv[kInstTile * 12];
+    __shared__ float4 s_sph[kInstTile];
     const int ray = blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = ray < R;
     float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f};
     if (live) for (int a = 0; a < 3; ++a) { o[a] = rays_o[3 * ray + a]; d[a] = rays_d[3 * ray + a]; }
     const float b0[3] = {b00, b01, b02}, b1[3] = {b10, b11, b12};
-    uint64_t hits[kMaxHits];
+    const float inv_dd = 1.0f / fmaxf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], 1e-30f);
+    // the ray's sorted hit list: the first kSmemHits entries in shared memory (entry k of thread t at
+    // s_hits[k * kTraceThreads + t], conflict-free), the tail in the ray's row of the global workspace.  (A per-thread
+    // array would be local memory: 1.6 KB per ray falls out of L1, and holding all 200 entries in shared memory leaves
+    // four warps per SM.)
+    extern __shared__ __align__(16) uint64_t s_hits[];
+    uint64_t* row = ws.hits + (size_t)(live ? ray : 0) * kMaxHits;
+    auto H = [&](int k) -> uint64_t& { return k < kSmemHits ? s_hits[k * kTraceThreads + threadIdx.x] : row[k]; };
     int n_hits = 0;
     auto insert = [&](float t, uint32_t inst) {         // keep the kMaxHits smallest (t, inst), sorted
         const uint64_t key = ((uint64_t)__float_as_uint(t + 0.0f) << 32) | inst;
         int k;
         if (n_hits < kMaxHits) k = n_hits++;
-        else if (key < hits[kMaxHits - 1]) k = kMaxHits - 1;
+        else if (key < H(kMaxHits - 1)) k = kMaxHits - 1;
         else return;
-        while (k > 0 && hits[k - 1] > key) { hits[k] = hits[k - 1]; --k; }
-        hits[k] = key;
+        while (k > 0) {
+            const uint64_t prev = H(k - 1);
+            if (prev <= key) break;
+            H(k) = prev;
+            --k;
+        }
+        H(k) = key;
     };
     for (int base = 0; base < n_inst; base += kInstTile) {
         const int cnt = min(kInstTile, n_inst - base);
         __syncthreads();
         for (int i = threadIdx.x; i < cnt * 12; i += blockDim.x) s_minv[i] = minv[(size_t)base * 12 + i];
+        if (spheres)
+            for (int i = threadIdx.x; i < cnt; i += blockDim.x) s_sph[i] = spheres[base + i];
         __syncthreads();
         if (!live) continue;
         for (int j = 0; j < cnt; ++j) {
+            if (spheres) {
+                // squared distance of the sphere centre from the ray's line against the (inflated) radius: rejects
+                // only instances whose box the ray certainly misses, so the hit list is unchanged
+                const float4 sp = s_sph[j];
+                const float cx = sp.x - o[0], cy = sp.y - o[1], cz = sp.z - o[2];
+                const float tc = (cx * d[0] + cy * d[1] + cz * d[2]) * inv_dd;
+                const float px = cx - tc * d[0], py = cy - tc * d[1], pz = cz - tc * d[2];
+                const float cc = cx * cx + cy * cy + cz * cz;
+                if (px * px + py * py + pz * pz > sp.w + 1e-5f * cc) continue;
+            }
             const float* M = s_minv + 12 * j;
             float tin = -CUDART_INF_F, tout = CUDART_INF_F;
 #pragma unroll
@@ -208,53 +248,142 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
         }
     }
     if (!live) return;
-    for (int k = 0; k < n_hits; ++k) ws_hits[(size_t)ray * kMaxHits + k] = hits[k];
-    ws_nhits[ray] = n_hits;
+    ws.n_hits[ray] = n_hits;
     hit_flag[ray] = n_hits > 0;
-    MarchOut none = {};
-    n_samples[ray] = march_ray<false>(hits, n_hits, o, d, nullptr, 0, minv, dirt, origins, n_pts, step_size, seed,
-                                      (uint32_t)ray, -1, 0, use_mean, 0, none);
+    n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, (uint32_t)ray, use_mean,
+                              ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray);
+    for (int k = 0; k < min(n_hits, kSmemHits); ++k) row[k] = H(k);     // with the partner indices walk_ray added
 }
 
-__global__ void __launch_bounds__(128)
-instancer_march_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ params,
-                       int n_param, int R, const float* __restrict__ minv, const float* __restrict__ dirt,
-                       const float* __restrict__ origins, float step_size, int n_pts, uint32_t seed, int light_idx, int method,
-                       int use_mean, const uint64_t* __restrict__ ws_hits, const int32_t* __restrict__ ws_nhits,
-                       const int64_t* __restrict__ ray_ptr, MarchOut out) {
-    const int ray = blockIdx.x * blockDim.x + threadIdx.x;
-    if (ray >= R) return;
-    const int n_hits = ws_nhits[ray];
-    if (n_hits == 0) return;
-    uint64_t hits[kMaxHits];
-    for (int k = 0; k < n_hits; ++k) hits[k] = ws_hits[(size_t)ray * kMaxHits + k];
-    float o[3], d[3], prm[16];
-    for (int a = 0; a < 3; ++a) { o[a] = rays_o[3 * ray + a]; d[a] = rays_d[3 * ray + a]; }
-    for (int q = 0; q < n_param; ++q) prm[q] = params[(size_t)ray * n_param + q];
-    march_ray<true>(hits, n_hits, o, d, prm, n_param, minv, dirt, origins, n_pts, step_size, seed, (uint32_t)ray, light_idx,
-                    method, use_mean, ray_ptr[ray], out);
+// Pass 2, one thread per sample: every store of a warp is contiguous.  The sample finds its ray (binary search in
+// ray_ptr) and the hit interval it was emitted in (binary search in the ray's step_at row), replays the hits before it
+// to get the set of patches it is inside, and writes its record.
+__global__ void __launch_bounds__(256)
+instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ params,
+                      int n_param, int R, const float* __restrict__ minv, const float* __restrict__ dirt,
+                      const float* __restrict__ origins, float step_size, uint32_t seed, int light_idx, int method, int use_mean,
+                      Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T, MarchOut out) {
+    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= T) return;
+    int lo = 0, hi = R;                                   // last ray with ray_ptr[ray] <= k
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(ray_ptr + mid) <= k) lo = mid; else hi = mid;
+    }
+    const int ray = lo;
+    const int step = (int)(k - __ldg(ray_ptr + ray));
+    const RayInfo ri = ws.info[ray];
+    const int n_hits = ws.n_hits[ray];
+    const uint64_t* hits = ws.hits + (size_t)ray * kMaxHits;
+    const int32_t* step_at = ws.step_at + (size_t)ray * kMaxHits;
+    int j = 0, jh = n_hits;                               // first hit consumed after this sample: step_at[j] > step
+    while (j < jh) {
+        const int mid = (j + jh) >> 1;
+        if (__ldg(step_at + mid) <= step) j = mid + 1; else jh = mid;
+    }
+    const float segment_offset = j > 0 ? ws.segoff[(size_t)ray * kMaxHits + j - 1] : 0.0f;
+    float o[3], d[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { o[a] = __ldg(rays_o + 3 * ray + a); d[a] = __ldg(rays_d + 3 * ray + a); }
+    const float t_mu = __fadd_rn(__fadd_rn(__fmul_rn((float)step, step_size), ri.t_offset), segment_offset);
+    const float t_pt = use_mean ? mean_distance(t_mu, step_size) : t_mu;
+    float pt[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) pt[a] = __fadd_rn(o[a], __fmul_rn(t_pt, d[a]));
+    // The patches this sample is inside: hit q < j whose partner (the instance's other hit) is not before j as well.
+    auto inside = [&](uint64_t h) { const uint32_t p = hit_partner(h); return p == kNoPartner || (int)p >= j; };
+    uint32_t sel = 0;
+    float w = 1.0f;
+    if (method == 0) {                                                        // random, :671-677
+        int n_act = 0;
+        for (int q = 0; q < j; ++q) {
+            const uint64_t h = __ldg(hits + q);
+            if (inside(h)) { ++n_act; sel = hit_inst(h); }
+        }
+        if (n_act > 1) {                                                      // the idx-th smallest id of the set
+            const int idx = (int)pick(seed, (uint32_t)ray, (uint32_t)step, (uint32_t)n_act);
+            w = (float)n_act;
+            for (int q = 0; q < j; ++q) {
+                const uint64_t h = __ldg(hits + q);
+                if (!inside(h)) continue;
+                const uint32_t id = hit_inst(h);
+                int rank = 0;
+                for (int r = 0; r < j; ++r) {
+                    const uint64_t g = __ldg(hits + r);
+                    rank += inside(g) && hit_inst(g) < id;
+                }
+                if (rank == idx) { sel = id; break; }
+            }
+        }
+    } else {                                                                  // nearest, :680-692
+        // smallest rounded distance, ties to the smaller id (the reference walks the set in ascending id order and
+        // keeps the first strict minimum); sqrt is monotone, so it is only taken for candidates that can win
+        float best = CUDART_INF_F, best_sq = CUDART_INF_F;
+        int n_act = 0;
+        for (int q = 0; q < j; ++q) {
+            const uint64_t h = __ldg(hits + q);
+            if (!inside(h)) continue;
+            const uint32_t id = hit_inst(h);
+            if (n_act++ == 0) sel = id;
+            const float* og = origins + 3 * id;
+            const float d0 = __fsub_rn(pt[0], __ldg(og)), d1 = __fsub_rn(pt[1], __ldg(og + 1)), d2 = __fsub_rn(pt[2], __ldg(og + 2));
+            const float sq = __fadd_rn(__fadd_rn(__fmul_rn(d0, d0), __fmul_rn(d1, d1)), __fmul_rn(d2, d2));
+            if (sq <= best_sq) {
+                const float dist = sqrtf(sq);
+                if (dist < best || (dist == best && id < sel)) { best = dist; best_sq = sq; sel = id; }
+            }
+        }
+    }
+    float M[12], Dt[9];
+#pragma unroll
+    for (int a = 0; a < 12; ++a) M[a] = __ldg(minv + 12 * sel + a);
+#pragma unroll
+    for (int a = 0; a < 9; ++a) Dt[a] = __ldg(dirt + 9 * sel + a);
+    const float nn = norm3(d);
+    const float dn[3] = {__fdiv_rn(d[0], nn), __fdiv_rn(d[1], nn), __fdiv_rn(d[2], nn)};
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        out.pts[3 * k + a] = __fadd_rn(dot3(M + 4 * a, pt), M[4 * a + 3]);      // getPt :556-558
+        out.dirs[3 * k + a] = dot3(Dt + 3 * a, dn);                           // getDir :561-563
+    }
+    const float* prm = params + (size_t)ray * n_param;
+    for (int q = 0; q < n_param; ++q) out.params[k * n_param + q] = __ldg(prm + q);
+    if (light_idx >= 0) {                                                     // :943-960
+        float lv[3] = {__ldg(prm + light_idx), __ldg(prm + light_idx + 1), __ldg(prm + light_idx + 2)};
+        const float ln = norm3(lv);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) lv[a] = __fdiv_rn(lv[a], ln);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) out.params[k * n_param + light_idx + a] = dot3(Dt + 3 * a, lv);
+    }
+    out.dists[k] = (ri.single || step == ri.n_steps - 1) ? ri.last_dist : step_size;
+    out.t[k] = t_mu;
+    out.weight[k] = w;
+    out.inst[k] = (int32_t)sel;
 }
 
 }  // namespace
 
 NTX_API int64_t ntx_instancer_workspace_bytes(int R) {
     if (R < 0) return -1;
-    return (int64_t)R * kMaxHits * 8 + (int64_t)R * 4;
+    return (int64_t)R * (kMaxHits * 16 + 16 + 4);
 }
 
 NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R, const float* minv, const float* dirt,
-                                const float* origins, int n_inst, const float* b_0, const float* b_1, float step_size,
-                                int n_pts, uint32_t seed, int use_mean_distance, void* workspace, int32_t* n_samples,
-                                int32_t* hit, void* stream) {
-    NTX_REQUIRE(R >= 0 && n_inst >= 0 && n_pts >= 1 && step_size > 0.0f, "instancer_trace: bad arguments");
+                                const float* origins, const float* spheres, int n_inst, const float* b_0, const float* b_1,
+                                float step_size, int n_pts, uint32_t seed, int use_mean_distance, void* workspace,
+                                int32_t* n_samples, int32_t* hit, void* stream) {
+    NTX_REQUIRE(R >= 0 && n_inst >= 0 && n_inst <= (int)kInstMask && n_pts >= 1 && step_size > 0.0f, "instancer_trace: bad arguments");
     if (R == 0) return NTX_OK;
     NTX_REQUIRE(rays_o && rays_d && minv && dirt && origins && b_0 && b_1 && workspace && n_samples && hit,
                 "instancer_trace: null pointer");
-    uint64_t* ws_hits = (uint64_t*)workspace;
-    int32_t* ws_nhits = (int32_t*)((uint8_t*)workspace + (int64_t)R * kMaxHits * 8);
-    instancer_trace_kernel<<<(R + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-        rays_o, rays_d, R, minv, dirt, origins, n_inst, b_0[0], b_0[1], b_0[2], b_1[0], b_1[1], b_1[2], step_size, n_pts, seed,
-        use_mean_distance, ws_hits, ws_nhits, n_samples, hit);
+    NTX_REQUIRE(((uintptr_t)workspace & 15) == 0, "instancer_trace: the workspace must be 16-byte aligned");
+    NTX_REQUIRE(!spheres || ((uintptr_t)spheres & 15) == 0, "instancer_trace: spheres must be 16-byte aligned");
+    const size_t smem = (size_t)kSmemHits * kTraceThreads * sizeof(uint64_t);
+    NTX_CUDA(cudaFuncSetAttribute(instancer_trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    instancer_trace_kernel<<<(R + kTraceThreads - 1) / kTraceThreads, kTraceThreads, smem, (cudaStream_t)stream>>>(
+        rays_o, rays_d, R, minv, dirt, origins, reinterpret_cast<const float4*>(spheres), n_inst, b_0[0], b_0[1], b_0[2],
+        b_1[0], b_1[1], b_1[2], step_size, n_pts, seed, use_mean_distance, carve_workspace(workspace, R), n_samples, hit);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
@@ -262,20 +391,21 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R,
 NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
                                 const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
                                 uint32_t seed, int light_dir_idx, int method, int use_mean_distance, const void* workspace,
-                                const int64_t* ray_ptr, float* pts, float* dirs, float* params_out, float* dists, float* t,
-                                float* alpha_weight, int32_t* instance_id, void* stream) {
-    NTX_REQUIRE(R >= 0 && n_param >= 0 && n_param <= 16, "instancer_march: bad arguments (at most 16 parameters)");
+                                const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists,
+                                float* t, float* alpha_weight, int32_t* instance_id, void* stream) {
+    NTX_REQUIRE(R >= 0 && T >= 0 && n_param >= 0 && n_param <= 16, "instancer_march: bad arguments (at most 16 parameters)");
     NTX_REQUIRE(light_dir_idx < 0 || light_dir_idx + 3 <= n_param, "instancer_march: light direction index out of range");
     NTX_REQUIRE(method == 0 || method == 1, "instancer_march: instance sampling method must be 0 (random) or 1 (nearest)");
-    if (R == 0) return NTX_OK;
+    if (R == 0 || T == 0) return NTX_OK;
     NTX_REQUIRE(rays_o && rays_d && (n_param == 0 || parameters) && minv && dirt && origins && workspace && ray_ptr,
                 "instancer_march: null pointer");
-    const uint64_t* ws_hits = (const uint64_t*)workspace;
-    const int32_t* ws_nhits = (const int32_t*)((const uint8_t*)workspace + (int64_t)R * kMaxHits * 8);
+    NTX_REQUIRE(pts && dirs && (n_param == 0 || params_out) && dists && t && alpha_weight && instance_id,
+                "instancer_march: null output pointer");
+    (void)n_pts;
     MarchOut out = {pts, dirs, params_out, dists, t, alpha_weight, instance_id};
-    instancer_march_kernel<<<(R + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-        rays_o, rays_d, parameters, n_param, R, minv, dirt, origins, step_size, n_pts, seed, light_dir_idx, method,
-        use_mean_distance, ws_hits, ws_nhits, ray_ptr, out);
+    instancer_emit_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        rays_o, rays_d, parameters, n_param, R, minv, dirt, origins, step_size, seed, light_dir_idx, method, use_mean_distance,
+        carve_workspace(const_cast<void*>(workspace), R), ray_ptr, T, out);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }

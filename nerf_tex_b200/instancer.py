@@ -153,6 +153,13 @@ class Instancer:
         self.minv = as_dev(np.linalg.inv(T)[:, :3, :])
         self.dirt = as_dev(rt / np.linalg.norm(rt, axis=2, keepdims=True))
         self.origins = as_dev(T[:, :3, 3])
+        # bounding sphere of every instanced box (centre, radius^2 inflated by 2 %): first-stage rejection in the trace
+        b0, b1 = np.asarray(b_0, np.float64), np.asarray(b_1, np.float64)
+        corners = np.array([[(b0, b1)[(c >> a) & 1][a] for a in range(3)] + [1.0] for c in range(8)])      # [8,4]
+        world = np.einsum("iab,cb->ica", T[:, :3, :], corners)                                              # [I,8,3]
+        centre = np.einsum("iab,b->ia", T[:, :3, :], np.append((b0 + b1) / 2, 1.0))
+        r2 = (np.linalg.norm(world - centre[:, None, :], axis=-1).max(1) * 1.01) ** 2 * 1.0 + 1e-12
+        self.spheres = as_dev(np.concatenate([centre, r2[:, None]], -1))
         self.transformations = T
         self.b_0, self.b_1 = [float(v) for v in b_0], [float(v) for v in b_1]
         self.patch_scale = float(patch_scale)
@@ -173,7 +180,7 @@ class Instancer:
             self._calls += 1
         return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.minv, self.dirt, self.origins,
                                              self.b_0, self.b_1, seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
-                                             use_mean_distance=self.use_mean_distance)
+                                             use_mean_distance=self.use_mean_distance, spheres=self.spheres)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

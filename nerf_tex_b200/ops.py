@@ -229,7 +229,8 @@ def rays_from_camera(image_plane_loc, height: int, width: int, focal: float, c2w
 # ------------------------------------------------------------------------------------------ instancer
 
 def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size: float, minv, dirt, origins, b_0, b_1, *,
-                              seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False):
+                              seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False,
+                              spheres=None):
     """Two-pass shell instancer (instancer/src/instancer.cpp:751-1037): trace + count, prefix sum, march.
     Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box)."""
     rays_o, rays_d, parameters = as_cuda(rays_o), as_cuda(rays_d), as_cuda(parameters)
@@ -240,9 +241,9 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     b1 = (C.c_float * 3)(*[float(v) for v in b_1])
     n_samples = torch.empty(R, dtype=torch.int32, device=dev)
     hit = torch.empty(R, dtype=torch.int32, device=dev)
-    ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R)), 8), dtype=torch.uint8, device=dev)
+    ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R)), 16), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), R, ptr(minv), ptr(dirt), ptr(origins), minv.shape[0], b0, b1,
+        check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), R, ptr(minv), ptr(dirt), ptr(origins), ptr(spheres), minv.shape[0], b0, b1,
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)),
                                       ptr(ws), ptr(n_samples), ptr(hit), stream_ptr()))
         ray_ptr_all = torch.zeros(R + 1, dtype=torch.int64, device=dev)
@@ -254,7 +255,7 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
                "instance_id": torch.empty(T, dtype=torch.int32, device=dev)}
         check(lib.ntx_instancer_march(ptr(rays_o), ptr(rays_d), ptr(parameters), p, R, ptr(minv), ptr(dirt), ptr(origins),
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(light_dir_idx), int(method),
-                                      int(bool(use_mean_distance)), ptr(ws), ptr(ray_ptr_all), ptr(out["pts"]), ptr(out["dirs"]),
+                                      int(bool(use_mean_distance)), ptr(ws), ptr(ray_ptr_all), T, ptr(out["pts"]), ptr(out["dirs"]),
                                       ptr(out["params"]), ptr(out["dists"]), ptr(out["t"]), ptr(out["alpha_weight"]),
                                       ptr(out["instance_id"]), stream_ptr()))
     H = ray_index.shape[0]

@@ -25,7 +25,7 @@ from __future__ import annotations
 import numpy as np
 
 F = np.float32
-MAX_HITS = 64
+MAX_HITS = 200                       # MAX_TOTAL_HITS, instancer.cpp:22
 T_FAR = F(100.0)
 
 

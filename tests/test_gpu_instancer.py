@@ -74,12 +74,12 @@ def test_records_bit_exact(method, mean_dist, light):
 
 
 def test_grazing_rays_clip_and_many_instances():
-    """Rays nearly parallel to the patch plane cross many patches: the per-ray hit list saturates at 64 entries,
+    """Rays nearly parallel to the patch plane cross many patches: the per-ray hit list saturates at 200 entries,
     n_pts clips the sample count, and more instances than one shared-memory tile (128) are walked."""
     from nerf_tex_b200.instancer import Instancer
-    Ts = patch_grid(14, seed=5, spacing=0.45)                      # 196 instances, heavy overlap
-    R = 300
-    o, d = rays_over(14, R, seed=6, spacing=0.45, grazing=True)
+    Ts = patch_grid(25, seed=5, spacing=0.2)                       # 625 instances, heavy overlap
+    R = 160
+    o, d = rays_over(25, R, seed=6, spacing=0.2, grazing=True)
     o[:, 2] = 0.3
     d[:, 2] = -0.05
     prm = np.zeros((R, 1), np.float32)
