@@ -296,6 +296,58 @@ def train_step_bench(dev, steps=5):
     return out
 
 
+def train_step_dp_bench(dev, rank: int, world: int, steps: int = 10):
+    """BASELINE.json configs[3] (fur training shape): data-parallel training, model [1,4], 4096 rays x
+    256 samples per rank (seed 1000 + rank), identical initial weights, one NCCL all-reduce of the flat fp32 gradient
+    buffer per step, Adam on every rank.  Step time = max over ranks; throughput = rays of all ranks / that time."""
+    import torch
+    import torch.distributed as dist
+    from nerf_tex_b200.loss import AlphaLoss
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.renderer import Renderer
+    from nerf_tex_b200.train import Trainer
+    g = torch.Generator(device=dev).manual_seed(1000 + rank)
+    R = 4096
+    ro = torch.tensor([[0., 0.5, 5.]], device=dev).repeat(R, 1)
+    rd = torch.rand((R, 3), device=dev, generator=g) * 2 - 1 - ro
+    rd = rd / rd.norm(dim=-1, keepdim=True)
+    data = {"rays_o": ro[None], "rays_d": rd[None],
+            "t": torch.stack([3 + torch.rand(R, device=dev, generator=g), 6 + torch.rand(R, device=dev, generator=g)], -1)[None],
+            "parameters": torch.rand((1, 5), device=dev, generator=g), "cone_scale": torch.rand((1, R, 1), device=dev, generator=g) * .01,
+            "color": torch.rand((1, R, 3), device=dev, generator=g), "alpha": torch.rand((1, R), device=dev, generator=g)}
+    models = {"model": FusedNerfTexMLP(1, 4, seed=1)}
+    r = Renderer(n_samples=256, n_importance=0, perturb=True, seed=rank, **models)
+    tr = Trainer(models, r, AlphaLoss("network.loss.smape", "network.loss.mse"), lrate=5e-4)
+    for _ in range(3):
+        tr.train_step(data)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        loss = tr.train_step(data)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1) / steps], device=dev)
+    e0.record()
+    for _ in range(20):
+        tr.allreduce_gradients()
+    e1.record()
+    torch.cuda.synchronize()
+    ar = torch.tensor([e0.elapsed_time(e1) / 20 * 1e3], device=dev)
+    chk = models["model"].master.detach().double().sum().reshape(1)          # replicas must stay identical
+    lo, hi = chk.clone(), chk.clone()
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ar, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+    return {"model": "[1,4]", "rays_per_rank": R, "samples_per_ray": 256, "ms_per_step": float(ms), "n_gpus": world,
+            "rays_per_sec": world * R / float(ms) * 1e3, "allreduce_us": float(ar), "grad_bytes": int(models["model"].n_params * 4),
+            "replicas_identical": bool(float(lo) == float(hi)), "loss_rank0": float(loss)}
+
+
 def c1_forward_bench(dev, steps=20):
     """BASELINE.json configs[0]: 4096 rays x (64 coarse + 128 fine), CoarseFine [1,4], forward only,
     through Renderer.__call__ (K3 -> K1 -> K2 -> K3 -> K1 -> K2)."""
@@ -576,6 +628,12 @@ def run_gpu(args):
     ms, ms_e2e, k1_ms = [float(x) for x in stats.tolist()]
     samples_all, k1_rows_all = [float(x) for x in tot.tolist()]
 
+    dp = None
+    if world > 1:                      # every rank takes part (one gradient all-reduce per step)
+        host = None
+        torch.cuda.empty_cache()
+        dp = train_step_dp_bench(dev, rank, world)
+
     if rank == 0:
         pk = peaks()
         sec = ms / 1e3
@@ -607,6 +665,8 @@ def run_gpu(args):
             "gpu_launches": int(2 * len(chunks) * args.steps),
             "clocks": clocks,
         }
+        if world > 1:
+            line["train_step_dp"] = dp
         if world == 1 and not args.no_cpu_baseline:
             del chunks, resident, host
             torch.cuda.empty_cache()
