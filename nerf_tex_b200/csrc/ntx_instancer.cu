@@ -261,8 +261,8 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
 __global__ void __launch_bounds__(256)
 instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ params,
                       int n_param, int R, const float* __restrict__ minv, const float* __restrict__ dirt,
-                      const float* __restrict__ origins, float step_size, uint32_t seed, int light_idx, int method, int use_mean,
-                      Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T, MarchOut out) {
+                      const float* __restrict__ origins, float step_size, uint32_t seed, int light_idx, int strength_idx,
+                      int method, int use_mean, Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T, MarchOut out) {
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
     int lo = 0, hi = R;                                   // last ray with ray_ptr[ray] <= k
@@ -348,8 +348,17 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
     }
     const float* prm = params + (size_t)ray * n_param;
     for (int q = 0; q < n_param; ++q) out.params[k * n_param + q] = __ldg(prm + q);
-    if (light_idx >= 0) {                                                     // :943-960
+    if (light_idx >= 0) {                                                     // :929-956
+        // directional light: the parameter is the direction; point light ('point' texture entry): it is the position,
+        // the direction becomes (position - sample) and the strength parameter the received radiance (:572-590)
         float lv[3] = {__ldg(prm + light_idx), __ldg(prm + light_idx + 1), __ldg(prm + light_idx + 2)};
+        if (strength_idx >= 0) {
+#pragma unroll
+            for (int a = 0; a < 3; ++a) lv[a] = __fsub_rn(lv[a], pt[a]);
+            const float dsq = __fadd_rn(__fadd_rn(__fmul_rn(lv[0], lv[0]), __fmul_rn(lv[1], lv[1])), __fmul_rn(lv[2], lv[2]));
+            out.params[k * n_param + strength_idx] =
+                __fdiv_rn(__ldg(prm + strength_idx), __fadd_rn(__fmul_rn(12.566370614359172f, dsq), 1e-6f));
+        }
         const float ln = norm3(lv);
 #pragma unroll
         for (int a = 0; a < 3; ++a) lv[a] = __fdiv_rn(lv[a], ln);
@@ -390,11 +399,13 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R,
 
 NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
                                 const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
-                                uint32_t seed, int light_dir_idx, int method, int use_mean_distance, const void* workspace,
-                                const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists,
+                                uint32_t seed, int light_dir_idx, int light_strength_idx, int method, int use_mean_distance,
+                                const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists,
                                 float* t, float* alpha_weight, int32_t* instance_id, void* stream) {
     NTX_REQUIRE(R >= 0 && T >= 0 && n_param >= 0 && n_param <= 16, "instancer_march: bad arguments (at most 16 parameters)");
     NTX_REQUIRE(light_dir_idx < 0 || light_dir_idx + 3 <= n_param, "instancer_march: light direction index out of range");
+    NTX_REQUIRE(light_strength_idx < 0 || (light_strength_idx < n_param && light_dir_idx >= 0),
+                "instancer_march: a light strength parameter needs a light position (light_dir_idx) too");
     NTX_REQUIRE(method == 0 || method == 1, "instancer_march: instance sampling method must be 0 (random) or 1 (nearest)");
     if (R == 0 || T == 0) return NTX_OK;
     NTX_REQUIRE(rays_o && rays_d && (n_param == 0 || parameters) && minv && dirt && origins && workspace && ray_ptr,
@@ -404,7 +415,8 @@ NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const 
     (void)n_pts;
     MarchOut out = {pts, dirs, params_out, dists, t, alpha_weight, instance_id};
     instancer_emit_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        rays_o, rays_d, parameters, n_param, R, minv, dirt, origins, step_size, seed, light_dir_idx, method, use_mean_distance,
+        rays_o, rays_d, parameters, n_param, R, minv, dirt, origins, step_size, seed, light_dir_idx, light_strength_idx, method,
+        use_mean_distance,
         carve_workspace(const_cast<void*>(workspace), R), ray_ptr, T, out);
     NTX_LAUNCH_CHECK();
     return NTX_OK;

@@ -121,7 +121,7 @@ def csr_to_dense(csr, rays_d, parameters, n_samples: int):
 class Instancer:
     """Device shell instancer behind the reference's constructor (instancer/instancer.pyx:6-36) for explicit patch
     `transformations` (AddInstance, instancer.cpp:125-141).  What needs the Embree scene of a base mesh is refused:
-    `mesh_path`, shadow rays, parameter textures other than '' / 'light' / 'point', auxiliary meshes, and the
+    `mesh_path`, shadow rays, image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes, and the
     'nearest_blend' sampling method."""
 
     def __init__(self, b_0: list, b_1: list, cast_shadow_rays=False, textures: list = [], transformations: list = [],
@@ -137,12 +137,21 @@ class Instancer:
             raise NotImplementedError("Instancer: shadow rays / auxiliary meshes need a mesh scene")
         if instance_sampling_method == 'nearest_blend':
             raise NotImplementedError("Instancer: 'nearest_blend' is not built; use 'random' or 'nearest'")
-        self.light_dir_idx = -1
-        for i, tex in enumerate(textures):                                             # instancer.pyx:20-28
-            if tex == 'light':
-                self.light_dir_idx = i
-            elif tex not in ('', None, 'point'):
+        self.light_dir_idx = self.light_strength_idx = -1
+        n_parameters = 0
+        for tex in textures:                                                           # instancer.cpp:75-92
+            if tex == 'light':                                                         # directional light: 3 parameters
+                self.light_dir_idx = n_parameters
+                n_parameters += 3
+            elif tex == 'point':                                                       # point light: strength + position
+                self.light_strength_idx = n_parameters
+                self.light_dir_idx = n_parameters + 1
+                n_parameters += 4
+            elif tex in ('', None):
+                n_parameters += 1
+            else:
                 raise NotImplementedError(f"Instancer: parameter texture {tex!r} needs a UV-mapped mesh")
+        self.n_parameters = n_parameters
         import numpy as np
         T = np.asarray(transformations, dtype=np.float64).reshape(-1, 4, 4)
         if T.shape[0] == 0:
@@ -180,7 +189,8 @@ class Instancer:
             self._calls += 1
         return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.minv, self.dirt, self.origins,
                                              self.b_0, self.b_1, seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
-                                             use_mean_distance=self.use_mean_distance, spheres=self.spheres)
+                                             use_mean_distance=self.use_mean_distance, spheres=self.spheres,
+                                             light_strength_idx=self.light_strength_idx)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

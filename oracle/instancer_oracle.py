@@ -11,7 +11,7 @@ What is restated (file:line of instancer.cpp):
   * number of marching steps, per-sample `dists`, random start offset                     :843-861
   * the march itself: samples are laid out along the concatenated segments              :871-1003
   * instance choice when patches overlap: 'random' (weight n) or 'nearest' (weight 1)     :671-692,:899-915
-  * world -> patch mapping of points, view directions and the light direction             :556-563,:943-960
+  * world -> patch mapping of points, view directions and the light direction; point lights  :556-590,:929-956
   * `use_mean_distance` (:746-748), no mesh hit: colour 0 / density 0                      :1020-1027
 
 Not reproducible by construction: the reference draws offsets / instance choices from a member
@@ -101,7 +101,7 @@ def mean_distance(mu, hw):
 
 
 def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformations, b_0, b_1, *, seed=0,
-                    light_dir_idx=-1, method="random", use_mean_distance=False):
+                    light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1):
     """Returns the CSR form over ALL rays: n_samples[R], hit[R] and per-sample records."""
     rays_o, rays_d, parameters = np.asarray(rays_o, F), np.asarray(rays_d, F), np.asarray(parameters, F)
     minv, dirt, origins = prepare_instances(transformations)
@@ -145,7 +145,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         dn_norm = _norm3(d)
         dn = [F(d[a] / dn_norm) for a in range(3)]
         light = None
-        if light_dir_idx >= 0:
+        if light_dir_idx >= 0 and light_strength_idx < 0:                              # directional light
             lv = parameters[i, light_dir_idx:light_dir_idx + 3]
             ln = _norm3(lv)
             light = [F(lv[a] / ln) for a in range(3)]
@@ -183,6 +183,13 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 prm = parameters[i].copy()
                 if light is not None:
                     prm[light_dir_idx:light_dir_idx + 3] = [_dot3(dirt[sel][a], light) for a in range(3)]
+                elif light_dir_idx >= 0:                            # point light: :572-590, :954-956
+                    lv = [F(parameters[i, light_dir_idx + a] - pt[a]) for a in range(3)]
+                    dsq = F(F(F(lv[0] * lv[0]) + F(lv[1] * lv[1])) + F(lv[2] * lv[2]))
+                    prm[light_strength_idx] = F(parameters[i, light_strength_idx] / F(F(F(12.566370614359172) * dsq) + F(1e-6)))
+                    ln = _norm3(lv)
+                    lvn = [F(lv[a] / ln) for a in range(3)]
+                    prm[light_dir_idx:light_dir_idx + 3] = [_dot3(dirt[sel][a], lvn) for a in range(3)]
                 recs["params"].append(prm)
                 recs["dists"].append(dists[step])
                 recs["t"].append(t_mu)

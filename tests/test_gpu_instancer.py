@@ -73,6 +73,27 @@ def test_records_bit_exact(method, mean_dist, light):
     assert 0 < want["hit"].sum() < R
 
 
+def test_point_light_and_parameter_layout():
+    """'point' occupies four parameters (strength, position): the direction becomes position - sample in the patch
+    frame, the strength the received radiance (instancer.cpp:75-92, :572-590, :954-956)."""
+    from nerf_tex_b200.instancer import Instancer
+    Ts = patch_grid(4, seed=3, tilt=0.25)
+    R = 400
+    o, d = rays_over(4, R, seed=4)
+    rng = np.random.default_rng(5)
+    prm = rng.uniform(0.1, 1.0, (R, 6)).astype(np.float32)
+    prm[:, 3:] = rng.uniform(-2, 4, (R, 3)).astype(np.float32) + np.array([0, 0, 3], np.float32)   # light position
+    inst = Instancer(B0, B1, textures=["", "", "point"], transformations=Ts.tolist())
+    assert (inst.light_strength_idx, inst.light_dir_idx, inst.n_parameters) == (2, 3, 6)
+    assert Instancer(B0, B1, textures=["light", "", ""], transformations=Ts.tolist()).light_dir_idx == 0
+    assert Instancer(B0, B1, textures=["", "point", "light"], transformations=Ts.tolist()).light_dir_idx == 5   # last one wins
+    want = IO.get_model_input(o, d, prm, 40, 0.02, Ts, B0, B1, seed=2, light_dir_idx=3, light_strength_idx=2)
+    got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), 40, 0.02, seed=2)
+    check_records(got, want, R)
+    p = want["params"]
+    assert np.allclose(np.linalg.norm(p[:, 3:], axis=1), 1, atol=1e-5) and (p[:, 2] > 0).all() and not np.allclose(p[:, 2], p[0, 2])
+
+
 def test_grazing_rays_clip_and_many_instances():
     """Rays nearly parallel to the patch plane cross many patches: the per-ray hit list saturates at 200 entries,
     n_pts clips the sample count, and more instances than one shared-memory tile (128) are walked."""
