@@ -285,7 +285,8 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
  *   patch frame, instancer.cpp:929-952; with light_strength_idx >= 0 the three entries are a point light's POSITION, the
  *   direction becomes position - sample and entry light_strength_idx the received radiance strength / (4 pi d^2 + 1e-6),
  *   instancer.cpp:572-590,954-956), dists[T], t[T], alpha_weight[T] (number of overlapping patches for method 0
- *   'random', 1 for method 1 'nearest'), instance_id[T].  n_param <= 16. */
+ *   'random', 1 for method 1 'nearest', 1 / probability for method 2 'nearest_blend' whose blend_range is the transition
+ *   range 0.2 times the patch scale, instancer.cpp:694-713), instance_id[T].  n_param <= 16. */
 int64_t ntx_instancer_workspace_bytes(int R);
 int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R, const float* minv, const float* dirt,
                         const float* origins, const float* spheres, int n_inst, const float* b_0, const float* b_1, float step_size, int n_pts,
@@ -293,7 +294,8 @@ int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R, const f
                         void* stream);
 int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
                         const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
-                        uint32_t seed, int light_dir_idx, int light_strength_idx, int method, int use_mean_distance, const void* workspace,
+                        uint32_t seed, int light_dir_idx, int light_strength_idx, int method, float blend_range, int use_mean_distance,
+                        const void* workspace,
                         const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists, float* t,
                         float* alpha_weight, int32_t* instance_id, void* stream);
 

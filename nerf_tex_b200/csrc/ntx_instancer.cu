@@ -30,6 +30,9 @@ __host__ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
 __device__ __forceinline__ float ray_uniform(uint32_t seed, uint32_t ray) {
     return (float)(hash_u32(hash_u32(seed) ^ (ray * 2u + 1u)) >> 8) * (1.0f / 16777216.0f);
 }
+__device__ __forceinline__ float step_uniform(uint32_t seed, uint32_t ray, uint32_t step) {
+    return (float)(hash_u32(hash_u32(seed ^ 0x85EBCA6Bu) ^ (ray * 1315423911u + step * 2u + 3u)) >> 8) * (1.0f / 16777216.0f);
+}
 __device__ __forceinline__ uint32_t pick(uint32_t seed, uint32_t ray, uint32_t step, uint32_t n) {
     return hash_u32(hash_u32(seed ^ 0x9E3779B9u) ^ (ray * 1315423911u + step * 2u + 2u)) % n;
 }
@@ -262,7 +265,8 @@ __global__ void __launch_bounds__(256)
 instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ params,
                       int n_param, int R, const float* __restrict__ minv, const float* __restrict__ dirt,
                       const float* __restrict__ origins, float step_size, uint32_t seed, int light_idx, int strength_idx,
-                      int method, int use_mean, Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T, MarchOut out) {
+                      int method, float blend_range, int use_mean, Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T,
+                      MarchOut out) {
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
     int lo = 0, hi = R;                                   // last ray with ray_ptr[ray] <= k
@@ -315,6 +319,44 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
                 if (rank == idx) { sel = id; break; }
             }
         }
+    } else if (method == 2) {                                                 // nearest_blend, :694-713
+        // weights max(range + min_dist - dist, 0) over the set in ascending id order, one draw from that discrete
+        // distribution, density weight 1 / probability
+        auto dist_to = [&](uint32_t id) {
+            const float* og = origins + 3 * id;
+            const float df[3] = {__fsub_rn(pt[0], __ldg(og)), __fsub_rn(pt[1], __ldg(og + 1)), __fsub_rn(pt[2], __ldg(og + 2))};
+            return norm3(df);
+        };
+        auto next_id = [&](int64_t cur) {                                     // smallest member id above cur, or -1
+            int64_t best = -1;
+            for (int q = 0; q < j; ++q) {
+                const uint64_t h = __ldg(hits + q);
+                const int64_t id = hit_inst(h);
+                if (inside(h) && id > cur && (best < 0 || id < best)) best = id;
+            }
+            return best;
+        };
+        float min_dist = CUDART_INF_F;
+        for (int q = 0; q < j; ++q) {
+            const uint64_t h = __ldg(hits + q);
+            if (inside(h)) min_dist = fminf(min_dist, dist_to(hit_inst(h)));
+        }
+        const float lim = __fadd_rn(blend_range, min_dist);
+        float total = 0.0f;
+        for (int64_t id = next_id(-1); id >= 0; id = next_id(id))
+            total = __fadd_rn(total, fmaxf(__fsub_rn(lim, dist_to((uint32_t)id)), 0.0f));
+        const float target = __fmul_rn(step_uniform(seed, (uint32_t)ray, (uint32_t)step), total);
+        float run = 0.0f, w_sel = 1.0f;
+        for (int64_t id = next_id(-1); id >= 0; id = next_id(id)) {
+            const float wi = fmaxf(__fsub_rn(lim, dist_to((uint32_t)id)), 0.0f);
+            run = __fadd_rn(run, wi);
+            if (wi > 0.0f) {
+                sel = (uint32_t)id;
+                w_sel = wi;
+                if (target < run) break;
+            }
+        }
+        w = __fdiv_rn(total, w_sel);
     } else {                                                                  // nearest, :680-692
         // smallest rounded distance, ties to the smaller id (the reference walks the set in ascending id order and
         // keeps the first strict minimum); sqrt is monotone, so it is only taken for candidates that can win
@@ -399,14 +441,14 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R,
 
 NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
                                 const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
-                                uint32_t seed, int light_dir_idx, int light_strength_idx, int method, int use_mean_distance,
-                                const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists,
+                                uint32_t seed, int light_dir_idx, int light_strength_idx, int method, float blend_range,
+                                int use_mean_distance, const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists,
                                 float* t, float* alpha_weight, int32_t* instance_id, void* stream) {
     NTX_REQUIRE(R >= 0 && T >= 0 && n_param >= 0 && n_param <= 16, "instancer_march: bad arguments (at most 16 parameters)");
     NTX_REQUIRE(light_dir_idx < 0 || light_dir_idx + 3 <= n_param, "instancer_march: light direction index out of range");
     NTX_REQUIRE(light_strength_idx < 0 || (light_strength_idx < n_param && light_dir_idx >= 0),
                 "instancer_march: a light strength parameter needs a light position (light_dir_idx) too");
-    NTX_REQUIRE(method == 0 || method == 1, "instancer_march: instance sampling method must be 0 (random) or 1 (nearest)");
+    NTX_REQUIRE(method >= 0 && method <= 2, "instancer_march: instance sampling method must be 0 (random), 1 (nearest) or 2 (nearest_blend)");
     if (R == 0 || T == 0) return NTX_OK;
     NTX_REQUIRE(rays_o && rays_d && (n_param == 0 || parameters) && minv && dirt && origins && workspace && ray_ptr,
                 "instancer_march: null pointer");
@@ -416,7 +458,7 @@ NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const 
     MarchOut out = {pts, dirs, params_out, dists, t, alpha_weight, instance_id};
     instancer_emit_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
         rays_o, rays_d, parameters, n_param, R, minv, dirt, origins, step_size, seed, light_dir_idx, light_strength_idx, method,
-        use_mean_distance,
+        blend_range, use_mean_distance,
         carve_workspace(const_cast<void*>(workspace), R), ray_ptr, T, out);
     NTX_LAUNCH_CHECK();
     return NTX_OK;

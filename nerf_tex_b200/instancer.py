@@ -121,8 +121,7 @@ def csr_to_dense(csr, rays_d, parameters, n_samples: int):
 class Instancer:
     """Device shell instancer behind the reference's constructor (instancer/instancer.pyx:6-36) for explicit patch
     `transformations` (AddInstance, instancer.cpp:125-141).  What needs the Embree scene of a base mesh is refused:
-    `mesh_path`, shadow rays, image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes, and the
-    'nearest_blend' sampling method."""
+    `mesh_path`, shadow rays, image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes."""
 
     def __init__(self, b_0: list, b_1: list, cast_shadow_rays=False, textures: list = [], transformations: list = [],
                  mesh_path: str = None, patch_scale: float = 1., patch_origins_path='', min_shadow_samples: int = 4,
@@ -135,8 +134,6 @@ class Instancer:
                                       "git-LFS meshes; pass explicit `transformations` (or use SyntheticInstancer)")
         if cast_shadow_rays or auxiliary_meshes:
             raise NotImplementedError("Instancer: shadow rays / auxiliary meshes need a mesh scene")
-        if instance_sampling_method == 'nearest_blend':
-            raise NotImplementedError("Instancer: 'nearest_blend' is not built; use 'random' or 'nearest'")
         self.light_dir_idx = self.light_strength_idx = -1
         n_parameters = 0
         for tex in textures:                                                           # instancer.cpp:75-92
@@ -172,7 +169,7 @@ class Instancer:
         self.transformations = T
         self.b_0, self.b_1 = [float(v) for v in b_0], [float(v) for v in b_1]
         self.patch_scale = float(patch_scale)
-        self.method = 0 if instance_sampling_method == 'random' else 1
+        self.method = {'random': 0, 'nearest': 1, 'nearest_blend': 2}[instance_sampling_method]   # instancer.pyx:12
         self.use_mean_distance = bool(use_mean_distance)
         self.seed = int(seed)
         self._calls = 0
@@ -190,7 +187,7 @@ class Instancer:
         return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.minv, self.dirt, self.origins,
                                              self.b_0, self.b_1, seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
                                              use_mean_distance=self.use_mean_distance, spheres=self.spheres,
-                                             light_strength_idx=self.light_strength_idx)
+                                             light_strength_idx=self.light_strength_idx, blend_range=0.2 * self.patch_scale)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

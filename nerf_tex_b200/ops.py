@@ -230,7 +230,7 @@ def rays_from_camera(image_plane_loc, height: int, width: int, focal: float, c2w
 
 def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size: float, minv, dirt, origins, b_0, b_1, *,
                               seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False,
-                              spheres=None, light_strength_idx: int = -1):
+                              spheres=None, light_strength_idx: int = -1, blend_range: float = 0.0):
     """Two-pass shell instancer (instancer/src/instancer.cpp:751-1037): trace + count, prefix sum, march.
     Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box)."""
     rays_o, rays_d, parameters = as_cuda(rays_o), as_cuda(rays_d), as_cuda(parameters)
@@ -255,7 +255,7 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
                "instance_id": torch.empty(T, dtype=torch.int32, device=dev)}
         check(lib.ntx_instancer_march(ptr(rays_o), ptr(rays_d), ptr(parameters), p, R, ptr(minv), ptr(dirt), ptr(origins),
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(light_dir_idx), int(light_strength_idx),
-                                      int(method),
+                                      int(method), float(blend_range),
                                       int(bool(use_mean_distance)), ptr(ws), ptr(ray_ptr_all), T, ptr(out["pts"]), ptr(out["dirs"]),
                                       ptr(out["params"]), ptr(out["dists"]), ptr(out["t"]), ptr(out["alpha_weight"]),
                                       ptr(out["instance_id"]), stream_ptr()))

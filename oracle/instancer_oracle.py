@@ -10,7 +10,8 @@ What is restated (file:line of instancer.cpp):
   * union of the in-shell intervals via the toggling `active_instances` set              :801-827
   * number of marching steps, per-sample `dists`, random start offset                     :843-861
   * the march itself: samples are laid out along the concatenated segments              :871-1003
-  * instance choice when patches overlap: 'random' (weight n) or 'nearest' (weight 1)     :671-692,:899-915
+  * instance choice when patches overlap: 'random' (weight n), 'nearest' (weight 1),       :671-713,:896-915
+    'nearest_blend' (draw from max(range + min_dist - dist, 0), weight 1 / probability)
   * world -> patch mapping of points, view directions and the light direction; point lights  :556-590,:929-956
   * `use_mean_distance` (:746-748), no mesh hit: colour 0 / density 0                      :1020-1027
 
@@ -46,6 +47,11 @@ def ray_uniform(seed: int, ray: int) -> np.float32:
 def pick(seed: int, ray: int, step: int, n: int) -> int:
     """Index of the instance chosen among n overlapping ones (instancer.cpp:671-677)."""
     return hash_u32(hash_u32(seed ^ 0x9E3779B9) ^ ((ray * 1315423911 + step * 2 + 2) & 0xFFFFFFFF)) % n
+
+
+def step_uniform(seed: int, ray: int, step: int) -> np.float32:
+    """Uniform [0,1) per (ray, step): the discrete-distribution draw of nearest_blend (instancer.cpp:709-710)."""
+    return F((hash_u32(hash_u32(seed ^ 0x85EBCA6B) ^ ((ray * 1315423911 + step * 2 + 3) & 0xFFFFFFFF)) >> 8) * (1.0 / 16777216.0))
 
 
 def prepare_instances(transformations):
@@ -101,7 +107,7 @@ def mean_distance(mu, hw):
 
 
 def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformations, b_0, b_1, *, seed=0,
-                    light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1):
+                    light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1, patch_scale=1.0):
     """Returns the CSR form over ALL rays: n_samples[R], hit[R] and per-sample records."""
     rays_o, rays_d, parameters = np.asarray(rays_o, F), np.asarray(rays_d, F), np.asarray(parameters, F)
     minv, dirt, origins = prepare_instances(transformations)
@@ -170,6 +176,22 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                     sel, w = act[0], F(1)
                 elif method == "random":
                     sel, w = act[pick(seed, i, step, len(act))], F(len(act))
+                elif method == "nearest_blend":                     # :694-713, transition_range 0.2 (instancer.hpp:84)
+                    ds = [_norm3([F(pt[c] - origins[a_][c]) for c in range(3)]) for a_ in act]
+                    lim = F(F(F(0.2) * F(patch_scale)) + min(ds))
+                    ws = [max(F(lim - d_), F(0)) for d_ in ds]
+                    total = F(0)
+                    for w_ in ws:
+                        total = F(total + w_)
+                    target = F(step_uniform(seed, i, step) * total)
+                    run, sel, w_sel = F(0), act[0], F(1)
+                    for a_, w_ in zip(act, ws):
+                        run = F(run + w_)
+                        if w_ > 0:
+                            sel, w_sel = a_, w_
+                            if target < run:
+                                break
+                    w = F(total / w_sel)
                 else:                                               # nearest, :680-692
                     best, sel = F(np.inf), act[0]
                     for a_ in act:

@@ -94,6 +94,24 @@ def test_point_light_and_parameter_layout():
     assert np.allclose(np.linalg.norm(p[:, 3:], axis=1), 1, atol=1e-5) and (p[:, 2] > 0).all() and not np.allclose(p[:, 2], p[0, 2])
 
 
+def test_nearest_blend():
+    """instance_sampling_method='nearest_blend' (instancer.cpp:694-713): bit-exact records; the density weight is
+    1 / probability, so it is 1 where one patch dominates and larger inside the transition band."""
+    from nerf_tex_b200.instancer import Instancer
+    Ts = patch_grid(5, seed=8, tilt=0.2)
+    R = 500
+    o, d = rays_over(5, R, seed=9)
+    prm = np.zeros((R, 2), np.float32)
+    inst = Instancer(B0, B1, transformations=Ts.tolist(), instance_sampling_method="nearest_blend", patch_scale=1.5)
+    want = IO.get_model_input(o, d, prm, 40, 0.02, Ts, B0, B1, seed=6, method="nearest_blend", patch_scale=1.5)
+    got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), 40, 0.02, seed=6)
+    check_records(got, want, R)
+    w = want["alpha_weight"]
+    assert w.min() >= 1 and (w == 1).any() and (w > 1.05).any()
+    near = IO.get_model_input(o, d, prm, 40, 0.02, Ts, B0, B1, seed=6, method="nearest")
+    assert 0.5 < (near["instance_id"] == want["instance_id"]).mean() < 1.0      # mostly, not always, the nearest patch
+
+
 def test_grazing_rays_clip_and_many_instances():
     """Rays nearly parallel to the patch plane cross many patches: the per-ray hit list saturates at 200 entries,
     n_pts clips the sample count, and more instances than one shared-memory tile (128) are walked."""
