@@ -70,6 +70,25 @@ def main():
         ok &= all(flags)
         if rank == 0:
             print(f"{name}: replicas bit-identical after 5 steps: {all(flags)}")
+    # (3) one frame sharded over the ranks (render_sharded): identical to the single-GPU render of the same rays
+    from nerf_tex_b200.sharded import render_sharded
+    g2 = torch.Generator(device=dev).manual_seed(7)                      # same rays on every rank
+    Rf = 5003
+    fo = torch.tensor([[0., 0.5, 5.]], device=dev).repeat(Rf, 1)
+    fd = torch.rand((Rf, 3), device=dev, generator=g2) * 2 - 1 - fo
+    fd = fd / fd.norm(dim=-1, keepdim=True)
+    ft = torch.stack([3 + torch.rand(Rf, device=dev, generator=g2), 6 + torch.rand(Rf, device=dev, generator=g2)], -1)
+    fp, fc = torch.rand((1, 5), device=dev, generator=g2), torch.full((1, Rf, 1), 1e-3, device=dev)
+    rr = Renderer(n_samples=64, n_importance=128, perturb=False, **models)        # deterministic depths; u drawn per call
+    rr.n_importance = 0                                                            # no random draws at all
+    whole = rr(fo[None], fd[None], ft[None], fp, fc, composite_bkgd=True, training=False)
+    parts = render_sharded(rr, fo[None], fd[None], ft[None], fp, fc, composite_bkgd=True, training=False)
+    same = all(torch.equal(whole[k], parts[k]) for k in whole)
+    flags = [None] * world
+    dist.all_gather_object(flags, same)
+    ok &= all(flags)
+    if rank == 0:
+        print(f"render_sharded == single-GPU render on every rank: {all(flags)}")
     dist.barrier()
     dist.destroy_process_group()
     if not ok:

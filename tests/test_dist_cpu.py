@@ -60,3 +60,39 @@ def test_shard_rays_covers_everything():
             s = shard_rays(n, r, w, block=16)
             covered += list(range(s.start, s.stop))
         assert covered == list(range(n))
+
+
+class _FakeRenderer:
+    """Per-ray function of the inputs (CPU tensors), shaped like Renderer.__call__'s result."""
+
+    def __call__(self, rays_o, rays_d, t, parameters, cone_scale, **kw):
+        c = rays_o * 2 + rays_d + parameters[:, None, :3] + cone_scale
+        return {"color_pred": c, "alpha_pred": t[..., 0] * t[..., 1]}
+
+
+def _shard_worker(rank, world, port, q):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from nerf_tex_b200.sharded import render_sharded
+    g = torch.Generator().manual_seed(0)
+    B, Nr = 2, 1003                                       # not a multiple of the block size or the world size
+    args = (torch.rand((B, Nr, 3), generator=g), torch.rand((B, Nr, 3), generator=g), torch.rand((B, Nr, 2), generator=g),
+            torch.rand((B, 5), generator=g), torch.rand((B, Nr, 1), generator=g))
+    got = render_sharded(_FakeRenderer(), *args, block=16)
+    want = _FakeRenderer()(*args)
+    q.put((rank, all(torch.equal(got[k], want[k]) for k in want), tuple(got["color_pred"].shape)))
+    dist.destroy_process_group()
+
+
+def test_render_sharded_gathers_the_whole_frame_world2():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_shard_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(60)
+        assert p.exitcode == 0
+    assert all(ok and shape == (2, 1003, 3) for _, ok, shape in res)
