@@ -359,66 +359,99 @@ composite_bwd_kernel(const float* __restrict__ rgbs, const float* __restrict__ z
     }
 }
 
-// Instanced variant over CSR-packed samples with the mesh hit appended (renderer.py:318-354).
+// Instanced variant over CSR-packed samples with the mesh hit appended (renderer.py:318-354).  A ray's samples
+// start anywhere in the packed arrays, so it stays one sample per lane; the rest follows the packed fast path: the
+// next round's loads are issued before the current one is scanned, exp / sigmoid are single MUFU ops with the
+// constant factors folded into one scale, the scan multiplies under the shuffle's own predicate, and the four per-ray
+// sums share six shuffles.
+struct InstIn {
+    float4 v;
+    float dist, aw;
+};
+
+__device__ __forceinline__ InstIn load_inst(const float4* __restrict__ rgbs, const float* __restrict__ dists,
+                                            const float* __restrict__ alpha_weight, int64_t k, int64_t end) {
+    InstIn r;
+    r.v = make_float4(0.f, 0.f, 0.f, 0.f);
+    r.dist = 0.0f;
+    r.aw = 1.0f;
+    if (k < end) {
+        r.v = ldg_stream_f4(rgbs + k);
+        r.dist = __ldg(dists + k);
+        if (alpha_weight) r.aw = __ldg(alpha_weight + k);
+    }
+    return r;
+}
+
+template <bool MAP_EXR>
 __global__ void __launch_bounds__(256)
-composite_inst_kernel(const float* __restrict__ rgbs, const float* __restrict__ dists,
+composite_inst_kernel(const float* __restrict__ rgbs_, const float* __restrict__ dists,
                       const float* __restrict__ alpha_weight, const int64_t* __restrict__ ray_ptr,
                       const float* __restrict__ color_last, const float* __restrict__ alpha_last,
                       const int32_t* __restrict__ ray_index, const float* __restrict__ instance_color, int H,
-                      float patch_scale, float density_scale, int map_exr, int composite_bkgd, float bk0, float bk1,
+                      float patch_scale, float density_scale, int composite_bkgd, float bk0, float bk1,
                       float bk2, float* __restrict__ color_map, float* __restrict__ alpha_map) {
+    constexpr float kLog2e = 1.4426950408889634f;
+    const float4* rgbs = reinterpret_cast<const float4*>(rgbs_);
     const int lane = threadIdx.x & 31;
+    const float scale = -kLog2e / patch_scale;                                   // renderer.py:339, folded into the exp2
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t h = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; h < H; h += nwarps) {
         const int64_t beg = __ldg(ray_ptr + h), end = __ldg(ray_ptr + h + 1);
         float carry = 1.0f, c0 = 0.0f, c1 = 0.0f, c2 = 0.0f, acc = 0.0f;
+        InstIn cur = load_inst(rgbs, dists, alpha_weight, beg + lane, end);
         for (int64_t base = beg; base < end; base += 32) {
             const int64_t k = base + lane;
-            const bool valid = k < end;
-            float a = 0.0f;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (valid) {
-                v = ldg_stream_f4(reinterpret_cast<const float4*>(rgbs) + k);
-                float s = v.w;
-                if (alpha_weight) s *= __ldg(alpha_weight + k) * density_scale;  // renderer.py:300
-                else s *= density_scale;
-                s = fmaxf(s, 0.0f);
-                a = 1.0f - expf(-(s * __ldg(dists + k)) / patch_scale);         // renderer.py:339
-            }
-            const float om = (1.0f - a) + 1e-10f;
-            const float incl = warp_scan_mul(om, lane);
+            const InstIn nxt = load_inst(rgbs, dists, alpha_weight, k + 32, end);
+            // lanes past the end hold sigma 0 -> alpha 0 -> factor 1 (1 + 1e-10 rounds to 1)
+            const float s = fmaxf(cur.v.w * (cur.aw * density_scale), 0.0f);     // renderer.py:300
+            const float a = 1.0f - ex2_approx((s * cur.dist) * scale);
+            float incl = (1.0f - a) + 1e-10f;
+            scan_mul_step(incl, 1);
+            scan_mul_step(incl, 2);
+            scan_mul_step(incl, 4);
+            scan_mul_step(incl, 8);
+            scan_mul_step(incl, 16);
             float excl = __shfl_up_sync(0xffffffffu, incl, 1);
             if (lane == 0) excl = 1.0f;
             const float w = a * (carry * excl);
             carry *= __shfl_sync(0xffffffffu, incl, 31);
-            if (valid) {
-                float y0, y1, y2;
-                if (instance_color) {                                           // renderer.py:306-307,322-323
+            float y0, y1, y2;
+            if (instance_color) {                                               // renderer.py:306-307,322-323
+                y0 = y1 = y2 = 0.0f;
+                if (k < end) {
                     y0 = __ldg(instance_color + 3 * k); y1 = __ldg(instance_color + 3 * k + 1);
                     y2 = __ldg(instance_color + 3 * k + 2);
-                } else {
-                    y0 = color_act(v.x, map_exr); y1 = color_act(v.y, map_exr); y2 = color_act(v.z, map_exr);
                 }
-                c0 += w * y0; c1 += w * y1; c2 += w * y2;
-                acc += w;
+            } else {
+                y0 = color_act2<MAP_EXR>(cur.v.x); y1 = color_act2<MAP_EXR>(cur.v.y); y2 = color_act2<MAP_EXR>(cur.v.z);
             }
+            c0 += w * y0; c1 += w * y1; c2 += w * y2;
+            acc += w;
+            cur = nxt;
         }
-        c0 = ntx_warp_sum(c0); c1 = ntx_warp_sum(c1); c2 = ntx_warp_sum(c2);
-        acc = ntx_warp_sum(acc);
-        if (lane == 0) {
-            // appended sample S+1: the opaque mesh hit (renderer.py:331,339)
-            const float al = __ldg(alpha_last + h);
-            const float wl = al * carry;
-            c0 += wl * __ldg(color_last + 3 * h); c1 += wl * __ldg(color_last + 3 * h + 1);
-            c2 += wl * __ldg(color_last + 3 * h + 2);
-            acc += wl;
-            if (composite_bkgd) {
-                const float om = 1.0f - acc;
-                c0 += om * bk0; c1 += om * bk1; c2 += om * bk2;
-            }
+        // four sums in six shuffles: halves of the warp trade what the other half keeps
+        const bool h16 = lane & 16, h8 = lane & 8;
+        float x = (h16 ? c1 : c0) + __shfl_xor_sync(0xffffffffu, h16 ? c0 : c1, 16);
+        float y = (h16 ? acc : c2) + __shfl_xor_sync(0xffffffffu, h16 ? c2 : acc, 16);
+        float u = (h8 ? y : x) + __shfl_xor_sync(0xffffffffu, h8 ? x : y, 8);
+        u += __shfl_xor_sync(0xffffffffu, u, 4);
+        u += __shfl_xor_sync(0xffffffffu, u, 2);
+        u += __shfl_xor_sync(0xffffffffu, u, 1);
+        // lane 0: r, lane 16: g, lane 8: b, lane 24: acc.  Appended sample S+1: the opaque mesh hit (renderer.py:331,339)
+        const float wl = __ldg(alpha_last + h) * carry;
+        const float acc_all = __shfl_sync(0xffffffffu, u, 24) + wl;
+        if ((lane & 7) == 0) {
+            const int comp = (lane >> 4) | ((lane >> 2) & 2);
             const int64_t dst = ray_index ? (int64_t)__ldg(ray_index + h) : h;
-            color_map[3 * dst] = c0; color_map[3 * dst + 1] = c1; color_map[3 * dst + 2] = c2;
-            alpha_map[dst] = acc;
+            if (comp == 3) {
+                alpha_map[dst] = acc_all;
+            } else {
+                const float bk = comp == 0 ? bk0 : comp == 1 ? bk1 : bk2;
+                float c = u + wl * __ldg(color_last + 3 * h + comp);
+                if (composite_bkgd) c += (1.0f - acc_all) * bk;
+                color_map[3 * dst + comp] = c;
+            }
         }
     }
 }
@@ -532,9 +565,14 @@ NTX_API int ntx_composite_instanced_forward(const float* rgbs, const float* dist
     const float b0 = composite_bkgd ? bkgd_color[0] : 0.f, b1 = composite_bkgd ? bkgd_color[1] : 0.f,
                 b2 = composite_bkgd ? bkgd_color[2] : 0.f;
     const int threads = 256;
-    composite_inst_kernel<<<grid_for_warps(H, threads), threads, 0, (cudaStream_t)stream>>>(
-        rgbs, dists, alpha_weight, ray_ptr, color_last, alpha_last, ray_index, instance_color, H, patch_scale,
-        density_scale, map_exr, composite_bkgd, b0, b1, b2, color_map, alpha_map);
+    if (map_exr)
+        composite_inst_kernel<true><<<grid_for_warps(H, threads), threads, 0, (cudaStream_t)stream>>>(
+            rgbs, dists, alpha_weight, ray_ptr, color_last, alpha_last, ray_index, instance_color, H, patch_scale,
+            density_scale, composite_bkgd, b0, b1, b2, color_map, alpha_map);
+    else
+        composite_inst_kernel<false><<<grid_for_warps(H, threads), threads, 0, (cudaStream_t)stream>>>(
+            rgbs, dists, alpha_weight, ray_ptr, color_last, alpha_last, ray_index, instance_color, H, patch_scale,
+            density_scale, composite_bkgd, b0, b1, b2, color_map, alpha_map);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
