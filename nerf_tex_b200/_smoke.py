@@ -4,7 +4,6 @@ checker, not the thing run."""
 
 from __future__ import annotations
 
-import math
 import sys
 from pathlib import Path
 

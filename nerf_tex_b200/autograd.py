@@ -15,7 +15,7 @@ Dense order, so any torch optimizer (or the NCCL all-reduce of train.py) works o
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import torch
 

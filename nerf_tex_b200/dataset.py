@@ -6,7 +6,7 @@ loading and the data.* distributions are out of scope."""
 from __future__ import annotations
 
 import math
-from typing import Iterator, List, Optional, Sequence
+from typing import Iterator, Optional, Sequence
 
 import numpy as np
 import torch

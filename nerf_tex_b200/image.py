@@ -7,7 +7,6 @@ in for ``tf.io.encode_png``."""
 from __future__ import annotations
 
 import ctypes as C
-import math
 import struct
 import zlib
 from typing import Optional, Tuple

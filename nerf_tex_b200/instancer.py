@@ -12,7 +12,7 @@ the same data into the reference's dense 10-tuple for callers written against in
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import torch
 

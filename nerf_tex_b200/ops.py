@@ -7,7 +7,7 @@ allocated torch CUDA tensors.  All launches go to torch's current stream.
 from __future__ import annotations
 
 import ctypes as C
-from typing import Optional, Sequence, Tuple
+from typing import Optional
 
 import torch
 

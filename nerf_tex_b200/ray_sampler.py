@@ -8,7 +8,6 @@ from typing import Any, Tuple
 import torch
 
 from . import ops
-from ._lib import as_cuda
 from .proxy import AABB
 
 

@@ -14,7 +14,7 @@ and the kernels identical draws).
 from __future__ import annotations
 
 import math
-from typing import Any, Dict, Optional, Tuple
+from typing import Dict, Optional
 
 import torch
 

@@ -4,7 +4,7 @@ finished per-ray outputs — equal, padded blocks in one all-gather per output, 
 
 from __future__ import annotations
 
-from typing import Dict, Optional
+from typing import Dict
 
 import torch
 import torch.distributed as dist

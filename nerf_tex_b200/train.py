@@ -7,7 +7,7 @@ flat fp32 gradient buffers are summed with one NCCL all-reduce per model over NV
 
 from __future__ import annotations
 
-from typing import Any, Dict, List, Optional
+from typing import Any, Dict
 
 import torch
 import torch.distributed as dist

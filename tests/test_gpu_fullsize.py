@@ -2,9 +2,6 @@
 sortedness / containment of the sampler, bounds of the compositor, and — the property that ray sharding rests on —
 results that do not depend on how the rays are chunked or split across calls."""
 
-import math
-
-import numpy as np
 import pytest
 import torch
 

@@ -2,9 +2,6 @@
 here, so these are known-answer tests of the primitives (CRC-32C, varints, snappy, protobuf fields) and round trips
 through the module's own writer — self-consistency with the published format, not proof of interoperability."""
 
-import os
-import struct
-
 import numpy as np
 import pytest
 
