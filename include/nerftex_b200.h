@@ -230,6 +230,23 @@ int ntx_rays_from_camera(const float* image_plane_loc, int64_t n, int height, in
                          float* rays_o, float* rays_d, float* t, float* cone_scale, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Training step: loss and optimiser (network/loss.py, network/train.py:49-67)
+ * ---------------------------------------------------------------------------------------- */
+
+/* AlphaLoss.__call__ (network/loss.py:30-49) with loss_fn / alpha_loss_fn in {0: mse (:51-54), 1: smape (:56-58)}:
+ * loss[1] (device) and the gradient of the loss with respect to color_pred[n,3], alpha_pred[n] (and the coarse pair,
+ * both NULL or both given) in one launch. */
+int ntx_alpha_loss(const float* color_true, const float* alpha_true, const float* color_pred, const float* alpha_pred,
+                   const float* color_pred_coarse, const float* alpha_pred_coarse, int64_t n_rays, int color_loss_kind,
+                   int alpha_loss_kind, float gamma, int filter_color_loss, int use_hard_mask, float* loss,
+                   float* d_color_pred, float* d_alpha_pred, float* d_color_pred_coarse, float* d_alpha_pred_coarse,
+                   void* stream);
+/* tf.keras.optimizers.Adam.apply_gradients (network/train.py:52,67) on a flat buffer: m, v updated in place,
+ * params -= lr_t * m / (sqrt(v) + epsilon) with lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t) computed by the caller. */
+int ntx_adam_step(float* params, const float* grad, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2,
+                  float epsilon, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * mip variants (network/renderer.py:356-587): cone-segment gaussians + compositing over S + 1 depth edges.
  * The integrated positional encoding itself (network/layer.py:25-41) is the n_pos = 6 mode of the fused MLP kernel.
  * ---------------------------------------------------------------------------------------- */

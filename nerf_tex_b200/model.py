@@ -107,6 +107,7 @@ class FusedNerfTexMLP:
     def mark_dirty(self) -> None:
         """Call after changing ``master`` in place (optimizer step, checkpoint load)."""
         self._packed_version = -1
+        self._packed_t_version = None                    # transposed image of the backward (autograd.py)
 
     def ensure_packed(self) -> torch.Tensor:
         if self._packed_version != self.master._version:

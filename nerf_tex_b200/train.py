@@ -68,6 +68,14 @@ class Trainer:
             if g is None:
                 continue
             m, v = self.m[k], self.v[k]
+            if model.master.is_cuda:                      # one launch (ntx_adam_step) instead of eight
+                from . import _lib
+                from ._lib import check, ptr, stream_ptr
+                with torch.no_grad(), torch.cuda.device(model.master.device):
+                    check(_lib.load().ntx_adam_step(ptr(model.master.detach()), ptr(g.contiguous()), ptr(m), ptr(v), m.numel(),
+                                                    float(lr_t), self.beta1, self.beta2, self.eps, stream_ptr()))
+                model.mark_dirty()                        # the packed weight images (forward and transposed) are stale
+                continue
             m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
             v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
             model.master.addcdiv_(m, v.sqrt().add_(self.eps), value=-lr_t)

@@ -197,3 +197,57 @@ def test_native_backward_kernels_match_library_gemm_backward(npar, n):
     # rows beyond n inside the last tile carry exactly zero gradient
     tail = untile(dy_img[0], saved[2].shape[1] * 128)[n:]
     assert float(tail.abs().max()) == 0.0 if tail.numel() else True
+
+
+@pytest.mark.parametrize("kinds,coarse,hard,filt", [(("smape", "mse"), True, True, True), (("mse", "mse"), False, True, True),
+                                                     (("smape", "smape"), True, False, True), (("mse", "smape"), True, True, False)])
+def test_fused_alpha_loss_matches_torch_expression(kinds, coarse, hard, filt):
+    """ntx_alpha_loss (value + gradients in one launch) against the generic torch form of network/loss.py:30-58."""
+    from nerf_tex_b200 import loss as L
+    g = torch.Generator(device="cuda").manual_seed(3)
+    B, Nr = 4, 777
+    ct = torch.rand((B, Nr, 3), device="cuda", generator=g)
+    at = torch.rand((B, Nr), device="cuda", generator=g)
+    at[at < 0.3] = 0.0
+    mk = lambda *s: torch.rand(s, device="cuda", generator=g).requires_grad_(True)
+    cp, ap = mk(B, Nr, 3), mk(B, Nr)
+    cc, ac = (mk(B, Nr, 3), mk(B, Nr)) if coarse else (None, None)
+    fn = L.AlphaLoss("network.loss." + kinds[0], "network.loss." + kinds[1], gamma=0.7, filter_color_loss=filt, use_hard_mask=hard)
+    assert fn._kinds is not None
+    fused = fn(ct, at, cp, ap, cc, ac)
+    (fused * 3.0).backward()
+    got = [x.grad.clone() for x in (cp, ap, cc, ac) if x is not None]
+    for x in (cp, ap, cc, ac):
+        if x is not None:
+            x.grad = None
+    fn._kinds = None                                                   # generic path
+    ref = fn(ct, at, cp, ap, cc, ac)
+    (ref * 3.0).backward()
+    want = [x.grad for x in (cp, ap, cc, ac) if x is not None]
+    assert abs(float(fused.detach()) - float(ref.detach())) < 1e-5 * max(1.0, abs(float(ref.detach())))
+    for a, b in zip(got, want):
+        assert torch.allclose(a, b, rtol=1e-4, atol=1e-9), float((a - b).abs().max())
+
+
+def test_adam_kernel_matches_keras_form():
+    """Trainer.adam_update through ntx_adam_step against the oracle's tf.keras-form Adam (train.py:52)."""
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.train import Trainer
+    m = FusedNerfTexMLP(1, 4, seed=1)
+    tr = Trainer({"model": m}, renderer=None, loss_fn=None, lrate=5e-4, lrate_decay=500)
+    rng = np.random.default_rng(0)
+    p = m.master.detach().cpu().numpy().copy()
+    mm, vv = np.zeros_like(p), np.zeros_like(p)
+    for step in range(1, 4):
+        gnp = rng.normal(size=p.shape).astype(np.float32) * 1e-2
+        m.master.grad = torch.as_tensor(gnp).cuda()
+        lr = tr.current_lr()
+        tr.step += 1
+        tr.adam_update(lr)
+        p, mm, vv = O.adam_step(p, gnp, mm, vv, step, lr)
+        assert m._packed_version == -1
+    np.testing.assert_allclose(m.master.detach().cpu().numpy(), p, rtol=2e-6, atol=5e-8)      # steps are ~5e-4
+    np.testing.assert_allclose(tr.m["model"].cpu().numpy(), mm, rtol=2e-6, atol=5e-9)          # |m| ~ 1e-3, fused multiply-adds
+    # beta2 = 0.999 is not an fp32 number: the kernel (like TF, which keeps hyper-parameters in the variable dtype) uses
+    # 1 - fl32(0.999), the oracle 1 - 0.999 in double: 1.3e-5 apart
+    np.testing.assert_allclose(tr.v["model"].cpu().numpy(), vv, rtol=3e-5, atol=1e-11)
