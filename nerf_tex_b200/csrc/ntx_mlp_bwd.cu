@@ -568,9 +568,8 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
 // A warp reads 32 consecutive rows of one 32-column block (2 KB contiguous); partial sums stay in registers
 // over all tiles of the CTA and are reduced across the warp once at the end.
 template <int ND>
-__global__ void __launch_bounds__(256)
-mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_img, int x_blocks, const float* __restrict__ d_rgbs, int d0,
-                       float* __restrict__ out, int64_t n_rows, int64_t n_tiles) {
+__device__ __forceinline__ void heads_wgrad_body(const uint8_t* __restrict__ x_img, int x_blocks, const float* __restrict__ d_rgbs,
+                                                 int d0, float* __restrict__ out, int64_t n_rows, int64_t n_tiles) {
     const int blk = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (blk >= x_blocks) return;
     float acc[32 * ND];
@@ -578,7 +577,7 @@ mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_img, int x_blocks, const fl
     for (int i = 0; i < 32 * ND; ++i) acc[i] = 0.0f;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint8_t* tb = x_img + tile * (int64_t)kMainBytes + blk * kBlockBytes;
-#pragma unroll 1
+#pragma unroll
         for (int rgp = 0; rgp < 4; ++rgp) {
             const int row = rgp * 32 + lane;
             const int64_t grow = tile * kTileRows + row;
@@ -606,6 +605,14 @@ mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_img, int x_blocks, const fl
         const float v = ntx_warp_sum(acc[i]);
         if (lane == 0) atomicAdd(out + (blk * 32 + i / ND) * ND + (i % ND), v);
     }
+}
+
+// both heads in one launch (blockIdx.y = 0: density head, 1: colour head): each alone leaves the memory system half idle
+__global__ void __launch_bounds__(256)
+mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_alpha, const uint8_t* __restrict__ x_rgb, const float* __restrict__ d_rgbs,
+                       float* __restrict__ out_alpha, float* __restrict__ out_rgb, int64_t n_rows, int64_t n_tiles) {
+    if (blockIdx.y == 0) heads_wgrad_body<1>(x_alpha, 8, d_rgbs, 3, out_alpha, n_rows, n_tiles);
+    else heads_wgrad_body<3>(x_rgb, 4, d_rgbs, 0, out_rgb, n_rows, n_tiles);
 }
 
 }  // namespace
@@ -721,12 +728,10 @@ NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img,
     // heads: density (input = last trunk layer's output), colour (input = the 128-wide last step's output)
     const Layer& la = p.layers[p.alpha_layer];
     const Layer& lr = p.layers[p.rgb_layer];
-    const int64_t gh = a.n_tiles < 2 * ntx_sm_count() ? a.n_tiles : 2 * ntx_sm_count();
-    mlp_heads_wgrad_kernel<1><<<(unsigned)gh, 256, 0, stc>>>((const uint8_t*)acts_img + (int64_t)(mlp->cfg.depth - 1) * step_bytes,
-                                                              8, d_rgbs, 3, grad + la.w_off, n_rows, a.n_tiles);
-    NTX_LAUNCH_CHECK();
-    mlp_heads_wgrad_kernel<3><<<(unsigned)gh, 256, 0, stc>>>((const uint8_t*)acts_img + (int64_t)(p.n_steps - 1) * step_bytes,
-                                                              4, d_rgbs, 0, grad + lr.w_off, n_rows, a.n_tiles);
+    const int64_t gh = a.n_tiles < 4 * ntx_sm_count() ? a.n_tiles : 4 * ntx_sm_count();
+    mlp_heads_wgrad_kernel<<<dim3((unsigned)gh, 2), 256, 0, stc>>>(
+        (const uint8_t*)acts_img + (int64_t)(mlp->cfg.depth - 1) * step_bytes,
+        (const uint8_t*)acts_img + (int64_t)(p.n_steps - 1) * step_bytes, d_rgbs, grad + la.w_off, grad + lr.w_off, n_rows, a.n_tiles);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
