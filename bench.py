@@ -45,7 +45,7 @@ PATCH_SCALE = 0.09
 NPAR = (1, 6)
 B0, B1 = [-1.4, -1.2, -.1], [1.2, 1.2, 1.8]
 DATASET_PARAMS = [1, 1, 1, .1, 0, 0, 1]          # config_carpet_render.py:40
-CPU_SAMPLE_RAYS = 2048
+CPU_SAMPLE_RAYS = 8192
 MACS_PER_SAMPLE = {(1, 6): 680832, (1, 4): 676224, (2, 3): 678528}
 
 
@@ -197,19 +197,21 @@ def cpu_baseline_run(steps: int, warmup: int):
     dense = (d, pts, np.zeros((R, S), np.float32), dists, np.zeros((R, 1, 3), np.float32),
              (rng.uniform(size=(R, 1)) < .5).astype(np.float32), np.ones((R, S), np.float32),
              np.zeros((R, S), np.int32), idxs, params)
+    from oracle.torch_port import TorchPort
     model = O.ParamNerfOracle(n_parameters=NPAR, seed=1)
-    n_in_shell = int(mask.sum())
+    port = TorchPort(model)                                   # threaded fp32 port of the same graph (pinned to the
+    n_in_shell = int(mask.sum())                              # NumPy oracle in tests/test_torch_port.py)
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        O.instance_evaluate_model(model, dense, R, patch_scale=PATCH_SCALE, net_chunk=32768)
+        port.instance_evaluate_model(dense, R, patch_scale=PATCH_SCALE, net_chunk=32768)
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     dt = float(np.mean(times))
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     return {"value": R / dt, "unit": "rays/s", "cores": cores, "kind": "port",
-            "sample": f"{R} rays of the frame ({n_in_shell} in-shell samples), oracle/nerftex_oracle.py "
-                      f"instance_evaluate_model (NumPy fp32 + multithreaded BLAS), mean of {steps} passes",
+            "sample": f"{R} rays of the frame ({n_in_shell} in-shell samples), oracle/torch_port.py "
+                      f"instance_evaluate_model (torch-CPU fp32, all host threads), mean of {steps} passes",
             "samples_per_sec": n_in_shell / dt, "ms_per_pass": dt * 1e3}
 
 
