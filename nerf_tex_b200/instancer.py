@@ -14,6 +14,7 @@ from __future__ import annotations
 import math
 from typing import Dict, Optional
 
+import numpy as np
 import torch
 
 from ._lib import as_cuda
@@ -187,7 +188,7 @@ class Instancer:
         return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.minv, self.dirt, self.origins,
                                              self.b_0, self.b_1, seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
                                              use_mean_distance=self.use_mean_distance, spheres=self.spheres,
-                                             light_strength_idx=self.light_strength_idx, blend_range=0.2 * self.patch_scale)
+                                             light_strength_idx=self.light_strength_idx, blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)))   # fp32 product, instancer.cpp:696
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""
