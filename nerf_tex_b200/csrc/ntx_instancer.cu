@@ -191,7 +191,8 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f};
     if (live) for (int a = 0; a < 3; ++a) { o[a] = rays_o[3 * ray + a]; d[a] = rays_d[3 * ray + a]; }
     const float b0[3] = {b00, b01, b02}, b1[3] = {b10, b11, b12};
-    const float inv_dd = 1.0f / fmaxf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], 1e-30f);
+    const float inv_dn = rsqrtf(fmaxf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], 1e-30f));
+    const float dh[3] = {d[0] * inv_dn, d[1] * inv_dn, d[2] * inv_dn};
     // the ray's sorted hit list: the first kSmemHits entries in shared memory (entry k of thread t at
     // s_hits[k * kTraceThreads + t], conflict-free), the tail in the ray's row of the global workspace.  (A per-thread
     // array would be local memory: 1.6 KB per ray falls out of L1, and holding all 200 entries in shared memory leaves
@@ -202,6 +203,18 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     int n_hits = 0;
     auto insert = [&](float t, uint32_t inst) {         // keep the kMaxHits smallest (t, inst), sorted
         const uint64_t key = ((uint64_t)__float_as_uint(t + 0.0f) << 32) | inst;
+        if (n_hits < kSmemHits) {                       // the usual case: the whole list is in shared memory
+            uint64_t* hs = s_hits + threadIdx.x;
+            int k = n_hits++;
+            while (k > 0) {
+                const uint64_t prev = hs[(k - 1) * kTraceThreads];
+                if (prev <= key) break;
+                hs[k * kTraceThreads] = prev;
+                --k;
+            }
+            hs[k * kTraceThreads] = key;
+            return;
+        }
         int k;
         if (n_hits < kMaxHits) k = n_hits++;
         else if (key < H(kMaxHits - 1)) k = kMaxHits - 1;
@@ -228,10 +241,9 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
                 // only instances whose box the ray certainly misses, so the hit list is unchanged
                 const float4 sp = s_sph[j];
                 const float cx = sp.x - o[0], cy = sp.y - o[1], cz = sp.z - o[2];
-                const float tc = (cx * d[0] + cy * d[1] + cz * d[2]) * inv_dd;
-                const float px = cx - tc * d[0], py = cy - tc * d[1], pz = cz - tc * d[2];
                 const float cc = cx * cx + cy * cy + cz * cz;
-                if (px * px + py * py + pz * pz > sp.w + 1e-5f * cc) continue;
+                const float along = cx * dh[0] + cy * dh[1] + cz * dh[2];          // dh: unit ray direction
+                if (fmaf(-along, along, cc) > fmaf(1e-5f, cc, sp.w)) continue;     // margin: rounding of cc - along^2
             }
             const float* M = s_minv + 12 * j;
             float tin = -CUDART_INF_F, tout = CUDART_INF_F;
