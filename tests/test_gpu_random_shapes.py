@@ -102,3 +102,31 @@ def test_instanced_compositor_ragged_csr():
         full_c[ridx], full_a[ridx] = wc, wa
         np.testing.assert_allclose(ga.cpu().numpy(), full_a, rtol=1e-5, atol=3e-6, err_msg=str(trial))
         np.testing.assert_allclose(gc.cpu().numpy(), full_c, rtol=1e-5, atol=3e-6 * max(1.0, float(np.abs(wc).max())), err_msg=str(trial))
+
+
+def test_mlp_random_architectures():
+    """The step / slice program builder over architectures nobody picked by hand: depth 1..12, any skip set, 0..2 extra
+    colour layers, 0..3 geometry and 0..7 appearance parameters, both encodings, ragged row counts (model.py:58-125)."""
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    rng = np.random.default_rng(77)
+    for trial in range(14):
+        depth = int(rng.integers(1, 13))
+        skips = sorted(set(int(x) for x in rng.integers(0, max(depth - 1, 1), size=int(rng.integers(0, 3))) if x < depth - 1))
+        cd, g, a = int(rng.integers(0, 3)), int(rng.integers(0, 4)), int(rng.integers(0, 8))
+        n_pos = 6 if (trial % 4 == 3 and g + a > 0) else 3
+        n = int(rng.integers(1, 3000))
+        om = O.ParamNerfOracle(n_parameters=(g, a), n_pos=n_pos, depth=depth, skips=skips, color_depth=cd, seed=trial)
+        om.randomize_biases(100 + trial, 0.1)
+        gm = FusedNerfTexMLP(n_geo=g, n_app=a, depth=depth, skips=skips, color_depth=cd, n_pos=n_pos)
+        gm.load_named_weights(om.named_weights())
+        pos = rng.uniform(-1.4, 1.5, (n, 3)).astype(np.float32)
+        if n_pos == 6:
+            pos = np.concatenate([pos, (10.0 ** rng.uniform(-7, -1, (n, 3))).astype(np.float32)], -1)
+        d = rng.normal(size=(n, 3)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=-1, keepdims=True)
+        prm = rng.uniform(0, 1, (n, g + a)).astype(np.float32)
+        color, alpha = gm((cu(pos), cu(d), cu(prm) if g + a else None))
+        ec, ea = O.forward_bf16_emulated(om, pos, d, prm)
+        tag = (trial, depth, skips, cd, g, a, n_pos, n)
+        assert np.abs(color.cpu().numpy() - ec).max() < 5e-3 * max(1.0, np.abs(ec).max()), tag
+        assert np.abs(alpha.cpu().numpy() - ea).max() < 5e-3 * max(1.0, np.abs(ea).max()), tag
