@@ -130,3 +130,40 @@ def test_mlp_random_architectures():
         tag = (trial, depth, skips, cd, g, a, n_pos, n)
         assert np.abs(color.cpu().numpy() - ec).max() < 5e-3 * max(1.0, np.abs(ec).max()), tag
         assert np.abs(alpha.cpu().numpy() - ea).max() < 5e-3 * max(1.0, np.abs(ea).max()), tag
+
+
+def test_backward_random_architectures():
+    """The data- and weight-gradient kernels over random architectures: against float64 autograd of the oracle graph on
+    the same rows and the same upstream gradient (model.py:104-123 in reverse)."""
+    import torch_ref as T
+    from nerf_tex_b200.autograd import mlp_backward, mlp_backward_native, mlp_forward_train
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    rng = np.random.default_rng(99)
+    for trial in range(8):
+        depth = int(rng.integers(2, 13))
+        skips = sorted(set(int(x) for x in rng.integers(0, depth - 1, size=int(rng.integers(0, 3)))))
+        cd, g, a = int(rng.integers(0, 3)), int(rng.integers(0, 4)), int(rng.integers(0, 8))
+        n = int(rng.integers(200, 2500))
+        om = O.ParamNerfOracle(n_parameters=(g, a), depth=depth, skips=skips, color_depth=cd, seed=40 + trial)
+        om.randomize_biases(60 + trial, 0.05)
+        gm = FusedNerfTexMLP(n_geo=g, n_app=a, depth=depth, skips=skips, color_depth=cd)
+        gm.load_named_weights(om.named_weights())
+        pos = rng.uniform(-1, 1, (n, 3)).astype(np.float32)
+        d = rng.normal(size=(n, 3)).astype(np.float32)
+        d /= np.linalg.norm(d, axis=-1, keepdims=True)
+        prm = rng.uniform(0, 1, (n, g + a)).astype(np.float32)
+        d_rgbs = (rng.normal(size=(n, 4)) * 0.01).astype(np.float32)
+        _, saved = mlp_forward_train(gm, n_rows=n, pos=cu(pos), dir=cu(d), params=cu(prm) if g + a else None, rows_per_group=1)
+        lib = mlp_backward(gm, saved, cu(d_rgbs))                      # layer-wise library GEMMs on the same saved operands
+        got = mlp_backward_native(gm, saved, cu(d_rgbs))
+        assert float((got - lib).norm() / lib.norm()) < 1e-2, (trial, depth, skips, cd, g, a, n)
+        got = got.cpu().double()
+        P = T.make_params(om)
+        t64 = lambda x: torch.tensor(x, dtype=torch.float64)
+        color, alpha = T.mlp(om, P, t64(pos), t64(d), t64(prm))
+        ((color * t64(d_rgbs[:, :3])).sum() + (alpha[:, 0] * t64(d_rgbs[:, 3])).sum()).backward()
+        want = T.flat_grads(om, P)
+        cos = float((got * want).sum() / (got.norm() * want.norm()))
+        rel = float((got - want).norm() / want.norm())
+        # against float64 the bf16 chain's error grows with depth (random upstream gradients flip ReLU masks freely: cos 0.996-0.999); the logic check is the line above
+        assert cos > 0.99 and rel < 0.15, (trial, depth, skips, cd, g, a, n, cos, rel)
