@@ -567,14 +567,17 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
 //   out[c * n_d + j] += sum_rows X[row][c] * d_rgbs[row][d0 + j]       (n_d = 1: density head, 3: colour head)
 // A warp reads 32 consecutive rows of one 32-column block (2 KB contiguous); partial sums stay in registers
 // over all tiles of the CTA and are reduced across the warp once at the end.
-template <int ND>
-__device__ __forceinline__ void heads_wgrad_body(const uint8_t* __restrict__ x_img, int x_blocks, const float* __restrict__ d_rgbs,
+// CH: 16-byte chunks (8 columns) of a 32-column block a warp owns: 4 (density head: 8 warps = 8 blocks) or 2 (colour
+// head: 8 warps = 4 blocks x 2 halves), which keeps the accumulators at <= 48 registers and two blocks resident per SM
+// (with 96 the kernel ran at one block per SM and 11 % occupancy, latency-bound at 3 TB/s).
+template <int ND, int CH>
+__device__ __forceinline__ void heads_wgrad_body(const uint8_t* __restrict__ x_img, const float* __restrict__ d_rgbs,
                                                  int d0, float* __restrict__ out, int64_t n_rows, int64_t n_tiles) {
-    const int blk = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    if (blk >= x_blocks) return;
-    float acc[32 * ND];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int blk = CH == 4 ? warp : warp >> 1, c0 = CH == 4 ? 0 : (warp & 1) * 2;
+    float acc[8 * CH * ND];
 #pragma unroll
-    for (int i = 0; i < 32 * ND; ++i) acc[i] = 0.0f;
+    for (int i = 0; i < 8 * CH * ND; ++i) acc[i] = 0.0f;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const uint8_t* tb = x_img + tile * (int64_t)kMainBytes + blk * kBlockBytes;
 #pragma unroll
@@ -585,8 +588,8 @@ __device__ __forceinline__ void heads_wgrad_body(const uint8_t* __restrict__ x_i
 #pragma unroll
             for (int j = 0; j < ND; ++j) d[j] = grow < n_rows ? __ldg(d_rgbs + 4 * grow + d0 + j) : 0.0f;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const uint4 v = __ldg(reinterpret_cast<const uint4*>(tb + row * 64 + ((c ^ ((row >> 1) & 3)) << 4)));
+            for (int c = 0; c < CH; ++c) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(tb + row * 64 + (((c0 + c) ^ ((row >> 1) & 3)) << 4)));
                 const uint32_t w[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
@@ -601,18 +604,18 @@ __device__ __forceinline__ void heads_wgrad_body(const uint8_t* __restrict__ x_i
         }
     }
 #pragma unroll
-    for (int i = 0; i < 32 * ND; ++i) {
+    for (int i = 0; i < 8 * CH * ND; ++i) {
         const float v = ntx_warp_sum(acc[i]);
-        if (lane == 0) atomicAdd(out + (blk * 32 + i / ND) * ND + (i % ND), v);
+        if (lane == 0) atomicAdd(out + (blk * 32 + c0 * 8 + i / ND) * ND + (i % ND), v);
     }
 }
 
-// both heads in one launch (blockIdx.y = 0: density head, 1: colour head): each alone leaves the memory system half idle
-__global__ void __launch_bounds__(256)
+// both heads in one launch (blockIdx.y = 0: density head, 1: colour head)
+__global__ void __launch_bounds__(256, 2)
 mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_alpha, const uint8_t* __restrict__ x_rgb, const float* __restrict__ d_rgbs,
                        float* __restrict__ out_alpha, float* __restrict__ out_rgb, int64_t n_rows, int64_t n_tiles) {
-    if (blockIdx.y == 0) heads_wgrad_body<1>(x_alpha, 8, d_rgbs, 3, out_alpha, n_rows, n_tiles);
-    else heads_wgrad_body<3>(x_rgb, 4, d_rgbs, 0, out_rgb, n_rows, n_tiles);
+    if (blockIdx.y == 0) heads_wgrad_body<1, 4>(x_alpha, d_rgbs, 3, out_alpha, n_rows, n_tiles);
+    else heads_wgrad_body<3, 2>(x_rgb, d_rgbs, 0, out_rgb, n_rows, n_tiles);
 }
 
 }  // namespace
