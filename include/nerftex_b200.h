@@ -372,6 +372,13 @@ int ntx_render_rays(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_t* m
  *     split the chunk, or use ntx_render_rays;
  *   - the first call on each device looks up the array's device address (with that device
  *     current).  Make that first call during set-up, before any stream capture begins;
+ *   - "never allocates" holds from that first call on, not for it: the CUDA runtime loads a
+ *     library's device image lazily, and it is that load — triggered by the first call into this
+ *     file on a device — that reserves the NTX_STATIC_SCRATCH_BYTES.  So load the library and make
+ *     the first call (a one-ray chunk will do) BEFORE the host framework takes the rest of the
+ *     GPU's memory, or run the process with CUDA_MODULE_LOADING=EAGER so that the reservation
+ *     happens when the library is loaded; otherwise that first call can fail with CUDA's
+ *     out-of-memory error (reported through ntx_last_error());
  *   - all calls share the one array and it keeps whatever the last call wrote.  Nothing in it
  *     needs clearing — each call overwrites every region before reading it — but two calls that
  *     can overlap on the GPU (different streams, or host threads on the same device) race on

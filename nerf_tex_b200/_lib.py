@@ -99,10 +99,12 @@ def load() -> C.CDLL:
         raise NtxError(f"{LIB_PATH} not found: the CUDA library is required (no CPU fallback). "
                        f"Build it with `python -m nerf_tex_b200._build`.")
     lib = C.CDLL(str(LIB_PATH))
+    missing = [name for name in SIGNATURES if not hasattr(lib, name)]
+    if missing:                                           # a stale prebuilt library must fail here, not at first use
+        raise NtxError(f"{LIB_PATH} does not export {', '.join(missing)}: rebuild it with "
+                       f"`python -m nerf_tex_b200._build -f`")
     for name, (res, args) in SIGNATURES.items():
-        fn = getattr(lib, name, None)
-        if fn is None:
-            continue  # symbols added by later rounds are checked by tests/test_abi.py
+        fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
     _lib = lib

@@ -110,8 +110,8 @@ int ntx_render_rays_impl(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp
 
 int ntx_render_rays_check(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_t* mlp_fine, const void* packed_fine,
                           const ntx_render_config* cfg, const float* rays_o, const float* rays_d, const float* t,
-                          const float* z_rand, const float* u, int R, float* color_pred, float* alpha_pred,
-                          float* color_pred_coarse, float* alpha_pred_coarse) {
+                          const float* cone_scale, const float* z_rand, const float* u, int R, float* color_pred,
+                          float* alpha_pred, float* color_pred_coarse, float* alpha_pred_coarse) {
     NTX_REQUIRE(mlp && packed && cfg, "render_rays: null model / config");
     NTX_REQUIRE(R >= 0 && cfg->n_samples >= 2 && cfg->n_importance >= 0, "render_rays: bad shape R=%d S=%d N=%d", R,
                 cfg->n_samples, cfg->n_importance);
@@ -119,6 +119,8 @@ int ntx_render_rays_check(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     if (R == 0) return NTX_OK;
     NTX_REQUIRE(rays_o && rays_d && t && color_pred && alpha_pred, "render_rays: null pointer");
     NTX_REQUIRE(!cfg->perturb || z_rand, "render_rays: perturb requires z_rand");
+    NTX_REQUIRE(cfg->blur_idx < 0 || cone_scale, "render_rays: blur_idx = %d scales that parameter by cone_scale * z "
+                "(renderer.py:155-158): pass cone_scale[R]", cfg->blur_idx);
     if (cfg->n_importance > 0) {
         NTX_REQUIRE(color_pred_coarse && alpha_pred_coarse, "render_rays: n_importance > 0 needs the coarse outputs");
         NTX_REQUIRE(cfg->perturb || u, "render_rays: perturb == 0 draws random u (det = perturb): pass u");
@@ -133,8 +135,8 @@ NTX_API int ntx_render_rays(const ntx_mlp_t* mlp, const void* packed, const ntx_
                             const float* noise, const float* noise_fine, int R, float* color_pred, float* alpha_pred,
                             float* color_pred_coarse, float* alpha_pred_coarse, void* workspace,
                             int64_t workspace_bytes, void* stream) {
-    int rc = ntx_render_rays_check(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, z_rand, u, R, color_pred,
-                                   alpha_pred, color_pred_coarse, alpha_pred_coarse);
+    int rc = ntx_render_rays_check(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, cone_scale, z_rand, u, R,
+                                   color_pred, alpha_pred, color_pred_coarse, alpha_pred_coarse);
     if (rc || R == 0) return rc;
     const int64_t need = ntx_render_rays_workspace_bytes(R, cfg->n_samples, cfg->n_importance);
     NTX_REQUIRE(workspace && workspace_bytes >= need, "render_rays: workspace of %lld B needed, %lld B given",
@@ -170,8 +172,8 @@ NTX_API int ntx_render_rays_static(const ntx_mlp_t* mlp, const void* packed, con
                                    const float* cone_scale, const float* z_rand, const float* u, const float* noise,
                                    const float* noise_fine, int R, float* color_pred, float* alpha_pred,
                                    float* color_pred_coarse, float* alpha_pred_coarse, void* stream) {
-    int rc = ntx_render_rays_check(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, z_rand, u, R, color_pred,
-                                   alpha_pred, color_pred_coarse, alpha_pred_coarse);
+    int rc = ntx_render_rays_check(mlp, packed, mlp_fine, packed_fine, cfg, rays_o, rays_d, t, cone_scale, z_rand, u, R,
+                                   color_pred, alpha_pred, color_pred_coarse, alpha_pred_coarse);
     if (rc || R == 0) return rc;
     const int64_t need = ntx_render_rays_workspace_bytes(R, cfg->n_samples, cfg->n_importance);
     NTX_REQUIRE(need <= (int64_t)NTX_STATIC_SCRATCH_BYTES,

@@ -69,7 +69,8 @@ class FusedNerfTexMLP:
         for wo, bo, fi, fo in self.layers:
             lim = math.sqrt(6.0 / (fi + fo))
             flat[wo:wo + fi * fo] = (torch.rand(fi * fo, generator=gen) * 2 - 1) * lim
-        self.master.copy_(flat)
+        with torch.no_grad():                                # master may already be a trainable leaf (Trainer)
+            self.master.copy_(flat)
         self.mark_dirty()
 
     def load_named_weights(self, named: Dict[str, Tuple]) -> None:
@@ -81,7 +82,8 @@ class FusedNerfTexMLP:
             assert tuple(W.shape) == (fi, fo) and tuple(b.shape) == (fo,), (name, W.shape, (fi, fo))
             flat[wo:wo + fi * fo] = W.reshape(-1)
             flat[bo:bo + fo] = b
-        self.master.copy_(flat)
+        with torch.no_grad():                                # Logger restores checkpoints after Trainer made master a leaf
+            self.master.copy_(flat)
         self.mark_dirty()
 
     @property

@@ -293,8 +293,15 @@ def render_rays(model, model_fine, cfg, rays_o, rays_d, t, parameters, cone_scal
                 noise_fine=None, workspace: Optional[torch.Tensor] = None, entry: str = "ntx_render_rays"):
     """One chunk of Renderer.render_rays (network/renderer.py:92-143) in a single C call."""
     lib = _lib.load()
-    R = rays_o.shape[0]
+    rays_o = as_cuda(rays_o)
     dev = rays_o.device
+    f32 = lambda a: None if a is None else as_cuda(a, device=dev)            # dtype / device / contiguity checked once
+    rays_d, t, parameters, z_rand, u, noise, noise_fine = (f32(a) for a in (rays_d, t, parameters, z_rand, u, noise,
+                                                                             noise_fine))
+    # bound to a local so that a reshaped / re-laid-out copy outlives the launch (it must not be freed and its block
+    # handed to the workspace allocation below)
+    cone_flat = None if cone_scale is None else as_cuda(cone_scale, device=dev).reshape(-1).contiguous()
+    R = rays_o.shape[0]
     fine = cfg.n_importance > 0
     color = torch.empty((R, 3), dtype=torch.float32, device=dev)
     alpha = torch.empty((R,), dtype=torch.float32, device=dev)
@@ -305,7 +312,7 @@ def render_rays(model, model_fine, cfg, rays_o, rays_d, t, parameters, cone_scal
     packed_f = model_fine.ensure_packed() if model_fine is not None else None
     args = [model._h, ptr(packed), model_fine._h if model_fine is not None else None, ptr(packed_f), C.byref(cfg),
             ptr(rays_o), ptr(rays_d), ptr(t), ptr(parameters) if npar > 0 else None,
-            ptr(cone_scale.reshape(-1).contiguous()) if cone_scale is not None else None, ptr(z_rand), ptr(u), ptr(noise),
+            ptr(cone_flat), ptr(z_rand), ptr(u), ptr(noise),
             ptr(noise_fine), R, ptr(color), ptr(alpha), ptr(color_c), ptr(alpha_c)]
     if entry == "ntx_render_rays":
         need = lib.ntx_render_rays_workspace_bytes(R, cfg.n_samples, cfg.n_importance)

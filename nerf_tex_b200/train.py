@@ -32,6 +32,20 @@ class Trainer:
         self.beta1, self.beta2, self.eps = 0.9, 0.999, 1e-7
         self.m = {k: torch.zeros_like(v.master) for k, v in models.items()}
         self.v = {k: torch.zeros_like(v.master) for k, v in models.items()}
+        self.sync_replicas()
+
+    def sync_replicas(self) -> None:
+        """Data-parallel replicas must start identical (the all-reduce only averages gradients): rank 0's weights and
+        Adam moments are broadcast to every rank.  Unseeded constructors (seed=None) would otherwise leave each rank
+        with its own glorot draw."""
+        if self.world_size() == 1:
+            return
+        with torch.no_grad():
+            for k in sorted(self.models):
+                model = self.models[k]
+                for buf in (model.master, self.m[k], self.v[k]):
+                    dist.broadcast(buf.detach(), 0, group=self.pg)
+                model.mark_dirty()
 
     def current_lr(self) -> float:
         """ExponentialDecay(lrate, decay_steps=lrate_decay*1e3, decay_rate=0.1), non-staircase (train.py:49-50)."""
@@ -68,17 +82,12 @@ class Trainer:
             if g is None:
                 continue
             m, v = self.m[k], self.v[k]
-            if model.master.is_cuda:                      # one launch (ntx_adam_step) instead of eight
-                from . import _lib
-                from ._lib import check, ptr, stream_ptr
-                with torch.no_grad(), torch.cuda.device(model.master.device):
-                    check(_lib.load().ntx_adam_step(ptr(model.master.detach()), ptr(g.contiguous()), ptr(m), ptr(v), m.numel(),
-                                                    float(lr_t), self.beta1, self.beta2, self.eps, stream_ptr()))
-                model.mark_dirty()                        # the packed weight images (forward and transposed) are stale
-                continue
-            m.mul_(self.beta1).add_(g, alpha=1.0 - self.beta1)
-            v.mul_(self.beta2).addcmul_(g, g, value=1.0 - self.beta2)
-            model.master.addcdiv_(m, v.sqrt().add_(self.eps), value=-lr_t)
+            from . import _lib
+            from ._lib import check, ptr, stream_ptr
+            with torch.cuda.device(model.master.device):  # one launch (ntx_adam_step); ptr() refuses CPU tensors
+                check(_lib.load().ntx_adam_step(ptr(model.master.detach()), ptr(g.contiguous()), ptr(m), ptr(v), m.numel(),
+                                                float(lr_t), self.beta1, self.beta2, self.eps, stream_ptr()))
+            model.mark_dirty()                            # the packed weight images (forward and transposed) are stale
 
     def allreduce_gradients(self) -> None:
         """Mean of the per-rank gradients: one all-reduce per model on its flat buffer."""

@@ -63,11 +63,23 @@ def test_shard_rays_covers_everything():
 
 
 class _FakeRenderer:
-    """Per-ray function of the inputs (CPU tensors), shaped like Renderer.__call__'s result."""
+    """Per-ray function of the inputs (CPU tensors), shaped like Renderer.__call__'s result, with its culling
+    (network/renderer.py:58-88): rays with t == inf get zeros (the background colour under composite_bkgd) and a call
+    in which no ray hits returns an empty dict."""
 
-    def __call__(self, rays_o, rays_d, t, parameters, cone_scale, **kw):
+    n_importance = 0
+
+    def __call__(self, rays_o, rays_d, t, parameters, cone_scale, composite_bkgd=False, bkgd_color=(1., 1., 1.), **kw):
+        hit = t[..., 0] != float("inf")
+        if not bool(hit.any()):
+            return {}
         c = rays_o * 2 + rays_d + parameters[:, None, :3] + cone_scale
-        return {"color_pred": c, "alpha_pred": t[..., 0] * t[..., 1]}
+        c = torch.where(hit[..., None], c, torch.tensor(bkgd_color) if composite_bkgd else torch.zeros(3))
+        a = torch.where(hit, t[..., 0] * t[..., 1], torch.zeros(()))
+        out = {"color_pred": c, "alpha_pred": a}
+        if self.n_importance > 0:
+            out.update({"color_pred_coarse": c * 0.5, "alpha_pred_coarse": a * 0.5})
+        return out
 
 
 def _shard_worker(rank, world, port, q):
@@ -80,7 +92,30 @@ def _shard_worker(rank, world, port, q):
             torch.rand((B, 5), generator=g), torch.rand((B, Nr, 1), generator=g))
     got = render_sharded(_FakeRenderer(), *args, block=16)
     want = _FakeRenderer()(*args)
-    q.put((rank, all(torch.equal(got[k], want[k]) for k in want), tuple(got["color_pred"].shape)))
+    ok = set(got) == set(want) and all(torch.equal(got[k], want[k]) for k in want)
+    # round-robin stripes (the instanced renderer's split) and the coarse pair of a resampling renderer
+    fr = _FakeRenderer()
+    fr.n_importance = 128
+    got2 = render_sharded(fr, *args, block=16, interleave=True)
+    want2 = fr(*args)
+    ok = ok and set(got2) == set(want2) and all(torch.equal(got2[k], want2[k]) for k in want2)
+    # rank 1's whole contiguous block misses the proxy (t == inf): it must still join the gather
+    t_miss = args[2].clone()
+    t_miss[:, 512:] = float("inf")
+    for bk in (False, True):
+        a3 = (args[0], args[1], t_miss, args[3], args[4])
+        got3 = render_sharded(_FakeRenderer(), *a3, block=16, composite_bkgd=bk, bkgd_color=(0.25, 0.5, 1.0))
+        want3 = _FakeRenderer()(*a3, composite_bkgd=bk, bkgd_color=(0.25, 0.5, 1.0))
+        ok = ok and set(got3) == set(want3) and all(torch.equal(got3[k], want3[k]) for k in want3)
+    # nobody hits: the reference returns an empty dict
+    t_none = torch.full_like(args[2], float("inf"))
+    ok = ok and render_sharded(_FakeRenderer(), args[0], args[1], t_none, args[3], args[4], block=16) == {}
+    # fewer rays than world * block: rank 1's share is empty
+    small = tuple(a[:, :10] if a.dim() == 3 else a for a in args)
+    got5 = render_sharded(_FakeRenderer(), *small, block=16)
+    want5 = _FakeRenderer()(*small)
+    ok = ok and all(torch.equal(got5[k], want5[k]) for k in want5)
+    q.put((rank, ok, tuple(got["color_pred"].shape)))
     dist.destroy_process_group()
 
 
@@ -96,3 +131,11 @@ def test_render_sharded_gathers_the_whole_frame_world2():
         p.join(60)
         assert p.exitcode == 0
     assert all(ok and shape == (2, 1003, 3) for _, ok, shape in res)
+
+
+def test_stripe_indices_partition_the_frame():
+    from nerf_tex_b200.sharded import stripe_count, stripe_indices
+    for n, w, b in [(640000, 8, 256), (1003, 2, 16), (10, 4, 16), (33, 3, 16), (4096, 8, 800)]:
+        seen = torch.cat([stripe_indices(n, r, w, b) for r in range(w)])
+        assert sorted(seen.tolist()) == list(range(n))
+        assert [stripe_count(n, r, w, b) for r in range(w)] == [int(stripe_indices(n, r, w, b).numel()) for r in range(w)]

@@ -136,7 +136,8 @@ def test_backward_random_architectures():
     """The data- and weight-gradient kernels over random architectures: against float64 autograd of the oracle graph on
     the same rows and the same upstream gradient (model.py:104-123 in reverse)."""
     import torch_ref as T
-    from nerf_tex_b200.autograd import mlp_backward, mlp_backward_native, mlp_forward_train
+    from library_backward import mlp_backward
+    from nerf_tex_b200.autograd import mlp_backward_native, mlp_forward_train
     from nerf_tex_b200.model import FusedNerfTexMLP
     rng = np.random.default_rng(99)
     for trial in range(8):

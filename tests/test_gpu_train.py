@@ -173,7 +173,8 @@ def test_native_backward_kernels_match_library_gemm_backward(npar, n):
     """ntx_mlp_backward_data / _weights against the layer-wise torch.mm backward on the same saved
     operands: both use bf16 operands with fp32 accumulation, so they agree far tighter than either
     agrees with float64."""
-    from nerf_tex_b200.autograd import mlp_backward, mlp_backward_native, mlp_forward_train, untile
+    from library_backward import mlp_backward
+    from nerf_tex_b200.autograd import mlp_backward_native, mlp_forward_train, untile
     from nerf_tex_b200.model import FusedNerfTexMLP
     cd = 0 if npar == (0, 0) else 1
     m = FusedNerfTexMLP(n_geo=npar[0], n_app=npar[1], color_depth=cd, seed=9)

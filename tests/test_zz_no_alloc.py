@@ -4,17 +4,17 @@ a frame loop that cannot afford the stall of an allocation).  Its scratch is a f
 the library image instead of a caller workspace.
 
 Checked here, through the C ABI: two calls in a row (the second with a different, smaller chunk, so
-stale contents of the shared array would show) give the same colours / alphas as ntx_render_rays
-with a caller workspace, within the compositing tolerance used across the GPU tests; a chunk beyond
-the built-in capacity is refused with a clear message.  Collected last (file name) so that a failure
+stale contents of the shared array would show) give bit-for-bit the colours / alphas of
+ntx_render_rays with a caller workspace (both entries launch the same kernels in the same order,
+only the scratch address differs); the free device memory is the same before and after a call made
+with caller-owned outputs; a blur parameter without cone scales and a chunk beyond the built-in
+capacity are refused with clear messages.  Collected last (file name) so that a failure
 here cannot hide any other test when the run stops at the first failure."""
 
 import pytest
 import torch
 
 pytestmark = pytest.mark.gpu
-
-RTOL, ATOL = 1e-5, 1e-6
 
 
 def _inputs(R, seed):
@@ -43,7 +43,7 @@ def test_static_scratch_entry_matches_workspace_entry_twice_in_a_row():
         torch.cuda.synchronize()
         assert set(got) == set(want) == {"color_pred", "alpha_pred", "color_pred_coarse", "alpha_pred_coarse"}
         for k in want:
-            torch.testing.assert_close(got[k], want[k], rtol=RTOL, atol=ATOL, msg=lambda m, k=k: f"{k}: {m}")
+            assert torch.equal(got[k], want[k]), f"{k}: max abs diff {float((got[k] - want[k]).abs().max())}"
         assert float(want["alpha_pred"].max()) > 0.05          # the comparison is about non-trivial renders
 
 
@@ -60,3 +60,38 @@ def test_static_scratch_entry_refuses_chunks_beyond_its_capacity():
         ops.render_rays(m, None, cfg, ro, rd, t, params, cone, z_rand=z_rand, entry="ntx_render_rays_static")
     # the capacity covers the 4096-ray, 64 + 128 sample batch of BASELINE.json configs[0]
     assert ops.render_rays_workspace_bytes(4096, 64, 128) <= (24 << 20)
+
+
+def test_static_scratch_entry_leaves_device_memory_as_it_found_it():
+    """The raw C call with outputs the caller already owns: cudaMemGetInfo reports the same free bytes before and
+    after (the first call on the device, which makes CUDA load the library's image with the array in it, is made
+    beforehand — that is the set-up step the header asks for)."""
+    import ctypes as C
+    from nerf_tex_b200 import _lib, ops
+    from nerf_tex_b200._lib import check, ptr, stream_ptr
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    lib = _lib.load()
+    m = FusedNerfTexMLP(n_geo=1, n_app=4, seed=21)
+    cfg = ops.render_config(64, 0, True, False, False, 0, (1., 1., 1.))          # blur_idx 0: cone scales are used
+    R = 512
+    ro, rd, t, params, cone, z_rand = _inputs(R, 9)
+    cone = cone.reshape(-1).contiguous()
+    color = torch.empty((R, 3), device="cuda")
+    alpha = torch.empty((R,), device="cuda")
+    packed = m.ensure_packed()
+
+    def call(cone_ptr):
+        return lib.ntx_render_rays_static(m._h, ptr(packed), None, None, C.byref(cfg), ptr(ro), ptr(rd), ptr(t), ptr(params),
+                                          cone_ptr, ptr(z_rand), None, None, None, R, ptr(color), ptr(alpha), None, None,
+                                          stream_ptr())
+    check(call(ptr(cone)))                                     # set-up call
+    torch.cuda.synchronize()
+    first = color.clone()
+    free_before, _ = torch.cuda.mem_get_info()
+    check(call(ptr(cone)))
+    torch.cuda.synchronize()
+    free_after, _ = torch.cuda.mem_get_info()
+    assert free_after == free_before, (free_before, free_after)
+    assert torch.equal(color, first)
+    assert call(None) != 0                                     # blur_idx >= 0 without cone scales is refused, not guessed
+    assert b"cone_scale" in lib.ntx_last_error()
