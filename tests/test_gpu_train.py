@@ -5,6 +5,8 @@ per layer cosine >= 0.995 and relative error <= 0.1 (with a bf16 forward the dis
 from 0.3 % at the heads to 4-9 % at trunk0, whose small gradient is a sum of cancelling terms; an
 fp32 gradient chain gives the same numbers, i.e. the residual is the bf16 forward); loss within 1e-3."""
 
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -252,3 +254,31 @@ def test_adam_kernel_matches_keras_form():
     # beta2 = 0.999 is not an fp32 number: the kernel (like TF, which keeps hyper-parameters in the variable dtype) uses
     # 1 - fl32(0.999), the oracle 1 - 0.999 in double: 1.3e-5 apart
     np.testing.assert_allclose(tr.v["model"].cpu().numpy(), vv, rtol=3e-5, atol=1e-11)
+
+
+def test_tensorflow_checkpoint_restores_into_trainable_models(tmp_path):
+    """Train() builds the Trainer (which makes every master buffer a trainable leaf) before the Logger, whose
+    TensorFlow-checkpoint path (logger.py:38-40 restore) then copies weights in place: must not trip autograd."""
+    from nerf_tex_b200 import tf_checkpoint as TF
+    from nerf_tex_b200.logger import Logger
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.train import Trainer
+    from test_tf_checkpoint import keras_keys
+    om = O.ParamNerfOracle((1, 4), seed=5)
+    om.randomize_biases(6, 0.1)
+    creation = [n for n, _, _ in om.layers]
+    tensors = {"step" + TF.VALUE_SUFFIX: np.array(77, np.int64)}
+    tensors.update(keras_keys(om, "model", creation))
+    os.makedirs(tmp_path / "checkpoints")
+    TF.write_bundle(str(tmp_path / "checkpoints" / "ckpt-1"), tensors)
+    with open(tmp_path / "checkpoints" / "checkpoint", "w") as f:
+        f.write('model_checkpoint_path: "ckpt-1"\n')
+    m = FusedNerfTexMLP(n_geo=1, n_app=4, seed=0)
+    tr = Trainer({"model": m}, renderer=None, loss_fn=None)
+    assert m.master.requires_grad
+    Logger(str(tmp_path), {"model": m, "step": 0, "optimizer": tr}, is_training=True)
+    assert tr.step == 77
+    flat = np.concatenate([np.concatenate([W.reshape(-1), b]) for _, W, b in om.layers])
+    assert np.array_equal(m.master.detach().cpu().numpy(), flat)
+    m.reset_parameters(seed=3)                                   # the other in-place writer
+    assert m.master.requires_grad and m.master.is_leaf
