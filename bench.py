@@ -320,6 +320,23 @@ def train_step_dp_bench(dev, rank: int, world: int, steps: int = 10):
     models = {"model": FusedNerfTexMLP(1, 4, seed=1)}
     r = Renderer(n_samples=256, n_importance=0, perturb=True, seed=rank, **models)
     tr = Trainer(models, r, AlphaLoss("network.loss.smape", "network.loss.mse"), lrate=5e-4)
+    # check: the all-reduced gradient is the mean of the per-rank gradients (gathered separately)
+    allreduce_eq_mean = True
+    if world > 1:
+        pred = r(**{k: data[k] for k in ("rays_o", "rays_d", "t", "parameters", "cone_scale")}, training=True)
+        tr.loss_fn(color_true=data["color"], alpha_true=data["alpha"], **pred).backward()
+        m = models["model"]
+        local_g = m.master.grad.detach().clone()
+        gathered = [torch.empty_like(local_g) for _ in range(world)]
+        dist.all_gather(gathered, local_g)
+        mean = torch.stack(gathered).double().sum(0) / world
+        differ = bool((gathered[0] != gathered[-1]).any())
+        tr.allreduce_gradients()
+        err = float((m.master.grad.double() - mean).abs().max() / (mean.abs().max() + 1e-30))
+        flags = [None] * world
+        dist.all_gather_object(flags, bool(err < 1e-6 and differ))
+        allreduce_eq_mean = all(flags)
+        m.master.grad = None
     for _ in range(3):
         tr.train_step(data)
     torch.cuda.synchronize()
@@ -347,7 +364,8 @@ def train_step_dp_bench(dev, rank: int, world: int, steps: int = 10):
         dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     return {"model": "[1,4]", "rays_per_rank": R, "samples_per_ray": 256, "ms_per_step": float(ms), "n_gpus": world,
             "rays_per_sec": world * R / float(ms) * 1e3, "allreduce_us": float(ar), "grad_bytes": int(models["model"].n_params * 4),
-            "replicas_identical": bool(float(lo) == float(hi)), "loss_rank0": float(loss)}
+            "loss_rank0": float(loss),
+            "checks": {"allreduce_eq_mean": bool(allreduce_eq_mean), "replicas_identical": bool(float(lo) == float(hi))}}
 
 
 def c1_forward_bench(dev, steps=20):
@@ -404,82 +422,6 @@ def carpet_patches(n: int, seed: int = 0, extent: float = 1.45, patch_scale: flo
     return T
 
 
-def device_instancer_bench(dev, steps=5):
-    """Rays in, image out with nothing per-sample crossing the host boundary: camera rays (ntx_rays_from_camera), the
-    device shell instancer (ntx_instancer_trace / _march over a procedural 1 500-patch carpet), K1, instanced K2 and the
-    image finishing kernel, for one 800x800 frame of the carpet render config (camera radius 6, angle 0.55, proxy box
-    [-1.5, 1.5]^3, step 0.002, patch box and scale of config_carpet_render.py:82-86)."""
-    import torch
-    from nerf_tex_b200.dataset import look_at
-    from nerf_tex_b200.image import finish_image
-    from nerf_tex_b200.instancer import Instancer
-    from nerf_tex_b200.model import FusedNerfTexMLP
-    from nerf_tex_b200.proxy import AABB
-    from nerf_tex_b200.ray_sampler import Proxy
-    from nerf_tex_b200.renderer import InstanceRenderer
-    n_inst = 1500
-    inst = Instancer(b_0=[-1.4, -1.2, -.1], b_1=[1.2, 1.2, 1.8], textures=["", "", "", "", "light"],
-                     transformations=carpet_patches(n_inst), patch_scale=0.09, instance_sampling_method="nearest", device=dev)
-    chunk = int(os.environ.get("NTX_BENCH_INST_CHUNK", "131072"))            # rays per instancer / K1 / K2 launch
-    r = InstanceRenderer(instancer_config=inst, model=FusedNerfTexMLP(*NPAR, seed=1, device=dev), n_samples=1024,
-                         render_chunk=chunk, step_size=0.002, density_reweighting=True)
-    focal = W / math.tan(0.55 / 2) / 2
-    sampler = Proxy(H, W, focal, AABB([-1.5, -1.5, -1.5], [1.5, 1.5, 1.5]))
-    z = 1 - 2 * 0.3                                                           # data.distribution.Sphere, u = 0.3
-    poses = [look_at([6 * math.cos(v) * math.sqrt(1 - z * z), 6 * math.sin(v) * math.sqrt(1 - z * z), 6 * z])
-             for v in (0.0, 1.3, 2.6, 3.9, 5.2)]
-    params = torch.tensor([[1, 1, 1, .1, 0, 0, 1.]], device=dev)
-    stats = {}
-
-    def frame(pose, count=False):
-        rays_o, rays_d, t, cone = sampler(None, pose)
-        if count:                                                             # workload statistics of this frame
-            hit = torch.isfinite(t[:, 0])
-            ro, rd = rays_o[hit].contiguous(), rays_d[hit].contiguous()
-            n_s = n_h = 0
-            for i in range(0, ro.shape[0], 16384):
-                csr = inst.get_model_input_csr(ro[i:i + 16384], rd[i:i + 16384], params.repeat(ro[i:i + 16384].shape[0], 1),
-                                               1024, 0.002, seed=0)
-                n_s, n_h = n_s + csr["pts"].shape[0], n_h + csr["ray_index"].shape[0]
-            stats.update({"proxy_hit_rays": int(ro.shape[0]), "shell_hit_rays": n_h, "in_shell_samples": n_s,
-                          "samples_per_shell_hit_ray": n_s / max(n_h, 1)})
-        out = r(rays_o[None], rays_d[None], t[None], params, cone[None], composite_bkgd=True, training=False)
-        _, u8 = finish_image(out["color_pred"], out["alpha_pred"], H, W, 1, straight_alpha=True, want_u8=True)
-        return u8
-
-    frame(poses[0], count=True)
-    frame(poses[1])
-    torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(steps):
-        u8 = frame(poses[i % len(poses)])
-        host = u8.cpu()                                                       # the finished 8-bit frame lands on the host
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    # the instancer alone on one chunk
-    rays_o, rays_d, t, cone = sampler(None, poses[0])
-    hit = torch.isfinite(t[:, 0])
-    mid = int(hit.sum()) // 2                                                 # a chunk from the middle of the frame
-    ro, rd = rays_o[hit][mid - chunk // 2:mid + chunk // 2].contiguous(), rays_d[hit][mid - chunk // 2:mid + chunk // 2].contiguous()
-    pf = params.repeat(ro.shape[0], 1)
-    for _ in range(2):
-        inst.get_model_input_csr(ro, rd, pf, 1024, 0.002, seed=0)
-    torch.cuda.synchronize()
-    e0.record()
-    for _ in range(10):
-        inst.get_model_input_csr(ro, rd, pf, 1024, 0.002, seed=0)
-    e1.record()
-    torch.cuda.synchronize()
-    stats.update({"rays": H * W, "instances": n_inst, "ms_per_frame": ms, "rays_per_sec": H * W / ms * 1e3,
-                  "render_chunk": chunk, "instancer_ms_per_chunk": e0.elapsed_time(e1) / 10, "instancer_chunk_rays": int(ro.shape[0]), "h2d_bytes_per_frame": 64 + 28,
-                  "d2h_bytes_per_frame": int(host.numel()),
-                  "api": "Proxy ray sampler -> InstanceRenderer(Instancer(transformations=...)) -> finish_image; pose and "
-                         "parameter vector in, 8-bit RGBA frame out"})
-    return stats
-
-
 def config_dict(extra=None):
     c = {"workload": "carpet-shape instanced render, 800x800 frame (640000 rays), n_parameters [1,6], "
                      "n_samples<=1024, step 0.002, patch_scale 0.09, render_chunk 16384, random-init weights",
@@ -505,13 +447,149 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+class FrameRecords:
+    """Instancer records of the whole 800x800 frame as ONE CSR over all rays (generated once by the seeded
+    SyntheticInstancer in 16 384-ray calls, identical on every rank), from which any ray subset — a rank's stripes, cut
+    into render chunks — is selected.  A ray's records do not depend on which rank or chunk it lands in, so the sharded
+    frame can be compared bit for bit with the single-GPU one."""
+
+    PER_SAMPLE = ("pts", "dirs", "params", "dists", "t", "alpha_weight", "instance_id")
+
+    def __init__(self, dev, d_o, d_d, d_p):
+        import torch
+        from nerf_tex_b200.instancer import SyntheticInstancer
+        synth = SyntheticInstancer(b_0=B0, b_1=B1, patch_scale=PATCH_SCALE, seed=0)
+        n_rays = d_o.shape[0]
+        parts = []
+        counts = torch.zeros(n_rays, dtype=torch.int64, device=dev)
+        self.hit = torch.zeros(n_rays, dtype=torch.bool, device=dev)
+        self.color_last = torch.zeros((n_rays, 3), dtype=torch.float32, device=dev)
+        self.alpha_last = torch.zeros(n_rays, dtype=torch.float32, device=dev)
+        for i in range(0, n_rays, RENDER_CHUNK):
+            c = synth.get_model_input_csr(d_o[i:i + RENDER_CHUNK], d_d[i:i + RENDER_CHUNK], d_p[i:i + RENDER_CHUNK],
+                                          N_SAMPLES, STEP_SIZE)
+            g = c["ray_index"].long() + i
+            counts[g] = c["ray_ptr"][1:] - c["ray_ptr"][:-1]
+            self.hit[g] = True
+            self.color_last[g], self.alpha_last[g] = c["color_last"], c["alpha_last"]
+            parts.append({k: c[k] for k in self.PER_SAMPLE})
+        self.rec = {k: torch.cat([q[k] for q in parts]) for k in self.PER_SAMPLE}
+        self.ptr = torch.zeros(n_rays + 1, dtype=torch.int64, device=dev)
+        self.ptr[1:] = torch.cumsum(counts, 0)
+        self.counts = counts
+        self.n_samples_total = int(self.ptr[-1])
+        self.n_hit = int(self.hit.sum())
+
+    def chunks_for(self, ray_ids):
+        """Render-chunk CSR dicts (RENDER_CHUNK rays each, in order) for the rays `ray_ids` of the frame."""
+        import torch
+        out = []
+        for i in range(0, ray_ids.shape[0], RENDER_CHUNK):
+            ids = ray_ids[i:i + RENDER_CHUNK]
+            local = torch.nonzero(self.hit[ids]).squeeze(1)
+            g = ids[local]
+            cnt, start = self.counts[g], self.ptr[:-1][g]
+            ptr = torch.zeros(g.shape[0] + 1, dtype=torch.int64, device=ids.device)
+            ptr[1:] = torch.cumsum(cnt, 0)
+            rows = torch.repeat_interleave(start - ptr[:-1], cnt) + torch.arange(int(ptr[-1]), device=ids.device)
+            c = {k: v[rows].contiguous() for k, v in self.rec.items()}
+            c.update({"ray_ptr": ptr, "ray_index": local.to(torch.int32), "color_last": self.color_last[g].contiguous(),
+                      "alpha_last": self.alpha_last[g].contiguous()})
+            out.append(c)
+        return out
+
+
+class DeviceFramePipeline:
+    """The call a user makes for a render with the device instancer: camera pose + parameter vector in (host), finished
+    8-bit RGBA frame out (pinned host memory).  Proxy ray sampler (ntx_rays_from_camera) -> InstanceRenderer over the
+    device shell Instancer (procedural 1 500-patch carpet) -> K1 -> instanced K2 -> [all-gather of the per-ray outputs
+    when the frame is sharded over ranks: round-robin stripes of 256 rays] -> ntx_image_finish -> D2H."""
+
+    STRIPE = 256
+
+    def __init__(self, dev, world):
+        import torch
+        from nerf_tex_b200.dataset import look_at
+        from nerf_tex_b200.instancer import Instancer
+        from nerf_tex_b200.model import FusedNerfTexMLP
+        from nerf_tex_b200.proxy import AABB
+        from nerf_tex_b200.ray_sampler import Proxy
+        from nerf_tex_b200.renderer import InstanceRenderer
+        self.dev, self.world = dev, world
+        self.n_inst = 1500
+        self.inst = Instancer(b_0=B0, b_1=B1, textures=["", "", "", "", "light"], transformations=carpet_patches(self.n_inst),
+                              patch_scale=PATCH_SCALE, instance_sampling_method="nearest", device=dev)
+        self.chunk = int(os.environ.get("NTX_BENCH_INST_CHUNK", "131072"))       # rays per instancer / K1 / K2 launch
+        self.r = InstanceRenderer(instancer_config=self.inst, model=FusedNerfTexMLP(*NPAR, seed=1, device=dev),
+                                  n_samples=N_SAMPLES, render_chunk=self.chunk, step_size=STEP_SIZE, density_reweighting=True)
+        focal = W / math.tan(0.55 / 2) / 2
+        self.sampler = Proxy(H, W, focal, AABB([-1.5, -1.5, -1.5], [1.5, 1.5, 1.5]))
+        z = 1 - 2 * 0.3                                                           # data.distribution.Sphere, u = 0.3
+        self.poses = [look_at([6 * math.cos(v) * math.sqrt(1 - z * z), 6 * math.sin(v) * math.sqrt(1 - z * z), 6 * z])
+                      for v in (0.0, 1.3, 2.6, 3.9, 5.2)]
+        self.params_host = torch.tensor([DATASET_PARAMS], dtype=torch.float32).pin_memory()
+        self.host_img = torch.empty((H, W, 4), dtype=torch.uint8).pin_memory()
+        self.h2d_bytes = 64 + 28                                                  # 4x4 pose (by value) + 7 parameters
+        self.d2h_bytes = H * W * 4
+
+    def render(self, pose, sharded: bool):
+        from nerf_tex_b200.sharded import render_sharded
+        params = self.params_host.to(self.dev, non_blocking=True)
+        rays_o, rays_d, t, cone = self.sampler(None, pose)
+        args = (rays_o[None], rays_d[None], t[None], params, cone[None])
+        if sharded and self.world > 1:
+            return render_sharded(self.r, *args, block=self.STRIPE, interleave=True, composite_bkgd=True, training=False)
+        return self.r(*args, composite_bkgd=True, training=False)
+
+    def workload_stats(self):
+        """Ray / sample counts of pose 0 (what the frame actually contains)."""
+        import torch
+        rays_o, rays_d, t, cone = self.sampler(None, self.poses[0])
+        hit = torch.isfinite(t[:, 0])
+        ro, rd = rays_o[hit].contiguous(), rays_d[hit].contiguous()
+        params = self.params_host.to(self.dev)
+        n_s = n_h = 0
+        for i in range(0, ro.shape[0], 16384):
+            csr = self.inst.get_model_input_csr(ro[i:i + 16384], rd[i:i + 16384], params.repeat(ro[i:i + 16384].shape[0], 1),
+                                                N_SAMPLES, STEP_SIZE, seed=0)
+            n_s, n_h = n_s + csr["pts"].shape[0], n_h + csr["ray_index"].shape[0]
+        return {"rays": H * W, "instances": self.n_inst, "proxy_hit_rays": int(ro.shape[0]), "shell_hit_rays": n_h,
+                "in_shell_samples": n_s, "samples_per_shell_hit_ray": n_s / max(n_h, 1), "render_chunk": self.chunk}
+
+    def instancer_chunk_ms(self):
+        """The instancer alone (trace + march) on one chunk from the middle of the frame."""
+        import torch
+        rays_o, rays_d, t, cone = self.sampler(None, self.poses[0])
+        hit = torch.isfinite(t[:, 0])
+        mid, c = int(hit.sum()) // 2, self.chunk
+        ro, rd = rays_o[hit][mid - c // 2:mid + c // 2].contiguous(), rays_d[hit][mid - c // 2:mid + c // 2].contiguous()
+        pf = self.params_host.to(self.dev).repeat(ro.shape[0], 1)
+        for _ in range(2):
+            self.inst.get_model_input_csr(ro, rd, pf, N_SAMPLES, STEP_SIZE, seed=0)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            self.inst.get_model_input_csr(ro, rd, pf, N_SAMPLES, STEP_SIZE, seed=0)
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / 10
+
+    def frame(self, i: int, sharded: bool = True):
+        from nerf_tex_b200.image import finish_image
+        out = self.render(self.poses[i % len(self.poses)], sharded)
+        _, u8 = finish_image(out["color_pred"], out["alpha_pred"], H, W, 1, straight_alpha=True, want_u8=True)
+        self.host_img.copy_(u8, non_blocking=True)
+        return u8
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
-    from nerf_tex_b200 import _lib, ops
-    from nerf_tex_b200.instancer import SyntheticInstancer
+    from nerf_tex_b200 import _lib
     from nerf_tex_b200.model import ParamNerf
     from nerf_tex_b200.renderer import InstanceRenderer
+    from nerf_tex_b200.sharded import render_sharded, shard_index
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -523,28 +601,55 @@ def run_gpu(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.load()
+    STRIPE = DeviceFramePipeline.STRIPE
 
     ff = lambda n: {"module": "network.model.FourierFeatures", "n_freq_bands": n}
     model = ParamNerf(ff(10), ff(4), ff(4), n_parameters=list(NPAR), seed=1)["model"]
-    rays_o, rays_d, t, params, cone = frame_rays(seed=1000 + rank)
+    rays_o, rays_d, t, params, cone = frame_rays(seed=1000)                  # ONE frame, the same on every rank
     n_rays = H * W
 
-    # ---- pre-generate the instancer records of every render chunk (not part of the hot path)
-    synth = SyntheticInstancer(b_0=B0, b_1=B1, patch_scale=PATCH_SCALE, seed=rank)
+    # ---- the frame's instancer records (not part of the hot path), then this rank's share of them
     d_o, d_d = torch.as_tensor(rays_o[0]).to(dev), torch.as_tensor(rays_d[0]).to(dev)
     d_p = torch.as_tensor(params).to(dev).repeat_interleave(n_rays, dim=0)
-    chunks = []
-    for i in range(0, n_rays, RENDER_CHUNK):
-        chunks.append(synth.get_model_input_csr(d_o[i:i + RENDER_CHUNK], d_d[i:i + RENDER_CHUNK],
-                                                d_p[i:i + RENDER_CHUNK], N_SAMPLES, STEP_SIZE))
-    n_samples_total = int(sum(c["pts"].shape[0] for c in chunks))
-    n_hit = int(sum(c["ray_index"].shape[0] for c in chunks))
+    records = FrameRecords(dev, d_o, d_d, d_p)
     del d_p
-
-    resident = ChunkReplayInstancer(chunks, resident=True)
-    renderer = InstanceRenderer(instancer_config=resident, model=model, n_samples=N_SAMPLES, render_chunk=RENDER_CHUNK,
-                                net_chunk=32768, step_size=STEP_SIZE, density_reweighting=True)
+    n_samples_total, n_hit = records.n_samples_total, records.n_hit
+    my_rays = shard_index(n_rays, rank, world, STRIPE, True, dev) if world > 1 else torch.arange(n_rays, device=dev)
+    chunks = records.chunks_for(my_rays)
+    my_samples = int(sum(c["pts"].shape[0] for c in chunks))
     dev_in = [torch.as_tensor(x).to(dev) for x in (rays_o, rays_d, t, params, cone)]
+    mk_renderer = lambda inst: InstanceRenderer(instancer_config=inst, model=model, n_samples=N_SAMPLES,
+                                                render_chunk=RENDER_CHUNK, net_chunk=32768, step_size=STEP_SIZE,
+                                                density_reweighting=True)
+    resident = ChunkReplayInstancer(chunks, resident=True)
+    renderer = mk_renderer(resident)
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def one_step():
+        """One frame: this rank's stripes through K1 / K2 chunk by chunk, then (N > 1) the final gather."""
+        resident.reset()
+        if world > 1:
+            return render_sharded(renderer, *dev_in, block=STRIPE, interleave=True, composite_bkgd=False, training=False)
+        return renderer(*dev_in, composite_bkgd=False, training=False)
+
+    # ---- N > 1: the gathered frame must be the single-GPU frame, bit for bit (checked once, outside the timed region)
+    checks = {}
+    if world > 1:
+        whole_inst = ChunkReplayInstancer(records.chunks_for(torch.arange(n_rays, device=dev)), resident=True)
+        whole = mk_renderer(whole_inst)(*dev_in, composite_bkgd=False, training=False)
+        parts = one_step()
+        same = all(torch.equal(whole[k], parts[k]) for k in whole) and set(whole) == set(parts)
+        flags = [None] * world
+        dist.all_gather_object(flags, bool(same))
+        checks["sharded_eq_single"] = all(flags)
+        del whole, parts
+    del records
+    torch.cuda.empty_cache()
 
     # K1 launch timing hooks (CUDA events on the launching stream)
     k1_events = []
@@ -557,16 +662,6 @@ def run_gpu(args):
         e.record()
         k1_events.append((s, e, kw["n_rows"]))
         return out
-
-    def sync_all():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def one_step():
-        resident.reset()
-        return renderer(*dev_in, composite_bkgd=False, training=False)
 
     for _ in range(max(args.warmup, 3)):
         one_step()
@@ -587,19 +682,143 @@ def run_gpu(args):
     k1_ms = sum(s.elapsed_time(e) for s, e, _ in k1_events)
     k1_rows = sum(n for _, _, n in k1_events)
     k1_launches = len(k1_events)
+    n_chunks = len(chunks)
+    del chunks, resident, renderer
 
-    # ---- e2e arm: host buffers in, host result out, copies inside the timed region
-    # `t` feeds only the blur_idx scaling (renderer.py:260-263) and `instance_id` only false-colour
-    # rendering (:306-307); neither is enabled in the carpet config, so the host does not send them
+    # ---- N > 1, extra key: round 1's weak-scaling figure (every rank renders the whole frame on its own, no gather)
+    ms_weak = 0.0
+    if world > 1:
+        whole_r = mk_renderer(whole_inst)
+
+        def weak_step():
+            whole_inst.reset()
+            return whole_r(*dev_in, composite_bkgd=False, training=False)
+        weak_step()
+        sync_all()
+        w_steps = max(1, min(args.steps, 3))
+        e0.record()
+        for _ in range(w_steps):
+            weak_step()
+        e1.record()
+        sync_all()
+        ms_weak = e0.elapsed_time(e1) / w_steps
+        del whole_inst, whole_r
+    torch.cuda.empty_cache()
+
+    # ---- e2e arm: the device-instancer pipeline through the public API — pose + parameters in from the host, finished
+    # frame out to pinned host memory, every frame, inside the timed region; sharded over the ranks for N > 1
+    pipe = DeviceFramePipeline(dev, world)
+    for i in range(3):
+        pipe.frame(i)
+    sync_all()
+    e_steps = max(1, args.steps)
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for i in range(e_steps):
+        pipe.frame(i)
+    e3.record()
+    sync_all()
+    ms_e2e = e2.elapsed_time(e3)
+
+    # ---- max over ranks
+    stats = torch.tensor([ms, ms_e2e, k1_ms, ms_weak], dtype=torch.float64, device=dev)
+    tot = torch.tensor([float(k1_rows), float(my_samples)], dtype=torch.float64, device=dev)
+    mx = torch.tensor([float(my_samples)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+    ms, ms_e2e, k1_ms_max, ms_weak = [float(x) for x in stats.tolist()]
+    k1_rows_all, samples_all = [float(x) for x in tot.tolist()]
+    assert int(samples_all) == n_samples_total, (samples_all, n_samples_total)   # the shards tile the frame
+
+    pipe_stats = pipe.workload_stats() if rank == 0 else {}
+    h2d, d2h = pipe.h2d_bytes, pipe.d2h_bytes
+    inst_ms = pipe.instancer_chunk_ms() if world == 1 else None
+    del pipe
+    torch.cuda.empty_cache()
+    dp = None
+    if world > 1:                      # every rank takes part (one gradient all-reduce per step)
+        dp = train_step_dp_bench(dev, rank, world)
+        checks.update(dp.pop("checks"))
+
+    if rank == 0:
+        pk = peaks()
+        sec = ms / 1e3
+        rays_per_s = n_rays * args.steps / sec
+        samples_per_s = n_samples_total * args.steps / sec
+        flops_per_row = 2.0 * MACS_PER_SAMPLE[NPAR]
+        k1_tflops = (k1_rows / max(k1_launches, 1)) * flops_per_row / ((k1_ms / max(k1_launches, 1)) / 1e3) / 1e12
+        traffic, traffic_src = k1_traffic()
+        line = {
+            "metric": "rays/s (800x800 carpet-shape instanced render; samples/s alongside)",
+            "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": config_dict({"hit_rays_per_frame": n_hit, "in_shell_samples_per_frame": n_samples_total,
+                                   "parallelism": (f"one frame over {world} GPUs: round-robin stripes of {STRIPE} rays, no collective "
+                                                   f"but the final all-gather of the per-ray outputs (inside the timed region)")
+                                   if world > 1 else "one GPU",
+                                   "load_balance": {"max_rank_samples": float(mx), "mean_rank_samples": samples_all / world}}),
+            "samples_per_sec": samples_per_s,
+            "roofline": {"kernel": "mlp_forward_kernel (K1 fused encoding + MLP, tcgen05)", "bound": "tensor",
+                         "achieved": k1_tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
+                         "frac": k1_tflops / pk["bf16_tflops_sustained"], "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": f"{pk['source']} bf16_tflops_sustained (kernel timed inside a long step)",
+                         "frac_of_burst_peak": k1_tflops / pk["bf16_tflops"],
+                         "flops_per_sample": flops_per_row, "rows_per_launch": k1_rows / max(k1_launches, 1),
+                         "launch_ms": k1_ms / max(k1_launches, 1), "k1_share_of_step": k1_ms_max / ms},
+            "e2e": {"value": n_rays * e_steps / (ms_e2e / 1e3), "unit": "rays/s",
+                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / e_steps,
+                    "workload": pipe_stats,
+                    "api": "Proxy ray sampler -> InstanceRenderer(Instancer(1500-patch procedural carpet)) -> finish_image "
+                           "[render_sharded for N > 1]: camera pose + parameter vector in from the host, finished 8-bit RGBA "
+                           "frame out to pinned host memory, every frame"},
+            "gpu_launches": int(2 * n_chunks * args.steps),
+            "clocks": clocks,
+        }
+        if world > 1:
+            line["checks"] = checks
+            line["train_step_dp"] = dp
+            line["weak_scaling"] = {"value": world * n_rays / (ms_weak / 1e3), "unit": "rays/s", "ms_per_step": ms_weak,
+                                    "what": "every rank renders the whole frame on its own (round 1's N > 1 figure)"}
+        if world == 1 and not args.no_cpu_baseline:
+            line["e2e"]["instancer_ms_per_131072_ray_chunk"] = inst_ms
+            line["e2e_host_records"] = host_records_e2e(dev, model, rays_o, rays_d, t, params, cone, min(args.steps, 3))
+            line["hbm_kernels"] = hbm_kernels_bench(dev, pk)
+            line["train_step"] = train_step_bench(dev)
+            line["c1_forward"] = c1_forward_bench(dev)
+            line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def host_records_e2e(dev, model, rays_o, rays_d, t, params, cone, steps):
+    """Round 1's end-to-end arm, kept for continuity: the same frame with a HOST-side instancer — rays and per-chunk
+    instancer records copied from pinned host memory inside the timed region (3.9 GB per frame), colour / alpha read back."""
+    import torch
+    from nerf_tex_b200.renderer import InstanceRenderer
+    n_rays = H * W
+    d_o, d_d = torch.as_tensor(rays_o[0]).to(dev), torch.as_tensor(rays_d[0]).to(dev)
+    d_p = torch.as_tensor(params).to(dev).repeat_interleave(n_rays, dim=0)
+    records = FrameRecords(dev, d_o, d_d, d_p)
+    chunks = records.chunks_for(torch.arange(n_rays, device=dev))
+    del records, d_p
+    # `t` feeds only the blur_idx scaling (renderer.py:260-263) and `instance_id` only false-colour rendering
+    # (:306-307); neither is enabled in the carpet config, so the host does not send them
     needed = {"ray_ptr", "ray_index", "pts", "dirs", "params", "dists", "alpha_weight", "color_last", "alpha_last"}
     host = ChunkReplayInstancer(chunks, resident=False, fields=needed)
+    del chunks
+    torch.cuda.empty_cache()
     renderer_h = InstanceRenderer(instancer_config=host, model=model, n_samples=N_SAMPLES, render_chunk=RENDER_CHUNK,
                                   net_chunk=32768, step_size=STEP_SIZE, density_reweighting=True)
     host_in = [torch.as_tensor(x).pin_memory() for x in (rays_o, rays_d, t, params, cone)]
     res_c = torch.empty((1, n_rays, 3), dtype=torch.float32).pin_memory()
     res_a = torch.empty((1, n_rays), dtype=torch.float32).pin_memory()
 
-    def one_step_e2e():
+    def step():
         host.reset()
         ins = [x.to(dev, non_blocking=True) for x in host_in]
         o = renderer_h(*ins, composite_bkgd=False, training=False)
@@ -607,80 +826,30 @@ def run_gpu(args):
         res_a.copy_(o["alpha_pred"], non_blocking=True)
 
     for _ in range(2):
-        one_step_e2e()
-    sync_all()
+        step()
+    torch.cuda.synchronize()
     host.h2d_bytes = 0
-    e_steps = max(1, min(args.steps, 3))
-    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e2.record()
-    for _ in range(e_steps):
-        one_step_e2e()
-    e3.record()
-    sync_all()
-    ms_e2e = e2.elapsed_time(e3)
-    h2d = host.h2d_bytes // e_steps + sum(x.numel() * 4 for x in host_in)
-    d2h = res_c.numel() * 4 + res_a.numel() * 4
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"value": n_rays / (ms / 1e3), "unit": "rays/s", "ms_per_step": ms,
+            "h2d_bytes_per_step": int(host.h2d_bytes // steps + sum(x.numel() * 4 for x in host_in)),
+            "d2h_bytes_per_step": int(res_c.numel() * 4 + res_a.numel() * 4),
+            "api": "InstanceRenderer.__call__ with pinned host rays + host instancer records (synthetic, as `value`)"}
 
-    # ---- max over ranks
-    stats = torch.tensor([ms, ms_e2e, k1_ms], dtype=torch.float64, device=dev)
-    tot = torch.tensor([float(n_samples_total), float(k1_rows)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(stats, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    ms, ms_e2e, k1_ms = [float(x) for x in stats.tolist()]
-    samples_all, k1_rows_all = [float(x) for x in tot.tolist()]
 
-    dp = None
-    if world > 1:                      # every rank takes part (one gradient all-reduce per step)
-        host = None
-        torch.cuda.empty_cache()
-        dp = train_step_dp_bench(dev, rank, world)
-
-    if rank == 0:
-        pk = peaks()
-        sec = ms / 1e3
-        rays_per_s = world * n_rays * args.steps / sec
-        samples_per_s = samples_all * args.steps / sec
-        flops_per_row = 2.0 * MACS_PER_SAMPLE[NPAR]
-        k1_tflops = (k1_rows / max(k1_launches, 1)) * flops_per_row / ((k1_ms / max(k1_launches, 1)) / 1e3) / 1e12
-        line = {
-            "metric": "rays/s (800x800 carpet-shape instanced render; samples/s alongside)",
-            "value": rays_per_s, "unit": "rays/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
-            "config": config_dict({"hit_rays_per_frame": n_hit, "in_shell_samples_per_frame": n_samples_total,
-                                   "parallelism": f"rays: one frame per GPU x{world}, no collective"}),
-            "samples_per_sec": samples_per_s,
-            "roofline": {"kernel": "mlp_forward_kernel (K1 fused encoding + MLP, tcgen05)", "bound": "tensor",
-                         "achieved": k1_tflops, "peak": pk["bf16_tflops_sustained"], "unit": "TFLOP/s",
-                         "frac": k1_tflops / pk["bf16_tflops_sustained"], "traffic": K1_NCU_DRAM_BYTES_PER_LAUNCH,
-                         "traffic_source": "ncu --set full capture of one chunk launch, dram__bytes_read.sum + dram__bytes_write.sum "
-                                           "(profiles/r01_v6_k1_full_raw.csv): inputs 52 B/row + weights; activations never leave the SM",
-                         "peak_source": f"{pk['source']} bf16_tflops_sustained (kernel timed inside a long step)",
-                         "frac_of_burst_peak": k1_tflops / pk["bf16_tflops"],
-                         "flops_per_sample": flops_per_row, "rows_per_launch": k1_rows / max(k1_launches, 1),
-                         "launch_ms": k1_ms / max(k1_launches, 1), "k1_share_of_step": k1_ms / ms},
-            "e2e": {"value": world * n_rays * e_steps / (ms_e2e / 1e3), "unit": "rays/s",
-                    "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "ms_per_step": ms_e2e / e_steps,
-                    "samples_per_sec": samples_all * e_steps / (ms_e2e / 1e3),
-                    "api": "InstanceRenderer.__call__ with pinned host rays + host instancer records"},
-            "gpu_launches": int(2 * len(chunks) * args.steps),
-            "clocks": clocks,
-        }
-        if world > 1:
-            line["train_step_dp"] = dp
-        if world == 1 and not args.no_cpu_baseline:
-            del chunks, resident, host
-            torch.cuda.empty_cache()
-            line["hbm_kernels"] = hbm_kernels_bench(dev, pk)
-            line["train_step"] = train_step_bench(dev)
-            line["c1_forward"] = c1_forward_bench(dev)
-            line["device_instancer_frame"] = device_instancer_bench(dev)
-            line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
-        print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+def k1_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum of one K1 chunk launch from the newest committed ncu capture
+    (profiles/*_k1_traffic.json, written by tools/ncu_traffic.py from `ncu --set full` of this very command)."""
+    cands = sorted((ROOT / "profiles").glob("*_k1_traffic.json"))
+    if cands:
+        d = json.loads(cands[-1].read_text())
+        return d["dram_bytes_per_launch"], f"profiles/{cands[-1].name}: {d['how']}"
+    return K1_NCU_DRAM_BYTES_PER_LAUNCH, "ncu --set full capture of one chunk launch (profiles/r01_v6_k1_full_raw.csv)"
 
 
 def main():
