@@ -245,6 +245,22 @@ def hbm_kernels_bench(dev, pk):
                                 "achieved_gbs": algo / dt / 1e9, "frac_of_measured_hbm": algo / dt / 1e9 / pk["hbm_gbs"],
                                 "rays_per_sec": R / dt}
     del rgbs
+    # the instanced compositor (the K2 variant the headline workload launches): ragged CSR rows, ~144 samples per ray
+    Hn = 1 << 17
+    cnt = torch.clamp(torch.round(torch.exp(torch.randn(Hn, device=dev, generator=g) * 0.6 + math.log(120.0))), 1, 1024).long()
+    ptr = torch.zeros(Hn + 1, dtype=torch.int64, device=dev)
+    ptr[1:] = torch.cumsum(cnt, 0)
+    T = int(ptr[-1])
+    rg = torch.randn((T, 4), device=dev, generator=g)
+    di = torch.full((T,), 0.002, device=dev)
+    aw = torch.ones(T, device=dev)
+    cl, al = torch.zeros((Hn, 3), device=dev), (torch.rand(Hn, device=dev, generator=g) < .5).float()
+    ri = torch.arange(Hn, device=dev, dtype=torch.int32)
+    dt = timeit(lambda: ops.composite_instanced_forward(rg, di, aw, ptr, cl, al, ri, Hn, patch_scale=0.09))
+    algo = 24 * T + 32 * Hn
+    out["composite_instanced_forward"] = {"rays": Hn, "samples": T, "bytes": algo, "ms": dt * 1e3, "achieved_gbs": algo / dt / 1e9,
+                                          "frac_of_measured_hbm": algo / dt / 1e9 / pk["hbm_gbs"], "rays_per_sec": Hn / dt}
+    del rg, di, aw
     S0, N = 64, 128
     R3 = 1 << 21
     z0 = torch.sort(torch.rand((R3, S0), device=dev, generator=g) * 4 + 2, -1).values

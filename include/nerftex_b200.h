@@ -285,16 +285,28 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
  * Shell instancer (the caller in front of the hot path)
  * ---------------------------------------------------------------------------------------- */
 
-/* Replace C_Instancer::GetModelInput (instancer/src/instancer.cpp:751-1037, bound in instancer/instancer.pyx:38-54)
- * for explicit patch instances: no mesh, no parameter textures, no shadow rays, no auxiliary meshes.
+/* Replace C_Instancer::GetModelInput (instancer/src/instancer.cpp:751-1037, bound in instancer/instancer.pyx:38-54):
+ * patch instances (explicit, or distributed on a base mesh by the host side), optional base mesh whose first hit ends a
+ * ray (:804-814,:983,:1019-1023); no parameter textures, no shadow rays, no auxiliary-mesh shading.
+ *
+ * ntx_instancer_scene — what CommitScene (instancer.cpp:420-424) leaves behind, all DEVICE pointers:
  *   minv[I,3,4]  rows 0..2 of the inverse instance transform (world -> patch), dirt[I,3,3] the row-normalised
  *   transposed rotation, origins[I,3] the instance translation (AddInstance, instancer.cpp:125-141);
  *   spheres[I,4] (optional, 16-byte aligned): world-space bounding sphere of every instanced box as (centre, radius^2),
  *   radius inflated by >= 1 %: a cheap first test that never changes the result;
- *   b_0/b_1: HOST pointers to the patch box corners.  Box hits are kept for t in [0, 100]; at most 200 hits per ray
- *   (MAX_TOTAL_HITS, instancer.cpp:22; the smallest t win).  Random draws are a counter hash of (seed, ray[, step]), not the reference's mt19937.
+ *   inst_grid (optional, cell_start == NULL: every ray tests every instance): uniform grid over the instances' world
+ *   boxes in place of the reference's Embree BVH — cell_start[nx*ny*nz + 1] / items[] list the instances whose
+ *   (slightly inflated) world box overlaps a cell, cell index = (z * ny + y) * nx + x; a ray walks the cells it crosses;
+ *   mesh_v[V,3] / mesh_f[F,3] (optional, n_faces == 0: no mesh) the base mesh (DistributeInstancesOnMesh :374-391),
+ *   tri_grid the same kind of grid over its triangles (optional).  The triangle test is the watertight one of Woop,
+ *   Benthin, Wald (JCGT 2013) in fp32 with the double fallback; ties to the smaller face index.
+ * b_0/b_1: HOST pointers to the patch box corners.  Box hits are kept for t in [0, 100] and up to the first mesh hit; at
+ * most 200 hits per ray (MAX_TOTAL_HITS, instancer.cpp:22; the smallest t win).  Random draws are a counter hash of
+ * (seed, ray id[, step]), not the reference's mt19937; ray_ids[R] (optional) names every ray for those draws — pass the
+ * ray's index in the frame and the records do not depend on how the frame is cut into chunks or spread over GPUs.
  * Pass 1 (trace) fills workspace (ntx_instancer_workspace_bytes(R) bytes), n_samples[R] (marching samples of every
- * ray, <= n_pts) and hit[R] (ray touched any patch box).  The caller turns n_samples into ray_ptr[R+1] (exclusive
+ * ray, <= n_pts), hit[R] (ray touched a patch box or the mesh) and alpha_last[R] (1 where the ray ends on the mesh:
+ * the opaque last sample of renderer.py:331,339, colour 0).  The caller turns n_samples into ray_ptr[R+1] (exclusive
  * prefix sum, int64; T = ray_ptr[R] samples in total) and sizes the outputs; pass 2 (march) writes the samples of ray r
  * at ray_ptr[r]...:
  *   pts[T,3] patch-local position, dirs[T,3] patch-local unit view direction, params_out[T,n_param] (the ray's
@@ -304,17 +316,36 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
  *   instancer.cpp:572-590,954-956), dists[T], t[T], alpha_weight[T] (number of overlapping patches for method 0
  *   'random', 1 for method 1 'nearest', 1 / probability for method 2 'nearest_blend' whose blend_range is the transition
  *   range 0.2 times the patch scale, instancer.cpp:694-713), instance_id[T].  n_param <= 16. */
+typedef struct ntx_scene_grid {
+    const int32_t* cell_start;
+    const int32_t* items;
+    float lo[3];
+    float cell[3];
+    int32_t res[3];
+} ntx_scene_grid;
+typedef struct ntx_instancer_scene {
+    const float* minv;
+    const float* dirt;
+    const float* origins;
+    const float* spheres;
+    int32_t n_inst;
+    int32_t n_faces;
+    const float* mesh_v;
+    const int32_t* mesh_f;
+    ntx_scene_grid inst_grid;
+    ntx_scene_grid tri_grid;
+} ntx_instancer_scene;
 int64_t ntx_instancer_workspace_bytes(int R);
-int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R, const float* minv, const float* dirt,
-                        const float* origins, const float* spheres, int n_inst, const float* b_0, const float* b_1, float step_size, int n_pts,
+int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
+                        const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size, int n_pts,
                         uint32_t seed, int use_mean_distance, void* workspace, int32_t* n_samples, int32_t* hit,
+                        float* alpha_last, void* stream);
+int ntx_instancer_march(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* parameters,
+                        int n_param, int R, const ntx_instancer_scene* scene, float step_size, int n_pts, uint32_t seed,
+                        int light_dir_idx, int light_strength_idx, int method, float blend_range, int use_mean_distance,
+                        const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts, float* dirs,
+                        float* params_out, float* dists, float* t, float* alpha_weight, int32_t* instance_id,
                         void* stream);
-int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
-                        const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
-                        uint32_t seed, int light_dir_idx, int light_strength_idx, int method, float blend_range, int use_mean_distance,
-                        const void* workspace,
-                        const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists, float* t,
-                        float* alpha_weight, int32_t* instance_id, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Whole ray chunk: K3 -> K1 -> K2 [-> K3 -> K1 -> K2]

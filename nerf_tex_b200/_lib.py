@@ -41,6 +41,17 @@ class MlpInputs(C.Structure):
                 ("blur_idx", C.c_int32), ("rows_per_group", C.c_int32), ("n_rows", C.c_int64), ("pos_cov", C.c_void_p)]
 
 
+class SceneGrid(C.Structure):
+    _fields_ = [("cell_start", C.c_void_p), ("items", C.c_void_p), ("lo", C.c_float * 3), ("cell", C.c_float * 3),
+                ("res", C.c_int32 * 3)]
+
+
+class InstancerScene(C.Structure):
+    _fields_ = [("minv", C.c_void_p), ("dirt", C.c_void_p), ("origins", C.c_void_p), ("spheres", C.c_void_p),
+                ("n_inst", C.c_int32), ("n_faces", C.c_int32), ("mesh_v", C.c_void_p), ("mesh_f", C.c_void_p),
+                ("inst_grid", SceneGrid), ("tri_grid", SceneGrid)]
+
+
 # name -> (restype, argtypes); must list every symbol include/nerftex_b200.h declares.
 _P, _I, _F, _I64, _U32 = C.c_void_p, C.c_int, C.c_float, C.c_int64, C.c_uint32
 SIGNATURES = {
@@ -80,8 +91,9 @@ SIGNATURES = {
     "ntx_composite_edges_backward": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
     "ntx_image_finish": (_I, [_P, _P, _I, _I, _I, _P, _I, _I, _P, _P, _P]),
     "ntx_instancer_workspace_bytes": (_I64, [_I]),
-    "ntx_instancer_trace": (_I, [_P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _F, _I, _U32, _I, _P, _P, _P, _P]),
-    "ntx_instancer_march": (_I, [_P, _P, _P, _I, _I, _P, _P, _P, _F, _I, _U32, _I, _I, _I, _F, _I, _P, _P, _I64] + [_P] * 7 + [_P]),
+    "ntx_instancer_trace": (_I, [_P, _P, _P, _I, C.POINTER(InstancerScene), _P, _P, _F, _I, _U32, _I, _P, _P, _P, _P, _P]),
+    "ntx_instancer_march": (_I, [_P, _P, _P, _P, _I, _I, C.POINTER(InstancerScene), _F, _I, _U32, _I, _I, _I, _F, _I, _P, _P, _I64]
+                            + [_P] * 7 + [_P]),
     "ntx_render_rays_workspace_bytes": (_I64, [_I, _I, _I]),
     "ntx_render_rays": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P, _I64, _P]),
     "ntx_render_rays_static": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P]),

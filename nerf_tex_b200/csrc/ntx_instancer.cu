@@ -20,6 +20,7 @@ constexpr int kMaxHits = 200;        // MAX_TOTAL_HITS, instancer.cpp:22
 constexpr int kInstTile = 128;
 constexpr int kTraceThreads = 128;   // rays per block of the trace pass
 constexpr int kSmemHits = 56;        // hit-list entries per ray kept in shared memory; the rest lives in the ray's workspace row
+constexpr int kMailbox = 16;         // per-ray direct-mapped cache of instances already tested (grid walk)
 constexpr float kTFar = 100.0f;
 
 __host__ __device__ __forceinline__ uint32_t hash_u32(uint32_t x) {
@@ -115,9 +116,12 @@ struct OpenList {
 // Pass 1, per ray: total in-shell length, step count, then the walk along the concatenated segments
 // (instancer.cpp:801-1003) — counting only; what each sample needs later is recorded per hit.
 // `hits(j)` is a reference to the j-th key of the ray in ascending order; the first loop also pairs entries with exits.
+// `t_mesh` < +inf: the ray ends on the base mesh there (the list holds no box hit behind it): the mesh closes an open
+// segment (:805-810) and samples go on behind the last box hit up to the mesh (:983).
 template <class Hits>
 __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint32_t seed, uint32_t ray, int use_mean,
-                        int32_t* __restrict__ step_at, float* __restrict__ segoff, RayInfo* __restrict__ info) {
+                        float t_mesh, int32_t* __restrict__ step_at, float* __restrict__ segoff,
+                        RayInfo* __restrict__ info) {
     OpenList act;
     // :801-827 total in-shell length
     float total = 0.0f, t_entry = 0.0f;
@@ -135,6 +139,7 @@ __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint
             if (was_empty) t_entry = tt;
         }
     }
+    if (t_mesh < CUDART_INF_F && act.n > 0) total = __fadd_rn(total, __fsub_rn(t_mesh, t_entry));
     RayInfo ri = {0.f, 0.f, 0, 0};
     if (!(total > 0.0f)) { *info = ri; return 0; }
     const uint32_t necessary = (uint32_t)__fdiv_rn(total, step_size);             // :845
@@ -175,97 +180,256 @@ __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint
         }
     }
     for (; j < n_hits; ++j) step_at[j] = 0x7fffffff;     // never consumed: no sample lies behind these hits
+    if (t_mesh < CUDART_INF_F && n_act > 0) {            // behind the last box hit, in front of the mesh
+        while (step < n_steps) {
+            const float t_mu = __fadd_rn(__fadd_rn(__fmul_rn((float)step, step_size), ri.t_offset), segment_offset);
+            const float t_pt = use_mean ? mean_distance(t_mu, step_size) : t_mu;
+            if (!(t_pt < t_mesh)) break;
+            ++step;
+        }
+    }
     return step;
 }
 
+// ---- uniform grid walk (Amanatides & Woo): calls visit(cell, t_exit) for every cell the ray crosses within
+// [tmin, tmax], front to back; visit returns false to stop.  The grid's item boxes were inflated when they were binned,
+// so the rounding of the walk (which may clip a corner cell by a few ulps) cannot lose an item the ray really hits.
+struct Grid {
+    const int32_t* __restrict__ start;
+    const int32_t* __restrict__ items;
+    float lo[3], cell[3];
+    int res[3];
+};
+__host__ inline Grid make_grid(const ntx_scene_grid& g) {
+    Grid r;
+    r.start = g.cell_start; r.items = g.items;
+    for (int a = 0; a < 3; ++a) { r.lo[a] = g.lo[a]; r.cell[a] = g.cell[a]; r.res[a] = g.res[a]; }
+    return r;
+}
+template <class Visit>
+__device__ __forceinline__ void grid_walk(const Grid& g, const float o[3], const float d[3], float tmin, float tmax,
+                                          Visit&& visit) {
+    float t0 = tmin, t1 = tmax;
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float hi = g.lo[a] + (float)g.res[a] * g.cell[a];
+        if (d[a] != 0.0f) {
+            const float inv = 1.0f / d[a];
+            float ta = (g.lo[a] - o[a]) * inv, tb = (hi - o[a]) * inv;
+            if (ta > tb) { const float s = ta; ta = tb; tb = s; }
+            t0 = fmaxf(t0, ta);
+            t1 = fminf(t1, tb);
+        } else if (o[a] < g.lo[a] || o[a] > hi) {
+            return;
+        }
+    }
+    if (!(t0 <= t1)) return;
+    int c[3], stp[3];
+    float tnext[3], tdelta[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const float p = o[a] + d[a] * t0;
+        int ci = (int)floorf((p - g.lo[a]) / g.cell[a]);
+        ci = max(0, min(g.res[a] - 1, ci));
+        c[a] = ci;
+        if (d[a] > 0.0f) {
+            stp[a] = 1; tnext[a] = (g.lo[a] + (float)(ci + 1) * g.cell[a] - o[a]) / d[a]; tdelta[a] = g.cell[a] / d[a];
+        } else if (d[a] < 0.0f) {
+            stp[a] = -1; tnext[a] = (g.lo[a] + (float)ci * g.cell[a] - o[a]) / d[a]; tdelta[a] = -g.cell[a] / d[a];
+        } else {
+            stp[a] = 0; tnext[a] = CUDART_INF_F; tdelta[a] = CUDART_INF_F;
+        }
+    }
+    for (;;) {
+        const int a = (tnext[0] <= tnext[1]) ? (tnext[0] <= tnext[2] ? 0 : 2) : (tnext[1] <= tnext[2] ? 1 : 2);
+        const float tn = a == 0 ? tnext[0] : (a == 1 ? tnext[1] : tnext[2]);
+        if (!visit((c[2] * g.res[1] + c[1]) * g.res[0] + c[0], fminf(tn, t1))) return;
+        if (!(tn <= t1)) return;
+        if (a == 0) { c[0] += stp[0]; if ((unsigned)c[0] >= (unsigned)g.res[0]) return; tnext[0] += tdelta[0]; }
+        else if (a == 1) { c[1] += stp[1]; if ((unsigned)c[1] >= (unsigned)g.res[1]) return; tnext[1] += tdelta[1]; }
+        else { c[2] += stp[2]; if ((unsigned)c[2] >= (unsigned)g.res[2]) return; tnext[2] += tdelta[2]; }
+    }
+}
+
+// ---- watertight ray / triangle test (Woop, Benthin, Wald, JCGT 2013) in the operation order of
+// oracle/instancer_oracle.py::mesh_first_hit.  RayFrame holds the per-ray constants.
+struct RayFrame { int kx, ky, kz; float Sx, Sy, Sz; };
+__device__ __forceinline__ float sel3(const float v[3], int k) { return k == 0 ? v[0] : (k == 1 ? v[1] : v[2]); }
+__device__ __forceinline__ RayFrame ray_frame(const float d[3]) {
+    RayFrame f;
+    const float ax = fabsf(d[0]), ay = fabsf(d[1]), az = fabsf(d[2]);
+    f.kz = (ax >= ay && ax >= az) ? 0 : (ay >= az ? 1 : 2);
+    f.kx = (f.kz + 1) % 3;
+    f.ky = (f.kx + 1) % 3;
+    const float dz = sel3(d, f.kz);
+    if (dz < 0.0f) { const int s = f.kx; f.kx = f.ky; f.ky = s; }
+    f.Sx = __fdiv_rn(sel3(d, f.kx), dz);
+    f.Sy = __fdiv_rn(sel3(d, f.ky), dz);
+    f.Sz = __fdiv_rn(1.0f, dz);
+    return f;
+}
+// true + (t, u, v) if the ray hits the triangle with t in [0, 100]
+__device__ __forceinline__ bool tri_hit(const RayFrame& f, const float o[3], const float* __restrict__ V,
+                                        const int32_t* __restrict__ face, float& t, float& u, float& v) {
+    float P[3][3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float* vp = V + 3 * (size_t)__ldg(face + k);
+#pragma unroll
+        for (int a = 0; a < 3; ++a) P[k][a] = __fsub_rn(__ldg(vp + a), o[a]);
+    }
+    float X[3], Y[3], Zk[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        Zk[k] = sel3(P[k], f.kz);
+        X[k] = __fsub_rn(sel3(P[k], f.kx), __fmul_rn(f.Sx, Zk[k]));
+        Y[k] = __fsub_rn(sel3(P[k], f.ky), __fmul_rn(f.Sy, Zk[k]));
+    }
+    float U = __fsub_rn(__fmul_rn(X[2], Y[1]), __fmul_rn(Y[2], X[1]));
+    float Vv = __fsub_rn(__fmul_rn(X[0], Y[2]), __fmul_rn(Y[0], X[2]));
+    float W = __fsub_rn(__fmul_rn(X[1], Y[0]), __fmul_rn(Y[1], X[0]));
+    if (U == 0.0f || Vv == 0.0f || W == 0.0f) {
+        U = __double2float_rn(__dsub_rn(__dmul_rn((double)X[2], (double)Y[1]), __dmul_rn((double)Y[2], (double)X[1])));
+        Vv = __double2float_rn(__dsub_rn(__dmul_rn((double)X[0], (double)Y[2]), __dmul_rn((double)Y[0], (double)X[2])));
+        W = __double2float_rn(__dsub_rn(__dmul_rn((double)X[1], (double)Y[0]), __dmul_rn((double)Y[1], (double)X[0])));
+    }
+    if ((U < 0.0f || Vv < 0.0f || W < 0.0f) && (U > 0.0f || Vv > 0.0f || W > 0.0f)) return false;
+    const float det = __fadd_rn(__fadd_rn(U, Vv), W);
+    if (det == 0.0f) return false;
+    const float T = __fadd_rn(__fadd_rn(__fmul_rn(U, __fmul_rn(f.Sz, Zk[0])), __fmul_rn(Vv, __fmul_rn(f.Sz, Zk[1]))),
+                              __fmul_rn(W, __fmul_rn(f.Sz, Zk[2])));
+    t = __fdiv_rn(T, det);
+    if (!(t >= 0.0f && t <= kTFar)) return false;
+    u = __fdiv_rn(Vv, det);
+    v = __fdiv_rn(W, det);
+    return true;
+}
+
+struct SceneDev {
+    const float* __restrict__ minv;
+    const float* __restrict__ dirt;
+    const float* __restrict__ origins;
+    const float4* __restrict__ spheres;
+    int n_inst, n_faces;
+    const float* __restrict__ mesh_v;
+    const int32_t* __restrict__ mesh_f;
+    Grid ig, tg;
+};
+
 __global__ void __launch_bounds__(kTraceThreads)
-instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, int R,
-                       const float* __restrict__ minv, const float* __restrict__ dirt, const float* __restrict__ origins,
-                       const float4* __restrict__ spheres, int n_inst, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
+instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const int32_t* __restrict__ ray_ids,
+                       int R, SceneDev sc, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
                        int n_pts, uint32_t seed, int use_mean, Workspace ws, int32_t* __restrict__ n_samples,
-                       int32_t* __restrict__ hit_flag) {
-    __shared__ float s_minv[kInstTile * 12];
-    __shared__ float4 s_sph[kInstTile];
+                       int32_t* __restrict__ hit_flag, float* __restrict__ alpha_last) {
     const int ray = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool live = ray < R;
-    float o[3] = {0.f, 0.f, 0.f}, d[3] = {0.f, 0.f, 1.f};
-    if (live) for (int a = 0; a < 3; ++a) { o[a] = rays_o[3 * ray + a]; d[a] = rays_d[3 * ray + a]; }
+    if (ray >= R) return;
+    float o[3], d[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { o[a] = rays_o[3 * ray + a]; d[a] = rays_d[3 * ray + a]; }
     const float b0[3] = {b00, b01, b02}, b1[3] = {b10, b11, b12};
     const float inv_dn = rsqrtf(fmaxf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2], 1e-30f));
     const float dh[3] = {d[0] * inv_dn, d[1] * inv_dn, d[2] * inv_dn};
+
+    // ---- the base mesh first: its nearest hit bounds everything else (instancer.cpp:804-814)
+    float t_mesh = CUDART_INF_F;
+    if (sc.n_faces > 0 && (d[0] != 0.0f || d[1] != 0.0f || d[2] != 0.0f)) {
+        const RayFrame rf = ray_frame(d);
+        int best = -1;
+        auto test = [&](int face) {
+            float t, u, v;
+            if (tri_hit(rf, o, sc.mesh_v, sc.mesh_f + 3 * (size_t)face, t, u, v) && (t < t_mesh || (t == t_mesh && face < best))) {
+                t_mesh = t;
+                best = face;
+            }
+        };
+        if (sc.tg.start) {
+            grid_walk(sc.tg, o, d, 0.0f, kTFar, [&](int cell, float t_exit) {
+                const int e = __ldg(sc.tg.start + cell + 1);
+                for (int q = __ldg(sc.tg.start + cell); q < e; ++q) test(__ldg(sc.tg.items + q));
+                return !(t_mesh <= t_exit);            // a hit inside the cells walked so far cannot be beaten behind them
+            });
+        } else {
+            for (int face = 0; face < sc.n_faces; ++face) test(face);
+        }
+    }
+    const float t_limit = fminf(t_mesh, kTFar);        // box hits at t <= t_mesh sort before the mesh hit (:444-455)
+
     // the ray's sorted hit list: the first kSmemHits entries in shared memory (entry k of thread t at
     // s_hits[k * kTraceThreads + t], conflict-free), the tail in the ray's row of the global workspace.  (A per-thread
     // array would be local memory: 1.6 KB per ray falls out of L1, and holding all 200 entries in shared memory leaves
     // four warps per SM.)
     extern __shared__ __align__(16) uint64_t s_hits[];
-    uint64_t* row = ws.hits + (size_t)(live ? ray : 0) * kMaxHits;
+    uint64_t* row = ws.hits + (size_t)ray * kMaxHits;
     auto H = [&](int k) -> uint64_t& { return k < kSmemHits ? s_hits[k * kTraceThreads + threadIdx.x] : row[k]; };
     int n_hits = 0;
-    auto insert = [&](float t, uint32_t inst) {         // keep the kMaxHits smallest (t, inst), sorted
+    // keep the kMaxHits smallest (t, inst), sorted, each once (an instance listed in several grid cells is tested once
+    // per cell the ray crosses; the same ray and box give the same t, so a repeat shows up as an equal key)
+    auto insert = [&](float t, uint32_t inst) {
         const uint64_t key = ((uint64_t)__float_as_uint(t + 0.0f) << 32) | inst;
-        if (n_hits < kSmemHits) {                       // the usual case: the whole list is in shared memory
-            uint64_t* hs = s_hits + threadIdx.x;
-            int k = n_hits++;
-            while (k > 0) {
-                const uint64_t prev = hs[(k - 1) * kTraceThreads];
-                if (prev <= key) break;
-                hs[k * kTraceThreads] = prev;
-                --k;
-            }
-            hs[k * kTraceThreads] = key;
-            return;
+        int k = n_hits;
+        while (k > 0 && H(k - 1) > key) --k;            // slot of the new key (hits arrive nearly in order: short scan)
+        if (k > 0 && H(k - 1) == key) return;
+        if (n_hits == kMaxHits) {
+            if (k == kMaxHits) return;
+        } else {
+            ++n_hits;
         }
-        int k;
-        if (n_hits < kMaxHits) k = n_hits++;
-        else if (key < H(kMaxHits - 1)) k = kMaxHits - 1;
-        else return;
-        while (k > 0) {
-            const uint64_t prev = H(k - 1);
-            if (prev <= key) break;
-            H(k) = prev;
-            --k;
-        }
+        for (int q = n_hits - 1; q > k; --q) H(q) = H(q - 1);
         H(k) = key;
     };
-    for (int base = 0; base < n_inst; base += kInstTile) {
-        const int cnt = min(kInstTile, n_inst - base);
-        __syncthreads();
-        for (int i = threadIdx.x; i < cnt * 12; i += blockDim.x) s_minv[i] = minv[(size_t)base * 12 + i];
-        if (spheres)
-            for (int i = threadIdx.x; i < cnt; i += blockDim.x) s_sph[i] = spheres[base + i];
-        __syncthreads();
-        if (!live) continue;
-        for (int j = 0; j < cnt; ++j) {
-            if (spheres) {
-                // squared distance of the sphere centre from the ray's line against the (inflated) radius: rejects
-                // only instances whose box the ray certainly misses, so the hit list is unchanged
-                const float4 sp = s_sph[j];
-                const float cx = sp.x - o[0], cy = sp.y - o[1], cz = sp.z - o[2];
-                const float cc = cx * cx + cy * cy + cz * cz;
-                const float along = cx * dh[0] + cy * dh[1] + cz * dh[2];          // dh: unit ray direction
-                if (fmaf(-along, along, cc) > fmaf(1e-5f, cc, sp.w)) continue;     // margin: rounding of cc - along^2
-            }
-            const float* M = s_minv + 12 * j;
-            float tin = -CUDART_INF_F, tout = CUDART_INF_F;
-#pragma unroll
-            for (int a = 0; a < 3; ++a) {
-                const float ol = __fadd_rn(dot3(M + 4 * a, o), M[4 * a + 3]);
-                const float dl = dot3(M + 4 * a, d);
-                const float inv = __fdiv_rn(1.0f, dl);
-                const float t0 = __fmul_rn(__fsub_rn(b0[a], ol), inv), t1 = __fmul_rn(__fsub_rn(b1[a], ol), inv);
-                const float lo = (t0 < t1) ? t0 : t1, hi = (t0 < t1) ? t1 : t0;
-                tin = (a == 0 || lo > tin) ? lo : tin;
-                tout = (a == 0 || hi < tout) ? hi : tout;
-            }
-            if (!(tin < tout) || !(tout >= 0.0f) || !(tin <= kTFar)) continue;
-            if (tin >= 0.0f) insert(tin, (uint32_t)(base + j));
-            if (tout <= kTFar) insert(tout, (uint32_t)(base + j));
+    // An instance is listed in every cell its box overlaps, so a ray meets it again in the next cells: a small
+    // direct-mapped cache of ids already tested filters most repeats (the equal-key test above catches the rest).
+    uint32_t* mail = reinterpret_cast<uint32_t*>(s_hits + (size_t)kSmemHits * kTraceThreads) + threadIdx.x;
+    if (sc.ig.start)
+        for (int k = 0; k < kMailbox; ++k) mail[k * kTraceThreads] = 0xFFFFFFFFu;
+    auto test_instance = [&](int inst) {
+        if (sc.ig.start) {
+            uint32_t& slot = mail[((uint32_t)inst % kMailbox) * kTraceThreads];
+            if (slot == (uint32_t)inst) return;
+            slot = (uint32_t)inst;
         }
+        if (sc.spheres) {
+            // squared distance of the sphere centre from the ray's line against the (inflated) radius: rejects
+            // only instances whose box the ray certainly misses, so the hit list is unchanged
+            const float4 sp = __ldg(sc.spheres + inst);
+            const float cx = sp.x - o[0], cy = sp.y - o[1], cz = sp.z - o[2];
+            const float cc = cx * cx + cy * cy + cz * cz;
+            const float along = cx * dh[0] + cy * dh[1] + cz * dh[2];          // dh: unit ray direction
+            if (fmaf(-along, along, cc) > fmaf(1e-5f, cc, sp.w)) return;       // margin: rounding of cc - along^2
+        }
+        const float4* Mp = reinterpret_cast<const float4*>(sc.minv) + 3 * (size_t)inst;
+        float tin = -CUDART_INF_F, tout = CUDART_INF_F;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float4 m4 = __ldg(Mp + a);
+            const float M[3] = {m4.x, m4.y, m4.z};
+            const float ol = __fadd_rn(dot3(M, o), m4.w);
+            const float dl = dot3(M, d);
+            const float inv = __fdiv_rn(1.0f, dl);
+            const float t0 = __fmul_rn(__fsub_rn(b0[a], ol), inv), t1 = __fmul_rn(__fsub_rn(b1[a], ol), inv);
+            const float lo = (t0 < t1) ? t0 : t1, hi = (t0 < t1) ? t1 : t0;
+            tin = (a == 0 || lo > tin) ? lo : tin;
+            tout = (a == 0 || hi < tout) ? hi : tout;
+        }
+        if (!(tin < tout) || !(tout >= 0.0f) || !(tin <= kTFar)) return;
+        if (tin >= 0.0f && tin <= t_limit) insert(tin, (uint32_t)inst);
+        if (tout <= t_limit) insert(tout, (uint32_t)inst);
+    };
+    if (sc.ig.start) {
+        grid_walk(sc.ig, o, d, 0.0f, t_limit, [&](int cell, float) {
+            const int e = __ldg(sc.ig.start + cell + 1);
+            for (int q = __ldg(sc.ig.start + cell); q < e; ++q) test_instance(__ldg(sc.ig.items + q));
+            return true;
+        });
+    } else {
+        for (int inst = 0; inst < sc.n_inst; ++inst) test_instance(inst);
     }
-    if (!live) return;
+    if (t_mesh < CUDART_INF_F && n_hits >= kMaxHits) t_mesh = CUDART_INF_F;   // the mesh hit would be entry 201 of the list
     ws.n_hits[ray] = n_hits;
-    hit_flag[ray] = n_hits > 0;
-    n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, (uint32_t)ray, use_mean,
+    hit_flag[ray] = n_hits > 0 || t_mesh < CUDART_INF_F;
+    alpha_last[ray] = t_mesh < CUDART_INF_F ? 1.0f : 0.0f;                    // instancer.cpp:1019-1027
+    const uint32_t rid = ray_ids ? (uint32_t)ray_ids[ray] : (uint32_t)ray;
+    n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, rid, use_mean, t_mesh,
                               ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray);
     for (int k = 0; k < min(n_hits, kSmemHits); ++k) row[k] = H(k);     // with the partner indices walk_ray added
 }
@@ -274,7 +438,8 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
 // ray_ptr) and the hit interval it was emitted in (binary search in the ray's step_at row), replays the hits before it
 // to get the set of patches it is inside, and writes its record.
 __global__ void __launch_bounds__(256)
-instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const float* __restrict__ params,
+instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const int32_t* __restrict__ ray_ids,
+                      const float* __restrict__ params,
                       int n_param, int R, const float* __restrict__ minv, const float* __restrict__ dirt,
                       const float* __restrict__ origins, float step_size, uint32_t seed, int light_idx, int strength_idx,
                       int method, float blend_range, int use_mean, Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T,
@@ -287,6 +452,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         if (__ldg(ray_ptr + mid) <= k) lo = mid; else hi = mid;
     }
     const int ray = lo;
+    const uint32_t rid = ray_ids ? (uint32_t)__ldg(ray_ids + ray) : (uint32_t)ray;     // the ray's name for the draws
     const int step = (int)(k - __ldg(ray_ptr + ray));
     const RayInfo ri = ws.info[ray];
     const int n_hits = ws.n_hits[ray];
@@ -317,7 +483,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
             if (inside(h)) { ++n_act; sel = hit_inst(h); }
         }
         if (n_act > 1) {                                                      // the idx-th smallest id of the set
-            const int idx = (int)pick(seed, (uint32_t)ray, (uint32_t)step, (uint32_t)n_act);
+            const int idx = (int)pick(seed, rid, (uint32_t)step, (uint32_t)n_act);
             w = (float)n_act;
             for (int q = 0; q < j; ++q) {
                 const uint64_t h = __ldg(hits + q);
@@ -357,7 +523,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         float total = 0.0f;
         for (int64_t id = next_id(-1); id >= 0; id = next_id(id))
             total = __fadd_rn(total, fmaxf(__fsub_rn(lim, dist_to((uint32_t)id)), 0.0f));
-        const float target = __fmul_rn(step_uniform(seed, (uint32_t)ray, (uint32_t)step), total);
+        const float target = __fmul_rn(step_uniform(seed, rid, (uint32_t)step), total);
         float run = 0.0f, w_sel = 1.0f;
         for (int64_t id = next_id(-1); id >= 0; id = next_id(id)) {
             const float wi = fmaxf(__fsub_rn(lim, dist_to((uint32_t)id)), 0.0f);
@@ -432,46 +598,72 @@ NTX_API int64_t ntx_instancer_workspace_bytes(int R) {
     return (int64_t)R * (kMaxHits * 16 + 16 + 4);
 }
 
-NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, int R, const float* minv, const float* dirt,
-                                const float* origins, const float* spheres, int n_inst, const float* b_0, const float* b_1,
-                                float step_size, int n_pts, uint32_t seed, int use_mean_distance, void* workspace,
-                                int32_t* n_samples, int32_t* hit, void* stream) {
-    NTX_REQUIRE(R >= 0 && n_inst >= 0 && n_inst <= (int)kInstMask && n_pts >= 1 && step_size > 0.0f, "instancer_trace: bad arguments");
+static int check_scene(const ntx_instancer_scene* s, SceneDev* out) {
+    NTX_REQUIRE(s, "instancer: null scene");
+    NTX_REQUIRE(s->n_inst >= 0 && s->n_inst <= (int)kInstMask && s->n_faces >= 0, "instancer: bad scene sizes");
+    NTX_REQUIRE(s->n_inst == 0 || (s->minv && s->dirt && s->origins), "instancer: null instance arrays");
+    NTX_REQUIRE(((uintptr_t)s->minv & 15) == 0, "instancer: minv must be 16-byte aligned");
+    NTX_REQUIRE(!s->spheres || ((uintptr_t)s->spheres & 15) == 0, "instancer: spheres must be 16-byte aligned");
+    NTX_REQUIRE(s->n_faces == 0 || (s->mesh_v && s->mesh_f), "instancer: a mesh needs vertices and faces");
+    for (const ntx_scene_grid* g : {&s->inst_grid, &s->tri_grid}) {
+        if (!g->cell_start) continue;
+        NTX_REQUIRE(g->items, "instancer: grid without item list");
+        for (int a = 0; a < 3; ++a)
+            NTX_REQUIRE(g->res[a] >= 1 && g->res[a] <= 1024 && g->cell[a] > 0.0f, "instancer: bad grid axis %d (res %d, cell %g)",
+                        a, g->res[a], (double)g->cell[a]);
+    }
+    out->minv = s->minv; out->dirt = s->dirt; out->origins = s->origins;
+    out->spheres = reinterpret_cast<const float4*>(s->spheres);
+    out->n_inst = s->n_inst; out->n_faces = s->n_faces; out->mesh_v = s->mesh_v; out->mesh_f = s->mesh_f;
+    out->ig = make_grid(s->inst_grid);
+    out->tg = make_grid(s->tri_grid);
+    return NTX_OK;
+}
+
+NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
+                                const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size,
+                                int n_pts, uint32_t seed, int use_mean_distance, void* workspace, int32_t* n_samples,
+                                int32_t* hit, float* alpha_last, void* stream) {
+    NTX_REQUIRE(R >= 0 && n_pts >= 1 && step_size > 0.0f, "instancer_trace: bad arguments");
+    SceneDev sc;
+    int rc = check_scene(scene, &sc);
+    if (rc) return rc;
     if (R == 0) return NTX_OK;
-    NTX_REQUIRE(rays_o && rays_d && minv && dirt && origins && b_0 && b_1 && workspace && n_samples && hit,
-                "instancer_trace: null pointer");
+    NTX_REQUIRE(rays_o && rays_d && b_0 && b_1 && workspace && n_samples && hit && alpha_last, "instancer_trace: null pointer");
     NTX_REQUIRE(((uintptr_t)workspace & 15) == 0, "instancer_trace: the workspace must be 16-byte aligned");
-    NTX_REQUIRE(!spheres || ((uintptr_t)spheres & 15) == 0, "instancer_trace: spheres must be 16-byte aligned");
-    const size_t smem = (size_t)kSmemHits * kTraceThreads * sizeof(uint64_t);
+    const size_t smem = (size_t)kSmemHits * kTraceThreads * sizeof(uint64_t) + (size_t)kMailbox * kTraceThreads * sizeof(uint32_t);
     NTX_CUDA(cudaFuncSetAttribute(instancer_trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     instancer_trace_kernel<<<(R + kTraceThreads - 1) / kTraceThreads, kTraceThreads, smem, (cudaStream_t)stream>>>(
-        rays_o, rays_d, R, minv, dirt, origins, reinterpret_cast<const float4*>(spheres), n_inst, b_0[0], b_0[1], b_0[2],
-        b_1[0], b_1[1], b_1[2], step_size, n_pts, seed, use_mean_distance, carve_workspace(workspace, R), n_samples, hit);
+        rays_o, rays_d, ray_ids, R, sc, b_0[0], b_0[1], b_0[2], b_1[0], b_1[1], b_1[2], step_size, n_pts, seed,
+        use_mean_distance, carve_workspace(workspace, R), n_samples, hit, alpha_last);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
 
-NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const float* parameters, int n_param, int R,
-                                const float* minv, const float* dirt, const float* origins, float step_size, int n_pts,
+NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* parameters,
+                                int n_param, int R, const ntx_instancer_scene* scene, float step_size, int n_pts,
                                 uint32_t seed, int light_dir_idx, int light_strength_idx, int method, float blend_range,
-                                int use_mean_distance, const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts, float* dirs, float* params_out, float* dists,
-                                float* t, float* alpha_weight, int32_t* instance_id, void* stream) {
+                                int use_mean_distance, const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts,
+                                float* dirs, float* params_out, float* dists, float* t, float* alpha_weight,
+                                int32_t* instance_id, void* stream) {
     NTX_REQUIRE(R >= 0 && T >= 0 && n_param >= 0 && n_param <= 16, "instancer_march: bad arguments (at most 16 parameters)");
     NTX_REQUIRE(light_dir_idx < 0 || light_dir_idx + 3 <= n_param, "instancer_march: light direction index out of range");
     NTX_REQUIRE(light_strength_idx < 0 || (light_strength_idx < n_param && light_dir_idx >= 0),
                 "instancer_march: a light strength parameter needs a light position (light_dir_idx) too");
     NTX_REQUIRE(method >= 0 && method <= 2, "instancer_march: instance sampling method must be 0 (random), 1 (nearest) or 2 (nearest_blend)");
+    SceneDev sc;
+    int rc = check_scene(scene, &sc);
+    if (rc) return rc;
     if (R == 0 || T == 0) return NTX_OK;
-    NTX_REQUIRE(rays_o && rays_d && (n_param == 0 || parameters) && minv && dirt && origins && workspace && ray_ptr,
-                "instancer_march: null pointer");
+    NTX_REQUIRE(rays_o && rays_d && (n_param == 0 || parameters) && workspace && ray_ptr, "instancer_march: null pointer");
     NTX_REQUIRE(pts && dirs && (n_param == 0 || params_out) && dists && t && alpha_weight && instance_id,
                 "instancer_march: null output pointer");
     (void)n_pts;
     MarchOut out = {pts, dirs, params_out, dists, t, alpha_weight, instance_id};
     instancer_emit_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        rays_o, rays_d, parameters, n_param, R, minv, dirt, origins, step_size, seed, light_dir_idx, light_strength_idx, method,
-        blend_range, use_mean_distance,
-        carve_workspace(const_cast<void*>(workspace), R), ray_ptr, T, out);
+        rays_o, rays_d, ray_ids, parameters, n_param, R, sc.minv, sc.dirt, sc.origins, step_size, seed, light_dir_idx,
+        light_strength_idx, method, blend_range, use_mean_distance, carve_workspace(const_cast<void*>(workspace), R), ray_ptr,
+        T, out);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }

@@ -2,7 +2,8 @@
 
 The reference's native instancer (Embree scene of shell patches on a mesh) cannot be built or
 fed in this environment (Embree 3 is a system dependency, every mesh/texture is a git-LFS stub;
-SURVEY.md D8).  ``Instancer`` is the device instancer for explicit patch transformations (no mesh);
+SURVEY.md D8).  ``Instancer`` is the device instancer (explicit patch transformations, or patches placed on a PLY
+base mesh that also ends the rays; uniform-grid traversal);
 ``SyntheticInstancer`` keeps the exact constructor / ``n_instances`` /
 ``get_model_input`` surface and produces seeded outputs with the statistics SURVEY.md section 8d
 prescribes, natively CSR-packed on the GPU (``get_model_input_csr``); ``get_model_input`` scatters
@@ -17,6 +18,7 @@ from typing import Dict, Optional
 import numpy as np
 import torch
 
+from . import _lib
 from ._lib import as_cuda
 
 
@@ -120,21 +122,27 @@ def csr_to_dense(csr, rays_d, parameters, n_samples: int):
 
 
 class Instancer:
-    """Device shell instancer behind the reference's constructor (instancer/instancer.pyx:6-36) for explicit patch
-    `transformations` (AddInstance, instancer.cpp:125-141).  What needs the Embree scene of a base mesh is refused:
-    `mesh_path`, shadow rays, image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes."""
+    """Device shell instancer behind the reference's constructor (instancer/instancer.pyx:6-36): explicit patch
+    `transformations` (AddInstance, instancer.cpp:125-141) and / or patches distributed on a base mesh
+    (`mesh_path`, `patch_origins_path`, `patch_scale`, `jitter_amount`: DistributeInstancesOnMesh, :233-391), whose
+    first hit ends a ray with an opaque black last sample (:804-814,:1019-1023).  Rays walk uniform grids over the patch
+    boxes and the mesh triangles (scene_grid.py) where the reference walks Embree BVHs.  Still refused: shadow rays,
+    image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes.
+    `mesh` = {'V','F','N','UV'} arrays may be given in place of `mesh_path` (procedural meshes), `patch_origins` [A,3]
+    in place of `patch_origins_path`."""
 
     def __init__(self, b_0: list, b_1: list, cast_shadow_rays=False, textures: list = [], transformations: list = [],
                  mesh_path: str = None, patch_scale: float = 1., patch_origins_path='', min_shadow_samples: int = 4,
                  n_shadow_samples: int = 512, min_texture_samples: int = 4, n_texture_samples: int = 512,
                  jitter_amount: float = 0, instance_sampling_method: str = 'random', use_mean_distance: bool = False,
-                 auxiliary_meshes=[], transformation_export_path=None, *, seed: int = 0, device=None) -> None:
+                 auxiliary_meshes=[], transformation_export_path=None, *, seed: int = 0, device=None, mesh=None,
+                 patch_origins=None, use_grid: bool = True) -> None:
         assert instance_sampling_method in ('random', 'nearest', 'nearest_blend')      # instancer.pyx:12
-        if mesh_path:
-            raise NotImplementedError("Instancer: placing patches on a mesh needs the reference's Embree scene and its "
-                                      "git-LFS meshes; pass explicit `transformations` (or use SyntheticInstancer)")
-        if cast_shadow_rays or auxiliary_meshes:
-            raise NotImplementedError("Instancer: shadow rays / auxiliary meshes need a mesh scene")
+        if cast_shadow_rays:
+            raise NotImplementedError("Instancer: shadow rays (instancer.cpp:593-603) are not implemented on the device yet")
+        if auxiliary_meshes:
+            raise NotImplementedError("Instancer: auxiliary meshes (AddMesh / shadeMesh, instancer.cpp:393-418,716-744) are "
+                                      "not implemented on the device yet")
         self.light_dir_idx = self.light_strength_idx = -1
         n_parameters = 0
         for tex in textures:                                                           # instancer.cpp:75-92
@@ -148,15 +156,37 @@ class Instancer:
             elif tex in ('', None):
                 n_parameters += 1
             else:
-                raise NotImplementedError(f"Instancer: parameter texture {tex!r} needs a UV-mapped mesh")
+                raise NotImplementedError(f"Instancer: parameter texture {tex!r} (getParameters, instancer.cpp:640-667) is "
+                                          "not implemented on the device yet")
         self.n_parameters = n_parameters
         import numpy as np
-        T = np.asarray(transformations, dtype=np.float64).reshape(-1, 4, 4)
+        from . import scene_grid
+        T = np.asarray(transformations, dtype=np.float64).reshape(-1, 4, 4)             # AddInstance calls come first (:17-18)
+        self.patch_scale = float(patch_scale)
+        self.mesh = None
+        if mesh_path is not None or mesh is not None:                                   # :20-23
+            from . import distribute, ply
+            m = ply.read_ply(mesh_path) if mesh is None else {k: mesh.get(k) for k in ("V", "F", "N", "UV")}
+            if m["F"] is None or len(m["F"]) == 0:
+                raise ValueError("Instancer: the base mesh has no faces")
+            if m["N"] is None or m["UV"] is None:
+                raise ValueError("Instancer: the base mesh needs per-vertex normals and texture coordinates "
+                                 "(the tangent frames of DistributeInstancesOnMesh come from them, instancer.cpp:248-277)")
+            if patch_origins is None and patch_origins_path:
+                try:
+                    patch_origins = ply.read_ply(patch_origins_path)["V"]
+                except (OSError, ValueError):
+                    patch_origins = None                                                # readPLY fails -> mesh vertices (:350)
+            placed, scale = distribute.distribute_instances_on_mesh(m["V"], m["F"], m["N"], m["UV"], patch_origins,
+                                                                    float(patch_scale), float(jitter_amount), seed=0)
+            self.patch_scale = scale                                                    # :245 (average edge length if <= 0)
+            T = np.concatenate([T, placed.astype(np.float64)], 0)
+            self.mesh = {"V": np.ascontiguousarray(m["V"], np.float32), "F": np.ascontiguousarray(m["F"], np.int32)}
         if T.shape[0] == 0:
-            raise ValueError("Instancer: no instances (empty `transformations`)")
+            raise ValueError("Instancer: no instances (empty `transformations` and no mesh)")
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         rt = np.transpose(T[:, :3, :3], (0, 2, 1))
-        as_dev = lambda a: torch.from_numpy(np.ascontiguousarray(a.astype(np.float32))).to(dev)
+        as_dev = lambda a, dt=np.float32: torch.from_numpy(np.ascontiguousarray(np.asarray(a).astype(dt))).to(dev)
         self.minv = as_dev(np.linalg.inv(T)[:, :3, :])
         self.dirt = as_dev(rt / np.linalg.norm(rt, axis=2, keepdims=True))
         self.origins = as_dev(T[:, :3, 3])
@@ -169,26 +199,58 @@ class Instancer:
         self.spheres = as_dev(np.concatenate([centre, r2[:, None]], -1))
         self.transformations = T
         self.b_0, self.b_1 = [float(v) for v in b_0], [float(v) for v in b_1]
-        self.patch_scale = float(patch_scale)
         self.method = {'random': 0, 'nearest': 1, 'nearest_blend': 2}[instance_sampling_method]   # instancer.pyx:12
         self.use_mean_distance = bool(use_mean_distance)
         self.seed = int(seed)
         self._calls = 0
+        self._frame = -1                       # new_frame() before the first named-ray call makes it 0
+        # CommitScene (:420-424): the acceleration structures
+        self._keep = []                                                                  # device arrays the scene points into
+        self.scene = _lib.InstancerScene()
+        self.scene.minv, self.scene.dirt, self.scene.origins = self.minv.data_ptr(), self.dirt.data_ptr(), self.origins.data_ptr()
+        self.scene.spheres = self.spheres.data_ptr()
+        self.scene.n_inst, self.scene.n_faces = int(T.shape[0]), 0
+        if use_grid:
+            self._set_grid(self.scene.inst_grid, scene_grid.build_grid(world.min(1), world.max(1)), as_dev)
+        if self.mesh is not None:
+            mv, mf = as_dev(self.mesh["V"]), as_dev(self.mesh["F"], np.int32)
+            self._keep += [mv, mf]
+            self.scene.mesh_v, self.scene.mesh_f, self.scene.n_faces = mv.data_ptr(), mf.data_ptr(), int(mf.shape[0])
+            if use_grid:
+                self._set_grid(self.scene.tri_grid, scene_grid.build_grid(*scene_grid.triangle_boxes(self.mesh["V"], self.mesh["F"])), as_dev)
         if transformation_export_path:
             np.save(transformation_export_path, T)                                    # instancer.pyx:33-36
+
+    def _set_grid(self, dst, g, as_dev) -> None:
+        import numpy as np
+        cs, it = as_dev(g["cell_start"], np.int32), as_dev(g["items"], np.int32)
+        self._keep += [cs, it]
+        dst.cell_start, dst.items = cs.data_ptr(), it.data_ptr()
+        for a in range(3):
+            dst.lo[a], dst.cell[a], dst.res[a] = float(g["lo"][a]), float(g["cell"][a]), int(g["res"][a])
 
     def n_instances(self) -> int:
         return int(self.minv.shape[0])
 
-    def get_model_input_csr(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
+    def new_frame(self) -> None:
+        """Advance the draw seed of calls that name their rays (`ray_ids`): one seed per frame, so that every chunk and
+        every GPU working on the frame draws from the same stream."""
+        self._frame += 1
+
+    def get_model_input_csr(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None,
+                            ray_ids=None):
         from . import ops
-        if seed is None:                       # a fresh draw every call, like the reference's running mt19937
-            seed = self.seed + 7919 * self._calls
-            self._calls += 1
-        return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.minv, self.dirt, self.origins,
-                                             self.b_0, self.b_1, seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
-                                             use_mean_distance=self.use_mean_distance, spheres=self.spheres,
-                                             light_strength_idx=self.light_strength_idx, blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)))   # fp32 product, instancer.cpp:696
+        if seed is None:
+            if ray_ids is not None:
+                seed = self.seed + 7919 * max(self._frame, 0)
+            else:                              # a fresh draw every call, like the reference's running mt19937
+                seed = self.seed + 7919 * self._calls
+                self._calls += 1
+        return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.scene, self.b_0, self.b_1,
+                                             seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
+                                             use_mean_distance=self.use_mean_distance, light_strength_idx=self.light_strength_idx,
+                                             blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)),   # fp32 product, instancer.cpp:696
+                                             ray_ids=ray_ids)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

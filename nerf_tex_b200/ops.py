@@ -228,24 +228,30 @@ def rays_from_camera(image_plane_loc, height: int, width: int, focal: float, c2w
 
 # ------------------------------------------------------------------------------------------ instancer
 
-def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size: float, minv, dirt, origins, b_0, b_1, *,
+def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size: float, scene, b_0, b_1, *,
                               seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False,
-                              spheres=None, light_strength_idx: int = -1, blend_range: float = 0.0):
+                              light_strength_idx: int = -1, blend_range: float = 0.0, ray_ids=None):
     """Two-pass shell instancer (instancer/src/instancer.cpp:751-1037): trace + count, prefix sum, march.
-    Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box)."""
+    `scene`: _lib.InstancerScene (device pointers kept alive by the caller).  `ray_ids` [R] int32: the rays' names for
+    the random draws.  Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box or
+    the base mesh)."""
     rays_o, rays_d, parameters = as_cuda(rays_o), as_cuda(rays_d), as_cuda(parameters)
     dev = rays_o.device
     R, p = rays_o.shape[0], parameters.shape[1]
+    if ray_ids is not None:
+        ray_ids = as_cuda(ray_ids, torch.int32, device=dev).reshape(-1)
+        assert ray_ids.shape[0] == R
     lib = _lib.load()
     b0 = (C.c_float * 3)(*[float(v) for v in b_0])
     b1 = (C.c_float * 3)(*[float(v) for v in b_1])
     n_samples = torch.empty(R, dtype=torch.int32, device=dev)
     hit = torch.empty(R, dtype=torch.int32, device=dev)
+    alpha_last_all = torch.empty(R, dtype=torch.float32, device=dev)
     ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R)), 16), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), R, ptr(minv), ptr(dirt), ptr(origins), ptr(spheres), minv.shape[0], b0, b1,
+        check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), ptr(ray_ids), R, C.byref(scene), b0, b1,
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)),
-                                      ptr(ws), ptr(n_samples), ptr(hit), stream_ptr()))
+                                      ptr(ws), ptr(n_samples), ptr(hit), ptr(alpha_last_all), stream_ptr()))
         ray_ptr_all = torch.zeros(R + 1, dtype=torch.int64, device=dev)
         torch.cumsum(n_samples, 0, out=ray_ptr_all[1:])
         ray_index = torch.nonzero(hit).squeeze(1)
@@ -253,7 +259,7 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
         f = lambda *shape: torch.empty(shape, dtype=torch.float32, device=dev)
         out = {"pts": f(T, 3), "dirs": f(T, 3), "params": f(T, p), "dists": f(T), "t": f(T), "alpha_weight": f(T),
                "instance_id": torch.empty(T, dtype=torch.int32, device=dev)}
-        check(lib.ntx_instancer_march(ptr(rays_o), ptr(rays_d), ptr(parameters), p, R, ptr(minv), ptr(dirt), ptr(origins),
+        check(lib.ntx_instancer_march(ptr(rays_o), ptr(rays_d), ptr(ray_ids), ptr(parameters), p, R, C.byref(scene),
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(light_dir_idx), int(light_strength_idx),
                                       int(method), float(blend_range),
                                       int(bool(use_mean_distance)), ptr(ws), ptr(ray_ptr_all), T, ptr(out["pts"]), ptr(out["dirs"]),
@@ -264,8 +270,8 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     out["ray_ptr"] = torch.cat([ray_ptr_all[:-1][ray_index], ray_ptr_all[-1:]]) if H > 0 else torch.zeros(1, dtype=torch.int64, device=dev)
     out["ray_index"] = ray_index.to(torch.int32)
     out["n_samples_all"] = n_samples
-    out["color_last"] = torch.zeros((H, 3), dtype=torch.float32, device=dev)      # no mesh: instancer.cpp:1020-1027
-    out["alpha_last"] = torch.zeros(H, dtype=torch.float32, device=dev)
+    out["color_last"] = torch.zeros((H, 3), dtype=torch.float32, device=dev)      # base mesh: black (instancer.cpp:1019-1021)
+    out["alpha_last"] = alpha_last_all[ray_index].contiguous()                     # 1 where the ray ends on the mesh
     return out
 
 

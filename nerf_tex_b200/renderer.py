@@ -78,6 +78,9 @@ class Renderer:
         all_hit = idxs.shape[0] == n_all
         extra = {k: as_cuda(v).reshape(n_all, -1) for k, v in kwargs.items()
                  if k in ("z_rand", "u", "noise", "noise_fine") and v is not None}
+        ray_ids = self._frame_ray_ids(kwargs.get("ray_ids"), n_all, dev)         # instanced renderers: names for the draws
+        if ray_ids is not None:
+            extra["ray_ids"] = ray_ids
         if not all_hit:
             ro, rd, tf_, pf, cf = ro[idxs], rd[idxs], tf_[idxs], pf[idxs], cf[idxs]
             extra = {k: v[idxs] for k, v in extra.items()}
@@ -106,6 +109,10 @@ class Renderer:
                     full[~hit] = bk
             res[k] = full.reshape((B, -1) + tuple(v.shape[1:]))
         return res
+
+    def _frame_ray_ids(self, ray_ids, n_all: int, dev):
+        """Hook of the instanced renderers (the plain renderer draws nothing per ray id)."""
+        return None
 
     # -- one chunk --------------------------------------------------------------------------
     def render_rays(self, rays_o, rays_d, t, parameters, cone_scale, composite_bkgd, bkgd_color, training,
@@ -230,22 +237,39 @@ class InstanceRenderer(Renderer):
         self.patch_scale = (instancer_config["patch_scale"] if isinstance(instancer_config, dict)
                             else getattr(self.instancer, "patch_scale", 1.0))                         # :228
 
-    def render_rays(self, rays_o, rays_d, t, parameters, cone_scale, composite_bkgd, bkgd_color, training, **kwargs):
+    def _frame_ray_ids(self, ray_ids, n_all: int, dev):
+        """One call = one frame for an instancer that draws per named ray (Instancer.new_frame / ray_ids): rays are named
+        by their position in the call unless the caller names them (render_sharded passes the positions in the frame)."""
+        if not hasattr(self.instancer, "new_frame"):
+            return None
+        self.instancer.new_frame()
+        if ray_ids is None:
+            return torch.arange(n_all, dtype=torch.int32, device=dev).reshape(n_all, 1)
+        return as_cuda(ray_ids, torch.int32, device=dev).reshape(n_all, 1)
+
+    def render_rays(self, rays_o, rays_d, t, parameters, cone_scale, composite_bkgd, bkgd_color, training,
+                    ray_ids=None, **kwargs):
         assert training is False or training == False, \
             "network.renderer.InstanceRenderer can only be used for evaluation."                      # :233
         color_map, alpha_map = self.evaluate_model(rays_o, rays_d, parameters, cone_scale, self.model, composite_bkgd,
-                                                   bkgd_color, False)
+                                                   bkgd_color, False, ray_ids=ray_ids)
         return {"color_pred": color_map, "alpha_pred": alpha_map}
 
-    def evaluate_model(self, rays_o, rays_d, parameters, cone_scale, model, composite_bkgd, bkgd_color, training):
+    def _instancer_records(self, rays_o, rays_d, parameters, ray_ids):
+        """The instancer call of renderer.py:253, CSR-packed."""
+        if hasattr(self.instancer, "get_model_input_csr"):
+            if ray_ids is not None and hasattr(self.instancer, "new_frame"):
+                return self.instancer.get_model_input_csr(rays_o, rays_d, parameters, self.n_samples, self.step_size,
+                                                          ray_ids=ray_ids.reshape(-1).contiguous())
+            return self.instancer.get_model_input_csr(rays_o, rays_d, parameters, self.n_samples, self.step_size)
+        return dense_to_csr(self.instancer.get_model_input(rays_o, rays_d, parameters, self.n_samples, self.step_size))
+
+    def evaluate_model(self, rays_o, rays_d, parameters, cone_scale, model, composite_bkgd, bkgd_color, training,
+                       ray_ids=None):
         """network/renderer.py:247-316."""
         n_rays = rays_o.shape[0]
         dev = rays_o.device
-        if hasattr(self.instancer, "get_model_input_csr"):
-            csr = self.instancer.get_model_input_csr(rays_o, rays_d, parameters, self.n_samples, self.step_size)
-        else:
-            csr = dense_to_csr(self.instancer.get_model_input(rays_o, rays_d, parameters, self.n_samples,
-                                                              self.step_size))
+        csr = self._instancer_records(rays_o, rays_d, parameters, ray_ids)
         H = csr["ray_index"].shape[0]
         if H == 0:                                                                # :256-257
             return (torch.zeros((n_rays, 3), dtype=torch.float32, device=dev),
@@ -346,12 +370,10 @@ class MipInstanceRenderer(InstanceRenderer):
         if blur_idx is None:
             raise ValueError("MipInstanceRenderer needs blur_idx (renderer.py:511)")
 
-    def evaluate_model(self, rays_o, rays_d, parameters, cone_scale, model, composite_bkgd, bkgd_color, training):
+    def evaluate_model(self, rays_o, rays_d, parameters, cone_scale, model, composite_bkgd, bkgd_color, training,
+                       ray_ids=None):
         n_rays, dev = rays_o.shape[0], rays_o.device
-        if hasattr(self.instancer, "get_model_input_csr"):
-            csr = self.instancer.get_model_input_csr(rays_o, rays_d, parameters, self.n_samples, self.step_size)
-        else:
-            csr = dense_to_csr(self.instancer.get_model_input(rays_o, rays_d, parameters, self.n_samples, self.step_size))
+        csr = self._instancer_records(rays_o, rays_d, parameters, ray_ids)
         H = csr["ray_index"].shape[0]
         if H == 0:                                                                # :494-495
             return (torch.zeros((n_rays, 3), dtype=torch.float32, device=dev),

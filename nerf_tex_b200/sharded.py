@@ -80,6 +80,10 @@ def render_sharded(renderer, rays_o, rays_d, t, parameters, cone_scale, *, group
     idx = shard_index(Nr, rank, world, block, interleave, dev)
     n_mine = int(idx.shape[0])
     out: Dict[str, torch.Tensor] = {}
+    from .renderer import InstanceRenderer
+    if isinstance(renderer, InstanceRenderer) and "ray_ids" not in kwargs and n_mine > 0:
+        # name the rays by their position in the whole frame: the instancer's per-ray draws then do not depend on the split
+        kwargs = dict(kwargs, ray_ids=(torch.arange(B, device=dev)[:, None] * Nr + idx[None, :]).reshape(-1).to(torch.int32))
     if n_mine > 0:
         pick = (lambda a: a[:, idx[0]:idx[0] + n_mine]) if not interleave else (lambda a: a[:, idx])
         out = renderer(pick(rays_o).contiguous(), pick(rays_d).contiguous(), pick(t).contiguous(), parameters,

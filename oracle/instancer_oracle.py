@@ -1,8 +1,9 @@
 """CPU oracle for the shell instancer (instancer/src/instancer.cpp:751-1037, GetModelInput).
 TEST INFRASTRUCTURE ONLY.  PARITY UNPINNED: the reference instancer needs Embree 3 (absent) and its
 meshes/textures are git-LFS stubs, so it can neither be built nor fed here; this is a restatement of
-its algorithm for the subset that needs no mesh: explicit patch instances (`transformations`), no
-parameter textures, no shadow rays, no auxiliary meshes.
+its algorithm: explicit patch instances (`transformations`) or patches distributed on a base mesh
+(DistributeInstancesOnMesh), termination of a ray at the first mesh hit; no parameter textures, no shadow
+rays, no auxiliary-mesh shading yet.
 
 What is restated (file:line of instancer.cpp):
   * all hits of a ray with every instanced patch box, sorted by (t, instance)            :780-799
@@ -14,6 +15,14 @@ What is restated (file:line of instancer.cpp):
     'nearest_blend' (draw from max(range + min_dist - dist, 0), weight 1 / probability)
   * world -> patch mapping of points, view directions and the light direction; point lights  :556-590,:929-956
   * `use_mean_distance` (:746-748), no mesh hit: colour 0 / density 0                      :1020-1027
+  * a base mesh in the scene (:374-391): its first hit along the ray ends the in-shell length (:804-814) and the
+    march (:983), and gives the ray's last sample colour 0 / density 1 (:1019-1023).  Embree's triangle test is not
+    in the reference tree; it is restated as the watertight test of Woop, Benthin and Wald (JCGT 2013) in fp32
+    with the double-precision fallback on zero edge functions, ties between triangles to the smaller face index
+    (the reference's Hit order, :444-455)
+  * DistributeInstancesOnMesh (:233-391): per-vertex tangent frames from the UV parametrisation, closest point on
+    the mesh for every anchor, interpolated frame, optional rotation about the normal by jitter_amount * U(0, pi)
+    drawn from std::mt19937(seed = 0) exactly as libstdc++ draws it, patch matrix [T B N | anchor] * scale
 
 Not reproducible by construction: the reference draws offsets / instance choices from a member
 `std::mt19937`; here they come from a counter-based hash of (seed, ray[, step]) so that a GPU kernel can
@@ -74,30 +83,95 @@ def _norm3(v):
     return F(np.sqrt(F(F(F(v[0] * v[0]) + F(v[1] * v[1])) + F(v[2] * v[2]))))
 
 
-def ray_hits(o, d, minv, b0, b1):
-    """Sorted, bounded list of (t, instance) box hits of one ray."""
+def _vdot3(M, v, add=None):
+    """Rows of M[.., 3] dotted with v in the fixed fp32 order of _dot3 (vectorised over the leading axes)."""
+    r = (M[..., 0] * v[0]).astype(F) + (M[..., 1] * v[1]).astype(F)
+    r = r.astype(F) + (M[..., 2] * v[2]).astype(F)
+    r = r.astype(F)
+    return r if add is None else (r + add).astype(F)
+
+
+def ray_hits(o, d, minv, b0, b1, t_max=None):
+    """Sorted, bounded list of (t, instance) box hits of one ray (slab test in every patch frame, all instances at
+    once; every elementwise numpy op rounds to fp32 exactly like the scalar form).  `t_max`: keep only hits with
+    t <= t_max (the first mesh hit; boxes sort before the mesh at equal t, instancer.cpp:444-455)."""
+    o, d = np.asarray(o, F), np.asarray(d, F)
+    ol = _vdot3(minv[:, :, :3], o, minv[:, :, 3])                     # [I,3]
+    dl = _vdot3(minv[:, :, :3], d)
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+        inv = (F(1.0) / dl).astype(F)
+        t0 = ((b0[None, :] - ol).astype(F) * inv).astype(F)
+        t1 = ((b1[None, :] - ol).astype(F) * inv).astype(F)
+        lt = t0 < t1
+        lo, hi = np.where(lt, t0, t1), np.where(lt, t1, t0)
+        tin, tout = lo[:, 0], hi[:, 0]
+        for a in (1, 2):
+            tin = np.where(lo[:, a] > tin, lo[:, a], tin)
+            tout = np.where(hi[:, a] < tout, hi[:, a], tout)
+        ok = (tin < tout) & (tout >= 0) & (tin <= T_FAR)
     hits = []
-    for inst in range(minv.shape[0]):
-        M = minv[inst]
-        ol = [_dot3(M[a, :3], o, M[a, 3]) for a in range(3)]
-        dl = [_dot3(M[a, :3], d) for a in range(3)]
-        tin, tout = F(-np.inf), F(np.inf)
-        with np.errstate(divide="ignore", invalid="ignore"):
-            for a in range(3):
-                inv = F(F(1.0) / dl[a])
-                t0 = F(F(b0[a] - ol[a]) * inv)
-                t1 = F(F(b1[a] - ol[a]) * inv)
-                lo, hi = (t0, t1) if t0 < t1 else (t1, t0)
-                tin = lo if (a == 0 or lo > tin) else tin
-                tout = hi if (a == 0 or hi < tout) else tout
-        if not (tin < tout) or not (tout >= 0) or not (tin <= T_FAR):
-            continue
-        if tin >= 0:
-            hits.append((float(tin + F(0.0)), inst))
-        if tout <= T_FAR:
-            hits.append((float(tout + F(0.0)), inst))
+    for inst in np.nonzero(ok)[0]:
+        if tin[inst] >= 0:
+            hits.append((float(tin[inst] + F(0.0)), int(inst)))
+        if tout[inst] <= T_FAR:
+            hits.append((float(tout[inst] + F(0.0)), int(inst)))
+    if t_max is not None:
+        hits = [h for h in hits if h[0] <= float(t_max)]
     hits.sort()
     return hits[:MAX_HITS]
+
+
+def ray_frame(d):
+    """Per-ray constants of the watertight triangle test: dominant axis kz, the other two in winding-preserving
+    order, and the shear (Woop et al., section 3)."""
+    d = np.asarray(d, F)
+    ad = np.abs(d)
+    kz = 0 if (ad[0] >= ad[1] and ad[0] >= ad[2]) else (1 if ad[1] >= ad[2] else 2)
+    kx = (kz + 1) % 3
+    ky = (kx + 1) % 3
+    if d[kz] < 0:
+        kx, ky = ky, kx
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+        Sx, Sy, Sz = F(d[kx] / d[kz]), F(d[ky] / d[kz]), F(F(1.0) / d[kz])
+    return kx, ky, kz, Sx, Sy, Sz
+
+
+def mesh_first_hit(o, d, V, Fc):
+    """Nearest hit of the ray with the triangles (V[n,3] fp32, Fc[m,3] int) for t in [0, 100]:
+    (t, face, u, v) with u, v the barycentric weights of the face's 2nd and 3rd vertex, or None."""
+    o, d = np.asarray(o, F), np.asarray(d, F)
+    if not np.any(d != 0):
+        return None
+    kx, ky, kz, Sx, Sy, Sz = ray_frame(d)
+    A, B, C = (V[Fc[:, k]] - o[None, :]).astype(F) if False else None, None, None
+    P = [(V[Fc[:, k]] - o[None, :]).astype(F) for k in range(3)]       # vertices relative to the origin
+    X = [(p[:, kx] - (Sx * p[:, kz]).astype(F)).astype(F) for p in P]
+    Y = [(p[:, ky] - (Sy * p[:, kz]).astype(F)).astype(F) for p in P]
+    (Ax, Bx, Cx), (Ay, By, Cy) = X, Y
+    U = ((Cx * By).astype(F) - (Cy * Bx).astype(F)).astype(F)
+    Vv = ((Ax * Cy).astype(F) - (Ay * Cx).astype(F)).astype(F)
+    W = ((Bx * Ay).astype(F) - (By * Ax).astype(F)).astype(F)
+    z = (U == 0) | (Vv == 0) | (W == 0)
+    if z.any():                                                        # exact products in double, rounded once
+        D = np.float64
+        U = np.where(z, (Cx.astype(D) * By.astype(D) - Cy.astype(D) * Bx.astype(D)).astype(F), U)
+        Vv = np.where(z, (Ax.astype(D) * Cy.astype(D) - Ay.astype(D) * Cx.astype(D)).astype(F), Vv)
+        W = np.where(z, (Bx.astype(D) * Ay.astype(D) - By.astype(D) * Ax.astype(D)).astype(F), W)
+    miss = ((U < 0) | (Vv < 0) | (W < 0)) & ((U > 0) | (Vv > 0) | (W > 0))
+    det = ((U + Vv).astype(F) + W).astype(F)
+    miss |= det == 0
+    Z = [(Sz * p[:, kz]).astype(F) for p in P]
+    T = (((U * Z[0]).astype(F) + (Vv * Z[1]).astype(F)).astype(F) + (W * Z[2]).astype(F)).astype(F)
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+        t = (T / det).astype(F)
+        u = (Vv / det).astype(F)
+        v = (W / det).astype(F)
+    miss |= ~((t >= 0) & (t <= T_FAR))
+    cand = np.nonzero(~miss)[0]
+    if cand.shape[0] == 0:
+        return None
+    best = cand[np.lexsort((cand, t[cand]))[0]]                        # smallest t, then smallest face index
+    return F(t[best]), int(best), F(u[best]), F(v[best])
 
 
 def mean_distance(mu, hw):
@@ -107,22 +181,36 @@ def mean_distance(mu, hw):
 
 
 def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformations, b_0, b_1, *, seed=0,
-                    light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1, patch_scale=1.0):
-    """Returns the CSR form over ALL rays: n_samples[R], hit[R] and per-sample records."""
+                    light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1, patch_scale=1.0,
+                    mesh=None, ray_ids=None):
+    """Returns the CSR form over ALL rays: n_samples[R], hit[R], alpha_last[R], color_last[R,3] and per-sample
+    records.  `mesh` = (V[n,3], F[m,3]): the base mesh the patches sit on (a ray ends at its first hit).  `ray_ids`:
+    the identity of every ray for the random draws (default: its index in this call), so that a frame cut into chunks
+    or spread over GPUs draws the same numbers."""
     rays_o, rays_d, parameters = np.asarray(rays_o, F), np.asarray(rays_d, F), np.asarray(parameters, F)
+    if mesh is not None:
+        mesh = (np.ascontiguousarray(mesh[0], F), np.ascontiguousarray(mesh[1], np.int64))
     minv, dirt, origins = prepare_instances(transformations)
     b0, b1 = np.asarray(b_0, F), np.asarray(b_1, F)
     step_size = F(step_size)
     R = rays_o.shape[0]
     n_samples = np.zeros(R, np.int32)
     hit = np.zeros(R, bool)
+    alpha_last = np.zeros(R, F)
+    color_last = np.zeros((R, 3), F)
     recs = dict(pts=[], dirs=[], params=[], dists=[], t=[], weight=[], inst=[])
     for i in range(R):
         o, d = rays_o[i], rays_d[i]
-        hits = ray_hits(o, d, minv, b0, b1)
-        if not hits:
+        rid = i if ray_ids is None else int(ray_ids[i])
+        mh = mesh_first_hit(o, d, *mesh) if mesh is not None else None
+        hits = ray_hits(o, d, minv, b0, b1, None if mh is None else mh[0])
+        if mh is not None and len(hits) >= MAX_HITS:                  # the mesh hit would be entry 201 of the sorted list
+            mh = None
+        if not hits and mh is None:
             continue
         hit[i] = True
+        if mh is not None:                                          # :1019-1023 (instancer mesh: black, opaque)
+            alpha_last[i] = F(1)
         # :801-827 total in-shell length
         active, total, t_entry = set(), F(0), F(0)
         for tt, inst in hits:
@@ -135,11 +223,13 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 if not active:
                     t_entry = tt
                 active.add(inst)
+        if mh is not None and active:                               # :805-810 the mesh closes the open segment
+            total = F(total + F(mh[0] - t_entry))
         if not (total > 0):
             continue
         necessary = int(F(total / step_size))                       # :845
         n_steps = min(necessary, n_pts)
-        u = ray_uniform(seed, i)
+        u = ray_uniform(seed, rid)
         dists = []
         if n_steps == 0:                                            # :848-851
             dists = [total]
@@ -159,7 +249,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         active = set()
         segment_offset, cleared, t_entry, step = F(0), F(0), F(0), 0
         emitted = 0
-        for tt, inst in hits:
+        for tt, inst in hits + ([(float(mh[0]), -1)] if mh is not None else []):
             tt = F(tt)
             if step >= n_steps:
                 break
@@ -175,7 +265,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 if len(act) == 1:
                     sel, w = act[0], F(1)
                 elif method == "random":
-                    sel, w = act[pick(seed, i, step, len(act))], F(len(act))
+                    sel, w = act[pick(seed, rid, step, len(act))], F(len(act))
                 elif method == "nearest_blend":                     # :694-713, transition_range 0.2 (instancer.hpp:84)
                     ds = [_norm3([F(pt[c] - origins[a_][c]) for c in range(3)]) for a_ in act]
                     lim = F(F(F(0.2) * F(patch_scale)) + min(ds))
@@ -183,7 +273,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                     total = F(0)
                     for w_ in ws:
                         total = F(total + w_)
-                    target = F(step_uniform(seed, i, step) * total)
+                    target = F(step_uniform(seed, rid, step) * total)
                     run, sel, w_sel = F(0), act[0], F(1)
                     for a_, w_ in zip(act, ws):
                         run = F(run + w_)
@@ -220,6 +310,8 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 emitted += 1
                 step += 1
                 t_mu, t_pt = t_of(step)
+            if inst < 0:                                            # :983 the mesh culls whatever lies behind it
+                break
             if inst in active:
                 active.discard(inst)
                 if not active:
@@ -232,10 +324,147 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         n_samples[i] = emitted
     p = parameters.shape[1]
     out = {
-        "n_samples": n_samples, "hit": hit,
+        "n_samples": n_samples, "hit": hit, "alpha_last": alpha_last, "color_last": color_last,
         "pts": np.asarray(recs["pts"], F).reshape(-1, 3), "dirs": np.asarray(recs["dirs"], F).reshape(-1, 3),
         "params": np.asarray(recs["params"], F).reshape(len(recs["params"]), p), "dists": np.asarray(recs["dists"], F),
         "t": np.asarray(recs["t"], F), "alpha_weight": np.asarray(recs["weight"], F),
         "instance_id": np.asarray(recs["inst"], np.int32),
     }
     return out
+
+
+# ----------------------------------------------------------------------------------------------------------------------
+# DistributeInstancesOnMesh (instancer.cpp:233-391), restated with plain loops (small meshes only)
+# ----------------------------------------------------------------------------------------------------------------------
+
+class MT19937:
+    """std::mt19937 (Matsumoto & Nishimura's reference recurrence; init_genrand seeding)."""
+
+    def __init__(self, seed=5489):
+        self.mt = [0] * 624
+        self.mt[0] = seed & 0xFFFFFFFF
+        for i in range(1, 624):
+            self.mt[i] = (1812433253 * (self.mt[i - 1] ^ (self.mt[i - 1] >> 30)) + i) & 0xFFFFFFFF
+        self.idx = 624
+
+    def __call__(self):
+        if self.idx >= 624:
+            mt = self.mt
+            for k in range(624):
+                y = (mt[k] & 0x80000000) | (mt[(k + 1) % 624] & 0x7FFFFFFF)
+                mt[k] = mt[(k + 397) % 624] ^ (y >> 1) ^ (0x9908B0DF if y & 1 else 0)
+            self.idx = 0
+        y = self.mt[self.idx]
+        self.idx += 1
+        y ^= y >> 11
+        y ^= (y << 7) & 0x9D2C5680
+        y ^= (y << 15) & 0xEFC60000
+        y ^= y >> 18
+        return y & 0xFFFFFFFF
+
+
+def uniform_real_float(gen, a, b):
+    """libstdc++ std::uniform_real_distribution<float>(a, b)(gen): generate_canonical<float, 24> takes one 32-bit
+    output, float(x) / 2^32, and replaces a result of 1 by the float below it."""
+    c = F(F(gen()) / F(4294967296.0))
+    if c >= F(1):
+        c = np.nextafter(F(1), F(0))
+    return F(F(c * F(F(b) - F(a))) + F(a))
+
+
+def closest_point_on_triangle(p, a, b, c):
+    """instancer.cpp:151-199 (Ericson, Real-Time Collision Detection 5.1.5): (point, barycentric weights)."""
+    ab, ac, ap = b - a, c - a, p - a
+    d1, d2 = ab @ ap, ac @ ap
+    if d1 <= 0 and d2 <= 0:
+        return a, np.array([1, 0, 0], F)
+    bp = p - b
+    d3, d4 = ab @ bp, ac @ bp
+    if d3 >= 0 and d4 <= d3:
+        return b, np.array([0, 1, 0], F)
+    cp = p - c
+    d5, d6 = ab @ cp, ac @ cp
+    if d6 >= 0 and d5 <= d6:
+        return c, np.array([0, 0, 1], F)
+    vc = d1 * d4 - d3 * d2
+    if vc <= 0 and d1 >= 0 and d3 <= 0:
+        v = d1 / (d1 - d3)
+        return a + v * ab, np.array([1 - v, v, 0], F)
+    vb = d5 * d2 - d1 * d6
+    if vb <= 0 and d2 >= 0 and d6 <= 0:
+        v = d2 / (d2 - d6)
+        return a + v * ac, np.array([1 - v, 0, v], F)
+    va = d3 * d6 - d5 * d4
+    if va <= 0 and (d4 - d3) >= 0 and (d5 - d6) >= 0:
+        v = (d4 - d3) / ((d4 - d3) + (d5 - d6))
+        return b + v * (c - b), np.array([0, 1 - v, v], F)
+    denom = 1 / (va + vb + vc)
+    v, w = vb * denom, vc * denom
+    return a + v * ab + w * ac, np.array([1 - v - w, v, w], F)
+
+
+def distribute_instances_on_mesh(V, Fc, N, UV, patch_origins=None, scale=1.0, jitter_amount=0.0, seed=0):
+    """instancer.cpp:233-372: list of 4x4 patch matrices (what AddInstance receives) and the patch scale."""
+    V, N, UV, Fc = np.asarray(V, F), np.asarray(N, F).copy(), np.asarray(UV, F), np.asarray(Fc, np.int64)
+    nv, nf = V.shape[0], Fc.shape[0]
+    ael = 0.0                                                          # igl::avg_edge_length
+    for f in Fc:
+        for k in range(3):
+            ael += float(np.linalg.norm(V[f[(k + 1) % 3]].astype(np.float64) - V[f[k]].astype(np.float64)))
+    ael /= 3 * nf
+    if scale <= 0:
+        scale = ael
+    T = np.zeros((nv, 3), F)
+    B = np.zeros((nv, 3), F)
+    for f in Fc:                                                       # :250-265
+        e0, e1 = V[f[1]] - V[f[0]], V[f[2]] - V[f[0]]
+        uv0, uv1 = UV[f[1]] - UV[f[0]], UV[f[2]] - UV[f[0]]
+        r = F(1) / (uv0[0] * uv1[1] - uv0[1] * uv1[0])
+        t = (e0 * uv1[1] - e1 * uv0[1]) * r
+        for k in range(3):
+            T[f[k]] += t
+    for i in range(nv):                                                # :266-277
+        N[i] = N[i] / np.linalg.norm(N[i])
+        n, t = N[i], T[i]
+        t = t - n * (n @ t)
+        t = t / np.linalg.norm(t)
+        T[i], B[i] = t, np.cross(n, t)
+    gen = MT19937(seed)
+    out = []
+    if patch_origins is not None and len(patch_origins) > 0:
+        for pt in np.asarray(patch_origins, F):                        # :299-345
+            radius, best, uvw = F(ael), -1, None
+            for j, f in enumerate(Fc):                                 # point query: strictly closer wins
+                cp, w = closest_point_on_triangle(pt, V[f[0]], V[f[1]], V[f[2]])
+                d = F(np.linalg.norm(pt - cp))
+                if d < radius:
+                    radius, best, uvw = d, j, w
+            assert best >= 0, "patch origin farther than the average edge length from the mesh"
+            f = Fc[best]
+            iN = N[f[0]] * uvw[0] + N[f[1]] * uvw[1] + N[f[2]] * uvw[2]
+            iT = T[f[0]] * uvw[0] + T[f[1]] * uvw[1] + T[f[2]] * uvw[2]
+            iN, iT = iN / np.linalg.norm(iN), iT / np.linalg.norm(iT)
+            iB = np.cross(iN, iT)
+            if jitter_amount > 0:
+                ang = F(F(jitter_amount) * uniform_real_float(gen, 0.0, np.pi))
+                iB = iB * np.cos(ang) + np.cross(iN, iB) * np.sin(ang) + iN * (iN @ iB) * (1 - np.cos(ang))
+            iT = np.cross(iB, iN)
+            M = np.eye(4, dtype=F)
+            M[:3, 0], M[:3, 1], M[:3, 2], M[:3, 3] = iT * F(scale), iB * F(scale), iN * F(scale), pt
+            out.append(M)
+    else:
+        seen = []
+        for i in range(nv):                                            # :350-372
+            if any(np.array_equal(V[i], s) for s in seen):
+                continue
+            tT, tB, tN = T[i], B[i], N[i]
+            if jitter_amount > 0:
+                ang = F(F(jitter_amount) * uniform_real_float(gen, 0.0, np.pi))
+                tB = tB * np.cos(ang) + np.cross(tN, tB) * np.sin(ang) + tN * (tN @ tB) * (1 - np.cos(ang))
+                tc = np.cross(tN, tB)
+                tT = (F(-1) if tT @ tc < 0 else F(1)) * tc
+            M = np.eye(4, dtype=F)
+            M[:3, 0], M[:3, 1], M[:3, 2], M[:3, 3] = tT * F(scale), tB * F(scale), tN * F(scale), V[i]
+            out.append(M)
+            seen.append(V[i])
+    return np.asarray(out, F), float(scale)

@@ -148,9 +148,9 @@ def test_edge_inputs():
     got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), 8, 0.05, seed=1)
     check_records(got, want, 4)
     assert not want["hit"][0] and want["hit"][1]
-    # refusals of what needs a mesh scene
-    with pytest.raises(NotImplementedError):
-        Instancer(B0, B1, mesh_path="meshes/carpet.obj")
+    # refusals: a mesh file that is not there, and what is not on the device yet
+    with pytest.raises((OSError, ValueError)):
+        Instancer(B0, B1, mesh_path="meshes/no_such_mesh.ply")
     with pytest.raises(NotImplementedError):
         Instancer(B0, B1, transformations=Ts.tolist(), cast_shadow_rays=True)
     with pytest.raises(NotImplementedError):
@@ -158,8 +158,7 @@ def test_edge_inputs():
     with pytest.raises(ValueError):
         Instancer(B0, B1)
     with pytest.raises(RuntimeError):
-        ops.instancer_get_model_input(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 17), 8, 0.05, inst.minv, inst.dirt,
-                                      inst.origins, B0, B1)
+        ops.instancer_get_model_input(torch.zeros(4, 3), torch.zeros(4, 3), torch.zeros(4, 17), 8, 0.05, inst.scene, B0, B1)
 
 
 def test_dense_tuple_and_instance_renderer():
@@ -203,3 +202,148 @@ def test_dense_tuple_and_instance_renderer():
     print("instancer e2e: max |d alpha|", np.abs(ga - wa).max(), "max |d color|", np.abs(gc - wc).max(), "psnr", psnr(gc, wc))
     assert np.abs(ga - wa).max() < 1e-2 and np.abs(gc - wc).max() < 1e-2, (np.abs(ga - wa).max(), np.abs(gc - wc).max())
     assert psnr(gc, wc) > 45
+
+
+# ------------------------------------------------------------------------------------------ acceleration grid, base mesh
+def big_carpet(n, seed, density_extent=1.45, base_n=1500, patch_scale=0.09):
+    """`n` patches at the areal density of the bench's 1 500-patch carpet (bench.carpet_patches), box of the carpet config."""
+    import bench
+    extent = density_extent * math.sqrt(n / base_n)
+    return bench.carpet_patches(n, seed=seed, extent=extent, patch_scale=patch_scale), extent
+
+
+def plane_mesh(n, extent, z=0.0, wobble=0.0, seed=0):
+    """(n+1)^2 vertex grid over [-extent, extent]^2 with normals and UVs: a procedural stand-in for the LFS meshes."""
+    rng = np.random.default_rng(seed)
+    xs = np.linspace(-extent, extent, n + 1)
+    X, Y = np.meshgrid(xs, xs, indexing="ij")
+    Z = z + wobble * np.sin(2.1 * X) * np.cos(1.7 * Y)
+    V = np.stack([X, Y, Z], -1).reshape(-1, 3).astype(np.float32)
+    dzdx, dzdy = wobble * 2.1 * np.cos(2.1 * X) * np.cos(1.7 * Y), -wobble * 1.7 * np.sin(2.1 * X) * np.sin(1.7 * Y)
+    N = np.stack([-dzdx, -dzdy, np.ones_like(X)], -1).reshape(-1, 3)
+    N = (N / np.linalg.norm(N, axis=-1, keepdims=True)).astype(np.float32)
+    UV = np.stack([(X + extent) / (2 * extent), (Y + extent) / (2 * extent)], -1).reshape(-1, 2).astype(np.float32)
+    idx = lambda i, j: i * (n + 1) + j
+    F = []
+    for i in range(n):
+        for j in range(n):
+            F += [[idx(i, j), idx(i + 1, j), idx(i + 1, j + 1)], [idx(i, j), idx(i + 1, j + 1), idx(i, j + 1)]]
+    return {"V": V, "F": np.asarray(F, np.int32), "N": N, "UV": UV}
+
+
+CB0, CB1 = [-1.4, -1.2, -.1], [1.2, 1.2, 1.8]
+
+
+def test_grid_equals_brute_force_and_oracle_at_20000_instances():
+    """The uniform grid must not change a single record: against the all-instances loop on every ray, and against the
+    oracle (which knows no grid) on a subset."""
+    from nerf_tex_b200.instancer import Instancer
+    Ts, extent = big_carpet(20000, seed=3)
+    R = 6000
+    rng = np.random.default_rng(4)
+    o = np.stack([rng.uniform(-extent, extent, R), rng.uniform(-extent, extent, R), rng.uniform(1.0, 3.0, R)], 1).astype(np.float32)
+    d = np.stack([rng.uniform(-1.2, 1.2, R), rng.uniform(-1.2, 1.2, R), np.full(R, -1.0)], 1).astype(np.float32)
+    d[::7, 2] = -0.05                                             # grazing rays cross many cells and many patches
+    d[::11] *= -1                                                 # some look away from the carpet
+    o[::13] = [0.0, 0.0, 0.05]                                    # origins inside the shell layer
+    prm = np.tile(np.array([[1, 1, 1, .1, 0, 0, 1]], np.float32), (R, 1))
+    kw = dict(b_0=CB0, b_1=CB1, textures=["", "", "", "", "light"], transformations=Ts, patch_scale=0.09,
+              instance_sampling_method="nearest")
+    grid, brute = Instancer(**kw), Instancer(use_grid=False, **kw)
+    assert grid.scene.inst_grid.cell_start and not brute.scene.inst_grid.cell_start
+    cu = lambda a: torch.as_tensor(a).cuda()
+    a = grid.get_model_input_csr(cu(o), cu(d), cu(prm), 1024, 0.002, seed=2)
+    b = brute.get_model_input_csr(cu(o), cu(d), cu(prm), 1024, 0.002, seed=2)
+    assert a["pts"].shape[0] > 100 * R / 4
+    for k in a:
+        assert torch.equal(a[k], b[k]), k
+    sub = np.concatenate([np.arange(0, 200), np.arange(0, R, 7)[:60], np.arange(0, R, 13)[:20]])
+    want = IO.get_model_input(o[sub], d[sub], prm[sub], 1024, 0.002, Ts, CB0, CB1, seed=2, light_dir_idx=4, method="nearest",
+                              patch_scale=0.09, ray_ids=sub)
+    got = grid.get_model_input_csr(cu(o[sub]), cu(d[sub]), cu(prm[sub]), 1024, 0.002, seed=2, ray_ids=cu(sub.astype(np.int32)))
+    check_records(got, want, len(sub))
+    assert want["n_samples"].max() > 300
+
+
+def test_ray_names_make_records_independent_of_chunking():
+    from nerf_tex_b200.instancer import Instancer
+    Ts = patch_grid(5, seed=1, tilt=0.3)
+    R = 900
+    o, d = rays_over(5, R, seed=3)
+    prm = np.zeros((R, 1), np.float32)
+    inst = Instancer(B0, B1, transformations=Ts.tolist(), instance_sampling_method="random")
+    cu = lambda a: torch.as_tensor(a).cuda()
+    ids = np.arange(R, dtype=np.int32)
+    whole = inst.get_model_input_csr(cu(o), cu(d), cu(prm), 40, 0.02, seed=9, ray_ids=cu(ids))
+    perm = np.random.default_rng(0).permutation(R)                 # any subset, any order
+    for part in (perm[:300], perm[300:]):
+        got = inst.get_model_input_csr(cu(o[part]), cu(d[part]), cu(prm[part]), 40, 0.02, seed=9, ray_ids=cu(ids[part]))
+        want = IO.get_model_input(o[part], d[part], prm[part], 40, 0.02, Ts, B0, B1, seed=9, ray_ids=ids[part])
+        check_records(got, want, len(part))
+    # and the whole call is the concatenation of its rays' records
+    want = IO.get_model_input(o, d, prm, 40, 0.02, Ts, B0, B1, seed=9)
+    check_records(whole, want, R)
+
+
+@pytest.mark.parametrize("use_grid", [True, False])
+def test_base_mesh_ends_rays(use_grid):
+    """Patches distributed on a wobbly plane (DistributeInstancesOnMesh), rays from above, from below and grazing:
+    box hits behind the first mesh hit are dropped, the mesh closes the open segment, rays that end on the mesh carry
+    alpha_last = 1 — all bit-exact against the oracle's brute-force watertight test."""
+    from nerf_tex_b200.instancer import Instancer
+    mesh = plane_mesh(24, 1.5, wobble=0.08)
+    rng = np.random.default_rng(5)
+    anchors = np.stack([rng.uniform(-1.3, 1.3, 300), rng.uniform(-1.3, 1.3, 300)], 1)
+    anchors = np.concatenate([anchors, 0.08 * np.sin(2.1 * anchors[:, :1]) * np.cos(1.7 * anchors[:, 1:])], 1).astype(np.float32)
+    inst = Instancer(CB0, CB1, textures=["", "light"], mesh=mesh, patch_origins=anchors, patch_scale=0.09, jitter_amount=1.0,
+                     instance_sampling_method="nearest", use_grid=use_grid)
+    assert inst.n_instances() == 300 and inst.scene.n_faces == 2 * 24 * 24
+    Ts = inst.transformations
+    R = 500
+    o = np.stack([rng.uniform(-1.6, 1.6, R), rng.uniform(-1.6, 1.6, R), rng.uniform(0.5, 2.0, R)], 1).astype(np.float32)
+    d = np.stack([rng.uniform(-1, 1, R), rng.uniform(-1, 1, R), np.full(R, -1.0)], 1).astype(np.float32)
+    o[::5, 2] *= -1                                               # from below: only the sliver of the boxes under the mesh
+    d[::5, 2] = 1.0
+    d[1::9, 2] = -0.03                                            # grazing
+    o[2::17] = [0.1, 0.2, 0.05]                                   # start inside the shell layer
+    prm = np.tile(np.array([[0.7, 0, 0, 1]], np.float32), (R, 1))
+    want = IO.get_model_input(o, d, prm, 256, 0.004, Ts, CB0, CB1, seed=1, light_dir_idx=1, method="nearest", patch_scale=0.09,
+                              mesh=(mesh["V"], mesh["F"]))
+    cu = lambda a: torch.as_tensor(a).cuda()
+    got = inst.get_model_input_csr(cu(o), cu(d), cu(prm), 256, 0.004, seed=1)
+    check_records(got, want, R)
+    hit = want["hit"]
+    assert np.array_equal(got["alpha_last"].cpu().numpy(), want["alpha_last"][hit]) and not got["color_last"].any()
+    below = np.arange(R) % 5 == 0
+    assert want["alpha_last"][below & hit].mean() > 0.8 and want["n_samples"][below].max() < 40       # 0.009 deep under the mesh
+    assert (want["alpha_last"][~below] == 1).mean() > 0.6 and (want["alpha_last"] == 0)[hit].any()
+    assert want["n_samples"][~below].max() > 30
+
+
+def test_instancer_from_ply_files_matches_distribute_oracle(tmp_path):
+    """mesh_path / patch_origins_path through the PLY reader (binary and ascii), placement against the loop oracle."""
+    from nerf_tex_b200 import ply
+    from nerf_tex_b200.instancer import Instancer
+    mesh = plane_mesh(6, 1.0, wobble=0.1)
+    rng = np.random.default_rng(2)
+    anchors = np.stack([rng.uniform(-.9, .9, 40), rng.uniform(-.9, .9, 40)], 1)
+    anchors = np.concatenate([anchors, 0.1 * np.sin(2.1 * anchors[:, :1]) * np.cos(1.7 * anchors[:, 1:]) + 0.01], 1).astype(np.float32)
+    ply.write_ply(str(tmp_path / "mesh.ply"), mesh["V"], mesh["F"], mesh["N"], mesh["UV"], binary=True)
+    ply.write_ply(str(tmp_path / "anchors.ply"), anchors, binary=False)
+    back = ply.read_ply(str(tmp_path / "mesh.ply"))
+    assert all(np.array_equal(back[k], mesh[k]) for k in ("V", "F", "N", "UV"))
+    assert np.allclose(ply.read_ply(str(tmp_path / "anchors.ply"))["V"], anchors, atol=0)
+    for jitter in (0.0, 1.0):
+        inst = Instancer(CB0, CB1, mesh_path=str(tmp_path / "mesh.ply"), patch_origins_path=str(tmp_path / "anchors.ply"),
+                         patch_scale=0.09, jitter_amount=jitter)
+        want, scale = IO.distribute_instances_on_mesh(mesh["V"], mesh["F"], mesh["N"], mesh["UV"], anchors, 0.09, jitter, seed=0)
+        assert scale == inst.patch_scale and inst.n_instances() == 40
+        np.testing.assert_allclose(inst.transformations, want, atol=2e-6)
+        R = want[:, :3, :3] / 0.09                                # orthonormal frames, third axis = surface normal
+        np.testing.assert_allclose(np.einsum("iab,iac->ibc", R, R), np.tile(np.eye(3), (40, 1, 1)), atol=1e-5)
+    # no anchor file: one patch per distinct vertex (:350-372); scale <= 0: the average edge length (:244)
+    inst = Instancer(CB0, CB1, mesh_path=str(tmp_path / "mesh.ply"), patch_origins_path=str(tmp_path / "missing.ply"),
+                     patch_scale=0.0, jitter_amount=0.5)
+    want, scale = IO.distribute_instances_on_mesh(mesh["V"], mesh["F"], mesh["N"], mesh["UV"], None, 0.0, 0.5, seed=0)
+    assert inst.n_instances() == 49 and abs(inst.patch_scale - scale) < 1e-7
+    np.testing.assert_allclose(inst.transformations, want, atol=2e-6)
