@@ -287,7 +287,11 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
 
 /* Replace C_Instancer::GetModelInput (instancer/src/instancer.cpp:751-1037, bound in instancer/instancer.pyx:38-54):
  * patch instances (explicit, or distributed on a base mesh by the host side), optional base mesh whose first hit ends a
- * ray (:804-814,:983,:1019-1023); no parameter textures, no shadow rays, no auxiliary-mesh shading.
+ * ray (:804-814,:983,:1019-1023), optional shadow rays (isShadowed :593-603 with the filter of :539-551: a sample whose
+ * ray towards the light enters a patch box through its top face, crosses a box's bottom face or hits a mesh triangle on
+ * its front side gets the ambient light direction (0, 0, -1), :572-575; looked up at min_shadow_samples /
+ * n_shadow_samples points per ray as in :863,:936-951,:992-1000; cast_shadow_rays != 0 adds 1600 B per ray to the
+ * workspace); no parameter textures, no auxiliary-mesh shading.
  *
  * ntx_instancer_scene — what CommitScene (instancer.cpp:420-424) leaves behind, all DEVICE pointers:
  *   minv[I,3,4]  rows 0..2 of the inverse instance transform (world -> patch), dirt[I,3,3] the row-normalised
@@ -335,17 +339,18 @@ typedef struct ntx_instancer_scene {
     ntx_scene_grid inst_grid;
     ntx_scene_grid tri_grid;
 } ntx_instancer_scene;
-int64_t ntx_instancer_workspace_bytes(int R);
+int64_t ntx_instancer_workspace_bytes(int R, int cast_shadow_rays);
 int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
                         const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size, int n_pts,
-                        uint32_t seed, int use_mean_distance, void* workspace, int32_t* n_samples, int32_t* hit,
-                        float* alpha_last, void* stream);
+                        uint32_t seed, int use_mean_distance, int cast_shadow_rays, void* workspace, int32_t* n_samples,
+                        int32_t* hit, float* alpha_last, void* stream);
 int ntx_instancer_march(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* parameters,
                         int n_param, int R, const ntx_instancer_scene* scene, float step_size, int n_pts, uint32_t seed,
                         int light_dir_idx, int light_strength_idx, int method, float blend_range, int use_mean_distance,
-                        const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts, float* dirs,
-                        float* params_out, float* dists, float* t, float* alpha_weight, int32_t* instance_id,
-                        void* stream);
+                        int cast_shadow_rays, int min_shadow_samples, int n_shadow_samples, const float* b_0,
+                        const float* b_1, const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts,
+                        float* dirs, float* params_out, float* dists, float* t, float* alpha_weight,
+                        int32_t* instance_id, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Whole ray chunk: K3 -> K1 -> K2 [-> K3 -> K1 -> K2]

@@ -58,7 +58,8 @@ struct MarchOut {
 // before the walk consumed it and the segment offset in force after it, plus the per-ray constants.
 struct RayInfo {
     float t_offset, last_dist;
-    int32_t n_steps, single;
+    int32_t n_steps;         // negative: the whole crossing is shorter than one step (one sample, :848-851)
+    float total;             // total in-shell length of the ray (shadow / texture sample counts, :863-864)
 };
 
 struct Workspace {
@@ -67,6 +68,7 @@ struct Workspace {
     float* segoff;       // [R][kMaxHits]
     RayInfo* info;       // [R]
     int32_t* n_hits;     // [R]
+    float2* seg;         // [R][kMaxHits] (only with shadow rays): (entry t, length) of the segment open after hit j
 };
 __host__ __device__ inline Workspace carve_workspace(void* base, int64_t R) {
     uint8_t* p = (uint8_t*)base;
@@ -75,7 +77,8 @@ __host__ __device__ inline Workspace carve_workspace(void* base, int64_t R) {
     w.step_at = (int32_t*)p; p += R * kMaxHits * 4;
     w.segoff = (float*)p;    p += R * kMaxHits * 4;
     w.info = (RayInfo*)p;    p += R * 16;
-    w.n_hits = (int32_t*)p;
+    w.n_hits = (int32_t*)p;  p += ((R * 4 + 15) / 16) * 16;
+    w.seg = (float2*)p;
     return w;
 }
 
@@ -121,10 +124,15 @@ struct OpenList {
 template <class Hits>
 __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint32_t seed, uint32_t ray, int use_mean,
                         float t_mesh, int32_t* __restrict__ step_at, float* __restrict__ segoff,
-                        RayInfo* __restrict__ info) {
+                        RayInfo* __restrict__ info, float2* __restrict__ seg) {
     OpenList act;
     // :801-827 total in-shell length
     float total = 0.0f, t_entry = 0.0f;
+    int seg_begin = 0;                                   // first hit of the segment being walked
+    auto close_segment = [&](int end, float len) {       // hits [seg_begin, end) see this segment behind them
+        if (seg)
+            for (int q = seg_begin; q < end; ++q) seg[q] = make_float2(t_entry, len);
+    };
     for (int j = 0; j < n_hits; ++j) {
         const uint64_t hj = hits(j);
         const float tt = hit_t(hj);
@@ -133,25 +141,35 @@ __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint
         if (f >= 0) {
             hits(j) = hj | ((uint64_t)f << 24);
             hits(f) = (hits(f) & ~((uint64_t)kNoPartner << 24)) | ((uint64_t)j << 24);
-            if (act.n == 0) total = __fadd_rn(total, __fsub_rn(tt, t_entry));
+            if (act.n == 0) {
+                const float len = __fsub_rn(tt, t_entry);
+                total = __fadd_rn(total, len);
+                close_segment(j, len);
+            }
         } else {
             hits(j) = hj | ((uint64_t)kNoPartner << 24);
-            if (was_empty) t_entry = tt;
+            if (was_empty) { t_entry = tt; seg_begin = j; }
         }
     }
-    if (t_mesh < CUDART_INF_F && act.n > 0) total = __fadd_rn(total, __fsub_rn(t_mesh, t_entry));
-    RayInfo ri = {0.f, 0.f, 0, 0};
+    if (t_mesh < CUDART_INF_F && act.n > 0) {
+        const float len = __fsub_rn(t_mesh, t_entry);
+        total = __fadd_rn(total, len);
+        close_segment(n_hits, len);
+    }
+    RayInfo ri = {0.f, 0.f, 0, 0.f};
+    ri.total = total;
     if (!(total > 0.0f)) { *info = ri; return 0; }
     const uint32_t necessary = (uint32_t)__fdiv_rn(total, step_size);             // :845
     int n_steps = (int)min(necessary, (uint32_t)n_pts);
     const float u = ray_uniform(seed, ray);
     if (n_steps == 0) {                                                           // :848-851
-        ri.single = 1; ri.last_dist = total; ri.t_offset = __fmul_rn(u, total); n_steps = 1;
+        ri.last_dist = total; ri.t_offset = __fmul_rn(u, total); n_steps = 1;
+        ri.n_steps = -1;
     } else {                                                                      // :852-861
         ri.last_dist = __fsub_rn(__fadd_rn(step_size, total), __fmul_rn((float)n_steps, step_size));
         ri.t_offset = __fmul_rn(u, step_size);
     }
-    ri.n_steps = n_steps;
+    if (ri.n_steps == 0) ri.n_steps = n_steps;
     *info = ri;
     // One loop whose iteration either emits (here: counts) the next sample or consumes the next hit — the
     // reference nests a sample loop inside the hit loop (:871-1003); same order of events.
@@ -430,9 +448,89 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     alpha_last[ray] = t_mesh < CUDART_INF_F ? 1.0f : 0.0f;                    // instancer.cpp:1019-1027
     const uint32_t rid = ray_ids ? (uint32_t)ray_ids[ray] : (uint32_t)ray;
     n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, rid, use_mean, t_mesh,
-                              ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray);
+                              ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray,
+                              ws.seg ? ws.seg + (size_t)ray * kMaxHits : nullptr);
     for (int k = 0; k < min(n_hits, kSmemHits); ++k) row[k] = H(k);     // with the partner indices walk_ray added
 }
+
+// isShadowed (instancer.cpp:593-603) with shadow_ray_filter_function (:539-551), in the operation order of
+// oracle/instancer_oracle.py::is_shadowed: a ray from `pt` along `dir` (not normalised), t in [0, 100], is blocked by the
+// top face of a patch box entered from above (patch frame), by the bottom face of a patch box from either side, or by a
+// mesh triangle hit on its front side.  Any-hit: the walk stops at the first blocker.
+struct ShadowBox { float b0[3], b1[3]; };
+__device__ bool shadow_blocked(const SceneDev& sc, const ShadowBox& bx, const float pt[3], const float dir[3]) {
+    bool blocked = false;
+    const float inv_dn = rsqrtf(fmaxf(dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2], 1e-30f));
+    const float dh[3] = {dir[0] * inv_dn, dir[1] * inv_dn, dir[2] * inv_dn};
+    auto test_instance = [&](int inst) {
+        if (sc.spheres) {
+            const float4 sp = __ldg(sc.spheres + inst);
+            const float cx = sp.x - pt[0], cy = sp.y - pt[1], cz = sp.z - pt[2];
+            const float cc = cx * cx + cy * cy + cz * cz;
+            const float along = cx * dh[0] + cy * dh[1] + cz * dh[2];
+            if (fmaf(-along, along, cc) > fmaf(1e-5f, cc, sp.w)) return;
+        }
+        const float4* Mp = reinterpret_cast<const float4*>(sc.minv) + 3 * (size_t)inst;
+        float ol[3], dl[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float4 m4 = __ldg(Mp + a);
+            const float M[3] = {m4.x, m4.y, m4.z};
+            ol[a] = __fadd_rn(dot3(M, pt), m4.w);
+            dl[a] = dot3(M, dir);
+        }
+        const float inv = __fdiv_rn(1.0f, dl[2]);
+#pragma unroll
+        for (int face = 0; face < 2; ++face) {                                 // top (from above only), bottom
+            if (face == 0 ? !(dl[2] < 0.0f) : !(dl[2] != 0.0f)) continue;
+            const float t = __fmul_rn(__fsub_rn(face == 0 ? bx.b1[2] : bx.b0[2], ol[2]), inv);
+            const float x = __fadd_rn(ol[0], __fmul_rn(t, dl[0])), y = __fadd_rn(ol[1], __fmul_rn(t, dl[1]));
+            if (t >= 0.0f && t <= kTFar && x >= bx.b0[0] && x <= bx.b1[0] && y >= bx.b0[1] && y <= bx.b1[1]) blocked = true;
+        }
+    };
+    if (sc.ig.start) {
+        grid_walk(sc.ig, pt, dir, 0.0f, kTFar, [&](int cell, float) {
+            const int e = __ldg(sc.ig.start + cell + 1);
+            for (int q = __ldg(sc.ig.start + cell); q < e && !blocked; ++q) test_instance(__ldg(sc.ig.items + q));
+            return !blocked;
+        });
+    } else {
+        for (int inst = 0; inst < sc.n_inst && !blocked; ++inst) test_instance(inst);
+    }
+    if (blocked || sc.n_faces == 0 || (dir[0] == 0.0f && dir[1] == 0.0f && dir[2] == 0.0f)) return blocked;
+    const RayFrame rf = ray_frame(dir);
+    auto test_face = [&](int face) {
+        float t, u, v;
+        const int32_t* fp = sc.mesh_f + 3 * (size_t)face;
+        if (!tri_hit(rf, pt, sc.mesh_v, fp, t, u, v)) return;
+        float P[3][3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) P[k][a] = __ldg(sc.mesh_v + 3 * (size_t)__ldg(fp + k) + a);
+        const float e1[3] = {__fsub_rn(P[1][0], P[0][0]), __fsub_rn(P[1][1], P[0][1]), __fsub_rn(P[1][2], P[0][2])};
+        const float e2[3] = {__fsub_rn(P[2][0], P[0][0]), __fsub_rn(P[2][1], P[0][1]), __fsub_rn(P[2][2], P[0][2])};
+        const float ng[3] = {__fsub_rn(__fmul_rn(e1[1], e2[2]), __fmul_rn(e1[2], e2[1])),
+                             __fsub_rn(__fmul_rn(e1[2], e2[0]), __fmul_rn(e1[0], e2[2])),
+                             __fsub_rn(__fmul_rn(e1[0], e2[1]), __fmul_rn(e1[1], e2[0]))};
+        if (dot3(ng, dir) < 0.0f) blocked = true;
+    };
+    if (sc.tg.start) {
+        grid_walk(sc.tg, pt, dir, 0.0f, kTFar, [&](int cell, float) {
+            const int e = __ldg(sc.tg.start + cell + 1);
+            for (int q = __ldg(sc.tg.start + cell); q < e && !blocked; ++q) test_face(__ldg(sc.tg.items + q));
+            return !blocked;
+        });
+    } else {
+        for (int face = 0; face < sc.n_faces && !blocked; ++face) test_face(face);
+    }
+    return blocked;
+}
+
+struct ShadowArgs {
+    int enabled, min_samples, n_samples, n_pts;
+    ShadowBox box;
+};
 
 // Pass 2, one thread per sample: every store of a warp is contiguous.  The sample finds its ray (binary search in
 // ray_ptr) and the hit interval it was emitted in (binary search in the ray's step_at row), replays the hits before it
@@ -440,10 +538,12 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
 __global__ void __launch_bounds__(256)
 instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const int32_t* __restrict__ ray_ids,
                       const float* __restrict__ params,
-                      int n_param, int R, const float* __restrict__ minv, const float* __restrict__ dirt,
-                      const float* __restrict__ origins, float step_size, uint32_t seed, int light_idx, int strength_idx,
+                      int n_param, int R, const SceneDev sc, float step_size, uint32_t seed, int light_idx, int strength_idx,
                       int method, float blend_range, int use_mean, Workspace ws, const int64_t* __restrict__ ray_ptr, int64_t T,
-                      MarchOut out) {
+                      MarchOut out, const ShadowArgs sh) {
+    const float* __restrict__ minv = sc.minv;
+    const float* __restrict__ dirt = sc.dirt;
+    const float* __restrict__ origins = sc.origins;
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= T) return;
     int lo = 0, hi = R;                                   // last ray with ray_ptr[ray] <= k
@@ -571,7 +671,30 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
     if (light_idx >= 0) {                                                     // :929-956
         // directional light: the parameter is the direction; point light ('point' texture entry): it is the position,
         // the direction becomes (position - sample) and the strength parameter the received radiance (:572-590)
-        float lv[3] = {__ldg(prm + light_idx), __ldg(prm + light_idx + 1), __ldg(prm + light_idx + 2)};
+        const float raw[3] = {__ldg(prm + light_idx), __ldg(prm + light_idx + 1), __ldg(prm + light_idx + 2)};
+        bool shadowed = false;
+        if (sh.enabled) {                                                     // :863, :936-951
+            const uint32_t n_shadow = max((uint32_t)sh.min_samples, (uint32_t)__fmul_rn((float)sh.n_samples, ri.total));
+            float q[3] = {pt[0], pt[1], pt[2]};
+            if (n_shadow < (uint32_t)sh.n_pts) {
+                // occlusion is sampled at points spaced evenly along the segment (:992-1000); the nearer neighbour counts
+                const float2 sg = ws.seg[(size_t)ray * kMaxHits + (j > 0 ? j - 1 : 0)];
+                const uint32_t n_seg = max((uint32_t)sh.min_samples,
+                                           (uint32_t)__fdiv_rn(__fmul_rn((float)n_shadow, sg.y), ri.total));
+                const float sstep = __fdiv_rn(sg.y, (float)(n_seg - 1u));
+                auto t_at = [&](int kk) { return __fadd_rn(sg.x, __fmul_rn((float)kk, sstep)); };
+                int kk = max(1, (int)ceilf((t_pt - sg.x) / sstep));
+                if (!(kk < (1 << 24))) kk = 1;                                // degenerate step: walk from the start
+                while (kk > 1 && !(t_pt > t_at(kk - 1))) --kk;
+                for (int guard = 0; t_pt > t_at(kk) && guard < (1 << 20); ++guard) ++kk;
+                const float t0 = kk == 1 ? sg.x : t_at(kk - 1);
+                const float tq = (__fdiv_rn(__fsub_rn(t_pt, t0), sstep) >= 0.5f) ? t_at(kk) : t0;
+#pragma unroll
+                for (int a = 0; a < 3; ++a) q[a] = __fadd_rn(o[a], __fmul_rn(tq, d[a]));
+            }
+            shadowed = shadow_blocked(sc, sh.box, q, raw);
+        }
+        float lv[3] = {raw[0], raw[1], raw[2]};
         if (strength_idx >= 0) {
 #pragma unroll
             for (int a = 0; a < 3; ++a) lv[a] = __fsub_rn(lv[a], pt[a]);
@@ -579,13 +702,19 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
             out.params[k * n_param + strength_idx] =
                 __fdiv_rn(__ldg(prm + strength_idx), __fadd_rn(__fmul_rn(12.566370614359172f, dsq), 1e-6f));
         }
-        const float ln = norm3(lv);
+        if (shadowed) {                                                       // ambient only (:572-575)
+            out.params[k * n_param + light_idx] = 0.0f;
+            out.params[k * n_param + light_idx + 1] = 0.0f;
+            out.params[k * n_param + light_idx + 2] = -1.0f;
+        } else {
+            const float ln = norm3(lv);
 #pragma unroll
-        for (int a = 0; a < 3; ++a) lv[a] = __fdiv_rn(lv[a], ln);
+            for (int a = 0; a < 3; ++a) lv[a] = __fdiv_rn(lv[a], ln);
 #pragma unroll
-        for (int a = 0; a < 3; ++a) out.params[k * n_param + light_idx + a] = dot3(Dt + 3 * a, lv);
+            for (int a = 0; a < 3; ++a) out.params[k * n_param + light_idx + a] = dot3(Dt + 3 * a, lv);
+        }
     }
-    out.dists[k] = (ri.single || step == ri.n_steps - 1) ? ri.last_dist : step_size;
+    out.dists[k] = (ri.n_steps < 0 || step == ri.n_steps - 1) ? ri.last_dist : step_size;
     out.t[k] = t_mu;
     out.weight[k] = w;
     out.inst[k] = (int32_t)sel;
@@ -593,9 +722,9 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
 
 }  // namespace
 
-NTX_API int64_t ntx_instancer_workspace_bytes(int R) {
+NTX_API int64_t ntx_instancer_workspace_bytes(int R, int cast_shadow_rays) {
     if (R < 0) return -1;
-    return (int64_t)R * (kMaxHits * 16 + 16 + 4);
+    return (int64_t)R * (kMaxHits * 16 + 16 + 4) + 16 + (cast_shadow_rays ? (int64_t)R * kMaxHits * 8 : 0);
 }
 
 static int check_scene(const ntx_instancer_scene* s, SceneDev* out) {
@@ -622,8 +751,8 @@ static int check_scene(const ntx_instancer_scene* s, SceneDev* out) {
 
 NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
                                 const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size,
-                                int n_pts, uint32_t seed, int use_mean_distance, void* workspace, int32_t* n_samples,
-                                int32_t* hit, float* alpha_last, void* stream) {
+                                int n_pts, uint32_t seed, int use_mean_distance, int cast_shadow_rays, void* workspace,
+                                int32_t* n_samples, int32_t* hit, float* alpha_last, void* stream) {
     NTX_REQUIRE(R >= 0 && n_pts >= 1 && step_size > 0.0f, "instancer_trace: bad arguments");
     SceneDev sc;
     int rc = check_scene(scene, &sc);
@@ -633,9 +762,11 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const 
     NTX_REQUIRE(((uintptr_t)workspace & 15) == 0, "instancer_trace: the workspace must be 16-byte aligned");
     const size_t smem = (size_t)kSmemHits * kTraceThreads * sizeof(uint64_t) + (size_t)kMailbox * kTraceThreads * sizeof(uint32_t);
     NTX_CUDA(cudaFuncSetAttribute(instancer_trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    Workspace wsp = carve_workspace(workspace, R);
+    if (!cast_shadow_rays) wsp.seg = nullptr;            // that part of the workspace is not there
     instancer_trace_kernel<<<(R + kTraceThreads - 1) / kTraceThreads, kTraceThreads, smem, (cudaStream_t)stream>>>(
         rays_o, rays_d, ray_ids, R, sc, b_0[0], b_0[1], b_0[2], b_1[0], b_1[1], b_1[2], step_size, n_pts, seed,
-        use_mean_distance, carve_workspace(workspace, R), n_samples, hit, alpha_last);
+        use_mean_distance, wsp, n_samples, hit, alpha_last);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
@@ -643,8 +774,9 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const 
 NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* parameters,
                                 int n_param, int R, const ntx_instancer_scene* scene, float step_size, int n_pts,
                                 uint32_t seed, int light_dir_idx, int light_strength_idx, int method, float blend_range,
-                                int use_mean_distance, const void* workspace, const int64_t* ray_ptr, int64_t T, float* pts,
-                                float* dirs, float* params_out, float* dists, float* t, float* alpha_weight,
+                                int use_mean_distance, int cast_shadow_rays, int min_shadow_samples, int n_shadow_samples,
+                                const float* b_0, const float* b_1, const void* workspace, const int64_t* ray_ptr, int64_t T,
+                                float* pts, float* dirs, float* params_out, float* dists, float* t, float* alpha_weight,
                                 int32_t* instance_id, void* stream) {
     NTX_REQUIRE(R >= 0 && T >= 0 && n_param >= 0 && n_param <= 16, "instancer_march: bad arguments (at most 16 parameters)");
     NTX_REQUIRE(light_dir_idx < 0 || light_dir_idx + 3 <= n_param, "instancer_march: light direction index out of range");
@@ -658,12 +790,18 @@ NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const 
     NTX_REQUIRE(rays_o && rays_d && (n_param == 0 || parameters) && workspace && ray_ptr, "instancer_march: null pointer");
     NTX_REQUIRE(pts && dirs && (n_param == 0 || params_out) && dists && t && alpha_weight && instance_id,
                 "instancer_march: null output pointer");
-    (void)n_pts;
+    ShadowArgs sh;
+    memset(&sh, 0, sizeof(sh));
+    if (cast_shadow_rays && light_dir_idx >= 0) {        // :936 shadows only matter where a light is mapped
+        NTX_REQUIRE(b_0 && b_1 && min_shadow_samples >= 0 && n_shadow_samples >= 0, "instancer_march: shadow rays need b_0 / b_1 and sample counts");
+        sh.enabled = 1; sh.min_samples = min_shadow_samples; sh.n_samples = n_shadow_samples; sh.n_pts = n_pts;
+        for (int a = 0; a < 3; ++a) { sh.box.b0[a] = b_0[a]; sh.box.b1[a] = b_1[a]; }
+    }
     MarchOut out = {pts, dirs, params_out, dists, t, alpha_weight, instance_id};
     instancer_emit_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        rays_o, rays_d, ray_ids, parameters, n_param, R, sc.minv, sc.dirt, sc.origins, step_size, seed, light_dir_idx,
+        rays_o, rays_d, ray_ids, parameters, n_param, R, sc, step_size, seed, light_dir_idx,
         light_strength_idx, method, blend_range, use_mean_distance, carve_workspace(const_cast<void*>(workspace), R), ray_ptr,
-        T, out);
+        T, out, sh);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }

@@ -126,8 +126,8 @@ class Instancer:
     `transformations` (AddInstance, instancer.cpp:125-141) and / or patches distributed on a base mesh
     (`mesh_path`, `patch_origins_path`, `patch_scale`, `jitter_amount`: DistributeInstancesOnMesh, :233-391), whose
     first hit ends a ray with an opaque black last sample (:804-814,:1019-1023).  Rays walk uniform grids over the patch
-    boxes and the mesh triangles (scene_grid.py) where the reference walks Embree BVHs.  Still refused: shadow rays,
-    image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes.
+    boxes and the mesh triangles (scene_grid.py) where the reference walks Embree BVHs; shadow rays towards the light
+    (`cast_shadow_rays`, :593-603) walk the same grids.  Still refused: image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes.
     `mesh` = {'V','F','N','UV'} arrays may be given in place of `mesh_path` (procedural meshes), `patch_origins` [A,3]
     in place of `patch_origins_path`."""
 
@@ -138,8 +138,8 @@ class Instancer:
                  auxiliary_meshes=[], transformation_export_path=None, *, seed: int = 0, device=None, mesh=None,
                  patch_origins=None, use_grid: bool = True) -> None:
         assert instance_sampling_method in ('random', 'nearest', 'nearest_blend')      # instancer.pyx:12
-        if cast_shadow_rays:
-            raise NotImplementedError("Instancer: shadow rays (instancer.cpp:593-603) are not implemented on the device yet")
+        self.cast_shadow_rays = bool(cast_shadow_rays)
+        self.min_shadow_samples, self.n_shadow_samples = int(min_shadow_samples), int(n_shadow_samples)
         if auxiliary_meshes:
             raise NotImplementedError("Instancer: auxiliary meshes (AddMesh / shadeMesh, instancer.cpp:393-418,716-744) are "
                                       "not implemented on the device yet")
@@ -250,7 +250,8 @@ class Instancer:
                                              seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
                                              use_mean_distance=self.use_mean_distance, light_strength_idx=self.light_strength_idx,
                                              blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)),   # fp32 product, instancer.cpp:696
-                                             ray_ids=ray_ids)
+                                             ray_ids=ray_ids, cast_shadow_rays=self.cast_shadow_rays,
+                                             min_shadow_samples=self.min_shadow_samples, n_shadow_samples=self.n_shadow_samples)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

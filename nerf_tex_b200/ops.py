@@ -230,7 +230,8 @@ def rays_from_camera(image_plane_loc, height: int, width: int, focal: float, c2w
 
 def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size: float, scene, b_0, b_1, *,
                               seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False,
-                              light_strength_idx: int = -1, blend_range: float = 0.0, ray_ids=None):
+                              light_strength_idx: int = -1, blend_range: float = 0.0, ray_ids=None,
+                              cast_shadow_rays: bool = False, min_shadow_samples: int = 4, n_shadow_samples: int = 512):
     """Two-pass shell instancer (instancer/src/instancer.cpp:751-1037): trace + count, prefix sum, march.
     `scene`: _lib.InstancerScene (device pointers kept alive by the caller).  `ray_ids` [R] int32: the rays' names for
     the random draws.  Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box or
@@ -247,10 +248,11 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     n_samples = torch.empty(R, dtype=torch.int32, device=dev)
     hit = torch.empty(R, dtype=torch.int32, device=dev)
     alpha_last_all = torch.empty(R, dtype=torch.float32, device=dev)
-    ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R)), 16), dtype=torch.uint8, device=dev)
+    shadows = int(bool(cast_shadow_rays) and light_dir_idx >= 0)
+    ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R, shadows)), 16), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), ptr(ray_ids), R, C.byref(scene), b0, b1,
-                                      float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)),
+                                      float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)), shadows,
                                       ptr(ws), ptr(n_samples), ptr(hit), ptr(alpha_last_all), stream_ptr()))
         ray_ptr_all = torch.zeros(R + 1, dtype=torch.int64, device=dev)
         torch.cumsum(n_samples, 0, out=ray_ptr_all[1:])
@@ -262,7 +264,8 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
         check(lib.ntx_instancer_march(ptr(rays_o), ptr(rays_d), ptr(ray_ids), ptr(parameters), p, R, C.byref(scene),
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(light_dir_idx), int(light_strength_idx),
                                       int(method), float(blend_range),
-                                      int(bool(use_mean_distance)), ptr(ws), ptr(ray_ptr_all), T, ptr(out["pts"]), ptr(out["dirs"]),
+                                      int(bool(use_mean_distance)), shadows, int(min_shadow_samples), int(n_shadow_samples), b0, b1,
+                                      ptr(ws), ptr(ray_ptr_all), T, ptr(out["pts"]), ptr(out["dirs"]),
                                       ptr(out["params"]), ptr(out["dists"]), ptr(out["t"]), ptr(out["alpha_weight"]),
                                       ptr(out["instance_id"]), stream_ptr()))
     H = ray_index.shape[0]

@@ -136,14 +136,27 @@ def ray_frame(d):
     return kx, ky, kz, Sx, Sy, Sz
 
 
+def mesh_hits(o, d, V, Fc, want_tuv=False):
+    """Mask of the triangles the ray hits with t in [0, 100] (watertight test)."""
+    return _mesh_test(np.asarray(o, F), np.asarray(d, F), V, Fc)[0]
+
+
 def mesh_first_hit(o, d, V, Fc):
     """Nearest hit of the ray with the triangles (V[n,3] fp32, Fc[m,3] int) for t in [0, 100]:
     (t, face, u, v) with u, v the barycentric weights of the face's 2nd and 3rd vertex, or None."""
     o, d = np.asarray(o, F), np.asarray(d, F)
     if not np.any(d != 0):
         return None
+    hit, t, u, v = _mesh_test(o, d, V, Fc)
+    cand = np.nonzero(hit)[0]
+    if cand.shape[0] == 0:
+        return None
+    best = cand[np.lexsort((cand, t[cand]))[0]]                        # smallest t, then smallest face index
+    return F(t[best]), int(best), F(u[best]), F(v[best])
+
+
+def _mesh_test(o, d, V, Fc):
     kx, ky, kz, Sx, Sy, Sz = ray_frame(d)
-    A, B, C = (V[Fc[:, k]] - o[None, :]).astype(F) if False else None, None, None
     P = [(V[Fc[:, k]] - o[None, :]).astype(F) for k in range(3)]       # vertices relative to the origin
     X = [(p[:, kx] - (Sx * p[:, kz]).astype(F)).astype(F) for p in P]
     Y = [(p[:, ky] - (Sy * p[:, kz]).astype(F)).astype(F) for p in P]
@@ -167,11 +180,42 @@ def mesh_first_hit(o, d, V, Fc):
         u = (Vv / det).astype(F)
         v = (W / det).astype(F)
     miss |= ~((t >= 0) & (t <= T_FAR))
-    cand = np.nonzero(~miss)[0]
-    if cand.shape[0] == 0:
-        return None
-    best = cand[np.lexsort((cand, t[cand]))[0]]                        # smallest t, then smallest face index
-    return F(t[best]), int(best), F(u[best]), F(v[best])
+    return ~miss, t, u, v
+
+
+def is_shadowed(pt, direction, minv, b0, b1, mesh=None):
+    """isShadowed (instancer.cpp:593-603) with shadow_ray_filter_function (:539-551): a ray from `pt` along `direction`
+    (not normalised), t in [0, 100], is blocked by
+      * the TOP face of a patch box (quad 4 of createAABB, :117: z = b_1[2]) entered from outside, i.e. travelling
+        towards -z in the patch frame,
+      * the BOTTOM face of a patch box (quad 1: z = b_0[2]) from either side,
+      * a mesh triangle hit on its front side (direction . Ng < 0, Ng = (v1 - v0) x (v2 - v0)).
+    Side faces and top faces left from inside let the ray pass."""
+    pt, direction = np.asarray(pt, F), np.asarray(direction, F)
+    ol = _vdot3(minv[:, :, :3], pt, minv[:, :, 3])
+    dl = _vdot3(minv[:, :, :3], direction)
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+        inv = (F(1.0) / dl[:, 2]).astype(F)
+        for plane, need_down in ((b1[2], True), (b0[2], False)):
+            t = ((plane - ol[:, 2]).astype(F) * inv).astype(F)
+            x = (ol[:, 0] + (t * dl[:, 0]).astype(F)).astype(F)
+            y = (ol[:, 1] + (t * dl[:, 1]).astype(F)).astype(F)
+            ok = (t >= 0) & (t <= T_FAR) & (x >= b0[0]) & (x <= b1[0]) & (y >= b0[1]) & (y <= b1[1])
+            ok &= (dl[:, 2] < 0) if need_down else (dl[:, 2] != 0)
+            if ok.any():
+                return True
+    if mesh is not None and np.any(direction != 0):
+        V, Fc = mesh
+        hit = mesh_hits(pt, direction, V, Fc)
+        if hit.any():
+            P = V[Fc[hit]]
+            e1, e2 = (P[:, 1] - P[:, 0]).astype(F), (P[:, 2] - P[:, 0]).astype(F)
+            ng = np.stack([((e1[:, 1] * e2[:, 2]).astype(F) - (e1[:, 2] * e2[:, 1]).astype(F)).astype(F),
+                           ((e1[:, 2] * e2[:, 0]).astype(F) - (e1[:, 0] * e2[:, 2]).astype(F)).astype(F),
+                           ((e1[:, 0] * e2[:, 1]).astype(F) - (e1[:, 1] * e2[:, 0]).astype(F)).astype(F)], -1)
+            if (_vdot3(ng, direction) < 0).any():
+                return True
+    return False
 
 
 def mean_distance(mu, hw):
@@ -182,7 +226,7 @@ def mean_distance(mu, hw):
 
 def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformations, b_0, b_1, *, seed=0,
                     light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1, patch_scale=1.0,
-                    mesh=None, ray_ids=None):
+                    mesh=None, ray_ids=None, cast_shadow_rays=False, min_shadow_samples=4, n_shadow_samples=512):
     """Returns the CSR form over ALL rays: n_samples[R], hit[R], alpha_last[R], color_last[R,3] and per-sample
     records.  `mesh` = (V[n,3], F[m,3]): the base mesh the patches sit on (a ray ends at its first hit).  `ray_ids`:
     the identity of every ray for the random draws (default: its index in this call), so that a frame cut into chunks
@@ -213,18 +257,21 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
             alpha_last[i] = F(1)
         # :801-827 total in-shell length
         active, total, t_entry = set(), F(0), F(0)
+        segment_lengths = []
         for tt, inst in hits:
             tt = F(tt)
             if inst in active:
                 active.discard(inst)
                 if not active:
                     total = F(total + F(tt - t_entry))
+                    segment_lengths.append(F(tt - t_entry))
             else:
                 if not active:
                     t_entry = tt
                 active.add(inst)
         if mh is not None and active:                               # :805-810 the mesh closes the open segment
             total = F(total + F(mh[0] - t_entry))
+            segment_lengths.append(F(mh[0] - t_entry))
         if not (total > 0):
             continue
         necessary = int(F(total / step_size))                       # :845
@@ -249,6 +296,15 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         active = set()
         segment_offset, cleared, t_entry, step = F(0), F(0), F(0), 0
         emitted = 0
+        # shadow rays (:863, :936-952, :992-1000): with fewer shadow samples than marching samples the occlusion is
+        # looked up at points spaced evenly along each segment and the nearer of the two neighbours is used
+        total_len = total
+        shadow_on = cast_shadow_rays and light_dir_idx >= 0
+        n_shadow = max(int(min_shadow_samples), int(F(F(n_shadow_samples) * total_len))) if shadow_on else 0
+        shadow_interp = shadow_on and n_shadow < n_pts
+        raw_light = parameters[i, light_dir_idx:light_dir_idx + 3].copy() if light_dir_idx >= 0 else None
+        seg_l, sh_step, sh_entry = 0, F(0), F(0)
+        occluded = lambda tq: is_shadowed([F(o[a] + F(F(tq) * d[a])) for a in range(3)], raw_light, minv, b0, b1, mesh)
         for tt, inst in hits + ([(float(mh[0]), -1)] if mh is not None else []):
             tt = F(tt)
             if step >= n_steps:
@@ -293,7 +349,23 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 recs["pts"].append([_dot3(M[a, :3], pt, M[a, 3]) for a in range(3)])        # getPt :556-558
                 recs["dirs"].append([_dot3(dirt[sel][a], dn) for a in range(3)])           # getDir :561-563
                 prm = parameters[i].copy()
-                if light is not None:
+                shadowed = False
+                if shadow_interp:                                   # :937-948 nearest of the two shadow samples around t_pt
+                    k = 1
+                    while t_pt > F(sh_entry + F(F(k) * sh_step)):
+                        k += 1
+                    t0 = sh_entry if k == 1 else F(sh_entry + F(F(k - 1) * sh_step))
+                    t1 = F(sh_entry + F(F(k) * sh_step))
+                    shadowed = occluded(t1 if F(F(t_pt - t0) / sh_step) >= F(0.5) else t0)
+                elif shadow_on:                                     # :949-951 at the sample itself
+                    shadowed = is_shadowed(pt, raw_light, minv, b0, b1, mesh)
+                if shadowed:                                        # :572-575 ambient only
+                    prm[light_dir_idx:light_dir_idx + 3] = [F(0), F(0), F(-1)]
+                    if light_strength_idx >= 0:                     # :954-956 the strength is mapped regardless
+                        lv = [F(parameters[i, light_dir_idx + a] - pt[a]) for a in range(3)]
+                        dsq = F(F(F(lv[0] * lv[0]) + F(lv[1] * lv[1])) + F(lv[2] * lv[2]))
+                        prm[light_strength_idx] = F(parameters[i, light_strength_idx] / F(F(F(12.566370614359172) * dsq) + F(1e-6)))
+                elif light is not None:
                     prm[light_dir_idx:light_dir_idx + 3] = [_dot3(dirt[sel][a], light) for a in range(3)]
                 elif light_dir_idx >= 0:                            # point light: :572-590, :954-956
                     lv = [F(parameters[i, light_dir_idx + a] - pt[a]) for a in range(3)]
@@ -320,6 +392,11 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 if not active:
                     segment_offset = F(tt - cleared)
                     t_entry = tt
+                    if shadow_interp:                               # :992-1000
+                        seg_len = segment_lengths[seg_l]
+                        n_seg = max(int(min_shadow_samples), int(F(F(F(n_shadow) * seg_len) / total_len)))
+                        sh_step, sh_entry = F(seg_len / F(n_seg - 1)), t_entry
+                    seg_l += 1
                 active.add(inst)
         n_samples[i] = emitted
     p = parameters.shape[1]

@@ -152,7 +152,7 @@ def test_edge_inputs():
     with pytest.raises((OSError, ValueError)):
         Instancer(B0, B1, mesh_path="meshes/no_such_mesh.ply")
     with pytest.raises(NotImplementedError):
-        Instancer(B0, B1, transformations=Ts.tolist(), cast_shadow_rays=True)
+        Instancer(B0, B1, transformations=Ts.tolist(), auxiliary_meshes=[("meshes/table.ply", "")])
     with pytest.raises(NotImplementedError):
         Instancer(B0, B1, transformations=Ts.tolist(), textures=["textures/height.png"])
     with pytest.raises(ValueError):
@@ -347,3 +347,49 @@ def test_instancer_from_ply_files_matches_distribute_oracle(tmp_path):
     want, scale = IO.distribute_instances_on_mesh(mesh["V"], mesh["F"], mesh["N"], mesh["UV"], None, 0.0, 0.5, seed=0)
     assert inst.n_instances() == 49 and abs(inst.patch_scale - scale) < 1e-7
     np.testing.assert_allclose(inst.transformations, want, atol=2e-6)
+
+
+def shadow_scene(seed=7):
+    """Patches on a hilly plane (the plane is the base mesh) plus a few patches floating above it: with a low sun the
+    hills (front faces of the mesh), the floating boxes' bottom faces and tilted boxes' top faces cast shadows."""
+    mesh = plane_mesh(16, 1.5, wobble=0.15)
+    rng = np.random.default_rng(seed)
+    xy = rng.uniform(-1.3, 1.3, (200, 2))
+    anchors = np.concatenate([xy, 0.15 * np.sin(2.1 * xy[:, :1]) * np.cos(1.7 * xy[:, 1:])], 1).astype(np.float32)
+    floating = np.tile(np.eye(4), (25, 1, 1))
+    floating[:, :3, :3] *= 0.09
+    floating[:, :3, 3] = np.concatenate([rng.uniform(-1.2, 1.2, (25, 2)), rng.uniform(0.3, 0.5, (25, 1))], 1)
+    return mesh, anchors, floating
+
+
+@pytest.mark.parametrize("light,use_grid,n_shadow", [("light", True, 64), ("point", True, 64), ("light", False, 4000)])
+def test_shadow_rays(light, use_grid, n_shadow):
+    """cast_shadow_rays (instancer.cpp:593-603, filter :539-551, sampling :863,:936-951,:992-1000): interpolated shadow
+    samples (n_shadow < n_pts) and the per-sample path (n_shadow >= n_pts); directional and point light.  Bit-exact."""
+    from nerf_tex_b200.instancer import Instancer
+    mesh, anchors, floating = shadow_scene()
+    inst = Instancer(CB0, CB1, textures=["", light], transformations=floating, mesh=mesh, patch_origins=anchors, patch_scale=0.09,
+                     jitter_amount=1.0, instance_sampling_method="nearest", use_grid=use_grid, cast_shadow_rays=True,
+                     min_shadow_samples=8, n_shadow_samples=n_shadow)
+    rng = np.random.default_rng(8)
+    R = 300
+    o = np.stack([rng.uniform(-1.4, 1.4, R), rng.uniform(-1.4, 1.4, R), rng.uniform(0.7, 2.0, R)], 1).astype(np.float32)
+    d = np.stack([rng.uniform(-1, 1, R), rng.uniform(-1, 1, R), np.full(R, -1.0)], 1).astype(np.float32)
+    if light == "light":
+        prm = np.tile(np.array([[0.7, 0.95, 0.1, 0.08]], np.float32), (R, 1))          # low sun
+        kw = dict(light_dir_idx=1)
+    else:
+        prm = np.tile(np.array([[0.7, 3.0, 1.2, 0.3, 0.1]], np.float32), (R, 1))       # strength, position
+        kw = dict(light_dir_idx=2, light_strength_idx=1)
+    n_pts = 128
+    ref = dict(seed=3, method="nearest", patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), **kw)
+    want = IO.get_model_input(o, d, prm, n_pts, 0.004, inst.transformations, CB0, CB1, cast_shadow_rays=True,
+                              min_shadow_samples=8, n_shadow_samples=n_shadow, **ref)
+    cu = lambda a: torch.as_tensor(a).cuda()
+    got = inst.get_model_input_csr(cu(o), cu(d), cu(prm), n_pts, 0.004, seed=3)
+    check_records(got, want, R)
+    li = kw["light_dir_idx"]
+    dark = np.all(want["params"][:, li:li + 3] == np.array([0, 0, -1], np.float32), -1)
+    assert 0.05 < dark.mean() < 0.95, dark.mean()                                      # both outcomes occur
+    unshadowed = IO.get_model_input(o, d, prm, n_pts, 0.004, inst.transformations, CB0, CB1, **ref)
+    assert np.array_equal(unshadowed["params"][~dark], want["params"][~dark])          # lit samples are untouched

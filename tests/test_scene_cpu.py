@@ -121,3 +121,38 @@ def test_oracle_mesh_termination_closed_form():
     # a ray that misses every box but hits the mesh is a hit ray too (hits.size() > 0, instancer.cpp:783-785)
     far = IO.get_model_input(np.array([[1.5, 1.5, 3.0]], np.float32), d, prm, 64, 0.02, [np.eye(4)], B0, B1, seed=1, mesh=(V, F))
     assert far["hit"][0] and far["alpha_last"][0] == 1 and far["n_samples"][0] == 0
+
+
+def test_oracle_shadow_rays_closed_form():
+    """shadow_ray_filter_function (instancer.cpp:539-551): own top face left from inside does not block; a bottom face
+    does (either side); another patch's top face entered from above does; side faces do not."""
+    B0, B1 = [-0.5, -0.5, -0.1], [0.5, 0.5, 0.1]
+    M1 = IO.prepare_instances([np.eye(4)])[0]
+    b0, b1 = np.float32(B0), np.float32(B1)
+    inside = [0.1, 0.0, 0.0]
+    assert not IO.is_shadowed(inside, [0, 0, 1.0], M1, b0, b1)             # up through the own top face, from inside
+    assert IO.is_shadowed(inside, [0, 0, -1.0], M1, b0, b1)                # down through the own bottom face
+    assert not IO.is_shadowed(inside, [1.0, 0, 0], M1, b0, b1)             # out through a side face
+    assert IO.is_shadowed([0.1, 0, 1.0], [0, 0, -1.0], M1, b0, b1)         # from above into the top face
+    assert not IO.is_shadowed([0.1, 0, 1.0], [0, 0, 1.0], M1, b0, b1)      # pointing away
+    assert not IO.is_shadowed([3.0, 0, 1.0], [0, 0, -1.0], M1, b0, b1)     # beside the patch
+    up = np.eye(4)
+    up[2, 3] = 1.0
+    M2 = IO.prepare_instances([np.eye(4), up])[0]
+    assert IO.is_shadowed(inside, [0, 0, 1.0], M2, b0, b1)                 # the second patch's bottom face is in the way
+    V = np.array([[-2, -2, 0.5], [2, -2, 0.5], [2, 2, 0.5], [-2, 2, 0.5]], np.float32)
+    F = np.array([[0, 1, 2], [0, 2, 3]])                                   # counter-clockwise seen from +z: front = +z
+    assert not IO.is_shadowed(inside, [0, 0, 1.0], M1, b0, b1, (V, F))     # reaches the sheet from behind
+    assert IO.is_shadowed([0.1, 0, 2.0], [0.3, 0, -1.0], M1 * 0 + M1, b0, b1, (V, F))      # from its front side
+    # through the whole pipeline: light from straight above a single patch lights every sample, from below none
+    o, d = np.array([[0.1, -0.2, 3.0]], np.float32), np.array([[0.2, 0, -1.0]], np.float32)
+    kw = dict(seed=1, light_dir_idx=1, cast_shadow_rays=True, min_shadow_samples=4, n_shadow_samples=64)
+    lit = IO.get_model_input(o, d, np.array([[0.5, 0, 0, 2.0]], np.float32), 64, 0.02, [np.eye(4)], B0, B1, **kw)
+    dark = IO.get_model_input(o, d, np.array([[0.5, 0, 0, -2.0]], np.float32), 64, 0.02, [np.eye(4)], B0, B1, **kw)
+    plain = IO.get_model_input(o, d, np.array([[0.5, 0, 0, 2.0]], np.float32), 64, 0.02, [np.eye(4)], B0, B1, seed=1, light_dir_idx=1)
+    assert np.array_equal(lit["params"], plain["params"]) and np.array_equal(lit["t"], dark["t"])
+    assert np.all(dark["params"][:, 1:] == [0, 0, -1]) and np.all(lit["params"][:, 3] == 1)
+    # per-sample path (n_shadow >= n_pts) agrees here, since the occlusion is constant along the ray
+    dark2 = IO.get_model_input(o, d, np.array([[0.5, 0, 0, -2.0]], np.float32), 8, 0.02, [np.eye(4)], B0, B1,
+                               **dict(kw, min_shadow_samples=100))
+    assert np.all(dark2["params"][:, 1:] == [0, 0, -1])
