@@ -43,7 +43,7 @@ __global__ void stratified_z_kernel(const float* __restrict__ t, const float* __
 //               -> z_out[R,S+N] sorted, optional samples / inds
 // C_CT / N_CT: compile-time copies of C / N for the common 64 + 128 configuration (0 = run-time sizes).
 struct SampleSmem {           // per-warp layout, in floats
-    int cdf, zst, zb, mids, sm, merged, end, marks, total;
+    int cdf, zst, zb, mids, sm, merged, end, total;
 };
 __host__ __device__ inline int pow2_at_least(int v) { int p = 1; while (p < v) p <<= 1; return p; }
 __host__ __device__ inline SampleSmem sample_smem(bool hier, int C, int N, int rpw, int cstride) {
@@ -57,8 +57,7 @@ __host__ __device__ inline SampleSmem sample_smem(bool hier, int C, int N, int r
     L.sm = L.mids + (hier ? C : 0);                         // samples (sortable)
     L.merged = (L.sm + (hier ? pow2_at_least(N) : 0) + 3) & ~3;   // read back with 16-byte loads
     L.end = L.merged + (hier ? S + N : 0);
-    L.marks = L.end + (hier ? S + 1 : 0);                   // deterministic u: per-sample bin markers (N + 1 ints)
-    L.total = L.marks + N + 1;
+    L.total = L.end + (hier ? S + 1 : 0);
     L.total = (L.total + 3) & ~3;                           // keep every warp's block 16-byte aligned
     return L;
 }
@@ -99,7 +98,6 @@ sample_pdf_kernel(const float* __restrict__ src, const float* __restrict__ weigh
     float* sm = base + L.sm;
     float* merged = base + L.merged;
     int* endv = reinterpret_cast<int*>(base + L.end);
-    int* marks = reinterpret_cast<int*>(base + L.marks);
 
     const int W = C - 1;
     const int S = C + 1;  // only meaningful when HIER
@@ -195,46 +193,16 @@ sample_pdf_kernel(const float* __restrict__ src, const float* __restrict__ weigh
         // the fly and checks the assumption; if it fails, the slow path after the loop redoes the merge.
         bool sm_ok = true;
         float carry_s = -CUDART_INF_F;
-        // Deterministic u (renderer.py:599-601, every shipped config): u_n = linspace(0, 1, N) and the CDF are both
-        // ascending, so instead of N searches each CDF entry i finds the first sample k_i with u_k >= c_i (a rounded
-        // guess c_i * (N - 1), corrected by exact comparisons with the very u values) and marks it with i + 1;
-        // searchsorted(cdf, u_n, 'right') = #{i : c_i <= u_n} is then the running maximum of the marks up to n.
-        auto u_of = [&](int n) { return (n == 0) ? 0.0f : (n == N - 1) ? 1.0f : __fmul_rn(delta, (float)n); };
-        int carry_lo = 0;
-        if (det) {
-            for (int n = lane; n <= N; n += 32) marks[n] = 0;
-            __syncwarp();
-            for (int i = lane; i < C; i += 32) {
-                const float ci = c[i];
-                int k = min(max((int)ceilf(ci * (float)(N - 1)), 0), N);
-                while (k > 0 && u_of(k - 1) >= ci) --k;
-                while (k < N && u_of(k) < ci) ++k;
-                atomicMax(&marks[k], i + 1);
-            }
-            __syncwarp();
-        }
         for (int n0 = 0; n0 < N; n0 += 32) {
             const int n = n0 + lane;
             const bool live = n < N;
             float s = CUDART_INF_F;
-            int lo = 0;
-            if (det) {
-                int v = live ? marks[n] : 0;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const int t = __shfl_up_sync(0xffffffffu, v, o);
-                    if (lane >= o) v = max(v, t);
-                }
-                lo = max(v, carry_lo);
-                carry_lo = __shfl_sync(0xffffffffu, lo, 31);
-            }
             if (live) {
-                const float u = det ? u_of(n) : u_in[ray * N + n];
-                if (!det) {                            // upper_bound == searchsorted(side='right'), branch-free
-                    for (int step = top; step > 0; step >>= 1) {
-                        const int t = lo + step;
-                        if (t <= C && c[t - 1] <= u) lo = t;
-                    }
+                const float u = det ? ((n == 0) ? 0.0f : (n == N - 1) ? 1.0f : __fmul_rn(delta, (float)n)) : u_in[ray * N + n];
+                int lo = 0;                            // upper_bound == searchsorted(side='right'), branch-free
+                for (int step = top; step > 0; step >>= 1) {
+                    const int t = lo + step;
+                    if (t <= C && c[t - 1] <= u) lo = t;
                 }
                 const int below = max(lo - 1, 0);
                 const int above = min(lo, C - 1);
@@ -338,9 +306,6 @@ int launch_sample_t(const float* src, const float* weights, const float* u, int 
     NTX_REQUIRE(smem <= 46 * 1024, "sample_pdf: C=%d N=%d needs %zu B of shared memory", C, N, smem);
     const int64_t rays_per_block = (int64_t)rpw * warps;
     const int64_t blocks = (R + rays_per_block - 1) / rays_per_block;
-    // ask for the largest shared-memory split: the default one capped the kernel at 5 blocks per SM
-    NTX_CUDA(cudaFuncSetAttribute(sample_pdf_kernel<HIER, C_CT, N_CT>, cudaFuncAttributePreferredSharedMemoryCarveout,
-                                  (int)cudaSharedmemCarveoutMaxShared));
     sample_pdf_kernel<HIER, C_CT, N_CT><<<(unsigned)blocks, warps * 32, smem, st>>>(src, weights, u, R, C, N, det, rpw, cstride,
                                                                                    samples, inds, z_out);
     NTX_LAUNCH_CHECK();

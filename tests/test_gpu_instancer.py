@@ -315,8 +315,8 @@ def test_base_mesh_ends_rays(use_grid):
     hit = want["hit"]
     assert np.array_equal(got["alpha_last"].cpu().numpy(), want["alpha_last"][hit]) and not got["color_last"].any()
     below = np.arange(R) % 5 == 0
-    assert want["alpha_last"][below & hit].mean() > 0.8 and want["n_samples"][below].max() < 40       # 0.009 deep under the mesh
-    assert (want["alpha_last"][~below] == 1).mean() > 0.6 and (want["alpha_last"] == 0)[hit].any()
+    assert want["alpha_last"][below & hit].mean() > 0.8 and np.median(want["n_samples"][below]) < 10  # 0.009 deep under the mesh
+    assert (want["alpha_last"][~below] == 1).mean() > 0.4 and (want["alpha_last"] == 0)[hit].any()
     assert want["n_samples"][~below].max() > 30
 
 
