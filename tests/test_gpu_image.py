@@ -116,8 +116,10 @@ def test_render_entry_end_to_end(tmp_path):
         hitp = np.isfinite(t[:, 0])
         R = int(hitp.sum())
         pf = np.tile(np.asarray(prm, np.float32), (R, 1))
-        # the renderer culls proxy misses first (renderer.py:58-66), so the instancer sees the surviving rays, in order
-        rec = IO.get_model_input(ro[hitp], rd[hitp], pf, 32, 0.01, Ts, B0, B1, seed=4 + 7919 * i, light_dir_idx=4)
+        # the renderer culls proxy misses first (renderer.py:58-66), so the instancer sees the surviving rays, in order;
+        # it names every ray by its position in the frame (the draws do not depend on chunking) and seeds per frame
+        rec = IO.get_model_input(ro[hitp], rd[hitp], pf, 32, 0.01, Ts, B0, B1, seed=4 + 7919 * i, light_dir_idx=4,
+                                 ray_ids=np.nonzero(hitp)[0])
         csr = {k: torch.as_tensor(rec[k]) for k in ("pts", "dirs", "params", "dists", "t", "alpha_weight", "instance_id")}
         idx = np.nonzero(rec["hit"])[0]
         ptr_all = np.concatenate([[0], np.cumsum(rec["n_samples"])])
