@@ -291,7 +291,9 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
  * ray towards the light enters a patch box through its top face, crosses a box's bottom face or hits a mesh triangle on
  * its front side gets the ambient light direction (0, 0, -1), :572-575; looked up at min_shadow_samples /
  * n_shadow_samples points per ray as in :863,:936-951,:992-1000; cast_shadow_rays != 0 adds 1600 B per ray to the
- * workspace); no parameter textures, no auxiliary-mesh shading.
+ * workspace), optional parameter textures and auxiliary meshes (ntx_instancer_shading below).  The trace takes the rays'
+ * parameters[R,n_param] and light_dir_idx for the shading of auxiliary-mesh hits (NULL / -1 without them) and writes
+ * color_last[R,3] (0 except on auxiliary meshes).
  *
  * ntx_instancer_scene — what CommitScene (instancer.cpp:420-424) leaves behind, all DEVICE pointers:
  *   minv[I,3,4]  rows 0..2 of the inverse instance transform (world -> patch), dirt[I,3,3] the row-normalised
@@ -327,6 +329,37 @@ typedef struct ntx_scene_grid {
     float cell[3];
     int32_t res[3];
 } ntx_scene_grid;
+/* One texture channel in the pool: element (i, j) at pool[offset + i * cols + j]; rows follow the image's x, columns
+ * its y counted from the bottom (loadTexture, instancer.cpp:34-52). */
+typedef struct ntx_texture {
+    int64_t offset;
+    int32_t rows, cols;
+} ntx_texture;
+#define NTX_MAX_PARAM_TEXTURES 8
+#define NTX_MAX_AUX_MESHES 8
+/* Optional per-scene shading data (HOST struct of DEVICE pointers, read at call time):
+ *   parameter textures (getParameters, instancer.cpp:640-667): texture file i multiplies parameter param_idx[i] by
+ *   param_tex[i] looked up at the UV of the base-mesh point nearest to the sample (within `radius` = the patch extent,
+ *   :63,:246), sampled along the ray at min_samples / n_samples points and linearly interpolated (:864,:916-926,:985-991);
+ *   auxiliary meshes (AddMesh :393-418, shadeMesh :716-744): faces [aux_face_begin[k], aux_face_begin[k+1]) of the scene's
+ *   face list belong to auxiliary mesh k (the base mesh's n_base_faces faces come first); a ray ending there gets the
+ *   colour albedo * min(max(n . l, 0) [0 if shadowed] + 0.2, 1), albedo = aux_tex[k][0..2] at the hit's UV (one channel
+ *   is used for all three) or 0.8 without a texture.  mesh_uv[V,2] / mesh_n[V,3] are per vertex of the scene's mesh_v. */
+typedef struct ntx_instancer_shading {
+    const float* pool;
+    const float* mesh_uv;
+    const float* mesh_n;
+    int32_t n_base_faces;
+    int32_t n_param_tex;
+    int32_t param_idx[NTX_MAX_PARAM_TEXTURES];
+    ntx_texture param_tex[NTX_MAX_PARAM_TEXTURES];
+    float radius;
+    int32_t min_samples, n_samples;
+    int32_t n_aux;
+    int32_t aux_face_begin[NTX_MAX_AUX_MESHES + 1];
+    int32_t aux_channels[NTX_MAX_AUX_MESHES];
+    ntx_texture aux_tex[NTX_MAX_AUX_MESHES][3];
+} ntx_instancer_shading;
 typedef struct ntx_instancer_scene {
     const float* minv;
     const float* dirt;
@@ -338,12 +371,14 @@ typedef struct ntx_instancer_scene {
     const int32_t* mesh_f;
     ntx_scene_grid inst_grid;
     ntx_scene_grid tri_grid;
+    const ntx_instancer_shading* shading;   /* NULL: no parameter textures, no auxiliary meshes */
 } ntx_instancer_scene;
 int64_t ntx_instancer_workspace_bytes(int R, int cast_shadow_rays);
 int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
                         const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size, int n_pts,
-                        uint32_t seed, int use_mean_distance, int cast_shadow_rays, void* workspace, int32_t* n_samples,
-                        int32_t* hit, float* alpha_last, void* stream);
+                        uint32_t seed, int use_mean_distance, int cast_shadow_rays, const float* parameters, int n_param,
+                        int light_dir_idx, void* workspace, int32_t* n_samples, int32_t* hit, float* alpha_last,
+                        float* color_last, void* stream);
 int ntx_instancer_march(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* parameters,
                         int n_param, int R, const ntx_instancer_scene* scene, float step_size, int n_pts, uint32_t seed,
                         int light_dir_idx, int light_strength_idx, int method, float blend_range, int use_mean_distance,

@@ -46,10 +46,25 @@ class SceneGrid(C.Structure):
                 ("res", C.c_int32 * 3)]
 
 
+class Texture(C.Structure):
+    _fields_ = [("offset", C.c_int64), ("rows", C.c_int32), ("cols", C.c_int32)]
+
+
+MAX_PARAM_TEXTURES = MAX_AUX_MESHES = 8
+
+
+class InstancerShading(C.Structure):
+    _fields_ = [("pool", C.c_void_p), ("mesh_uv", C.c_void_p), ("mesh_n", C.c_void_p), ("n_base_faces", C.c_int32),
+                ("n_param_tex", C.c_int32), ("param_idx", C.c_int32 * MAX_PARAM_TEXTURES),
+                ("param_tex", Texture * MAX_PARAM_TEXTURES), ("radius", C.c_float), ("min_samples", C.c_int32),
+                ("n_samples", C.c_int32), ("n_aux", C.c_int32), ("aux_face_begin", C.c_int32 * (MAX_AUX_MESHES + 1)),
+                ("aux_channels", C.c_int32 * MAX_AUX_MESHES), ("aux_tex", (Texture * 3) * MAX_AUX_MESHES)]
+
+
 class InstancerScene(C.Structure):
     _fields_ = [("minv", C.c_void_p), ("dirt", C.c_void_p), ("origins", C.c_void_p), ("spheres", C.c_void_p),
                 ("n_inst", C.c_int32), ("n_faces", C.c_int32), ("mesh_v", C.c_void_p), ("mesh_f", C.c_void_p),
-                ("inst_grid", SceneGrid), ("tri_grid", SceneGrid)]
+                ("inst_grid", SceneGrid), ("tri_grid", SceneGrid), ("shading", C.POINTER(InstancerShading))]
 
 
 # name -> (restype, argtypes); must list every symbol include/nerftex_b200.h declares.
@@ -91,7 +106,8 @@ SIGNATURES = {
     "ntx_composite_edges_backward": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
     "ntx_image_finish": (_I, [_P, _P, _I, _I, _I, _P, _I, _I, _P, _P, _P]),
     "ntx_instancer_workspace_bytes": (_I64, [_I, _I]),
-    "ntx_instancer_trace": (_I, [_P, _P, _P, _I, C.POINTER(InstancerScene), _P, _P, _F, _I, _U32, _I, _I, _P, _P, _P, _P, _P]),
+    "ntx_instancer_trace": (_I, [_P, _P, _P, _I, C.POINTER(InstancerScene), _P, _P, _F, _I, _U32, _I, _I, _P, _I, _I,
+                                 _P, _P, _P, _P, _P, _P]),
     "ntx_instancer_march": (_I, [_P, _P, _P, _P, _I, _I, C.POINTER(InstancerScene), _F, _I, _U32, _I, _I, _I, _F, _I,
                                  _I, _I, _I, _P, _P, _P, _P, _I64] + [_P] * 7 + [_P]),
     "ntx_render_rays_workspace_bytes": (_I64, [_I, _I, _I]),

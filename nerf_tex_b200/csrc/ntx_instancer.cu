@@ -332,13 +332,231 @@ struct SceneDev {
     const float* __restrict__ mesh_v;
     const int32_t* __restrict__ mesh_f;
     Grid ig, tg;
+    ntx_instancer_shading sh;          // pool == NULL and n_aux == 0: nothing to shade
+};
+
+// ---- parameter textures (instancer.cpp:606-667) in the operation order of oracle/instancer_oracle.py
+__device__ __forceinline__ float tex_lookup(const float* __restrict__ pool, const ntx_texture& tx, float u, float v) {
+    const int rows = tx.rows, cols = tx.cols;
+    const float x0 = __fmul_rn(u, (float)(rows - 1)), x1 = __fmul_rn(v, (float)(cols - 1));
+    const float w0 = __fsub_rn(x0, floorf(x0)), w1 = __fsub_rn(x1, floorf(x1));
+    const int i0 = min(max((int)x0, 0), rows - 1), j0 = min(max((int)x1, 0), cols - 1);
+    const int i1 = min(i0 + 1, rows - 1), j1 = min(j0 + 1, cols - 1);
+    const float m0 = __fsub_rn(1.0f, w0), m1 = __fsub_rn(1.0f, w1);
+    const float* t = pool + tx.offset;
+    float y = __fmul_rn(__fmul_rn(__ldg(t + (size_t)i0 * cols + j0), m0), m1);
+    y = __fadd_rn(y, __fmul_rn(__fmul_rn(__ldg(t + (size_t)i0 * cols + j1), m0), w1));
+    y = __fadd_rn(y, __fmul_rn(__fmul_rn(__ldg(t + (size_t)i1 * cols + j0), w0), m1));
+    return __fadd_rn(y, __fmul_rn(__fmul_rn(__ldg(t + (size_t)i1 * cols + j1), w0), w1));
+}
+
+// closest point of triangle `face` to p (Ericson; closest_point_triangle, instancer.cpp:151-199): barycentric weights
+// and the distance, every op rounded as in oracle closest_face
+__device__ __forceinline__ float closest_on_face(const float* __restrict__ V, const int32_t* __restrict__ fp, const float p[3],
+                                                 float uvw[3]) {
+    float a[3], b[3], c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        a[k] = __ldg(V + 3 * (size_t)__ldg(fp) + k);
+        b[k] = __ldg(V + 3 * (size_t)__ldg(fp + 1) + k);
+        c[k] = __ldg(V + 3 * (size_t)__ldg(fp + 2) + k);
+    }
+    float ab[3], ac[3], ap[3], bp[3], cp[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        ab[k] = __fsub_rn(b[k], a[k]); ac[k] = __fsub_rn(c[k], a[k]);
+        ap[k] = __fsub_rn(p[k], a[k]); bp[k] = __fsub_rn(p[k], b[k]); cp[k] = __fsub_rn(p[k], c[k]);
+    }
+    const float d1 = dot3(ab, ap), d2 = dot3(ac, ap), d3 = dot3(ab, bp), d4 = dot3(ac, bp), d5 = dot3(ab, cp), d6 = dot3(ac, cp);
+    const float vc = __fsub_rn(__fmul_rn(d1, d4), __fmul_rn(d3, d2));
+    const float vb = __fsub_rn(__fmul_rn(d5, d2), __fmul_rn(d1, d6));
+    const float va = __fsub_rn(__fmul_rn(d3, d6), __fmul_rn(d5, d4));
+    if (d1 <= 0.0f && d2 <= 0.0f) { uvw[0] = 1.0f; uvw[1] = 0.0f; uvw[2] = 0.0f; }
+    else if (d3 >= 0.0f && d4 <= d3) { uvw[0] = 0.0f; uvw[1] = 1.0f; uvw[2] = 0.0f; }
+    else if (d6 >= 0.0f && d5 <= d6) { uvw[0] = 0.0f; uvw[1] = 0.0f; uvw[2] = 1.0f; }
+    else if (vc <= 0.0f && d1 >= 0.0f && d3 <= 0.0f) {
+        const float v = __fdiv_rn(d1, __fsub_rn(d1, d3));
+        uvw[0] = __fsub_rn(1.0f, v); uvw[1] = v; uvw[2] = 0.0f;
+    } else if (vb <= 0.0f && d2 >= 0.0f && d6 <= 0.0f) {
+        const float v = __fdiv_rn(d2, __fsub_rn(d2, d6));
+        uvw[0] = __fsub_rn(1.0f, v); uvw[1] = 0.0f; uvw[2] = v;
+    } else {
+        const float e43 = __fsub_rn(d4, d3), e56 = __fsub_rn(d5, d6);
+        if (va <= 0.0f && e43 >= 0.0f && e56 >= 0.0f) {
+            const float v = __fdiv_rn(e43, __fadd_rn(e43, e56));
+            uvw[0] = 0.0f; uvw[1] = __fsub_rn(1.0f, v); uvw[2] = v;
+        } else {
+            const float denom = __fdiv_rn(1.0f, __fadd_rn(__fadd_rn(va, vb), vc));
+            const float v = __fmul_rn(vb, denom), w = __fmul_rn(vc, denom);
+            uvw[0] = __fsub_rn(__fsub_rn(1.0f, v), w); uvw[1] = v; uvw[2] = w;
+        }
+    }
+    float df[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float q = __fadd_rn(__fadd_rn(__fmul_rn(a[k], uvw[0]), __fmul_rn(b[k], uvw[1])), __fmul_rn(c[k], uvw[2]));
+        df[k] = __fsub_rn(p[k], q);
+    }
+    return sqrtf(dot3(df, df));
+}
+
+// the base-mesh face nearest to p within `radius` (strictly), ties to the smaller face index; -1 if none
+__device__ int closest_face(const SceneDev& sc, const float p[3], float radius, float uvw[3]) {
+    int best = -1;
+    float best_d = radius;
+    const int n_base = sc.sh.n_base_faces;
+    auto test = [&](int face) {
+        if (face >= n_base) return;
+        float w[3];
+        const float d = closest_on_face(sc.mesh_v, sc.mesh_f + 3 * (size_t)face, p, w);
+        if (d < best_d || (d == best_d && best >= 0 && face < best)) {
+            best_d = d; best = face;
+            uvw[0] = w[0]; uvw[1] = w[1]; uvw[2] = w[2];
+        }
+    };
+    if (!sc.tg.start) {
+        for (int face = 0; face < n_base; ++face) test(face);
+        return best;
+    }
+    const Grid& g = sc.tg;
+    int c0[3], c1[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        c0[a] = max(0, min(g.res[a] - 1, (int)floorf((p[a] - radius - g.lo[a]) / g.cell[a])));
+        c1[a] = max(0, min(g.res[a] - 1, (int)floorf((p[a] + radius - g.lo[a]) / g.cell[a])));
+    }
+    // the cell of p first: its faces usually shrink the search radius to a fraction of the patch extent
+    int pc[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) pc[a] = max(c0[a], min(c1[a], (int)floorf((p[a] - g.lo[a]) / g.cell[a])));
+    auto visit = [&](int x, int y, int z) {
+        // distance from p to the cell's box: a face listed here has a point in the cell, so it cannot be nearer than that
+        float dd = 0.0f;
+        const int cc[3] = {x, y, z};
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float lo = g.lo[a] + (float)cc[a] * g.cell[a], hi = lo + g.cell[a];
+            const float e = fmaxf(fmaxf(lo - p[a], p[a] - hi), 0.0f);
+            dd += e * e;
+        }
+        if (dd > best_d * best_d * 1.0001f + 1e-12f) return;
+        const int cell = (z * g.res[1] + y) * g.res[0] + x;
+        const int e = __ldg(g.start + cell + 1);
+        for (int q = __ldg(g.start + cell); q < e; ++q) test(__ldg(g.items + q));
+    };
+    visit(pc[0], pc[1], pc[2]);
+    for (int z = c0[2]; z <= c1[2]; ++z)
+        for (int y = c0[1]; y <= c1[1]; ++y)
+            for (int x = c0[0]; x <= c1[0]; ++x)
+                if (x != pc[0] || y != pc[1] || z != pc[2]) visit(x, y, z);
+    return best;
+}
+
+// getParameters (:640-667): out[] = the ray's parameters, textured ones multiplied by their texture at the UV of the
+// nearest base-mesh point
+__device__ void get_parameters(const SceneDev& sc, const float p[3], const float* __restrict__ prm, int n_param, float* out) {
+    for (int q = 0; q < n_param; ++q) out[q] = __ldg(prm + q);
+    float w[3];
+    const int face = closest_face(sc, p, sc.sh.radius, w);
+    if (face < 0) return;
+    const int32_t* fp = sc.mesh_f + 3 * (size_t)face;
+    float uv[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k)
+        uv[k] = __fadd_rn(__fadd_rn(__fmul_rn(__ldg(sc.sh.mesh_uv + 2 * (size_t)__ldg(fp) + k), w[0]),
+                                    __fmul_rn(__ldg(sc.sh.mesh_uv + 2 * (size_t)__ldg(fp + 1) + k), w[1])),
+                          __fmul_rn(__ldg(sc.sh.mesh_uv + 2 * (size_t)__ldg(fp + 2) + k), w[2]));
+    for (int i = 0; i < sc.sh.n_param_tex; ++i) {
+        const int idx = sc.sh.param_idx[i];
+        out[idx] = __fmul_rn(out[idx], tex_lookup(sc.sh.pool, sc.sh.param_tex[i], uv[0], uv[1]));
+    }
+}
+
+// isShadowed (instancer.cpp:593-603) with shadow_ray_filter_function (:539-551), in the operation order of
+// oracle/instancer_oracle.py::is_shadowed: a ray from `pt` along `dir` (not normalised), t in [0, 100], is blocked by the
+// top face of a patch box entered from above (patch frame), by the bottom face of a patch box from either side, or by a
+// mesh triangle hit on its front side.  Any-hit: the walk stops at the first blocker.
+struct ShadowBox { float b0[3], b1[3]; };
+__device__ bool shadow_blocked(const SceneDev& sc, const ShadowBox& bx, const float pt[3], const float dir[3]) {
+    bool blocked = false;
+    const float inv_dn = rsqrtf(fmaxf(dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2], 1e-30f));
+    const float dh[3] = {dir[0] * inv_dn, dir[1] * inv_dn, dir[2] * inv_dn};
+    auto test_instance = [&](int inst) {
+        if (sc.spheres) {
+            const float4 sp = __ldg(sc.spheres + inst);
+            const float cx = sp.x - pt[0], cy = sp.y - pt[1], cz = sp.z - pt[2];
+            const float cc = cx * cx + cy * cy + cz * cz;
+            const float along = cx * dh[0] + cy * dh[1] + cz * dh[2];
+            if (fmaf(-along, along, cc) > fmaf(1e-5f, cc, sp.w)) return;
+        }
+        const float4* Mp = reinterpret_cast<const float4*>(sc.minv) + 3 * (size_t)inst;
+        float ol[3], dl[3];
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float4 m4 = __ldg(Mp + a);
+            const float M[3] = {m4.x, m4.y, m4.z};
+            ol[a] = __fadd_rn(dot3(M, pt), m4.w);
+            dl[a] = dot3(M, dir);
+        }
+        const float inv = __fdiv_rn(1.0f, dl[2]);
+#pragma unroll
+        for (int face = 0; face < 2; ++face) {                                 // top (from above only), bottom
+            if (face == 0 ? !(dl[2] < 0.0f) : !(dl[2] != 0.0f)) continue;
+            const float t = __fmul_rn(__fsub_rn(face == 0 ? bx.b1[2] : bx.b0[2], ol[2]), inv);
+            const float x = __fadd_rn(ol[0], __fmul_rn(t, dl[0])), y = __fadd_rn(ol[1], __fmul_rn(t, dl[1]));
+            if (t >= 0.0f && t <= kTFar && x >= bx.b0[0] && x <= bx.b1[0] && y >= bx.b0[1] && y <= bx.b1[1]) blocked = true;
+        }
+    };
+    if (sc.ig.start) {
+        grid_walk(sc.ig, pt, dir, 0.0f, kTFar, [&](int cell, float) {
+            const int e = __ldg(sc.ig.start + cell + 1);
+            for (int q = __ldg(sc.ig.start + cell); q < e && !blocked; ++q) test_instance(__ldg(sc.ig.items + q));
+            return !blocked;
+        });
+    } else {
+        for (int inst = 0; inst < sc.n_inst && !blocked; ++inst) test_instance(inst);
+    }
+    if (blocked || sc.n_faces == 0 || (dir[0] == 0.0f && dir[1] == 0.0f && dir[2] == 0.0f)) return blocked;
+    const RayFrame rf = ray_frame(dir);
+    auto test_face = [&](int face) {
+        float t, u, v;
+        const int32_t* fp = sc.mesh_f + 3 * (size_t)face;
+        if (!tri_hit(rf, pt, sc.mesh_v, fp, t, u, v)) return;
+        float P[3][3];
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+#pragma unroll
+            for (int a = 0; a < 3; ++a) P[k][a] = __ldg(sc.mesh_v + 3 * (size_t)__ldg(fp + k) + a);
+        const float e1[3] = {__fsub_rn(P[1][0], P[0][0]), __fsub_rn(P[1][1], P[0][1]), __fsub_rn(P[1][2], P[0][2])};
+        const float e2[3] = {__fsub_rn(P[2][0], P[0][0]), __fsub_rn(P[2][1], P[0][1]), __fsub_rn(P[2][2], P[0][2])};
+        const float ng[3] = {__fsub_rn(__fmul_rn(e1[1], e2[2]), __fmul_rn(e1[2], e2[1])),
+                             __fsub_rn(__fmul_rn(e1[2], e2[0]), __fmul_rn(e1[0], e2[2])),
+                             __fsub_rn(__fmul_rn(e1[0], e2[1]), __fmul_rn(e1[1], e2[0]))};
+        if (dot3(ng, dir) < 0.0f) blocked = true;
+    };
+    if (sc.tg.start) {
+        grid_walk(sc.tg, pt, dir, 0.0f, kTFar, [&](int cell, float) {
+            const int e = __ldg(sc.tg.start + cell + 1);
+            for (int q = __ldg(sc.tg.start + cell); q < e && !blocked; ++q) test_face(__ldg(sc.tg.items + q));
+            return !blocked;
+        });
+    } else {
+        for (int face = 0; face < sc.n_faces && !blocked; ++face) test_face(face);
+    }
+    return blocked;
+}
+
+struct ShadowArgs {
+    int enabled, min_samples, n_samples, n_pts;
+    ShadowBox box;
 };
 
 __global__ void __launch_bounds__(kTraceThreads)
 instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const int32_t* __restrict__ ray_ids,
                        int R, SceneDev sc, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
                        int n_pts, uint32_t seed, int use_mean, Workspace ws, int32_t* __restrict__ n_samples,
-                       int32_t* __restrict__ hit_flag, float* __restrict__ alpha_last) {
+                       int32_t* __restrict__ hit_flag, float* __restrict__ alpha_last, const float* __restrict__ params,
+                       int n_param, int light_idx, float* __restrict__ color_last) {
     const int ray = blockIdx.x * blockDim.x + threadIdx.x;
     if (ray >= R) return;
     float o[3], d[3];
@@ -349,14 +567,14 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     const float dh[3] = {d[0] * inv_dn, d[1] * inv_dn, d[2] * inv_dn};
 
     // ---- the base mesh first: its nearest hit bounds everything else (instancer.cpp:804-814)
-    float t_mesh = CUDART_INF_F;
+    float t_mesh = CUDART_INF_F, u_mesh = 0.0f, v_mesh = 0.0f;
+    int best = -1;
     if (sc.n_faces > 0 && (d[0] != 0.0f || d[1] != 0.0f || d[2] != 0.0f)) {
         const RayFrame rf = ray_frame(d);
-        int best = -1;
         auto test = [&](int face) {
             float t, u, v;
             if (tri_hit(rf, o, sc.mesh_v, sc.mesh_f + 3 * (size_t)face, t, u, v) && (t < t_mesh || (t == t_mesh && face < best))) {
-                t_mesh = t;
+                t_mesh = t; u_mesh = u; v_mesh = v;
                 best = face;
             }
         };
@@ -446,91 +664,60 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     ws.n_hits[ray] = n_hits;
     hit_flag[ray] = n_hits > 0 || t_mesh < CUDART_INF_F;
     alpha_last[ray] = t_mesh < CUDART_INF_F ? 1.0f : 0.0f;                    // instancer.cpp:1019-1027
+    if (color_last) {
+        float col[3] = {0.0f, 0.0f, 0.0f};                                    // base mesh: black (:1020)
+        if (t_mesh < CUDART_INF_F && best >= sc.sh.n_base_faces && sc.sh.n_aux > 0) {     // auxiliary mesh: shadeMesh (:716-744)
+            int m = 0;
+            while (m + 1 < sc.sh.n_aux && best >= sc.sh.aux_face_begin[m + 1]) ++m;
+            const int32_t* fp = sc.mesh_f + 3 * (size_t)best;
+            const float w[3] = {__fsub_rn(__fsub_rn(1.0f, u_mesh), v_mesh), u_mesh, v_mesh};
+            float n[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k)
+                n[k] = __fadd_rn(__fadd_rn(__fmul_rn(__ldg(sc.sh.mesh_n + 3 * (size_t)__ldg(fp) + k), w[0]),
+                                           __fmul_rn(__ldg(sc.sh.mesh_n + 3 * (size_t)__ldg(fp + 1) + k), w[1])),
+                                 __fmul_rn(__ldg(sc.sh.mesh_n + 3 * (size_t)__ldg(fp + 2) + k), w[2]));
+            const float nn = norm3(n);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) n[k] = __fdiv_rn(n[k], nn);
+            float albedo[3] = {0.8f, 0.8f, 0.8f};
+            const int nch = sc.sh.aux_channels[m];
+            if (nch > 0) {
+                float uv[2];
+#pragma unroll
+                for (int k = 0; k < 2; ++k)
+                    uv[k] = __fadd_rn(__fadd_rn(__fmul_rn(__ldg(sc.sh.mesh_uv + 2 * (size_t)__ldg(fp) + k), w[0]),
+                                                __fmul_rn(__ldg(sc.sh.mesh_uv + 2 * (size_t)__ldg(fp + 1) + k), w[1])),
+                                      __fmul_rn(__ldg(sc.sh.mesh_uv + 2 * (size_t)__ldg(fp + 2) + k), w[2]));
+                for (int k = 0; k < 3; ++k) albedo[k] = tex_lookup(sc.sh.pool, sc.sh.aux_tex[m][nch == 3 ? k : 0], uv[0], uv[1]);
+            }
+            float diffuse = 0.0f;
+            if (light_idx >= 0 && params) {
+                const float* prm = params + (size_t)ray * n_param + light_idx;
+                const float raw[3] = {__ldg(prm), __ldg(prm + 1), __ldg(prm + 2)};
+                float lifted[3];
+#pragma unroll
+                for (int k = 0; k < 3; ++k) lifted[k] = __fadd_rn(__fadd_rn(o[k], __fmul_rn(t_mesh, d[k])), __fmul_rn(n[k], 1e-6f));
+                ShadowBox bx;
+                for (int k = 0; k < 3; ++k) { bx.b0[k] = b0[k]; bx.b1[k] = b1[k]; }
+                if (!shadow_blocked(sc, bx, lifted, raw)) {
+                    const float ln = norm3(raw);
+                    const float ld[3] = {__fdiv_rn(raw[0], ln), __fdiv_rn(raw[1], ln), __fdiv_rn(raw[2], ln)};
+                    diffuse = __fmul_rn(1.0f, fmaxf(dot3(n, ld), 0.0f));
+                }
+            }
+            const float shade = fminf(__fadd_rn(diffuse, 0.2f), 1.0f);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) col[k] = __fmul_rn(albedo[k], shade);
+        }
+        color_last[3 * (size_t)ray] = col[0]; color_last[3 * (size_t)ray + 1] = col[1]; color_last[3 * (size_t)ray + 2] = col[2];
+    }
     const uint32_t rid = ray_ids ? (uint32_t)ray_ids[ray] : (uint32_t)ray;
     n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, rid, use_mean, t_mesh,
                               ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray,
                               ws.seg ? ws.seg + (size_t)ray * kMaxHits : nullptr);
     for (int k = 0; k < min(n_hits, kSmemHits); ++k) row[k] = H(k);     // with the partner indices walk_ray added
 }
-
-// isShadowed (instancer.cpp:593-603) with shadow_ray_filter_function (:539-551), in the operation order of
-// oracle/instancer_oracle.py::is_shadowed: a ray from `pt` along `dir` (not normalised), t in [0, 100], is blocked by the
-// top face of a patch box entered from above (patch frame), by the bottom face of a patch box from either side, or by a
-// mesh triangle hit on its front side.  Any-hit: the walk stops at the first blocker.
-struct ShadowBox { float b0[3], b1[3]; };
-__device__ bool shadow_blocked(const SceneDev& sc, const ShadowBox& bx, const float pt[3], const float dir[3]) {
-    bool blocked = false;
-    const float inv_dn = rsqrtf(fmaxf(dir[0] * dir[0] + dir[1] * dir[1] + dir[2] * dir[2], 1e-30f));
-    const float dh[3] = {dir[0] * inv_dn, dir[1] * inv_dn, dir[2] * inv_dn};
-    auto test_instance = [&](int inst) {
-        if (sc.spheres) {
-            const float4 sp = __ldg(sc.spheres + inst);
-            const float cx = sp.x - pt[0], cy = sp.y - pt[1], cz = sp.z - pt[2];
-            const float cc = cx * cx + cy * cy + cz * cz;
-            const float along = cx * dh[0] + cy * dh[1] + cz * dh[2];
-            if (fmaf(-along, along, cc) > fmaf(1e-5f, cc, sp.w)) return;
-        }
-        const float4* Mp = reinterpret_cast<const float4*>(sc.minv) + 3 * (size_t)inst;
-        float ol[3], dl[3];
-#pragma unroll
-        for (int a = 0; a < 3; ++a) {
-            const float4 m4 = __ldg(Mp + a);
-            const float M[3] = {m4.x, m4.y, m4.z};
-            ol[a] = __fadd_rn(dot3(M, pt), m4.w);
-            dl[a] = dot3(M, dir);
-        }
-        const float inv = __fdiv_rn(1.0f, dl[2]);
-#pragma unroll
-        for (int face = 0; face < 2; ++face) {                                 // top (from above only), bottom
-            if (face == 0 ? !(dl[2] < 0.0f) : !(dl[2] != 0.0f)) continue;
-            const float t = __fmul_rn(__fsub_rn(face == 0 ? bx.b1[2] : bx.b0[2], ol[2]), inv);
-            const float x = __fadd_rn(ol[0], __fmul_rn(t, dl[0])), y = __fadd_rn(ol[1], __fmul_rn(t, dl[1]));
-            if (t >= 0.0f && t <= kTFar && x >= bx.b0[0] && x <= bx.b1[0] && y >= bx.b0[1] && y <= bx.b1[1]) blocked = true;
-        }
-    };
-    if (sc.ig.start) {
-        grid_walk(sc.ig, pt, dir, 0.0f, kTFar, [&](int cell, float) {
-            const int e = __ldg(sc.ig.start + cell + 1);
-            for (int q = __ldg(sc.ig.start + cell); q < e && !blocked; ++q) test_instance(__ldg(sc.ig.items + q));
-            return !blocked;
-        });
-    } else {
-        for (int inst = 0; inst < sc.n_inst && !blocked; ++inst) test_instance(inst);
-    }
-    if (blocked || sc.n_faces == 0 || (dir[0] == 0.0f && dir[1] == 0.0f && dir[2] == 0.0f)) return blocked;
-    const RayFrame rf = ray_frame(dir);
-    auto test_face = [&](int face) {
-        float t, u, v;
-        const int32_t* fp = sc.mesh_f + 3 * (size_t)face;
-        if (!tri_hit(rf, pt, sc.mesh_v, fp, t, u, v)) return;
-        float P[3][3];
-#pragma unroll
-        for (int k = 0; k < 3; ++k)
-#pragma unroll
-            for (int a = 0; a < 3; ++a) P[k][a] = __ldg(sc.mesh_v + 3 * (size_t)__ldg(fp + k) + a);
-        const float e1[3] = {__fsub_rn(P[1][0], P[0][0]), __fsub_rn(P[1][1], P[0][1]), __fsub_rn(P[1][2], P[0][2])};
-        const float e2[3] = {__fsub_rn(P[2][0], P[0][0]), __fsub_rn(P[2][1], P[0][1]), __fsub_rn(P[2][2], P[0][2])};
-        const float ng[3] = {__fsub_rn(__fmul_rn(e1[1], e2[2]), __fmul_rn(e1[2], e2[1])),
-                             __fsub_rn(__fmul_rn(e1[2], e2[0]), __fmul_rn(e1[0], e2[2])),
-                             __fsub_rn(__fmul_rn(e1[0], e2[1]), __fmul_rn(e1[1], e2[0]))};
-        if (dot3(ng, dir) < 0.0f) blocked = true;
-    };
-    if (sc.tg.start) {
-        grid_walk(sc.tg, pt, dir, 0.0f, kTFar, [&](int cell, float) {
-            const int e = __ldg(sc.tg.start + cell + 1);
-            for (int q = __ldg(sc.tg.start + cell); q < e && !blocked; ++q) test_face(__ldg(sc.tg.items + q));
-            return !blocked;
-        });
-    } else {
-        for (int face = 0; face < sc.n_faces && !blocked; ++face) test_face(face);
-    }
-    return blocked;
-}
-
-struct ShadowArgs {
-    int enabled, min_samples, n_samples, n_pts;
-    ShadowBox box;
-};
 
 // Pass 2, one thread per sample: every store of a warp is contiguous.  The sample finds its ray (binary search in
 // ray_ptr) and the hit interval it was emitted in (binary search in the ray's step_at row), replays the hits before it
@@ -667,7 +854,37 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         out.dirs[3 * k + a] = dot3(Dt + 3 * a, dn);                           // getDir :561-563
     }
     const float* prm = params + (size_t)ray * n_param;
-    for (int q = 0; q < n_param; ++q) out.params[k * n_param + q] = __ldg(prm + q);
+    if (sc.sh.n_param_tex > 0 && sc.sh.n_base_faces > 0) {                    // :864, :916-926, :985-991
+        const uint32_t n_tex = max((uint32_t)sc.sh.min_samples, (uint32_t)__fmul_rn((float)sc.sh.n_samples, ri.total));
+        float pv[16];
+        if (n_tex < (uint32_t)sh.n_pts) {
+            // textures are looked up at points spaced evenly along the segment and interpolated linearly
+            const float2 sg = ws.seg[(size_t)ray * kMaxHits + (j > 0 ? j - 1 : 0)];
+            const uint32_t n_seg = max((uint32_t)sc.sh.min_samples, (uint32_t)__fdiv_rn(__fmul_rn((float)n_tex, sg.y), ri.total));
+            const float sstep = __fdiv_rn(sg.y, (float)(n_seg - 1u));
+            auto t_at = [&](int kk) { return __fadd_rn(sg.x, __fmul_rn((float)kk, sstep)); };
+            int kk = max(1, (int)ceilf((t_pt - sg.x) / sstep));
+            if (!(kk < (1 << 24))) kk = 1;
+            while (kk > 1 && !(t_pt > t_at(kk - 1))) --kk;
+            for (int guard = 0; t_pt > t_at(kk) && guard < (1 << 20); ++guard) ++kk;
+            const float t0 = kk == 1 ? sg.x : t_at(kk - 1), t1 = t_at(kk);
+            const float wt = __fdiv_rn(__fsub_rn(t_pt, t0), sstep), mt = __fsub_rn(1.0f, wt);
+            float q0[3], q1[3], p1[16];
+#pragma unroll
+            for (int a = 0; a < 3; ++a) {
+                q0[a] = __fadd_rn(o[a], __fmul_rn(t0, d[a]));
+                q1[a] = __fadd_rn(o[a], __fmul_rn(t1, d[a]));
+            }
+            get_parameters(sc, q0, prm, n_param, pv);
+            get_parameters(sc, q1, prm, n_param, p1);
+            for (int q = 0; q < n_param; ++q) pv[q] = __fadd_rn(__fmul_rn(pv[q], mt), __fmul_rn(p1[q], wt));
+        } else {
+            get_parameters(sc, pt, prm, n_param, pv);
+        }
+        for (int q = 0; q < n_param; ++q) out.params[k * n_param + q] = pv[q];
+    } else {
+        for (int q = 0; q < n_param; ++q) out.params[k * n_param + q] = __ldg(prm + q);
+    }
     if (light_idx >= 0) {                                                     // :929-956
         // directional light: the parameter is the direction; point light ('point' texture entry): it is the position,
         // the direction becomes (position - sample) and the strength parameter the received radiance (:572-590)
@@ -746,13 +963,29 @@ static int check_scene(const ntx_instancer_scene* s, SceneDev* out) {
     out->n_inst = s->n_inst; out->n_faces = s->n_faces; out->mesh_v = s->mesh_v; out->mesh_f = s->mesh_f;
     out->ig = make_grid(s->inst_grid);
     out->tg = make_grid(s->tri_grid);
+    memset(&out->sh, 0, sizeof(out->sh));
+    out->sh.n_base_faces = s->n_faces;                   // without a shading block every face is the base mesh's
+    if (s->shading) {
+        const ntx_instancer_shading& h = *s->shading;
+        NTX_REQUIRE(h.n_base_faces >= 0 && h.n_base_faces <= s->n_faces && h.n_param_tex >= 0 &&
+                    h.n_param_tex <= NTX_MAX_PARAM_TEXTURES && h.n_aux >= 0 && h.n_aux <= NTX_MAX_AUX_MESHES,
+                    "instancer: bad shading block");
+        NTX_REQUIRE(h.n_param_tex == 0 || (h.pool && h.mesh_uv && h.radius > 0.0f && h.min_samples >= 0 && h.n_samples >= 0),
+                    "instancer: parameter textures need the pool, the mesh UVs and a search radius");
+        NTX_REQUIRE(h.n_aux == 0 || h.mesh_n, "instancer: auxiliary meshes need vertex normals");
+        for (int i = 0; i < h.n_aux; ++i)
+            NTX_REQUIRE(h.aux_channels[i] == 0 || (h.pool && h.mesh_uv && (h.aux_channels[i] == 1 || h.aux_channels[i] == 3)),
+                        "instancer: an auxiliary mesh texture has 1 or 3 channels and needs the pool and UVs");
+        out->sh = h;
+    }
     return NTX_OK;
 }
 
 NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
                                 const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size,
-                                int n_pts, uint32_t seed, int use_mean_distance, int cast_shadow_rays, void* workspace,
-                                int32_t* n_samples, int32_t* hit, float* alpha_last, void* stream) {
+                                int n_pts, uint32_t seed, int use_mean_distance, int cast_shadow_rays, const float* parameters,
+                                int n_param, int light_dir_idx, void* workspace, int32_t* n_samples, int32_t* hit,
+                                float* alpha_last, float* color_last, void* stream) {
     NTX_REQUIRE(R >= 0 && n_pts >= 1 && step_size > 0.0f, "instancer_trace: bad arguments");
     SceneDev sc;
     int rc = check_scene(scene, &sc);
@@ -762,11 +995,13 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const 
     NTX_REQUIRE(((uintptr_t)workspace & 15) == 0, "instancer_trace: the workspace must be 16-byte aligned");
     const size_t smem = (size_t)kSmemHits * kTraceThreads * sizeof(uint64_t) + (size_t)kMailbox * kTraceThreads * sizeof(uint32_t);
     NTX_CUDA(cudaFuncSetAttribute(instancer_trace_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    NTX_REQUIRE(sc.sh.n_aux == 0 || color_last, "instancer_trace: auxiliary meshes need the color_last output");
+    NTX_REQUIRE(light_dir_idx < 0 || (parameters && light_dir_idx + 3 <= n_param), "instancer_trace: light index out of range");
     Workspace wsp = carve_workspace(workspace, R);
     if (!cast_shadow_rays) wsp.seg = nullptr;            // that part of the workspace is not there
     instancer_trace_kernel<<<(R + kTraceThreads - 1) / kTraceThreads, kTraceThreads, smem, (cudaStream_t)stream>>>(
         rays_o, rays_d, ray_ids, R, sc, b_0[0], b_0[1], b_0[2], b_1[0], b_1[1], b_1[2], step_size, n_pts, seed,
-        use_mean_distance, wsp, n_samples, hit, alpha_last);
+        use_mean_distance, wsp, n_samples, hit, alpha_last, parameters, n_param, light_dir_idx, color_last);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
@@ -792,6 +1027,7 @@ NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const 
                 "instancer_march: null output pointer");
     ShadowArgs sh;
     memset(&sh, 0, sizeof(sh));
+    sh.n_pts = n_pts;
     if (cast_shadow_rays && light_dir_idx >= 0) {        // :936 shadows only matter where a light is mapped
         NTX_REQUIRE(b_0 && b_1 && min_shadow_samples >= 0 && n_shadow_samples >= 0, "instancer_march: shadow rays need b_0 / b_1 and sample counts");
         sh.enabled = 1; sh.min_samples = min_shadow_samples; sh.n_samples = n_shadow_samples; sh.n_pts = n_pts;

@@ -12,6 +12,7 @@ the same data into the reference's dense 10-tuple for callers written against in
 
 from __future__ import annotations
 
+import ctypes as C
 import math
 from typing import Dict, Optional
 
@@ -121,13 +122,35 @@ def csr_to_dense(csr, rays_d, parameters, n_samples: int):
     return rays_d_map, pts, t, dists, color_last, alpha_last, alpha_weight, instance_id, idxs, params_map
 
 
+def load_texture(tex):
+    """loadTexture (instancer.cpp:34-52): per channel a [width, height] fp32 matrix of value / 255, columns counted from
+    the image's bottom row.  `tex`: a PNG path, or an array [h, w] / [h, w, c] of uint8 (or of floats in [0, 1])."""
+    if isinstance(tex, str):
+        from .image import decode_png
+        try:
+            with open(tex, "rb") as f:
+                img = decode_png(f.read())
+        except OSError:
+            return []                                                                  # stbi_load returns NULL: no texture
+    else:
+        img = np.asarray(tex)
+        if img.dtype != np.uint8:
+            img = np.clip(np.round(img.astype(np.float64) * 255.0), 0, 255).astype(np.uint8)
+    if img.ndim == 2:
+        img = img[:, :, None]
+    return [np.ascontiguousarray((img[::-1, :, c].T.astype(np.float32) / np.float32(255.0)).astype(np.float32))
+            for c in range(img.shape[2])]
+
+
 class Instancer:
     """Device shell instancer behind the reference's constructor (instancer/instancer.pyx:6-36): explicit patch
     `transformations` (AddInstance, instancer.cpp:125-141) and / or patches distributed on a base mesh
     (`mesh_path`, `patch_origins_path`, `patch_scale`, `jitter_amount`: DistributeInstancesOnMesh, :233-391), whose
     first hit ends a ray with an opaque black last sample (:804-814,:1019-1023).  Rays walk uniform grids over the patch
     boxes and the mesh triangles (scene_grid.py) where the reference walks Embree BVHs; shadow rays towards the light
-    (`cast_shadow_rays`, :593-603) walk the same grids.  Still refused: image parameter textures (entries other than '' / 'light' / 'point'), auxiliary meshes.
+    (`cast_shadow_rays`, :593-603) walk the same grids; image entries of `textures` (PNG files or arrays) modulate
+    their parameter through the base mesh's UVs (getParameters, :640-667); `auxiliary_meshes` = [(mesh, texture)] end
+    rays too and are shaded (AddMesh / shadeMesh, :393-418, :716-744).
     `mesh` = {'V','F','N','UV'} arrays may be given in place of `mesh_path` (procedural meshes), `patch_origins` [A,3]
     in place of `patch_origins_path`."""
 
@@ -140,24 +163,27 @@ class Instancer:
         assert instance_sampling_method in ('random', 'nearest', 'nearest_blend')      # instancer.pyx:12
         self.cast_shadow_rays = bool(cast_shadow_rays)
         self.min_shadow_samples, self.n_shadow_samples = int(min_shadow_samples), int(n_shadow_samples)
-        if auxiliary_meshes:
-            raise NotImplementedError("Instancer: auxiliary meshes (AddMesh / shadeMesh, instancer.cpp:393-418,716-744) are "
-                                      "not implemented on the device yet")
         self.light_dir_idx = self.light_strength_idx = -1
         n_parameters = 0
+        tex_channels, tex_param_idxs = [], []                                          # flat channel list, index per file
         for tex in textures:                                                           # instancer.cpp:75-92
-            if tex == 'light':                                                         # directional light: 3 parameters
+            name = tex if isinstance(tex, str) or tex is None else None
+            if name == 'light':                                                        # directional light: 3 parameters
                 self.light_dir_idx = n_parameters
                 n_parameters += 3
-            elif tex == 'point':                                                       # point light: strength + position
+            elif name == 'point':                                                      # point light: strength + position
                 self.light_strength_idx = n_parameters
                 self.light_dir_idx = n_parameters + 1
                 n_parameters += 4
-            elif tex in ('', None):
+            elif tex is None or name == '':
                 n_parameters += 1
-            else:
-                raise NotImplementedError(f"Instancer: parameter texture {tex!r} (getParameters, instancer.cpp:640-667) is "
-                                          "not implemented on the device yet")
+            else:                                                                      # an image: one parameter per channel
+                ch = load_texture(tex)
+                if not ch:                                                             # stbi_load failed: nothing is added (:38)
+                    continue
+                tex_channels += ch
+                tex_param_idxs.append(n_parameters)
+                n_parameters += len(ch)
         self.n_parameters = n_parameters
         import numpy as np
         from . import scene_grid
@@ -181,7 +207,8 @@ class Instancer:
                                                                     float(patch_scale), float(jitter_amount), seed=0)
             self.patch_scale = scale                                                    # :245 (average edge length if <= 0)
             T = np.concatenate([T, placed.astype(np.float64)], 0)
-            self.mesh = {"V": np.ascontiguousarray(m["V"], np.float32), "F": np.ascontiguousarray(m["F"], np.int32)}
+            self.mesh = {"V": np.ascontiguousarray(m["V"], np.float32), "F": np.ascontiguousarray(m["F"], np.int32),
+                         "N": np.ascontiguousarray(m["N"], np.float32), "UV": np.ascontiguousarray(m["UV"], np.float32)}
         if T.shape[0] == 0:
             raise ValueError("Instancer: no instances (empty `transformations` and no mesh)")
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
@@ -212,12 +239,71 @@ class Instancer:
         self.scene.n_inst, self.scene.n_faces = int(T.shape[0]), 0
         if use_grid:
             self._set_grid(self.scene.inst_grid, scene_grid.build_grid(world.min(1), world.max(1)), as_dev)
-        if self.mesh is not None:
-            mv, mf = as_dev(self.mesh["V"]), as_dev(self.mesh["F"], np.int32)
+        # every mesh of the scene in one vertex / face list, the base mesh first (geomID order, :374-418)
+        from . import ply as _ply
+        self.aux_meshes = []
+        for am, atex in auxiliary_meshes:                                               # instancer.pyx:25-26
+            a = _ply.read_ply(am) if isinstance(am, str) else {k: am.get(k) for k in ("V", "F", "N", "UV")}
+            if a["N"] is None:
+                raise ValueError("Instancer: an auxiliary mesh needs per-vertex normals (shadeMesh, instancer.cpp:722-724)")
+            ch = load_texture(atex) if atex is not None and not (isinstance(atex, str) and atex == "") else []
+            if ch and a["UV"] is None:
+                raise ValueError("Instancer: a textured auxiliary mesh needs texture coordinates")
+            self.aux_meshes.append({"V": np.ascontiguousarray(a["V"], np.float32), "F": np.ascontiguousarray(a["F"], np.int32),
+                                    "N": np.ascontiguousarray(a["N"], np.float32),
+                                    "UV": None if a["UV"] is None else np.ascontiguousarray(a["UV"], np.float32),
+                                    "textures": ch if len(ch) in (0, 1, 3) else ch[:1]})   # :733 other counts: first channel
+        if len(self.aux_meshes) > _lib.MAX_AUX_MESHES or len(tex_param_idxs) > _lib.MAX_PARAM_TEXTURES:
+            raise ValueError("Instancer: at most 8 auxiliary meshes and 8 parameter textures")
+        meshes = ([self.mesh] if self.mesh is not None else []) + self.aux_meshes
+        self.tex_channels, self.tex_param_idxs = tex_channels, tex_param_idxs
+        # getParameters searches the base mesh within the patch extent (:63, :246)
+        self.patch_max_extent = float(np.linalg.norm(np.maximum(np.asarray(b_0, np.float32), np.asarray(b_1, np.float32)))) * \
+            (self.patch_scale if self.mesh is not None else 1.0)
+        if meshes:
+            n_v = np.cumsum([0] + [m["V"].shape[0] for m in meshes])
+            V = np.concatenate([m["V"] for m in meshes])
+            F = np.concatenate([m["F"] + n_v[i] for i, m in enumerate(meshes)]).astype(np.int32)
+            Nn = np.concatenate([m["N"] for m in meshes])
+            UV = np.concatenate([m["UV"] if m.get("UV") is not None else np.zeros((m["V"].shape[0], 2), np.float32) for m in meshes])
+            self.scene_mesh = (V, F)
+            mv, mf = as_dev(V), as_dev(F, np.int32)
             self._keep += [mv, mf]
             self.scene.mesh_v, self.scene.mesh_f, self.scene.n_faces = mv.data_ptr(), mf.data_ptr(), int(mf.shape[0])
             if use_grid:
-                self._set_grid(self.scene.tri_grid, scene_grid.build_grid(*scene_grid.triangle_boxes(self.mesh["V"], self.mesh["F"])), as_dev)
+                self._set_grid(self.scene.tri_grid, scene_grid.build_grid(*scene_grid.triangle_boxes(V, F)), as_dev)
+            param_tex = bool(tex_param_idxs) and self.mesh is not None
+            if param_tex or self.aux_meshes:
+                sh = _lib.InstancerShading()
+                pool, chans = [], []
+
+                def add(ch):
+                    t = _lib.Texture(sum(c.size for c in pool), ch.shape[0], ch.shape[1])
+                    pool.append(np.ascontiguousarray(ch, np.float32).reshape(-1))
+                    return t
+                sh.n_base_faces = 0 if self.mesh is None else int(self.mesh["F"].shape[0])
+                if param_tex:
+                    sh.n_param_tex = len(tex_param_idxs)
+                    for i, idx in enumerate(tex_param_idxs):                            # file i <-> channel i of the flat list (:661)
+                        sh.param_idx[i] = int(idx)
+                        sh.param_tex[i] = add(tex_channels[i])
+                    sh.radius, sh.min_samples, sh.n_samples = self.patch_max_extent, int(min_texture_samples), int(n_texture_samples)
+                sh.n_aux = len(self.aux_meshes)
+                f0 = sh.n_base_faces
+                for k, am in enumerate(self.aux_meshes):
+                    sh.aux_face_begin[k] = f0
+                    f0 += int(am["F"].shape[0])
+                    sh.aux_channels[k] = len(am["textures"])
+                    for c, ch in enumerate(am["textures"]):
+                        sh.aux_tex[k][c] = add(ch)
+                sh.aux_face_begin[len(self.aux_meshes)] = f0
+                d_uv, d_n = as_dev(UV), as_dev(Nn)
+                d_pool = as_dev(np.concatenate(pool) if pool else np.zeros(1, np.float32))
+                self._keep += [d_uv, d_n, d_pool]
+                sh.mesh_uv, sh.mesh_n, sh.pool = d_uv.data_ptr(), d_n.data_ptr(), d_pool.data_ptr()
+                self._shading = sh
+                self.scene.shading = C.pointer(sh)
+        self.param_textures = bool(tex_param_idxs) and self.mesh is not None
         if transformation_export_path:
             np.save(transformation_export_path, T)                                    # instancer.pyx:33-36
 
@@ -251,7 +337,8 @@ class Instancer:
                                              use_mean_distance=self.use_mean_distance, light_strength_idx=self.light_strength_idx,
                                              blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)),   # fp32 product, instancer.cpp:696
                                              ray_ids=ray_ids, cast_shadow_rays=self.cast_shadow_rays,
-                                             min_shadow_samples=self.min_shadow_samples, n_shadow_samples=self.n_shadow_samples)
+                                             min_shadow_samples=self.min_shadow_samples, n_shadow_samples=self.n_shadow_samples,
+                                             param_textures=self.param_textures)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

@@ -231,7 +231,8 @@ def rays_from_camera(image_plane_loc, height: int, width: int, focal: float, c2w
 def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size: float, scene, b_0, b_1, *,
                               seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False,
                               light_strength_idx: int = -1, blend_range: float = 0.0, ray_ids=None,
-                              cast_shadow_rays: bool = False, min_shadow_samples: int = 4, n_shadow_samples: int = 512):
+                              cast_shadow_rays: bool = False, min_shadow_samples: int = 4, n_shadow_samples: int = 512,
+                              param_textures: bool = False):
     """Two-pass shell instancer (instancer/src/instancer.cpp:751-1037): trace + count, prefix sum, march.
     `scene`: _lib.InstancerScene (device pointers kept alive by the caller).  `ray_ids` [R] int32: the rays' names for
     the random draws.  Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box or
@@ -249,11 +250,14 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     hit = torch.empty(R, dtype=torch.int32, device=dev)
     alpha_last_all = torch.empty(R, dtype=torch.float32, device=dev)
     shadows = int(bool(cast_shadow_rays) and light_dir_idx >= 0)
-    ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R, shadows)), 16), dtype=torch.uint8, device=dev)
+    segments = int(shadows or param_textures)          # both look samples up along the ray's segments
+    ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R, segments)), 16), dtype=torch.uint8, device=dev)
+    color_last_all = torch.empty((R, 3), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
         check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), ptr(ray_ids), R, C.byref(scene), b0, b1,
-                                      float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)), shadows,
-                                      ptr(ws), ptr(n_samples), ptr(hit), ptr(alpha_last_all), stream_ptr()))
+                                      float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)), segments,
+                                      ptr(parameters) if p > 0 else None, p, int(light_dir_idx),
+                                      ptr(ws), ptr(n_samples), ptr(hit), ptr(alpha_last_all), ptr(color_last_all), stream_ptr()))
         ray_ptr_all = torch.zeros(R + 1, dtype=torch.int64, device=dev)
         torch.cumsum(n_samples, 0, out=ray_ptr_all[1:])
         ray_index = torch.nonzero(hit).squeeze(1)
@@ -273,7 +277,7 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     out["ray_ptr"] = torch.cat([ray_ptr_all[:-1][ray_index], ray_ptr_all[-1:]]) if H > 0 else torch.zeros(1, dtype=torch.int64, device=dev)
     out["ray_index"] = ray_index.to(torch.int32)
     out["n_samples_all"] = n_samples
-    out["color_last"] = torch.zeros((H, 3), dtype=torch.float32, device=dev)      # base mesh: black (instancer.cpp:1019-1021)
+    out["color_last"] = color_last_all[ray_index].contiguous()                     # black on the base mesh, shaded on auxiliary ones
     out["alpha_last"] = alpha_last_all[ray_index].contiguous()                     # 1 where the ray ends on the mesh
     return out
 

@@ -58,6 +58,28 @@ def shard_index(n_rays: int, rank: int, world: int, block: int, interleave: bool
     return torch.arange(sl.start, sl.stop, device=device)
 
 
+_PLAN_CACHE: dict = {}
+
+
+def shard_plan(n_rays: int, world: int, block: int, interleave: bool, device):
+    """(per, [index tensor of every rank], gather) for one way of splitting a frame, built once per shape: `per` is the
+    padded share length, `gather[i]` the row of the [world * per] gathered buffer that holds ray i."""
+    key = (n_rays, world, block, bool(interleave), str(device))
+    plan = _PLAN_CACHE.get(key)
+    if plan is None:
+        idx = [shard_index(n_rays, r, world, block, interleave, device) for r in range(world)]
+        per = max(int(i.shape[0]) for i in idx)
+        if not interleave:
+            per = max(per, shard_rays(n_rays, 0, world, block).stop)
+        gather = torch.empty(n_rays, dtype=torch.int64, device=device)
+        for r, i in enumerate(idx):
+            gather[i] = r * per + torch.arange(i.shape[0], device=device)
+        if len(_PLAN_CACHE) > 16:
+            _PLAN_CACHE.clear()
+        plan = _PLAN_CACHE[key] = (per, idx, gather)
+    return plan
+
+
 def render_sharded(renderer, rays_o, rays_d, t, parameters, cone_scale, *, group=None, block: int = 16,
                    interleave: Optional[bool] = None, **kwargs) -> Dict[str, torch.Tensor]:
     """`renderer(rays_o[B,Nr,3], rays_d, t[B,Nr,2], parameters[B,p], cone_scale[B,Nr,1], **kwargs)` with the Nr axis
@@ -73,11 +95,8 @@ def render_sharded(renderer, rays_o, rays_d, t, parameters, cone_scale, *, group
     if interleave is None:
         from .renderer import InstanceRenderer
         interleave = isinstance(renderer, InstanceRenderer)
-    if interleave:
-        per = max(stripe_count(Nr, r, world, block) for r in range(world))
-    else:
-        per = shard_rays(Nr, 0, world, block).stop                             # block length of every rank but the last
-    idx = shard_index(Nr, rank, world, block, interleave, dev)
+    per, all_idx, gather_rows = shard_plan(Nr, world, block, interleave, dev)
+    idx = all_idx[rank]
     n_mine = int(idx.shape[0])
     out: Dict[str, torch.Tensor] = {}
     from .renderer import InstanceRenderer
@@ -112,11 +131,7 @@ def render_sharded(renderer, rays_o, rays_d, t, parameters, cone_scale, *, group
     dist.all_gather_into_tensor(gathered.view(-1), rec, group=group)
     if not bool((gathered[:, -1] > 0).any()):                                   # no ray of the frame hit: renderer.py returns {}
         return {}
-    bodies = gathered[:, :-1].reshape(world, per, B, C)
-    full = torch.empty((Nr, B, C), dtype=torch.float32, device=dev)
-    for r in range(world):
-        ridx = shard_index(Nr, r, world, block, interleave, dev)
-        full[ridx] = bodies[r, :ridx.shape[0]]
+    full = gathered[:, :-1].reshape(world * per, B, C)[gather_rows]             # ray order of the frame, one gather
     res: Dict[str, torch.Tensor] = {}
     col = 0
     for k, w in zip(keys, widths):

@@ -218,6 +218,132 @@ def is_shadowed(pt, direction, minv, b0, b1, mesh=None):
     return False
 
 
+def texture_channels(img_u8):
+    """loadTexture (instancer.cpp:34-52): one [width, height] fp32 matrix per channel, value / 255, rows indexed by the
+    pixel column x and columns by the image row counted from the BOTTOM (the rowwise().reverse() of :46)."""
+    img = np.asarray(img_u8)
+    if img.ndim == 2:
+        img = img[:, :, None]
+    return [np.ascontiguousarray((img[::-1, :, c].T.astype(F) / F(255.0)).astype(F)) for c in range(img.shape[2])]
+
+
+def interpolate2d(uv, tex):
+    """instancer.cpp:606-626: bilinear lookup of tex[rows, cols] at uv in [0, 1]^2 (indices clamped at the far edge,
+    where the reference would read one past the end with weight 0)."""
+    rows, cols = tex.shape
+    x0, x1 = F(F(uv[0]) * F(rows - 1)), F(F(uv[1]) * F(cols - 1))
+    i0, j0 = int(x0), int(x1)
+    w0, w1 = F(x0 - F(np.floor(x0))), F(x1 - F(np.floor(x1)))
+    i0, j0 = min(max(i0, 0), rows - 1), min(max(j0, 0), cols - 1)
+    i1, j1 = min(i0 + 1, rows - 1), min(j0 + 1, cols - 1)
+    m0, m1 = F(F(1) - w0), F(F(1) - w1)
+    y = F(F(tex[i0, j0] * m0) * m1)
+    y = F(y + F(F(tex[i0, j1] * m0) * w1))
+    y = F(y + F(F(tex[i1, j0] * w0) * m1))
+    return F(y + F(F(tex[i1, j1] * w0) * w1))
+
+
+def closest_face(pt, V, Fc, radius):
+    """The rtcPointQuery of instancer.cpp:628-647 with closest_point_query_function (:201-231): the face nearest to
+    `pt` within `radius` (strictly), ties to the smaller face index, and the barycentric weights of the closest point;
+    fp32 in the fixed order below.  None if no face is in range."""
+    pt = np.asarray(pt, F)
+    a, b, c = V[Fc[:, 0]], V[Fc[:, 1]], V[Fc[:, 2]]
+    dot = lambda x, y: _vdot3(x, [y[:, 0], y[:, 1], y[:, 2]]) if False else (
+        ((x[:, 0] * y[:, 0]).astype(F) + (x[:, 1] * y[:, 1]).astype(F)).astype(F) + (x[:, 2] * y[:, 2]).astype(F)).astype(F)
+    sub = lambda x, y: (x - y).astype(F)
+    ab, ac, ap = sub(b, a), sub(c, a), sub(pt[None, :], a)
+    d1, d2 = dot(ab, ap), dot(ac, ap)
+    bp = sub(pt[None, :], b)
+    d3, d4 = dot(ab, bp), dot(ac, bp)
+    cp = sub(pt[None, :], c)
+    d5, d6 = dot(ab, cp), dot(ac, cp)
+    mul = lambda x, y: (x * y).astype(F)
+    vc = sub(mul(d1, d4), mul(d3, d2))
+    vb = sub(mul(d5, d2), mul(d1, d6))
+    va = sub(mul(d3, d6), mul(d5, d4))
+    n = Fc.shape[0]
+    uvw = np.zeros((n, 3), F)
+    done = np.zeros(n, bool)
+
+    def take(mask, w0, w1, w2):
+        m = mask & ~done
+        uvw[m, 0], uvw[m, 1], uvw[m, 2] = w0[m], w1[m], w2[m]
+        done[m] = True
+    one, zero = np.ones(n, F), np.zeros(n, F)
+    with np.errstate(divide="ignore", invalid="ignore", over="ignore"):
+        take((d1 <= 0) & (d2 <= 0), one, zero, zero)
+        take((d3 >= 0) & (d4 <= d3), zero, one, zero)
+        take((d6 >= 0) & (d5 <= d6), zero, zero, one)
+        v = (d1 / sub(d1, d3)).astype(F)
+        take((vc <= 0) & (d1 >= 0) & (d3 <= 0), sub(one, v), v, zero)
+        v = (d2 / sub(d2, d6)).astype(F)
+        take((vb <= 0) & (d2 >= 0) & (d6 <= 0), sub(one, v), zero, v)
+        e43, e56 = sub(d4, d3), sub(d5, d6)
+        v = (e43 / (e43 + e56).astype(F)).astype(F)
+        take((va <= 0) & (e43 >= 0) & (e56 >= 0), zero, sub(one, v), v)
+        denom = (F(1) / ((va + vb).astype(F) + vc).astype(F)).astype(F)
+        v, w = mul(vb, denom), mul(vc, denom)
+        take(np.ones(n, bool), sub(sub(one, v), w), v, w)
+    # closest point = a * u + b * v + c * w (the same form for every region), distance to it
+    q = ((a * uvw[:, 0:1]).astype(F) + (b * uvw[:, 1:2]).astype(F)).astype(F)
+    q = (q + (c * uvw[:, 2:3]).astype(F)).astype(F)
+    df = sub(pt[None, :], q)
+    d = np.sqrt(dot(df, df)).astype(F)
+    ok = d < F(radius)
+    if not ok.any():
+        return None
+    cand = np.nonzero(ok)[0]
+    best = cand[np.lexsort((cand, d[cand]))[0]]
+    return int(best), uvw[best].copy()
+
+
+def get_parameters(pt, parameters, V, Fc, UV, textures, texture_idxs, radius):
+    """getParameters (instancer.cpp:628-667): the parameters of a point, each textured one multiplied by its texture at
+    the UV of the nearest point of the base mesh (unchanged if the mesh is farther than `radius`).  Literal to :661:
+    the i-th texture FILE multiplies parameter texture_idxs[i] by channel i of the flat channel list."""
+    out = np.asarray(parameters, F).copy()
+    hit = closest_face(pt, V, Fc, radius)
+    if hit is None:
+        return out
+    f, w = Fc[hit[0]], hit[1]
+    uv = [F(F(F(UV[f[0], k] * w[0]) + F(UV[f[1], k] * w[1])) + F(UV[f[2], k] * w[2])) for k in range(2)]
+    for i, idx in enumerate(texture_idxs):
+        out[idx] = F(out[idx] * interpolate2d(uv, textures[i]))
+    return out
+
+
+def shade_mesh(pt, am, prim, uvw, light_raw, minv, b0, b1, mesh, diffuse=F(1.0), ambient=F(0.2)):
+    """shadeMesh (instancer.cpp:716-744): albedo (texture at the hit's UV, or 0.8) times min(diffuse + ambient, 1);
+    diffuse = max(n . l, 0) unless the point, lifted 1e-6 along the normal, is shadowed.  Without a light parameter the
+    reference reads an uninitialised vector; here that case is ambient only."""
+    f = np.asarray(am["F"], np.int64)[prim]
+    Nm = np.asarray(am["N"], F)
+    n = [F(F(F(Nm[f[0], k] * uvw[0]) + F(Nm[f[1], k] * uvw[1])) + F(Nm[f[2], k] * uvw[2])) for k in range(3)]
+    nn = _norm3(n)
+    n = [F(n[k] / nn) for k in range(3)]
+    tex = am.get("textures") or []
+    if not tex:
+        albedo = [F(0.8)] * 3
+    else:
+        UVm = np.asarray(am["UV"], F)
+        uv = [F(F(F(UVm[f[0], k] * uvw[0]) + F(UVm[f[1], k] * uvw[1])) + F(UVm[f[2], k] * uvw[2])) for k in range(2)]
+        a = [interpolate2d(uv, ch) for ch in tex]
+        albedo = a if len(a) == 3 else [a[0]] * 3
+    if light_raw is None:
+        diffuse = F(0)
+    else:
+        lifted = [F(F(pt[k]) + F(n[k] * F(1e-6))) for k in range(3)]
+        if not is_shadowed(lifted, light_raw, minv, b0, b1, mesh):
+            ln = _norm3(light_raw)
+            ld = [F(light_raw[k] / ln) for k in range(3)]
+            diffuse = F(diffuse * max(_dot3(n, ld), F(0)))
+        else:
+            diffuse = F(0)
+    shade = min(F(diffuse + ambient), F(1))
+    return [F(albedo[k] * shade) for k in range(3)]
+
+
 def mean_distance(mu, hw):
     """instancer.cpp:746-748 (std::pow promotes to double)."""
     mu, hw = float(mu), float(hw)
@@ -226,14 +352,32 @@ def mean_distance(mu, hw):
 
 def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformations, b_0, b_1, *, seed=0,
                     light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1, patch_scale=1.0,
-                    mesh=None, ray_ids=None, cast_shadow_rays=False, min_shadow_samples=4, n_shadow_samples=512):
+                    mesh=None, ray_ids=None, cast_shadow_rays=False, min_shadow_samples=4, n_shadow_samples=512,
+                    texture=None, aux_meshes=None):
     """Returns the CSR form over ALL rays: n_samples[R], hit[R], alpha_last[R], color_last[R,3] and per-sample
     records.  `mesh` = (V[n,3], F[m,3]): the base mesh the patches sit on (a ray ends at its first hit).  `ray_ids`:
     the identity of every ray for the random draws (default: its index in this call), so that a frame cut into chunks
-    or spread over GPUs draws the same numbers."""
+    or spread over GPUs draws the same numbers.  `texture` = dict(UV=[n,2] of the base mesh, textures=[channel
+    matrices], idxs=[parameter index per texture file], radius, min_samples, n_samples): parameter textures
+    (:640-667, :916-926, :985-991).  `aux_meshes` = [dict(V, F, N, UV or None, textures=[channel matrices])]: meshes
+    added with AddMesh (:393-418) — they end rays like the base mesh and colour the last sample with shadeMesh (:716-744)."""
     rays_o, rays_d, parameters = np.asarray(rays_o, F), np.asarray(rays_d, F), np.asarray(parameters, F)
+    base = None
     if mesh is not None:
-        mesh = (np.ascontiguousarray(mesh[0], F), np.ascontiguousarray(mesh[1], np.int64))
+        base = (np.ascontiguousarray(mesh[0], F), np.ascontiguousarray(mesh[1], np.int64))
+    n_base_faces = 0 if base is None else base[1].shape[0]
+    aux_ranges = []
+    if aux_meshes:                                                   # one face list in (geomID, primID) order (:444-455)
+        Vs, Fs = ([base[0]], [base[1]]) if base is not None else ([], [])
+        n_v, n_f = sum(v.shape[0] for v in Vs), n_base_faces
+        for am in aux_meshes:
+            Vs.append(np.ascontiguousarray(am["V"], F))
+            Fs.append(np.ascontiguousarray(am["F"], np.int64) + n_v)
+            aux_ranges.append((n_f, n_f + Fs[-1].shape[0]))
+            n_v, n_f = n_v + Vs[-1].shape[0], n_f + Fs[-1].shape[0]
+        mesh = (np.concatenate(Vs), np.concatenate(Fs))
+    else:
+        mesh = base
     minv, dirt, origins = prepare_instances(transformations)
     b0, b1 = np.asarray(b_0, F), np.asarray(b_1, F)
     step_size = F(step_size)
@@ -255,6 +399,11 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         hit[i] = True
         if mh is not None:                                          # :1019-1023 (instancer mesh: black, opaque)
             alpha_last[i] = F(1)
+            for am, (f0, f1) in zip(aux_meshes or [], aux_ranges):   # an auxiliary mesh: shaded (:1022)
+                if f0 <= mh[1] < f1:
+                    raw = parameters[i, light_dir_idx:light_dir_idx + 3] if light_dir_idx >= 0 else None
+                    color_last[i] = shade_mesh([F(o[a] + F(mh[0] * d[a])) for a in range(3)], am, mh[1] - f0,
+                                               [F(F(F(1) - mh[2]) - mh[3]), mh[2], mh[3]], raw, minv, b0, b1, mesh)
         # :801-827 total in-shell length
         active, total, t_entry = set(), F(0), F(0)
         segment_lengths = []
@@ -304,6 +453,13 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         shadow_interp = shadow_on and n_shadow < n_pts
         raw_light = parameters[i, light_dir_idx:light_dir_idx + 3].copy() if light_dir_idx >= 0 else None
         seg_l, sh_step, sh_entry = 0, F(0), F(0)
+        # parameter textures (:864, :916-926, :985-991): like the shadows, but linearly interpolated
+        tex_on = texture is not None and len(texture["idxs"]) > 0 and base is not None
+        n_tex = max(int(texture["min_samples"]), int(F(F(texture["n_samples"]) * total_len))) if tex_on else 0
+        tex_interp = tex_on and n_tex < n_pts
+        tx_step, tx_entry = F(0), F(0)
+        textured = lambda tq: get_parameters([F(o[a] + F(F(tq) * d[a])) for a in range(3)], parameters[i], base[0], base[1],
+                                             texture["UV"], texture["textures"], texture["idxs"], texture["radius"])
         occluded = lambda tq: is_shadowed([F(o[a] + F(F(tq) * d[a])) for a in range(3)], raw_light, minv, b0, b1, mesh)
         for tt, inst in hits + ([(float(mh[0]), -1)] if mh is not None else []):
             tt = F(tt)
@@ -349,6 +505,18 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 recs["pts"].append([_dot3(M[a, :3], pt, M[a, 3]) for a in range(3)])        # getPt :556-558
                 recs["dirs"].append([_dot3(dirt[sel][a], dn) for a in range(3)])           # getDir :561-563
                 prm = parameters[i].copy()
+                if tex_interp:                                      # :916-923
+                    k = 1
+                    while t_pt > F(tx_entry + F(F(k) * tx_step)):
+                        k += 1
+                    t0 = tx_entry if k == 1 else F(tx_entry + F(F(k - 1) * tx_step))
+                    t1 = F(tx_entry + F(F(k) * tx_step))
+                    wt = F(F(t_pt - t0) / tx_step)
+                    s0, s1 = textured(t0), textured(t1)
+                    prm = ((s0 * F(F(1) - wt)).astype(F) + (s1 * wt).astype(F)).astype(F)
+                elif tex_on:                                        # :924-926
+                    prm = get_parameters(pt, parameters[i], base[0], base[1], texture["UV"], texture["textures"],
+                                         texture["idxs"], texture["radius"])
                 shadowed = False
                 if shadow_interp:                                   # :937-948 nearest of the two shadow samples around t_pt
                     k = 1
@@ -396,6 +564,10 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                         seg_len = segment_lengths[seg_l]
                         n_seg = max(int(min_shadow_samples), int(F(F(F(n_shadow) * seg_len) / total_len)))
                         sh_step, sh_entry = F(seg_len / F(n_seg - 1)), t_entry
+                    if tex_interp:                                  # :985-991
+                        seg_len = segment_lengths[seg_l]
+                        n_seg = max(int(texture["min_samples"]), int(F(F(F(n_tex) * seg_len) / total_len)))
+                        tx_step, tx_entry = F(seg_len / F(n_seg - 1)), t_entry
                     seg_l += 1
                 active.add(inst)
         n_samples[i] = emitted

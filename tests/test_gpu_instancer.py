@@ -151,10 +151,10 @@ def test_edge_inputs():
     # refusals: a mesh file that is not there, and what is not on the device yet
     with pytest.raises((OSError, ValueError)):
         Instancer(B0, B1, mesh_path="meshes/no_such_mesh.ply")
-    with pytest.raises(NotImplementedError):
-        Instancer(B0, B1, transformations=Ts.tolist(), auxiliary_meshes=[("meshes/table.ply", "")])
-    with pytest.raises(NotImplementedError):
-        Instancer(B0, B1, transformations=Ts.tolist(), textures=["textures/height.png"])
+    with pytest.raises((OSError, ValueError)):
+        Instancer(B0, B1, transformations=Ts.tolist(), auxiliary_meshes=[("meshes/no_such_table.ply", "")])
+    # a texture file that cannot be read adds no parameter (stbi_load returns NULL, instancer.cpp:38-50)
+    assert Instancer(B0, B1, transformations=Ts.tolist(), textures=["", "textures/no_such.png", "light"]).n_parameters == 4
     with pytest.raises(ValueError):
         Instancer(B0, B1)
     with pytest.raises(RuntimeError):
@@ -393,3 +393,84 @@ def test_shadow_rays(light, use_grid, n_shadow):
     assert 0.05 < dark.mean() < 0.95, dark.mean()                                      # both outcomes occur
     unshadowed = IO.get_model_input(o, d, prm, n_pts, 0.004, inst.transformations, CB0, CB1, **ref)
     assert np.array_equal(unshadowed["params"][~dark], want["params"][~dark])          # lit samples are untouched
+
+
+def checker_texture(n=32, cells=4, seed=0):
+    rng = np.random.default_rng(seed)
+    yy, xx = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    img = (((xx * cells // n) + (yy * cells // n)) % 2) * 200 + rng.integers(0, 50, (n, n))
+    return img.astype(np.uint8)
+
+
+@pytest.mark.parametrize("use_grid,n_tex", [(True, 64), (False, 64), (True, 4000)])
+def test_parameter_textures(use_grid, n_tex, tmp_path):
+    """Image entries of `textures` (getParameters, instancer.cpp:640-667): nearest base-mesh point -> UV -> bilinear
+    lookup -> the parameter is multiplied; sampled along the ray's segments and linearly interpolated (n_tex < n_pts) or
+    looked up per sample.  One texture comes from a PNG file, one from an array.  Bit-exact."""
+    from nerf_tex_b200.image import encode_png
+    from nerf_tex_b200.instancer import Instancer
+    mesh, anchors, floating = shadow_scene(seed=11)
+    img0, img1 = checker_texture(32, 4, 1), checker_texture(17, 3, 2)
+    with open(tmp_path / "checker.png", "wb") as f:
+        f.write(encode_png(img0[:, :, None]))
+    textures = [str(tmp_path / "checker.png"), "", img1, "light"]
+    inst = Instancer(CB0, CB1, textures=textures, mesh=mesh, patch_origins=anchors, patch_scale=0.09, jitter_amount=1.0,
+                     instance_sampling_method="nearest", use_grid=use_grid, min_texture_samples=8, n_texture_samples=n_tex)
+    assert inst.n_parameters == 6 and inst.light_dir_idx == 3 and inst.tex_param_idxs == [0, 2]
+    rng = np.random.default_rng(12)
+    R = 250
+    o = np.stack([rng.uniform(-1.4, 1.4, R), rng.uniform(-1.4, 1.4, R), rng.uniform(0.7, 2.0, R)], 1).astype(np.float32)
+    d = np.stack([rng.uniform(-1, 1, R), rng.uniform(-1, 1, R), np.full(R, -1.0)], 1).astype(np.float32)
+    prm = np.tile(np.array([[0.9, 0.4, 0.7, 0.2, 0.1, 1.0]], np.float32), (R, 1))
+    tex = dict(UV=mesh["UV"], textures=IO.texture_channels(img0) + IO.texture_channels(img1), idxs=[0, 2],
+               radius=inst.patch_max_extent, min_samples=8, n_samples=n_tex)
+    n_pts = 128
+    want = IO.get_model_input(o, d, prm, n_pts, 0.004, inst.transformations, CB0, CB1, seed=3, light_dir_idx=3, method="nearest",
+                              patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), texture=tex)
+    cu = lambda a: torch.as_tensor(a).cuda()
+    got = inst.get_model_input_csr(cu(o), cu(d), cu(prm), n_pts, 0.004, seed=3)
+    check_records(got, want, R)
+    p = want["params"]
+    assert np.allclose(p[:, 1], 0.4, atol=1e-6) and p[:, 0].min() < 0.2 < 0.6 < p[:, 0].max() <= np.float32(0.9)   # both checker colours
+    assert len(np.unique(p[:, 2])) > 50 and p[:, 2].max() <= np.float32(0.7)
+
+
+def test_auxiliary_meshes_end_rays_and_are_shaded(tmp_path):
+    """AddMesh / shadeMesh (instancer.cpp:393-418, 716-744): a textured table top and an untextured wall beside the
+    carpet, directional light, shadows on; rays that end on them carry the shaded colour, on the base mesh black."""
+    from nerf_tex_b200 import ply
+    from nerf_tex_b200.instancer import Instancer
+    mesh, anchors, floating = shadow_scene(seed=13)
+    table = plane_mesh(4, 0.5, z=0.45)                                       # above part of the carpet, facing +z
+    table["V"][:, 0] += 0.3
+    wall = plane_mesh(3, 0.8, z=0.0)
+    wall["V"] = np.stack([np.full(16, -1.45), wall["V"][:, 0], wall["V"][:, 1] + 0.6], 1).astype(np.float32)   # x = -1.45 plane
+    wall["N"] = np.tile(np.array([[1, 0, 0]], np.float32), (16, 1))
+    ply.write_ply(str(tmp_path / "wall.ply"), wall["V"], wall["F"], wall["N"], wall["UV"])
+    rgb = np.stack([checker_texture(16, 2, 3), checker_texture(16, 2, 4), checker_texture(16, 2, 5)], -1)
+    aux = [(table, rgb), (str(tmp_path / "wall.ply"), "")]
+    inst = Instancer(CB0, CB1, textures=["", "light"], mesh=mesh, patch_origins=anchors, patch_scale=0.09, jitter_amount=1.0,
+                     instance_sampling_method="nearest", cast_shadow_rays=True, min_shadow_samples=8, n_shadow_samples=64,
+                     auxiliary_meshes=aux)
+    rng = np.random.default_rng(14)
+    R = 400
+    o = np.stack([rng.uniform(-1.4, 1.4, R), rng.uniform(-1.4, 1.4, R), rng.uniform(0.9, 2.0, R)], 1).astype(np.float32)
+    d = np.stack([rng.uniform(-1, 1, R), rng.uniform(-1, 1, R), np.full(R, -1.0)], 1).astype(np.float32)
+    d[::4] = np.array([-1.0, 0.1, -0.2], np.float32) + rng.uniform(-.1, .1, (len(d[::4]), 3)).astype(np.float32)   # towards the wall
+    prm = np.tile(np.array([[0.7, 0.3, 0.2, 0.9]], np.float32), (R, 1))
+    aux_o = [dict(V=table["V"], F=table["F"], N=table["N"], UV=table["UV"], textures=IO.texture_channels(rgb)),
+             dict(V=wall["V"], F=wall["F"], N=wall["N"], UV=wall["UV"], textures=[])]
+    want = IO.get_model_input(o, d, prm, 128, 0.004, inst.transformations, CB0, CB1, seed=3, light_dir_idx=1, method="nearest",
+                              patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), cast_shadow_rays=True, min_shadow_samples=8,
+                              n_shadow_samples=64, aux_meshes=aux_o)
+    cu = lambda a: torch.as_tensor(a).cuda()
+    got = inst.get_model_input_csr(cu(o), cu(d), cu(prm), 128, 0.004, seed=3)
+    check_records(got, want, R)
+    hit = want["hit"]
+    gc = got["color_last"].cpu().numpy()
+    assert np.array_equal(gc.view(np.uint32), want["color_last"][hit].view(np.uint32))
+    assert np.array_equal(got["alpha_last"].cpu().numpy(), want["alpha_last"][hit])
+    coloured = want["color_last"].any(-1)
+    assert coloured.sum() > 40 and (want["alpha_last"][~coloured] == 1).sum() > 40        # auxiliary hits and base-mesh hits
+    grey = coloured & (want["color_last"][:, 0] == want["color_last"][:, 1]) & (want["color_last"][:, 1] == want["color_last"][:, 2])
+    assert grey.any() and (coloured & ~grey).any()                                         # the wall (0.8 grey) and the textured table

@@ -156,3 +156,51 @@ def test_oracle_shadow_rays_closed_form():
     dark2 = IO.get_model_input(o, d, np.array([[0.5, 0, 0, -2.0]], np.float32), 8, 0.02, [np.eye(4)], B0, B1,
                                **dict(kw, min_shadow_samples=100))
     assert np.all(dark2["params"][:, 1:] == [0, 0, -1])
+
+
+def test_oracle_textures_and_aux_mesh_closed_form():
+    """interpolate2d / loadTexture orientation, getParameters through the base mesh's UVs, shadeMesh."""
+    img = (np.arange(12, dtype=np.uint8).reshape(3, 4) * 20)                # img[y, x] = (4 y + x) * 20, y from the top
+    tex = IO.texture_channels(img)[0]
+    assert tex.shape == (4, 3)                                               # [width, height]
+    assert IO.interpolate2d([0, 0], tex) == np.float32(160 / 255)            # u = v = 0: bottom-left pixel
+    assert IO.interpolate2d([1, 1], tex) == np.float32(60 / 255)             # top-right
+    np.testing.assert_allclose(IO.interpolate2d([0.5, 0.5], tex), 110 / 255, rtol=1e-6)    # centre: mean of the four middle pixels
+    np.testing.assert_allclose(IO.interpolate2d([1 / 3, 0.0], tex), 180 / 255, rtol=1e-6)  # on a pixel centre: that pixel
+    V = np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]], np.float32)
+    F = np.array([[0, 1, 2], [0, 2, 3]])
+    UV = np.array([[0, 0], [1, 0], [1, 1], [0, 1]], np.float32)
+    # a point above (x, y): nearest mesh point is (x, y, 0), UV = ((x + 1) / 2, (y + 1) / 2)
+    out = IO.get_parameters([-1.0, -1.0, 0.3], np.array([2.0, 5.0], np.float32), V, F, UV, [tex], [1], radius=1.0)
+    assert out[0] == 2 and out[1] == np.float32(5.0) * np.float32(160 / 255)
+    far = IO.get_parameters([0.0, 0.0, 3.0], np.array([2.0, 5.0], np.float32), V, F, UV, [tex], [1], radius=1.0)
+    assert np.array_equal(far, [2.0, 5.0])                                   # the mesh is out of reach: unchanged
+    f, w = IO.closest_face([0.2, -0.5, 0.3], V, F, 5.0)
+    assert f == 0 and np.allclose(V[F[0]].T @ w, [0.2, -0.5, 0.0], atol=1e-6)
+    assert IO.closest_face([3.0, 0.0, 0.0], V, F, 5.0)[0] == 0 and IO.closest_face([3.0, 0.0, 0.0], V, F, 1.0) is None
+    # shadeMesh: a floor facing +z lit from (0, 0, 1): diffuse 1 -> 0.8 * min(1 + 0.2, 1); lit at 60 degrees: 0.8 * 0.7
+    am = {"V": V, "F": F, "N": np.tile(np.array([[0, 0, 1]], np.float32), (4, 1)), "UV": UV, "textures": []}
+    M = IO.prepare_instances([np.eye(4)])[0][:0]                             # no patch boxes around
+    b0, b1 = np.float32([-.5, -.5, -.1]), np.float32([.5, .5, .1])
+    c = IO.shade_mesh([0.2, 0.1, 0.0], am, 0, [0.3, 0.3, 0.4], np.float32([0, 0, 2.0]), M, b0, b1, (V, F))
+    np.testing.assert_allclose(c, [0.8, 0.8, 0.8], rtol=1e-6)
+    c = IO.shade_mesh([0.2, 0.1, 0.0], am, 0, [0.3, 0.3, 0.4], np.float32([np.sqrt(3.0), 0, 1.0]), M, b0, b1, (V, F))
+    np.testing.assert_allclose(c, [0.56, 0.56, 0.56], rtol=1e-5)
+    c = IO.shade_mesh([0.2, 0.1, 0.0], am, 0, [0.3, 0.3, 0.4], np.float32([0, 0, -1.0]), M, b0, b1, (V, F))
+    np.testing.assert_allclose(c, [0.16, 0.16, 0.16], rtol=1e-6)            # light from behind: ambient only
+    am_t = dict(am, textures=[tex])                                          # one channel colours all three
+    c = IO.shade_mesh([-1.0, -1.0, 0.0], am_t, 0, [1.0, 0.0, 0.0], np.float32([0, 0, 1.0]), M, b0, b1, (V, F))
+    np.testing.assert_allclose(c, [160 / 255] * 3, rtol=1e-6)
+    # through get_model_input: a ray that ends on an auxiliary floor carries its shaded colour, on the base mesh black
+    o, d = np.array([[0.1, -0.2, 3.0]], np.float32), np.array([[0, 0, -1.0]], np.float32)
+    prm = np.array([[0.5, 0, 0, 1.0]], np.float32)
+    Vl = V - np.array([0, 0, 0.5], np.float32)                                # a floor below the patch box
+    am = dict(am, V=Vl)
+    aux = IO.get_model_input(o, d, prm, 64, 0.02, [np.eye(4)], [-.5, -.5, -.1], [.5, .5, .1], seed=1, light_dir_idx=1, aux_meshes=[am])
+    base = IO.get_model_input(o, d, prm, 64, 0.02, [np.eye(4)], [-.5, -.5, -.1], [.5, .5, .1], seed=1, light_dir_idx=1, mesh=(Vl, F))
+    assert aux["alpha_last"][0] == base["alpha_last"][0] == 1 and np.array_equal(aux["t"], base["t"])
+    assert not base["color_last"].any()
+    np.testing.assert_allclose(aux["color_last"][0], [0.16] * 3, rtol=1e-6)  # under the patch: its bottom face shadows the floor
+    side = IO.get_model_input(np.array([[0.9, 0.9, 3.0]], np.float32), d, prm, 64, 0.02, [np.eye(4)], [-.5, -.5, -.1], [.5, .5, .1],
+                              seed=1, light_dir_idx=1, aux_meshes=[am])
+    np.testing.assert_allclose(side["color_last"][0], [0.8] * 3, rtol=1e-6)  # beside the patch: fully lit
