@@ -179,3 +179,103 @@ def test_train_config_forward_gradients_and_step(name):
                                 np.zeros(g.numel(), np.float32), 1, c["lrate"])
     np.testing.assert_allclose(gm.master.detach().cpu().numpy(), stepped, rtol=1e-5, atol=1e-7)
     assert abs(tr.current_lr() - O.exponential_decay_lr(c["lrate"], c["lrate_decay"], 1)) < 1e-12
+
+
+# ----------------------------------------------------------------------------------------------- the device instancer
+def procedural_assets(root, ic):
+    """Files with the names an instancer_config asks for, generated: a hilly plane with normals and UVs for the mesh,
+    points on it for the patch origins, noisy checkerboards for the textures (the reference's assets are git-LFS stubs)."""
+    from nerf_tex_b200 import ply
+    from nerf_tex_b200.image import encode_png
+    from test_gpu_instancer import checker_texture, plane_mesh
+    rng = np.random.default_rng(21)
+    mesh = plane_mesh(20, 1.5, wobble=0.12)
+    os.makedirs(os.path.join(root, os.path.dirname(ic["mesh_path"])), exist_ok=True)
+    ply.write_ply(os.path.join(root, ic["mesh_path"]), mesh["V"], mesh["F"], mesh["N"], mesh["UV"])
+    anchors = None
+    if ic.get("patch_origins_path"):
+        xy = rng.uniform(-1.3, 1.3, (260, 2))
+        anchors = np.concatenate([xy, 0.12 * np.sin(2.1 * xy[:, :1]) * np.cos(1.7 * xy[:, 1:])], 1).astype(np.float32)
+        ply.write_ply(os.path.join(root, ic["patch_origins_path"]), anchors)
+    images = {}
+    for k, tex in enumerate(ic.get("textures", [])):
+        if tex not in ("", "light", "point"):
+            images[tex] = checker_texture(24, 3, seed=k)
+            with open(os.path.join(root, tex), "wb") as f:
+                f.write(encode_png(images[tex][:, :, None]))
+    return mesh, anchors, images
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", RENDER)
+def test_render_config_on_the_device_instancer(name, tmp_path, monkeypatch):
+    """Every shipped render config, instancer_config included, UNCHANGED through util.instantiate: mesh + anchor PLYs,
+    texture PNGs, shadow rays, point / directional lights, 'nearest' / 'nearest_blend' — on generated assets of the same
+    file names.  Records bit-exact against the instancer oracle, rendered colour / alpha against the oracle chain."""
+    from nerf_tex_b200 import util
+    from oracle import instancer_oracle as IO
+    c = copy.deepcopy(CONFIGS[name])
+    rc, ic = c["renderer_config"], c["renderer_config"]["instancer_config"]
+    mesh, anchors, images = procedural_assets(str(tmp_path), ic)
+    monkeypatch.chdir(tmp_path)                                      # the configs name their assets relative to the run directory
+    models = util.instantiate(util.EasyDict(c["model_config"]))
+    om = O.ParamNerfOracle(n_parameters=tuple(c["model_config"]["n_parameters"]), seed=3)
+    om.randomize_biases(91, 0.05)
+    models["model"].load_named_weights(om.named_weights())
+    renderer_config = util.EasyDict(rc)
+    renderer_config.update(models)
+    r = util.instantiate(renderer_config)
+    inst = r.instancer
+    p = sum(c["model_config"]["n_parameters"])
+    assert inst.n_parameters == p and inst.cast_shadow_rays == ic.get("cast_shadow_rays", False)
+    assert inst.n_instances() == (260 if anchors is not None else len(np.unique(mesh["V"], axis=0)))
+    S, step = rc["n_samples"], rc["step_size"]
+    R = 96
+    rng = np.random.default_rng(22)
+    o = np.stack([rng.uniform(-1.3, 1.3, R), rng.uniform(-1.3, 1.3, R), rng.uniform(0.8, 1.6, R)], 1).astype(np.float32)
+    d = np.stack([rng.uniform(-.6, .6, R), rng.uniform(-.6, .6, R), np.full(R, -1.0)], 1).astype(np.float32)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    if "point" in ic["textures"]:
+        light = [3.0, 1.0, 0.4, 0.8]                                 # strength, position
+    else:
+        light = [0.9, 0.1, 0.12]                                     # low sun
+    params = np.array([list(rng.uniform(0.3, 1.0, p - len(light))) + light], np.float32)
+    t = np.tile(np.array([[[0.1, 5.0]]], np.float32), (1, R, 1))
+    cone = rng.uniform(0.01, 0.05, (1, R, 1)).astype(np.float32)
+    r.density_scale = 3.0
+    got = r(dev(o[None]), dev(d[None]), dev(t), dev(params), dev(cone), composite_bkgd=True, training=False)
+    # the oracle chain on the same rays (ray names = positions in the call, frame 0)
+    tex_idx, n_par, chans = [], 0, []
+    for tex in ic["textures"]:
+        if tex == "light":
+            n_par += 3
+        elif tex == "point":
+            n_par += 4
+        elif tex == "":
+            n_par += 1
+        else:
+            tex_idx.append(n_par)
+            chans += IO.texture_channels(images[tex])
+            n_par += 1
+    texture = None
+    if tex_idx:
+        texture = dict(UV=mesh["UV"], textures=chans, idxs=tex_idx, radius=inst.patch_max_extent,
+                       min_samples=ic.get("min_texture_samples", 4), n_samples=ic.get("n_texture_samples", 512))
+    pf = np.repeat(params, R, 0)
+    want = IO.get_model_input(o, d, pf, S, step, inst.transformations, ic["b_0"], ic["b_1"], seed=0,
+                              light_dir_idx=inst.light_dir_idx, light_strength_idx=inst.light_strength_idx,
+                              method=ic["instance_sampling_method"], patch_scale=inst.patch_scale, mesh=(mesh["V"], mesh["F"]),
+                              cast_shadow_rays=ic.get("cast_shadow_rays", False), min_shadow_samples=ic.get("min_shadow_samples", 4),
+                              n_shadow_samples=ic.get("n_shadow_samples", 512), texture=texture)
+    rec = inst.get_model_input_csr(dev(o), dev(d), dev(pf), S, step, seed=0, ray_ids=torch.arange(R, dtype=torch.int32).cuda())
+    from test_gpu_instancer import check_records
+    check_records(rec, want, R)
+    assert np.array_equal(rec["alpha_last"].cpu().numpy(), want["alpha_last"][want["hit"]])
+    from nerf_tex_b200.instancer import csr_to_dense
+    dense = [x.cpu().numpy() for x in csr_to_dense(rec, dev(d), dev(pf), S)]
+    wc, wa = O.instance_evaluate_model(om, dense, R, cone_scale=cone[0], blur_idx=rc.get("blur_idx"), patch_scale=inst.patch_scale,
+                                       density_scale=3.0, density_reweighting=rc.get("density_reweighting", True), composite_bkgd=True)
+    gc, ga = got["color_pred"].cpu().numpy()[0], got["alpha_pred"].cpu().numpy()[0]
+    assert want["n_samples"].max() > 50 and (want["alpha_last"] == 1).mean() > 0.5
+    assert np.abs(ga - wa).max() < 2e-3 and np.abs(gc - wc).max() < 2e-3, (np.abs(ga - wa).max(), np.abs(gc - wc).max())
+    assert psnr(gc, wc) > 50
