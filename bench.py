@@ -419,6 +419,44 @@ def c1_forward_bench(dev, steps=20):
             "note": "4096-ray batch fills 148 SMs for only ~7 waves of 512-row CTA-pair batches; launch-latency sensitive"}
 
 
+def c5_plush_bench(dev, steps=3):
+    """BASELINE.json configs[4] / SURVEY.md C5 on one GPU: 800x800 frame, model [1,4], InstanceRenderer kwargs of
+    configs/config_plush_render.py:87-112 (n_samples 1280, step 0.0005, patch_scale 0.04, render_chunk 32768), seeded
+    synthetic instancer with ~LogNormal(ln 200, 0.6) in-shell samples per hit ray, records resident in HBM."""
+    import torch
+    from nerf_tex_b200.instancer import SyntheticInstancer
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.renderer import InstanceRenderer
+    chunk, S, step, ps = 32768, 1280, 0.0005, 0.04
+    rays_o, rays_d, t, _, cone = frame_rays(seed=1005)
+    params = np.array([[1, 1, 0, 0, 1]], np.float32)
+    synth = SyntheticInstancer(b_0=[-1.1, -1.1, -.2], b_1=[1.1, 1.1, 1.1], patch_scale=ps, seed=5, mean_valid=200.0)
+    d_o, d_d = torch.as_tensor(rays_o[0]).to(dev), torch.as_tensor(rays_d[0]).to(dev)
+    d_p = torch.as_tensor(params).to(dev).repeat_interleave(H * W, dim=0)
+    chunks = [synth.get_model_input_csr(d_o[i:i + chunk], d_d[i:i + chunk], d_p[i:i + chunk], S, step) for i in range(0, H * W, chunk)]
+    n_samples = int(sum(c["pts"].shape[0] for c in chunks))
+    inst = ChunkReplayInstancer(chunks, resident=True)
+    inst.patch_scale = ps
+    r = InstanceRenderer(instancer_config=inst, model=FusedNerfTexMLP(1, 4, seed=1, device=dev), n_samples=S, render_chunk=chunk,
+                         net_chunk=65536, step_size=step, density_reweighting=True)
+    dev_in = [torch.as_tensor(x).to(dev) for x in (rays_o, rays_d, t, params, cone)]
+
+    def frame():
+        inst.reset()
+        return r(*dev_in, composite_bkgd=False, training=False)
+    frame()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        frame()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    return {"rays": H * W, "in_shell_samples": n_samples, "ms_per_frame": ms, "rays_per_sec": H * W / ms * 1e3,
+            "samples_per_sec": n_samples / ms * 1e3, "mlp_tflops": n_samples * 2 * MACS_PER_SAMPLE[(1, 4)] / (ms / 1e3) / 1e12}
+
+
 def carpet_patches(n: int, seed: int = 0, extent: float = 1.45, patch_scale: float = 0.09):
     """Procedural stand-in for the reference's cloth mesh + anchor points (git-LFS stubs): `n` shell patches anchored
     on the z = 0 plane inside [-extent, extent]^2, each rotated about z, tilted a little and scaled by patch_scale
@@ -804,6 +842,7 @@ def run_gpu(args):
             line["hbm_kernels"] = hbm_kernels_bench(dev, pk)
             line["train_step"] = train_step_bench(dev)
             line["c1_forward"] = c1_forward_bench(dev)
+            line["c5_plush_frame"] = c5_plush_bench(dev)
             line["cpu_baseline"] = cpu_baseline_run(steps=3, warmup=1)
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -245,6 +245,11 @@ int ntx_alpha_loss(const float* color_true, const float* alpha_true, const float
  * params -= lr_t * m / (sqrt(v) + epsilon) with lr_t = lr * sqrt(1 - beta2^t) / (1 - beta1^t) computed by the caller. */
 int ntx_adam_step(float* params, const float* grad, float* m, float* v, int64_t n, float lr_t, float beta1, float beta2,
                   float epsilon, void* stream);
+/* Data-parallel training (not in the reference, which is single-device): the mean over the
+ * ranks of the flat fp32 gradient buffer that tape.gradient (network/train.py:66) would have produced on each —
+ * one ncclAllReduce(sum) over NVLink on `stream`, then a scale by 1 / world_size.  comm: the caller's ncclComm_t.  NCCL
+ * is resolved at run time from the process (or libnccl.so.2); failures return NTX_E_NCCL. */
+int ntx_nccl_allreduce_grads(void* comm, float* grad, int64_t n, int world_size, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * mip variants (network/renderer.py:356-587): cone-segment gaussians + compositing over S + 1 depth edges.

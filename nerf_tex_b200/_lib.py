@@ -100,6 +100,7 @@ SIGNATURES = {
     "ntx_normalize_dirs": (_I, [_P, _I, _P, _P]),
     "ntx_alpha_loss": (_I, [_P] * 6 + [_I64, _I, _I, _F, _I, _I] + [_P] * 5 + [_P]),
     "ntx_adam_step": (_I, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _P]),
+    "ntx_nccl_allreduce_grads": (_I, [_P, _P, _I64, _I, _P]),
     "ntx_mip_cone_gaussians": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _P]),
     "ntx_mip_cone_gaussians_instanced": (_I, [_P, _P, _P, _P, _I64, _P, _P]),
     "ntx_composite_edges_forward": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),

@@ -106,3 +106,46 @@ NTX_API int ntx_adam_step(float* params, const float* grad, float* m, float* v, 
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
+
+// ---- data-parallel gradient exchange: one ncclAllReduce(sum) of the flat fp32 gradient buffer,
+// then 1 / world on the same stream.  NCCL is not linked: the entry resolves ncclAllReduce in the process (the
+// communicator the caller passes can only come from an NCCL that is already loaded) or, failing that, in libnccl.so.2.
+#include <dlfcn.h>
+
+namespace {
+typedef int (*nccl_allreduce_t)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef const char* (*nccl_errstr_t)(int);
+__global__ void scale_kernel(float* __restrict__ x, int64_t n, float s) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] *= s;
+}
+}  // namespace
+
+NTX_API int ntx_nccl_allreduce_grads(void* comm, float* grad, int64_t n, int world_size, void* stream) {
+    NTX_REQUIRE(comm && n >= 0 && world_size >= 1, "nccl_allreduce_grads: bad arguments");
+    if (n == 0) return NTX_OK;
+    NTX_REQUIRE(grad, "nccl_allreduce_grads: null gradient buffer");
+    static nccl_allreduce_t allreduce = nullptr;
+    static nccl_errstr_t errstr = nullptr;
+    if (!allreduce) {
+        void* sym = dlsym(RTLD_DEFAULT, "ncclAllReduce");
+        void* h = nullptr;
+        if (!sym && (h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL))) sym = dlsym(h, "ncclAllReduce");
+        if (!sym) {
+            ntx_set_error("nccl_allreduce_grads: ncclAllReduce not found in the process nor in libnccl.so.2");
+            return NTX_E_NCCL;
+        }
+        allreduce = (nccl_allreduce_t)sym;
+        errstr = (nccl_errstr_t)(h ? dlsym(h, "ncclGetErrorString") : dlsym(RTLD_DEFAULT, "ncclGetErrorString"));
+    }
+    const int rc = allreduce(grad, grad, (size_t)n, /*ncclFloat32*/ 7, /*ncclSum*/ 0, comm, (cudaStream_t)stream);
+    if (rc != 0) {
+        ntx_set_error("nccl_allreduce_grads: ncclAllReduce failed: %s", errstr ? errstr(rc) : "unknown NCCL error");
+        return NTX_E_NCCL;
+    }
+    if (world_size > 1) {
+        scale_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(grad, n, 1.0f / (float)world_size);
+        NTX_LAUNCH_CHECK();
+    }
+    return NTX_OK;
+}

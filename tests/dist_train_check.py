@@ -89,12 +89,59 @@ def main():
     ok &= all(flags)
     if rank == 0:
         print(f"render_sharded == single-GPU render on every rank: {all(flags)}")
+    # (4) ntx_nccl_allreduce_grads on a communicator of our own (raw NCCL through ctypes; the id travels over torch.distributed)
+    ok &= c_abi_allreduce(rank, world, dev)
     dist.barrier()
     dist.destroy_process_group()
     if not ok:
         sys.exit(1)
     if rank == 0:
         print("DIST_TRAIN_OK")
+
+
+def c_abi_allreduce(rank, world, dev) -> bool:
+    import ctypes as C
+    import glob
+    from nerf_tex_b200 import _lib
+    from nerf_tex_b200._lib import check, ptr, stream_ptr
+    cands = glob.glob(os.path.join(os.path.dirname(torch.__file__), "..", "nvidia", "nccl", "lib", "libnccl.so*")) + ["libnccl.so.2"]
+    nccl = None
+    for cand in cands:
+        try:
+            nccl = C.CDLL(cand, mode=C.RTLD_GLOBAL)
+            break
+        except OSError:
+            continue
+    if nccl is None:
+        print("no libnccl found: skipping the C-ABI all-reduce check")
+        return True
+    uid = (C.c_byte * 128)()
+    if rank == 0:
+        assert nccl.ncclGetUniqueId(C.byref(uid)) == 0
+    t = torch.tensor(list(uid), dtype=torch.int8, device=dev)
+    dist.broadcast(t, 0)
+    uid = (C.c_byte * 128)(*t.cpu().tolist())
+    comm = C.c_void_p()
+
+    class UniqueId(C.Structure):
+        _fields_ = [("internal", C.c_byte * 128)]
+    nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, UniqueId, C.c_int]
+    assert nccl.ncclCommInitRank(C.byref(comm), world, UniqueId(uid), rank) == 0
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+    grad = torch.randn(678916, device=dev, generator=g)
+    gathered = [torch.empty_like(grad) for _ in range(world)]
+    dist.all_gather(gathered, grad)
+    want = torch.stack(gathered).sum(0) / world
+    check(_lib.load().ntx_nccl_allreduce_grads(comm, ptr(grad), grad.numel(), world, stream_ptr()))
+    torch.cuda.synchronize()
+    err = float((grad - want).abs().max() / want.abs().max())
+    nccl.ncclCommDestroy.argtypes = [C.c_void_p]
+    nccl.ncclCommDestroy(comm)
+    flags = [None] * world
+    dist.all_gather_object(flags, bool(err < 1e-6))
+    if rank == 0:
+        print(f"ntx_nccl_allreduce_grads == mean of the per-rank buffers: {all(flags)} (max rel err {err:.1e})")
+    return all(flags)
 
 
 if __name__ == "__main__":
