@@ -477,6 +477,9 @@ int ntx_selftest_umma(const float* A, const float* B, int N, int K, int layout, 
 /* D[128,N] = At^T * Bt, At[K,128] and Bt[K,N] row-major: both operands MN-major, SWIZZLE_64B row images
  * (the operand form of the weight-gradient GEMM, K = sample rows).  K in {64,128}, N in {128,256}. */
 int ntx_selftest_umma_mn(const float* At, const float* Bt, int N, int K, float* D, void* stream);
+/* The same product with both operands rounded to fp8 e4m3 (kind::f8f6f4, MN-major SWIZZLE_64B images of 64 elements per
+ * row, 32 K rows per instruction): probes whether 8-bit saved operands can feed the weight-gradient GEMM as they are. */
+int ntx_selftest_umma_mn8(const float* At, const float* Bt, int N, int K, float* D, void* stream);
 /* global -> shared through cp.async.bulk + mbarrier, then back out: dst[0:bytes] = src[0:bytes]. */
 int ntx_selftest_bulk_copy(const void* src, void* dst, int bytes, void* stream);
 

@@ -116,6 +116,7 @@ SIGNATURES = {
     "ntx_render_rays_static": (_I, [_P, _P, _P, _P, C.POINTER(RenderConfig)] + [_P] * 9 + [_I] + [_P] * 4 + [_P]),
     "ntx_selftest_umma": (_I, [_P, _P, _I, _I, _I, _P, _P]),
     "ntx_selftest_umma_mn": (_I, [_P, _P, _I, _I, _P, _P]),
+    "ntx_selftest_umma_mn8": (_I, [_P, _P, _I, _I, _P, _P]),
     "ntx_selftest_bulk_copy": (_I, [_P, _P, _I, _P]),
 }
 

@@ -144,6 +144,11 @@ __host__ __device__ constexpr uint32_t idesc_bf16_f32_mn(int M, int N) {
            ((uint32_t)(M >> 4) << 24);
 }
 
+// kind::f8f6f4 with A = B = e4m3 (format code 0), both MN-major, D = fp32
+__host__ __device__ constexpr uint32_t idesc_e4m3_f32_mn(int M, int N) {
+    return (1u << 4) | (0u << 7) | (0u << 10) | (1u << 15) | (1u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
 // kind::f16, A = B = bf16 (K-major), D = fp32, dense.
 __host__ __device__ constexpr uint32_t idesc_bf16_f32(int M, int N) {
     return (1u << 4)                       // D format  : F32
@@ -160,6 +165,15 @@ __device__ __forceinline__ void mma_bf16_ss(uint32_t d_tmem, uint64_t adesc, uin
         "{\n\t.reg .pred p;\n\t"
         "setp.ne.b32 p, %4, 0;\n\t"
         "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+
+// same with 8-bit operands (kind::f8f6f4; K = 32 per instruction)
+__device__ __forceinline__ void mma_f8_ss(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f8f6f4 [%0], %1, %2, %3, p;\n\t}"
         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 

@@ -358,6 +358,14 @@ def selftest_umma_mn(At: torch.Tensor, Bt: torch.Tensor) -> torch.Tensor:
     return D
 
 
+def selftest_umma_mn8(At: torch.Tensor, Bt: torch.Tensor) -> torch.Tensor:
+    At, Bt = as_cuda(At), as_cuda(Bt)
+    assert At.shape[1] == 128 and At.shape[0] == Bt.shape[0]
+    D = torch.empty((128, Bt.shape[1]), dtype=torch.float32, device=At.device)
+    check(_lib.load().ntx_selftest_umma_mn8(ptr(At), ptr(Bt), Bt.shape[1], At.shape[0], ptr(D), stream_ptr()))
+    return D
+
+
 def selftest_bulk_copy(src: torch.Tensor) -> torch.Tensor:
     dst = torch.empty_like(src)
     check(_lib.load().ntx_selftest_bulk_copy(ptr(src), ptr(dst), src.numel() * src.element_size(), stream_ptr()))

@@ -46,3 +46,17 @@ def test_umma_gemm_mn_major_operands(N, K):
     ref = _bf16(At).double().T @ _bf16(Bt).double()
     err = (D.cpu().double() - ref).abs().max().item()
     assert err < 1e-3, f"MN-major N={N} K={K}: max abs err {err}"
+
+
+@pytest.mark.parametrize("N,K", [(128, 64), (256, 64), (256, 128)])
+def test_umma_gemm_mn_major_fp8_operands(N, K):
+    """kind::f8f6f4 with e4m3 operands stored MN-major (the form 8-bit saved activation / gradient images would have for
+    the weight-gradient GEMM): exact against the product of the e4m3-rounded operands (fp32 accumulate)."""
+    from nerf_tex_b200 import ops
+    g = torch.Generator(device="cuda").manual_seed(N + K)
+    At = torch.randn((K, 128), device="cuda", generator=g) * 4
+    Bt = torch.randn((K, N), device="cuda", generator=g) * 0.05
+    D = ops.selftest_umma_mn8(At, Bt)
+    q = lambda x: x.to(torch.float8_e4m3fn).to(torch.float64)
+    want = (q(At).T @ q(Bt)).float()
+    torch.testing.assert_close(D, want, rtol=1e-5, atol=1e-5)
