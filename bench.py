@@ -292,10 +292,14 @@ def train_step_bench(dev, steps=5):
             "parameters": torch.rand((1, 5), device=dev, generator=g), "cone_scale": torch.rand((1, R, 1), device=dev, generator=g) * .01,
             "color": torch.rand((1, R, 3), device=dev, generator=g), "alpha": torch.rand((1, R), device=dev, generator=g)}
     out = {}
-    for name, (S, N) in (("single_256", (256, 0)), ("coarse_fine_64_128", (64, 128))):
+    for name, (S, N), fp8 in (("single_256", (256, 0), False), ("coarse_fine_64_128", (64, 128), False),
+                              ("single_256_fp8_saved", (256, 0), True), ("coarse_fine_64_128_fp8_saved", (64, 128), True)):
         models = {"model": FusedNerfTexMLP(2, 3, seed=1)}
         if N:
             models["model_fine"] = FusedNerfTexMLP(2, 3, seed=2, name="model_fine")
+        if fp8:                                    # saved tile images in fp8 e4m3 (first step calibrates in bf16)
+            for m in models.values():
+                m.enable_fp8_saved_operands()
         r = Renderer(n_samples=S, n_importance=N, perturb=True, blur_idx=0, raw_noise_std=0.1, seed=0, **models)
         tr = Trainer(models, r, AlphaLoss("network.loss.smape", "network.loss.mse"))
         for _ in range(3):

@@ -205,6 +205,26 @@ int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const v
                              const void* enc_dir, const float* d_rgbs, float* grad, float* enc_scratch,
                              int64_t n_rows, int64_t n_tiles, void* stream);
 
+/* 8-bit saved operands for the training step (no counterpart in the reference; it exists because the step is bound by the
+ * bytes of the saved images): the forward and the data-gradient chain leave their tile images as fp8 e4m3 / scale[step]
+ * (32 KB per tile instead of 64 KB) and the weight-gradient GEMM reads them as they are (tcgen05 kind::f8f6f4, MN-major),
+ * rescaling the products in its flush.  Scales are per step and per tensor, delayed by one training step:
+ * ntx_fp8_update_scales turns the maxima the kernels collected (amax, fp32 bit patterns, cleared by the call) into
+ * scale = margin * amax / 448 and its inverse, all on the device.  The encoded-input weight gradients keep bf16: the
+ * data-gradient kernel still writes the bf16 dY image of the (three) steps that read an encoding into dy_img.
+ * Gradient accuracy: tests/test_gpu_train.py holds this path to the same bars as the bf16 one. */
+int ntx_mlp_forward_train_fp8(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs, void* enc_pos,
+                              void* enc_dir, void* acts_img8, const float* inv_scale8, void* amax8, void* masks,
+                              int64_t n_tiles, void* stream);
+int ntx_mlp_backward_data_fp8(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks, void* dy_img,
+                              void* dy_img8, const float* inv_scale8, void* amax8, int64_t n_rows, int64_t n_tiles,
+                              void* stream);
+int ntx_mlp_backward_weights_fp8(const ntx_mlp_t* mlp, const void* acts_img8, const void* dy_img8, const void* dy_img,
+                                 const float* x_scale8, const float* dy_scale8, const void* enc_pos, const void* enc_dir,
+                                 const float* d_rgbs, float* grad, float* enc_scratch, int64_t n_rows, int64_t n_tiles,
+                                 void* stream);
+int ntx_fp8_update_scales(void* amax, float* scale, float* inv_scale, int n, float margin, void* stream);
+
 /* Schedule introspection for the host-side backward (nerf_tex_b200/autograd.py).  A "step" is one
  * tensor-core layer: trunk0..trunk{depth-1}, feature, colorhid*, colorhalf. */
 int ntx_mlp_num_steps(const ntx_mlp_t* mlp);

@@ -93,6 +93,10 @@ SIGNATURES = {
     "ntx_mlp_pack_weights_t": (_I, [_P, _P, _P, _P]),
     "ntx_mlp_backward_data": (_I, [_P, _P, _P, _P, _P, _I64, _I64, _P]),
     "ntx_mlp_backward_weights": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _P]),
+    "ntx_mlp_forward_train_fp8": (_I, [_P, _P, C.POINTER(MlpInputs), _P, _P, _P, _P, _P, _P, _P, _I64, _P]),
+    "ntx_mlp_backward_data_fp8": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I64, _I64, _P]),
+    "ntx_mlp_backward_weights_fp8": (_I, [_P] * 11 + [_I64, _I64, _P]),
+    "ntx_fp8_update_scales": (_I, [_P, _P, _P, _I, _F, _P]),
     "ntx_mlp_num_steps": (_I, [_P]),
     "ntx_mlp_step_info": (_I, [_P, _I] + [C.POINTER(C.c_int32)] * 6),
     "ntx_mlp_enc_columns": (_I, [_P, _I, C.POINTER(C.c_int32)]),

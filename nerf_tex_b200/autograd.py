@@ -74,14 +74,49 @@ def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, r
         enc_pos = torch.zeros((n_tiles, 128 * 128), dtype=torch.bfloat16, device=dev)
         enc_dir = torch.zeros((n_tiles, 128 * 128), dtype=torch.bfloat16, device=dev)
         pool.append([enc_pos, enc_dir, True])
-    acts_img = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=dev)
     masks = torch.empty((sched.n_steps, n_tiles * 128, 8), dtype=torch.int32, device=dev)
-    acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev) if row_major_acts else None
     inp = MlpInputs(ptr(pos), ptr(rays_o), ptr(rays_d), ptr(z), ptr(dir), ptr(params), ptr(row_scale), ptr(group_scale),
                     -1 if blur_idx is None else int(blur_idx), int(rows_per_group), int(n_rows), ptr(pos_cov))
+    f8 = fp8_state(model)
+    if f8 is not None and f8["calibrated"] and not row_major_acts:
+        # 8-bit saved operands: scales from the maxima of the previous step, images of 32 KB per tile
+        check(lib.ntx_fp8_update_scales(ptr(f8["amax_x"]), ptr(f8["scale_x"]), ptr(f8["inv_x"]), sched.n_steps, FP8_MARGIN, stream_ptr()))
+        acts_img8 = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.uint8, device=dev)
+        check(lib.ntx_mlp_forward_train_fp8(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
+                                            ptr(acts_img8), ptr(f8["inv_x"]), ptr(f8["amax_x"]), ptr(masks), n_tiles, stream_ptr()))
+        return rgbs, (enc_pos, enc_dir, acts_img8, masks, None, n_rows)
+    acts_img = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=dev)
+    acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev) if row_major_acts else None
     check(lib.ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
                                     ptr(acts), ptr(acts_img), ptr(masks), n_tiles, stream_ptr()))
     return rgbs, (enc_pos, enc_dir, acts_img, masks, acts, n_rows)
+
+
+FP8_MARGIN = 2.0          # head-room of the delayed scales: values up to twice last step's maximum stay finite
+
+
+def fp8_state(model):
+    """Per-model state of the 8-bit saved-operand mode (enabled with model.enable_fp8_saved_operands()): per-step
+    scales, their inverses and the running maxima, for the activations (x) and the output gradients (y)."""
+    return getattr(model, "_fp8", None)
+
+
+def enable_fp8_saved_operands(model, enable: bool = True) -> None:
+    """Training only: save the tile images the backward needs as fp8 e4m3 with per-step, per-tensor scales delayed by
+    one step.  The first pass after enabling runs with bf16 images and measures the maxima (calibration)."""
+    if not enable:
+        model._fp8 = None
+        return
+    dev = model.device
+    z32 = lambda: torch.zeros(16, dtype=torch.float32, device=dev)
+    model._fp8 = {"calibrated": False, "scale_x": z32() + 1, "inv_x": z32() + 1, "amax_x": torch.zeros(16, dtype=torch.int32, device=dev),
+                  "scale_y": z32() + 1, "inv_y": z32() + 1, "amax_y": torch.zeros(16, dtype=torch.int32, device=dev)}
+
+
+def _calibrate(f8, key, img) -> None:
+    """Maxima of a bf16 image stack [n_steps, ...] as fp32 bit patterns (what the kernels' atomicMax would have left)."""
+    am = img.reshape(img.shape[0], -1).abs().amax(1).float()
+    f8[key][:am.shape[0]] = torch.maximum(f8[key][:am.shape[0]].view(torch.float32), am).view(torch.int32)
 
 
 def release_saved(model, saved) -> None:
@@ -115,13 +150,29 @@ def mlp_backward_native(model, saved, d_rgbs: torch.Tensor, return_dy: bool = Fa
         check(lib.ntx_mlp_pack_weights_t(model._h, ptr(master), ptr(model._packed_t), stream_ptr()))
         model._packed_t_version = model.master._version
     d_rgbs = d_rgbs.contiguous()
-    dy_img = torch.empty_like(acts_img)
-    check(lib.ntx_mlp_backward_data(model._h, ptr(model._packed_t), ptr(d_rgbs), ptr(masks), ptr(dy_img), n_rows, n_tiles,
-                                    stream_ptr()))
     grad = torch.zeros_like(master)
     enc_scratch = torch.zeros((sched.n_steps, 128, 256), dtype=torch.float32, device=master.device)
-    check(lib.ntx_mlp_backward_weights(model._h, ptr(acts_img), ptr(dy_img), ptr(enc_pos), ptr(enc_dir), ptr(d_rgbs),
-                                       ptr(grad), ptr(enc_scratch), n_rows, n_tiles, stream_ptr()))
+    f8 = fp8_state(model)
+    if acts_img.dtype == torch.uint8:                                     # 8-bit saved operands
+        check(lib.ntx_fp8_update_scales(ptr(f8["amax_y"]), ptr(f8["scale_y"]), ptr(f8["inv_y"]), sched.n_steps, FP8_MARGIN, stream_ptr()))
+        dy_img8 = torch.empty_like(acts_img)
+        # bf16 dY only for the steps that read an encoding (their weight gradient keeps bf16 operands)
+        dy_img = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=master.device)
+        check(lib.ntx_mlp_backward_data_fp8(model._h, ptr(model._packed_t), ptr(d_rgbs), ptr(masks), ptr(dy_img), ptr(dy_img8),
+                                            ptr(f8["inv_y"]), ptr(f8["amax_y"]), n_rows, n_tiles, stream_ptr()))
+        check(lib.ntx_mlp_backward_weights_fp8(model._h, ptr(acts_img), ptr(dy_img8), ptr(dy_img), ptr(f8["scale_x"]),
+                                               ptr(f8["scale_y"]), ptr(enc_pos), ptr(enc_dir), ptr(d_rgbs), ptr(grad),
+                                               ptr(enc_scratch), n_rows, n_tiles, stream_ptr()))
+    else:
+        dy_img = torch.empty_like(acts_img)
+        check(lib.ntx_mlp_backward_data(model._h, ptr(model._packed_t), ptr(d_rgbs), ptr(masks), ptr(dy_img), n_rows, n_tiles,
+                                        stream_ptr()))
+        check(lib.ntx_mlp_backward_weights(model._h, ptr(acts_img), ptr(dy_img), ptr(enc_pos), ptr(enc_dir), ptr(d_rgbs),
+                                           ptr(grad), ptr(enc_scratch), n_rows, n_tiles, stream_ptr()))
+        if f8 is not None and not f8["calibrated"]:                       # calibration pass of the 8-bit mode
+            _calibrate(f8, "amax_x", acts_img)
+            _calibrate(f8, "amax_y", dy_img)
+            f8["calibrated"] = True
 
     def gview(layer):
         wo, bo, fi, fo = model.layers[layer]

@@ -47,7 +47,8 @@ constexpr uint32_t kOffBars = kOffHeads + kHeadFloats * 4;                 // +2
 constexpr uint32_t kMaxStages = 2 * kStages;
 constexpr uint32_t kNumBars = 2 * kMaxStages + 2 * kTilesPerCta;
 constexpr uint32_t kOffTmemSlot = kOffBars + kNumBars * 8;
-constexpr uint32_t kSmemBytes = kOffTmemSlot + 16;
+constexpr uint32_t kOffAmax = kOffTmemSlot + 16;                           // [16] per-step max |activation| (8-bit dumps)
+constexpr uint32_t kSmemBytes = kOffAmax + 64;
 static_assert(kSmemBytes <= 232448, "exceeds the 227 KB per-CTA shared memory limit");
 
 constexpr int kThreads = 320;
@@ -69,6 +70,11 @@ struct KernelArgs {
                            // operand buffer as it sits in shared memory), written by bulk stores; may be NULL
     uint4* dump_masks;     // [n_steps][n_tiles*128][8 x u32]: bit c of word j = output column 32 j + c is > 0
     int64_t n_tiles;       // tiles allocated per step in dump_img / dump_masks
+    // 8-bit variant of dump_img (the bf16 images are then not written): [n_steps][n_tiles][32 KB] e4m3 tile images of
+    // output / scale8[step]; amax8[step] receives max |output| (for the next training step's scales)
+    uint8_t* dump_img8;
+    const float* inv_scale8;
+    uint32_t* amax8;
 };
 
 // ----------------------------------------------------------------------------------------------
@@ -94,9 +100,18 @@ __device__ __forceinline__ uint32_t nonzero_bits4(const uint32_t (&w)[4]) {
     return m;
 }
 
-template <bool RELU, bool DUMP>
-__device__ __forceinline__ uint32_t store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32], uint4* grow_ptr) {
+struct Dump8 { uint8_t* tile_img; float inv_scale; float amax; bool track; };
+
+template <bool RELU, bool DUMP, bool F8>
+__device__ __forceinline__ uint32_t store_chunk32(uint32_t main_base, int j, int row, const uint32_t (&v)[32], uint4* grow_ptr,
+                                                  Dump8& d8) {
     uint32_t mask = 0;
+    if (F8) {
+        float x[32];
+#pragma unroll
+        for (int c = 0; c < 32; ++c) x[c] = __uint_as_float(v[c]);
+        dump_fp8_chunk32<RELU>(d8.tile_img, j, row, x, d8.inv_scale, d8.amax, d8.track);
+    }
 #pragma unroll
     for (int c = 0; c < 4; ++c) {
         uint32_t w[4];
@@ -113,9 +128,9 @@ __device__ __forceinline__ uint32_t store_chunk32(uint32_t main_base, int j, int
 }
 
 // plain hidden layer epilogue: TMEM loads software-pipelined against the convert + store
-template <bool RELU, bool DUMP>
+template <bool RELU, bool DUMP, bool F8>
 __device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t main_base, int row, int n_chunks,
-                                                     uint4* grow_ptr, uint32_t (&masks)[8]) {
+                                                     uint4* grow_ptr, uint32_t (&masks)[8], Dump8& d8) {
     uint32_t va[32], vb[32];
     tmem_ld_32x32b_x32(tmem_row, va);
     tmem_ld_wait();
@@ -123,10 +138,10 @@ __device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t
     for (int j = 0; j < 8; j += 2) {
         if (j < n_chunks) {
             tmem_ld_32x32b_x32(tmem_row + (j + 1) * 32, vb);
-            masks[j] = store_chunk32<RELU, DUMP>(main_base, j, row, va, grow_ptr);
+            masks[j] = store_chunk32<RELU, DUMP, F8>(main_base, j, row, va, grow_ptr, d8);
             tmem_ld_wait();
             if (j + 2 < n_chunks) tmem_ld_32x32b_x32(tmem_row + (j + 2) * 32, va);
-            masks[j + 1] = store_chunk32<RELU, DUMP>(main_base, j + 1, row, vb, grow_ptr);
+            masks[j + 1] = store_chunk32<RELU, DUMP, F8>(main_base, j + 1, row, vb, grow_ptr, d8);
             tmem_ld_wait();
         }
     }
@@ -136,7 +151,7 @@ __device__ __forceinline__ void epilogue_store_layer(uint32_t tmem_row, uint32_t
 // CTAS == 2: CTA pairs (cluster of 2, cta_group::2): one tcgen05.mma issued by the even CTA drives
 //            both SMs (M = 256), each CTA stages only its half of every weight slice (N/2 rows), so
 //            the L2->SM weight traffic per SM halves and the 48 KB ring holds 6 slices instead of 3.
-template <bool DUMP, int CTAS>
+template <bool DUMP, int CTAS, bool F8 = false>
 __global__ void __launch_bounds__(kThreads, 1)
 mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__ KernelArgs args) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -181,6 +196,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
     // fp32 head weights -> shared (broadcast reads in the epilogues)
     for (int i = threadIdx.x; i < kHeadFloats; i += kThreads)
         heads[i] = reinterpret_cast<const float*>(args.packed)[i];
+    if (F8 && threadIdx.x < 16) reinterpret_cast<uint32_t*>(smem + kOffAmax)[threadIdx.x] = 0u;
     tc_fence_before();
     __syncthreads();
     if (CTAS == 2) cluster_sync_all();          // peer barriers initialised before any remote arrive / multicast
@@ -439,6 +455,13 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 float o0 = 0.f, o1 = 0.f, o2 = 0.f;
                 uint4* gp = (DUMP && valid && args.dump_acts) ? args.dump_acts + ((int64_t)st * n_rows + grow) * (kWidth / 8) : nullptr;
                 uint32_t masks[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
+                Dump8 d8 = {nullptr, 0.0f, 0.0f, false};
+                if (F8) {
+                    const int64_t tile_g8 = (b * CTAS + rank) * kTilesPerCta + tile;
+                    d8.tile_img = args.dump_img8 + ((int64_t)st * args.n_tiles + tile_g8) * (int64_t)kMain8Bytes;
+                    d8.inv_scale = __ldg(args.inv_scale8 + st);
+                    d8.track = (tile_g8 & 7) == 0;          // maxima from every eighth tile
+                }
                 if (DUMP && args.dump_img) {
                     // the previous step's image store must have finished reading this tile's buffer
                     if (row == 0) tma_store_wait_read();
@@ -446,8 +469,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                 }
                 if ((epi & (EPI_ALPHA | EPI_FINAL)) == 0) {
                     // hidden layer: (ReLU) -> bf16 -> A operand of the next layer
-                    if (epi & EPI_RELU) epilogue_store_layer<true, DUMP>(tmem_row, main_base, row, n_chunks, gp, masks);
-                    else epilogue_store_layer<false, DUMP>(tmem_row, main_base, row, n_chunks, gp, masks);
+                    if (epi & EPI_RELU) epilogue_store_layer<true, DUMP, F8>(tmem_row, main_base, row, n_chunks, gp, masks, d8);
+                    else epilogue_store_layer<false, DUMP, F8>(tmem_row, main_base, row, n_chunks, gp, masks, d8);
                 } else {
                     // layers that also feed an fp32 head (density after the trunk, colour at the end)
                     for (int j = 0; j < n_chunks; ++j) {
@@ -477,6 +500,7 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                                 o2 += f[4 * c] * a2.x + f[4 * c + 1] * a2.y + f[4 * c + 2] * a2.z + f[4 * c + 3] * a2.w;
                             }
                         }
+                        if (F8) dump_fp8_chunk32<false>(d8.tile_img, j, row, f, d8.inv_scale, d8.amax, d8.track);
                         if (!(epi & EPI_FINAL) || DUMP) {
                             uint32_t mj = 0;
 #pragma unroll
@@ -529,6 +553,14 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
                         }
                     }
                 }
+                if (F8) {
+                    // relu sign bits; the 8-bit image left through the register stores above
+                    const int64_t tile_g = (b * CTAS + rank) * kTilesPerCta + tile;
+                    uint4* mp = args.dump_masks + (((int64_t)st * args.n_tiles + tile_g) * kTileRows + row) * 2;
+                    st_global_v4(mp, masks[0], masks[1], masks[2], masks[3]);
+                    st_global_v4(mp + 1, masks[4], masks[5], masks[6], masks[7]);
+                    amax_to_shared(d8.amax, reinterpret_cast<uint32_t*>(smem + kOffAmax) + st);
+                }
                 if (DUMP && args.dump_img) {
                     // relu sign bits (for the backward's masks) and the tile image of this step's stored output
                     const int64_t tile_g = (b * CTAS + rank) * kTilesPerCta + tile;
@@ -563,6 +595,10 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
     if (DUMP) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");   // image stores fully written
     tc_fence_before();
     __syncthreads();
+    if (F8 && threadIdx.x < 16) {
+        const uint32_t a = reinterpret_cast<uint32_t*>(smem + kOffAmax)[threadIdx.x];
+        if (a) atomicMax(args.amax8 + threadIdx.x, a);
+    }
     if (CTAS == 2) cluster_sync_all();          // no CTA leaves while its peer may still signal it
     if (warp == 1) {
         __syncwarp();
@@ -771,7 +807,8 @@ NTX_API int64_t ntx_mlp_train_tiles(int64_t n_rows) {
 
 static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
                           void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks, int64_t n_tiles,
-                          bool dump, void* stream) {
+                          bool dump, void* stream, void* acts_img8 = nullptr, const float* inv_scale8 = nullptr,
+                          uint32_t* amax8 = nullptr) {
     NTX_REQUIRE(mlp && packed && in, "mlp_forward: null pointer");
     NTX_REQUIRE(in->n_rows >= 0, "mlp_forward: negative row count");
     if (in->n_rows == 0) return NTX_OK;
@@ -784,7 +821,9 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     NTX_REQUIRE(in->blur_idx < np, "mlp_forward: blur_idx %d out of range", in->blur_idx);
     NTX_REQUIRE((((uintptr_t)packed | (uintptr_t)rgbs) & 15) == 0, "mlp_forward: packed / rgbs must be 16-byte aligned");
     if (dump) {
-        NTX_REQUIRE(enc_pos && enc_dir && acts_img, "mlp_forward_train: null save buffer");
+        NTX_REQUIRE(enc_pos && enc_dir && (acts_img || acts_img8), "mlp_forward_train: null save buffer");
+        NTX_REQUIRE(!acts_img8 || (inv_scale8 && amax8 && ((uintptr_t)acts_img8 & 15) == 0 && mlp->prog.n_steps <= 16),
+                    "mlp_forward_train: 8-bit images need inv_scale8[n_steps], amax8[n_steps] and 16-byte alignment");
         NTX_REQUIRE((((uintptr_t)enc_pos | (uintptr_t)enc_dir | (uintptr_t)acts | (uintptr_t)acts_img | (uintptr_t)masks) & 15) == 0,
                     "mlp_forward_train: save buffers must be 16-byte aligned");
         {
@@ -796,14 +835,15 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     // NTX_MLP_CTAS=1 selects the single-CTA kernel (cta_group::1); default is CTA pairs (cta_group::2)
     static const int ctas = [] { const char* e = getenv("NTX_MLP_CTAS"); return (e && e[0] == '1') ? 1 : 2; }();
     using KernelFn = void (*)(const Program, const KernelArgs);
-    KernelFn fn = ctas == 2 ? (dump ? mlp_forward_kernel<true, 2> : mlp_forward_kernel<false, 2>)
-                            : (dump ? mlp_forward_kernel<true, 1> : mlp_forward_kernel<false, 1>);
-    static bool attr_set[64][2][2] = {};
+    const int mode = acts_img8 ? 2 : (dump ? 1 : 0);
+    KernelFn fn = ctas == 2 ? (mode == 2 ? mlp_forward_kernel<true, 2, true> : mode == 1 ? mlp_forward_kernel<true, 2> : mlp_forward_kernel<false, 2>)
+                            : (mode == 2 ? mlp_forward_kernel<true, 1, true> : mode == 1 ? mlp_forward_kernel<true, 1> : mlp_forward_kernel<false, 1>);
+    static bool attr_set[64][3][2] = {};
     int dev = 0;
     NTX_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev][dump][ctas - 1]) {
+    if (dev < 64 && !attr_set[dev][mode][ctas - 1]) {
         NTX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-        attr_set[dev][dump][ctas - 1] = true;
+        attr_set[dev][mode][ctas - 1] = true;
     }
     KernelArgs ka;
     ka.in = *in;
@@ -815,6 +855,9 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     ka.dump_img = (uint8_t*)acts_img;
     ka.dump_masks = (uint4*)masks;
     ka.n_tiles = n_tiles;
+    ka.dump_img8 = (uint8_t*)acts_img8;
+    ka.inv_scale8 = inv_scale8;
+    ka.amax8 = amax8;
     const int64_t rows_per_unit = (int64_t)kRowsPerCta * ctas;
     const int64_t n_units = (in->n_rows + rows_per_unit - 1) / rows_per_unit;
     const int64_t max_units = ntx_sm_count() / ctas;
@@ -842,6 +885,14 @@ NTX_API int ntx_mlp_forward_train(const ntx_mlp_t* mlp, const void* packed, cons
                                   void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks,
                                   int64_t n_tiles, void* stream) {
     return launch_forward(mlp, packed, in, rgbs, enc_pos, enc_dir, acts, acts_img, masks, n_tiles, true, stream);
+}
+
+NTX_API int ntx_mlp_forward_train_fp8(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
+                                      void* enc_pos, void* enc_dir, void* acts_img8, const float* inv_scale8, void* amax8,
+                                      void* masks, int64_t n_tiles, void* stream) {
+    NTX_REQUIRE(acts_img8, "mlp_forward_train_fp8: null image buffer");
+    return launch_forward(mlp, packed, in, rgbs, enc_pos, enc_dir, nullptr, nullptr, masks, n_tiles, true, stream, acts_img8,
+                          inv_scale8, (uint32_t*)amax8);
 }
 
 NTX_API int ntx_untile(const void* img, int64_t n_rows, int cols, int64_t tile_bytes, void* out, void* stream) {

@@ -14,10 +14,14 @@
 //
 // No gradient flows into the encodings (nothing trainable upstream; network/renderer.py:129).
 // Reference: the tf.GradientTape of network/train.py:62-66 over network/model.py:104-123.
+#include <math_constants.h>
 #include <stdlib.h>
 
 #include "ntx_common.cuh"
 #include "ntx_mlp.cuh"
+#include <cuda_fp16.h>
+#include <cuda_fp8.h>
+
 #include "ntx_mlp_dev.cuh"
 #include "ntx_umma.cuh"
 
@@ -55,7 +59,8 @@ constexpr uint32_t kDgOffHeads = kDgOffStages + kStages * kStageBytes;        //
 constexpr uint32_t kDgOffBars = kDgOffHeads + kBwdHeadFloats * 4;
 constexpr uint32_t kDgNumBars = 2 * kStages + 2 * kTilesPerCta;
 constexpr uint32_t kDgOffTmemSlot = kDgOffBars + kDgNumBars * 8;
-constexpr uint32_t kDgSmemBytes = kDgOffTmemSlot + 16;
+constexpr uint32_t kDgOffAmax = kDgOffTmemSlot + 16;                          // [16] per-step max |dY| (8-bit images)
+constexpr uint32_t kDgSmemBytes = kDgOffAmax + 64;
 
 struct DgradArgs {
     const uint8_t* packed_t;     // head block + transposed weight slices
@@ -64,9 +69,15 @@ struct DgradArgs {
     uint8_t* dy_img;             // [n_steps][n_tiles][64 KB] out
     int64_t n_rows, n_tiles;
     int32_t depth;
+    // 8-bit variant: dy_img8[n_steps][n_tiles][32 KB] e4m3 images of dY / scale8[step]; the bf16 image of a step is then
+    // written only if bit `step` of need16 is set (the steps whose encoded-input weight gradient needs it)
+    uint32_t need16;
+    uint8_t* dy_img8;
+    const float* inv_scale8;
+    uint32_t* amax8;
 };
 
-template <int CTAS>
+template <int CTAS, bool F8 = false>
 __global__ void __launch_bounds__(kThreadsBwd, 1)
 mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant__ DgradArgs args) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -105,6 +116,7 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
     }
     for (int i = threadIdx.x; i < (int)kBwdHeadFloats; i += kThreadsBwd)
         heads[i] = reinterpret_cast<const float*>(args.packed_t)[i];
+    if (F8 && threadIdx.x < 16) reinterpret_cast<uint32_t*>(smem + kDgOffAmax)[threadIdx.x] = 0u;
     tc_fence_before();
     __syncthreads();
     if (CTAS == 2) cluster_sync_all();
@@ -231,10 +243,11 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
             float4 dr = make_float4(0.f, 0.f, 0.f, 0.f);
             if (valid) dr = __ldg(reinterpret_cast<const float4*>(args.d_rgbs) + grow);
             auto mask_ptr = [&](int st) { return args.masks + (((int64_t)st * args.n_tiles + tile_g) * kTileRows + row) * 2; };
+            auto img8 = [&](int st) { return args.dy_img8 + ((int64_t)st * args.n_tiles + tile_g) * (int64_t)kMain8Bytes; };
             auto store_image = [&](int st, uint32_t bytes) {
                 fence_proxy_async_smem();
                 named_bar_sync(1 + tile, kTileRows);
-                if (row == 0) {
+                if (row == 0 && (!F8 || ((args.need16 >> st) & 1u))) {
                     tma_bulk_s2g(args.dy_img + ((int64_t)st * args.n_tiles + tile_g) * (int64_t)kMainBytes, main_base, bytes);
                     tma_store_commit();
                 }
@@ -245,8 +258,11 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
                 named_bar_sync(1 + tile, kTileRows);
                 const uint4 m4 = __ldg(mask_ptr(last));
                 const uint32_t mw[4] = {m4.x, m4.y, m4.z, m4.w};
+                float am = 0.0f;
+                const float inv8 = F8 ? __ldg(args.inv_scale8 + last) : 0.0f;
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
+                    float x[32];
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         uint32_t w[4];
@@ -258,10 +274,13 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
                             if (!((mw[j] >> (c * 8 + 2 * e)) & 1u)) v0 = 0.0f;
                             if (!((mw[j] >> (c * 8 + 2 * e + 1)) & 1u)) v1 = 0.0f;
                             w[e] = pack_bf16(v0, v1);
+                            x[c * 8 + 2 * e] = v0; x[c * 8 + 2 * e + 1] = v1;
                         }
                         st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
                     }
+                    if (F8) dump_fp8_chunk32<false>(img8(last), j, row, x, inv8, am, (tile_g & 7) == 0);
                 }
+                if (F8) amax_to_shared(am, reinterpret_cast<uint32_t*>(smem + kDgOffAmax) + last);
                 store_image(last, (uint32_t)prog.last_n_out * kTileRows * 2);
                 fence_proxy_async_smem();
                 __syncwarp();
@@ -281,11 +300,14 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
                 tc_fence_after();
                 if (row == 0) tma_store_wait_read();        // the previous image store has read this buffer
                 named_bar_sync(1 + tile, kTileRows);
+                float am = 0.0f;
+                const float inv8 = F8 ? __ldg(args.inv_scale8 + st_prev) : 0.0f;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     uint32_t v[32];
                     tmem_ld_32x32b_x32(tmem_row + j * 32, v);
                     tmem_ld_wait();
+                    float x[32];
 #pragma unroll
                     for (int c = 0; c < 4; ++c) {
                         uint32_t w[4];
@@ -300,10 +322,13 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
                             if (!((mw[j] >> cc) & 1u)) v0 = 0.0f;
                             if (!((mw[j] >> (cc + 1)) & 1u)) v1 = 0.0f;
                             w[e] = pack_bf16(v0, v1);
+                            x[cc] = v0; x[cc + 1] = v1;
                         }
                         st_shared_v4(chunk_addr(main_base, j * 4 + c, row), w[0], w[1], w[2], w[3]);
                     }
+                    if (F8) dump_fp8_chunk32<false>(img8(st_prev), j, row, x, inv8, am, (tile_g & 7) == 0);
                 }
+                if (F8) amax_to_shared(am, reinterpret_cast<uint32_t*>(smem + kDgOffAmax) + st_prev);
                 store_image(st_prev, kMainBytes);
                 if (bs + 1 < prog.n_bwd) {
                     fence_proxy_async_smem();
@@ -320,6 +345,10 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
 
     tc_fence_before();
     __syncthreads();
+    if (F8 && threadIdx.x < 16) {
+        const uint32_t a = reinterpret_cast<uint32_t*>(smem + kDgOffAmax)[threadIdx.x];
+        if (a) atomicMax(args.amax8 + threadIdx.x, a);
+    }
     if (CTAS == 2) cluster_sync_all();
     if (warp == 1) {
         __syncwarp();
@@ -386,7 +415,7 @@ constexpr uint32_t kWgHalfRows = 64;                 // K rows per stage (half a
 constexpr uint32_t kWgOperandBytes = 8 * kWgHalfRows * 64;      // 32 KB: 8 blocks of [64 rows x 64 B]
 constexpr uint32_t kWgStageBytes = 2 * kWgOperandBytes;         // X half + dY half
 constexpr uint32_t kWgOffBias = kWgStages * kWgStageBytes;      // 196608: [4][256] fp32 scratch for the bias reduction
-constexpr uint32_t kWgOffBars = kWgOffBias + 4 * 256 * 4;
+constexpr uint32_t kWgOffBars = kWgOffBias + 8 * 256 * 4;          // (8 row groups in the 8-bit path, 4 in the bf16 path)
 constexpr uint32_t kWgOffTmemSlot = kWgOffBars + (2 * kWgStages + 2) * 8;
 constexpr uint32_t kWgSmemBytes = kWgOffTmemSlot + 16;
 static_assert(kWgSmemBytes <= 232448, "weight-gradient kernel exceeds shared memory");
@@ -398,10 +427,15 @@ struct WgJob {
     float* out;              // row m of the result goes to out + m * out_ld
     float* bias;             // 1^T dY goes here (NULL: skip)
     int64_t x_tile_bytes;    // 65536 (activation images) or 32768 (encoding images)
-    int32_t x_blocks;        // 8: M = 256 (two accumulators), 4: M = 128
-    int32_t n_out;           // N (256 or 128) = dY blocks * 32
+    int32_t x_blocks;        // 64-byte-wide column blocks of X.  bf16: 8 = 256 columns (two accumulators), 4 = 128;
+                             // e4m3: 4 = 256 columns (two accumulators), 2 = 128
+    int32_t n_out;           // N (256 or 128)
     int32_t out_ld;
+    int32_t fp8;             // both operands are e4m3 tile images (32 KB per tile); `scale` rescales the product
     int32_t pad_;
+    const float* x_scale;    // device scalars: value = stored e4m3 * scale (NULL: 1)
+    const float* dy_scale;
+    int64_t dy_tile_bytes;   // 65536 (bf16) or 32768 (e4m3)
 };
 
 struct WgradArgs {
@@ -448,7 +482,7 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
             uint32_t stage = 0, parity = 1;
             for (int jb = 0; jb < args.n_jobs; ++jb) {
                 const WgJob& J = args.jobs[jb];
-                const int xb = J.x_blocks, n_blk = J.n_out / 32;
+                const int xb = J.x_blocks, n_blk = J.fp8 ? J.n_out / 64 : J.n_out / 32;
                 for (int64_t i = 0; i < my_tiles; ++i) {
                     const int64_t tile = blockIdx.x + i * gridDim.x;
                     for (int half = 0; half < 2; ++half) {
@@ -456,7 +490,7 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
                         mbar_arrive_expect_tx(bar_full + 8 * stage, (xb + n_blk) * kHalf);
                         const uint32_t dst = sbase + stage * kWgStageBytes;
                         const uint8_t* xt = J.x + tile * J.x_tile_bytes + half * kHalf;
-                        const uint8_t* dt = J.dy + tile * (int64_t)kMainBytes + half * kHalf;
+                        const uint8_t* dt = J.dy + tile * J.dy_tile_bytes + half * kHalf;
                         for (int blk = 0; blk < xb; ++blk)
                             tma_bulk_g2s(dst + blk * kHalf, xt + blk * kBlockBytes, kHalf, bar_full + 8 * stage);
                         for (int blk = 0; blk < n_blk; ++blk)
@@ -469,8 +503,9 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
     } else if (warp == 1) {
         uint32_t stage = 0, parity = 0, free_phase = 0;
         for (int jb = 0; jb < args.n_jobs; ++jb) {
-            const uint32_t idesc = idesc_bf16_f32_mn(128, args.jobs[jb].n_out);
-            const bool two = args.jobs[jb].x_blocks == 8;
+            const bool f8 = args.jobs[jb].fp8 != 0;
+            const uint32_t idesc = f8 ? idesc_e4m3_f32_mn(128, args.jobs[jb].n_out) : idesc_bf16_f32_mn(128, args.jobs[jb].n_out);
+            const bool two = args.jobs[jb].x_blocks == (f8 ? 4 : 8);
             if (jb > 0) { mbar_wait(bar_free, free_phase); free_phase ^= 1; tc_fence_after(); }
             uint32_t accumulate = 0;
             for (int64_t i = 0; i < my_tiles * 2; ++i) {
@@ -478,14 +513,26 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
                 tc_fence_after();
                 const uint32_t xa = sbase + stage * kWgStageBytes, da = xa + kWgOperandBytes;
                 if (elect_one_sync()) {
+                    if (f8) {
 #pragma unroll
-                    for (int ks = 0; ks < 4; ++ks) {                     // 16 K rows per MMA
-                        const uint64_t bd = smem_desc(da + ks * 1024, kHalf, 512, LAYOUT_SW64);
-                        mma_bf16_ss(tmem_base, smem_desc(xa + ks * 1024, kHalf, 512, LAYOUT_SW64), bd, idesc, accumulate);
-                        if (two)
-                            mma_bf16_ss(tmem_base + 256, smem_desc(xa + 4 * kHalf + ks * 1024, kHalf, 512, LAYOUT_SW64), bd, idesc,
-                                        accumulate);
-                        accumulate = 1;
+                        for (int ks = 0; ks < 2; ++ks) {                 // 32 K rows per MMA (kind::f8f6f4)
+                            const uint64_t bd = smem_desc(da + ks * 2048, kHalf, 512, LAYOUT_SW64);
+                            mma_f8_ss(tmem_base, smem_desc(xa + ks * 2048, kHalf, 512, LAYOUT_SW64), bd, idesc, accumulate);
+                            if (two)
+                                mma_f8_ss(tmem_base + 256, smem_desc(xa + 2 * kHalf + ks * 2048, kHalf, 512, LAYOUT_SW64), bd, idesc,
+                                          accumulate);
+                            accumulate = 1;
+                        }
+                    } else {
+#pragma unroll
+                        for (int ks = 0; ks < 4; ++ks) {                 // 16 K rows per MMA
+                            const uint64_t bd = smem_desc(da + ks * 1024, kHalf, 512, LAYOUT_SW64);
+                            mma_bf16_ss(tmem_base, smem_desc(xa + ks * 1024, kHalf, 512, LAYOUT_SW64), bd, idesc, accumulate);
+                            if (two)
+                                mma_bf16_ss(tmem_base + 256, smem_desc(xa + 4 * kHalf + ks * 1024, kHalf, 512, LAYOUT_SW64), bd, idesc,
+                                            accumulate);
+                            accumulate = 1;
+                        }
                     }
                     mma_commit(bar_empty + 8 * stage);
                 }
@@ -505,11 +552,30 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
         for (int jb = 0; jb < args.n_jobs; ++jb) {
             const WgJob& J = args.jobs[jb];
             const int n_out = J.n_out;
-            float bsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            const bool do_bias = J.bias != nullptr && cc * 8 < n_out;
+            float bsum[16];
+#pragma unroll
+            for (int e = 0; e < 16; ++e) bsum[e] = 0.0f;
+            const bool f8 = J.fp8 != 0;
+            const int c16 = tid & 15, rg8 = tid >> 4;                  // 8-bit path: 16-column chunk, group of 8 rows
+            const bool do_bias = J.bias != nullptr && (f8 ? c16 * 16 < n_out : cc * 8 < n_out);
             for (int64_t i = 0; i < my_tiles * 2; ++i) {
                 mbar_wait(bar_full + 8 * stage, parity);
-                if (do_bias) {
+                if (do_bias && f8) {
+                    const uint8_t* dy = smem + stage * kWgStageBytes + kWgOperandBytes + (c16 >> 2) * kHalf;
+#pragma unroll 4
+                    for (int r = rg8 * 8; r < rg8 * 8 + 8; ++r) {
+                        const uint4 v = *reinterpret_cast<const uint4*>(dy + r * 64 + (((c16 & 3) ^ ((r >> 1) & 3)) << 4));
+                        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) {
+                            const __half2_raw lo = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(w[e] & 0xFFFFu), __NV_E4M3);
+                            const __half2_raw hi = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(w[e] >> 16), __NV_E4M3);
+                            const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&lo));
+                            const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+                            bsum[4 * e] += a.x; bsum[4 * e + 1] += a.y; bsum[4 * e + 2] += b.x; bsum[4 * e + 3] += b.y;
+                        }
+                    }
+                } else if (do_bias) {
                     const uint8_t* dy = smem + stage * kWgStageBytes + kWgOperandBytes + (cc >> 2) * kHalf;
 #pragma unroll 4
                     for (int r = rg * 16; r < rg * 16 + 16; ++r) {
@@ -526,7 +592,18 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
                 if (lane == 0) mbar_arrive(bar_empty + 8 * stage);
                 if (++stage == kWgStages) { stage = 0; parity ^= 1; }
             }
-            if (J.bias != nullptr) {
+            if (J.bias != nullptr && f8) {
+#pragma unroll
+                for (int e = 0; e < 16; ++e) bias_scratch[rg8 * 256 + c16 * 16 + e] = bsum[e];
+                named_bar_sync(1, 128);
+                for (int c = tid; c < n_out; c += 128) {
+                    float sm = 0.0f;
+#pragma unroll
+                    for (int g8 = 0; g8 < 8; ++g8) sm += bias_scratch[g8 * 256 + c];
+                    if (my_tiles > 0) atomicAdd(J.bias + c, sm * (J.dy_scale ? __ldg(J.dy_scale) : 1.0f));
+                }
+                named_bar_sync(1, 128);
+            } else if (J.bias != nullptr) {
 #pragma unroll
                 for (int e = 0; e < 8; ++e) bias_scratch[rg * 256 + cc * 8 + e] = bsum[e];
                 named_bar_sync(1, 128);
@@ -542,14 +619,15 @@ mlp_wgrad_kernel(const __grid_constant__ WgradArgs args) {
             tc_fence_after();
             if (my_tiles > 0) {
                 const int m = quarter * 32 + lane;
-                for (int mh = 0; mh < J.x_blocks / 4; ++mh) {
+                const float oscale = (J.x_scale ? __ldg(J.x_scale) : 1.0f) * (J.dy_scale ? __ldg(J.dy_scale) : 1.0f);
+                for (int mh = 0; mh < (f8 ? J.x_blocks / 2 : J.x_blocks / 4); ++mh) {
                     float* orow = J.out + (int64_t)(mh * 128 + m) * J.out_ld;
                     for (int j = 0; j < n_out / 32; ++j) {
                         uint32_t v[32];
                         tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(quarter * 32) << 16) + mh * 256 + j * 32, v);
                         tmem_ld_wait();
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) atomicAdd(orow + j * 32 + c, __uint_as_float(v[c]));
+                        for (int c = 0; c < 32; ++c) atomicAdd(orow + j * 32 + c, __uint_as_float(v[c]) * oscale);
                     }
                 }
             }
@@ -610,6 +688,75 @@ __device__ __forceinline__ void heads_wgrad_body(const uint8_t* __restrict__ x_i
     }
 }
 
+// the same on e4m3 tile images (64 columns per 64-byte row): a warp owns CH chunks of 16 columns
+template <int ND, int CH>
+__device__ __forceinline__ void heads_wgrad_body8(const uint8_t* __restrict__ x_img, const float* __restrict__ x_scale,
+                                                  const float* __restrict__ d_rgbs, int d0, float* __restrict__ out, int64_t n_rows,
+                                                  int64_t n_tiles) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int blk = CH == 2 ? warp >> 1 : warp >> 2, c0 = CH == 2 ? (warp & 1) * 2 : (warp & 3);
+    float acc[16 * CH * ND];
+#pragma unroll
+    for (int i = 0; i < 16 * CH * ND; ++i) acc[i] = 0.0f;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint8_t* tb = x_img + tile * (int64_t)kMain8Bytes + blk * kBlockBytes;
+#pragma unroll
+        for (int rgp = 0; rgp < 4; ++rgp) {
+            const int row = rgp * 32 + lane;
+            const int64_t grow = tile * kTileRows + row;
+            float d[ND];
+#pragma unroll
+            for (int j = 0; j < ND; ++j) d[j] = grow < n_rows ? __ldg(d_rgbs + 4 * grow + d0 + j) : 0.0f;
+#pragma unroll
+            for (int c = 0; c < CH; ++c) {
+                const uint4 v = __ldg(reinterpret_cast<const uint4*>(tb + row * 64 + (((c0 + c) ^ ((row >> 1) & 3)) << 4)));
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const __half2_raw lo = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(w[e] & 0xFFFFu), __NV_E4M3);
+                    const __half2_raw hi = __nv_cvt_fp8x2_to_halfraw2((__nv_fp8x2_storage_t)(w[e] >> 16), __NV_E4M3);
+                    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&lo));
+                    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&hi));
+                    const float x[4] = {a.x, a.y, b.x, b.y};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q)
+#pragma unroll
+                        for (int j = 0; j < ND; ++j) acc[(c * 16 + 4 * e + q) * ND + j] += x[q] * d[j];
+                }
+            }
+        }
+    }
+    const float sx = __ldg(x_scale);
+#pragma unroll
+    for (int i = 0; i < 16 * CH * ND; ++i) {
+        const float v = ntx_warp_sum(acc[i]);
+        if (lane == 0) atomicAdd(out + (blk * 64 + c0 * 16 + i / ND) * ND + (i % ND), v * sx);
+    }
+}
+
+__global__ void __launch_bounds__(256, 2)
+mlp_heads_wgrad8_kernel(const uint8_t* __restrict__ x_alpha, const float* __restrict__ sx_alpha, const uint8_t* __restrict__ x_rgb,
+                        const float* __restrict__ sx_rgb, const float* __restrict__ d_rgbs, float* __restrict__ out_alpha,
+                        float* __restrict__ out_rgb, int64_t n_rows, int64_t n_tiles) {
+    if (blockIdx.y == 0) heads_wgrad_body8<1, 2>(x_alpha, sx_alpha, d_rgbs, 3, out_alpha, n_rows, n_tiles);
+    else heads_wgrad_body8<3, 1>(x_rgb, sx_rgb, d_rgbs, 0, out_rgb, n_rows, n_tiles);
+}
+
+// per-step scales of the 8-bit images from the maxima the previous step saw: scale = margin * amax / 448 (e4m3's largest
+// finite value), kept where nothing was seen; the maxima are cleared for the step to come
+__global__ void fp8_update_scales_kernel(uint32_t* __restrict__ amax, float* __restrict__ scale, float* __restrict__ inv_scale, int n,
+                                         float margin) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float a = __uint_as_float(amax[i]);
+    if (a > 0.0f && a < CUDART_INF_F) {
+        const float sc = fmaxf(a * margin / 448.0f, 1e-30f);
+        scale[i] = sc;
+        inv_scale[i] = 1.0f / sc;
+    }
+    amax[i] = 0u;
+}
+
 // both heads in one launch (blockIdx.y = 0: density head, 1: colour head)
 __global__ void __launch_bounds__(256, 2)
 mlp_heads_wgrad_kernel(const uint8_t* __restrict__ x_alpha, const uint8_t* __restrict__ x_rgb, const float* __restrict__ d_rgbs,
@@ -637,9 +784,12 @@ NTX_API int ntx_mlp_pack_weights_t(const ntx_mlp_t* mlp, const float* master, vo
     return NTX_OK;
 }
 
-NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
-                                  void* dy_img, int64_t n_rows, int64_t n_tiles, void* stream) {
+static int backward_data_impl(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
+                              void* dy_img, int64_t n_rows, int64_t n_tiles, void* stream, void* dy_img8,
+                              const float* inv_scale8, uint32_t* amax8) {
     NTX_REQUIRE(mlp && packed_t && d_rgbs && masks && dy_img, "mlp_backward_data: null pointer");
+    NTX_REQUIRE(!dy_img8 || (inv_scale8 && amax8 && ((uintptr_t)dy_img8 & 15) == 0 && mlp->prog.n_steps <= 16),
+                "mlp_backward_data: 8-bit images need inv_scale8[n_steps], amax8[n_steps] and 16-byte alignment");
     NTX_REQUIRE(n_rows >= 0 && n_tiles >= ((n_rows + 511) / 512) * 4, "mlp_backward_data: %lld tiles for %lld rows",
                 (long long)n_tiles, (long long)n_rows);
     if (n_rows == 0) return NTX_OK;
@@ -647,13 +797,14 @@ NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, co
                 "mlp_backward_data: buffers must be 16-byte aligned");
     static const int ctas = [] { const char* e = getenv("NTX_MLP_CTAS"); return (e && e[0] == '1') ? 1 : 2; }();
     using KernelFn = void (*)(const BwdProgram, const DgradArgs);
-    KernelFn fn = ctas == 2 ? mlp_dgrad_kernel<2> : mlp_dgrad_kernel<1>;
-    static bool attr_set[64][2] = {};
+    const int f8 = dy_img8 ? 1 : 0;
+    KernelFn fn = ctas == 2 ? (f8 ? mlp_dgrad_kernel<2, true> : mlp_dgrad_kernel<2>) : (f8 ? mlp_dgrad_kernel<1, true> : mlp_dgrad_kernel<1>);
+    static bool attr_set[64][2][2] = {};
     int dev = 0;
     NTX_CUDA(cudaGetDevice(&dev));
-    if (dev < 64 && !attr_set[dev][ctas - 1]) {
+    if (dev < 64 && !attr_set[dev][ctas - 1][f8]) {
         NTX_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDgSmemBytes));
-        attr_set[dev][ctas - 1] = true;
+        attr_set[dev][ctas - 1][f8] = true;
     }
     BwdProgram bp;
     build_bwd_program(mlp, &bp);
@@ -665,6 +816,12 @@ NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, co
     a.n_rows = n_rows;
     a.n_tiles = n_tiles;
     a.depth = mlp->cfg.depth;
+    a.dy_img8 = (uint8_t*)dy_img8;
+    a.inv_scale8 = inv_scale8;
+    a.amax8 = amax8;
+    a.need16 = 0;
+    for (int st = 0; st < mlp->prog.n_steps; ++st)
+        if (mlp->prog.steps[st].enc_data) a.need16 |= 1u << st;       // their encoded-input weight gradient reads bf16 dY
     const int64_t rows_per_unit = (int64_t)kRowsPerCta * ctas;
     const int64_t n_units = (n_rows + rows_per_unit - 1) / rows_per_unit;
     const int64_t max_units = ntx_sm_count() / ctas;
@@ -683,11 +840,26 @@ NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, co
     return NTX_OK;
 }
 
-NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, const void* enc_pos,
-                                     const void* enc_dir, const float* d_rgbs, float* grad, float* enc_scratch,
-                                     int64_t n_rows, int64_t n_tiles, void* stream) {
-    NTX_REQUIRE(mlp && acts_img && dy_img && enc_pos && enc_dir && d_rgbs && grad && enc_scratch,
+NTX_API int ntx_mlp_backward_data(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
+                                  void* dy_img, int64_t n_rows, int64_t n_tiles, void* stream) {
+    return backward_data_impl(mlp, packed_t, d_rgbs, masks, dy_img, n_rows, n_tiles, stream, nullptr, nullptr, nullptr);
+}
+
+NTX_API int ntx_mlp_backward_data_fp8(const ntx_mlp_t* mlp, const void* packed_t, const float* d_rgbs, const void* masks,
+                                      void* dy_img, void* dy_img8, const float* inv_scale8, void* amax8, int64_t n_rows,
+                                      int64_t n_tiles, void* stream) {
+    NTX_REQUIRE(dy_img8, "mlp_backward_data_fp8: null image buffer");
+    return backward_data_impl(mlp, packed_t, d_rgbs, masks, dy_img, n_rows, n_tiles, stream, dy_img8, inv_scale8, (uint32_t*)amax8);
+}
+
+static int backward_weights_impl(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, const void* enc_pos,
+                                 const void* enc_dir, const float* d_rgbs, float* grad, float* enc_scratch,
+                                 int64_t n_rows, int64_t n_tiles, void* stream, const void* acts_img8, const void* dy_img8,
+                                 const float* x_scale8, const float* dy_scale8) {
+    const bool f8 = acts_img8 != nullptr;
+    NTX_REQUIRE(mlp && (acts_img || f8) && dy_img && enc_pos && enc_dir && d_rgbs && grad && enc_scratch,
                 "mlp_backward_weights: null pointer");
+    NTX_REQUIRE(!f8 || (dy_img8 && x_scale8 && dy_scale8), "mlp_backward_weights_fp8: null 8-bit image / scale pointer");
     NTX_REQUIRE(n_rows >= 0 && n_tiles >= (n_rows + 127) / 128, "mlp_backward_weights: bad tile count");
     if (n_rows == 0) return NTX_OK;
     static bool attr_set[64] = {};
@@ -699,6 +871,7 @@ NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img,
     }
     const Program& p = mlp->prog;
     const int64_t step_bytes = n_tiles * (int64_t)kMainBytes;
+    const int64_t step8_bytes = n_tiles * (int64_t)kMain8Bytes;
     WgradArgs a;
     memset(&a, 0, sizeof(a));
     a.n_tiles = (n_rows + 127) / 128;
@@ -708,11 +881,19 @@ NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img,
         const Layer& L = p.layers[S.layer];
         if (st > 0) {                                   // main operand: the previous step's stored output
             WgJob& J = a.jobs[nj++];
-            J.x = (const uint8_t*)acts_img + (st - 1) * step_bytes;
-            J.dy = (const uint8_t*)dy_img + st * step_bytes;
             J.out = grad + L.w_off + (int64_t)S.main_row0 * L.fan_out;
             J.bias = grad + L.b_off;
-            J.x_tile_bytes = kMainBytes; J.x_blocks = 8; J.n_out = S.n_out; J.out_ld = L.fan_out;
+            J.n_out = S.n_out; J.out_ld = L.fan_out;
+            if (f8) {                                   // both operands as e4m3 images, rescaled in the flush
+                J.x = (const uint8_t*)acts_img8 + (st - 1) * step8_bytes;
+                J.dy = (const uint8_t*)dy_img8 + st * step8_bytes;
+                J.x_tile_bytes = kMain8Bytes; J.dy_tile_bytes = kMain8Bytes; J.x_blocks = 4; J.fp8 = 1;
+                J.x_scale = x_scale8 + (st - 1); J.dy_scale = dy_scale8 + st;
+            } else {
+                J.x = (const uint8_t*)acts_img + (st - 1) * step_bytes;
+                J.dy = (const uint8_t*)dy_img + st * step_bytes;
+                J.x_tile_bytes = kMainBytes; J.dy_tile_bytes = kMainBytes; J.x_blocks = 8;
+            }
         }
         if (S.enc_data) {                               // encoded inputs: rows in kernel column order -> scratch
             WgJob& J = a.jobs[nj++];
@@ -720,7 +901,7 @@ NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img,
             J.dy = (const uint8_t*)dy_img + st * step_bytes;
             J.out = enc_scratch + (int64_t)st * 128 * 256;
             J.bias = nullptr;
-            J.x_tile_bytes = 4 * kBlockBytes; J.x_blocks = 4; J.n_out = S.n_out; J.out_ld = 256;
+            J.x_tile_bytes = 4 * kBlockBytes; J.dy_tile_bytes = kMainBytes; J.x_blocks = 4; J.n_out = S.n_out; J.out_ld = 256;
         }
     }
     a.n_jobs = nj;
@@ -732,9 +913,40 @@ NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img,
     const Layer& la = p.layers[p.alpha_layer];
     const Layer& lr = p.layers[p.rgb_layer];
     const int64_t gh = a.n_tiles < 4 * ntx_sm_count() ? a.n_tiles : 4 * ntx_sm_count();
-    mlp_heads_wgrad_kernel<<<dim3((unsigned)gh, 2), 256, 0, stc>>>(
-        (const uint8_t*)acts_img + (int64_t)(mlp->cfg.depth - 1) * step_bytes,
-        (const uint8_t*)acts_img + (int64_t)(p.n_steps - 1) * step_bytes, d_rgbs, grad + la.w_off, grad + lr.w_off, n_rows, a.n_tiles);
+    if (f8)
+        mlp_heads_wgrad8_kernel<<<dim3((unsigned)gh, 2), 256, 0, stc>>>(
+            (const uint8_t*)acts_img8 + (int64_t)(mlp->cfg.depth - 1) * step8_bytes, x_scale8 + (mlp->cfg.depth - 1),
+            (const uint8_t*)acts_img8 + (int64_t)(p.n_steps - 1) * step8_bytes, x_scale8 + (p.n_steps - 1), d_rgbs, grad + la.w_off,
+            grad + lr.w_off, n_rows, a.n_tiles);
+    else
+        mlp_heads_wgrad_kernel<<<dim3((unsigned)gh, 2), 256, 0, stc>>>(
+            (const uint8_t*)acts_img + (int64_t)(mlp->cfg.depth - 1) * step_bytes,
+            (const uint8_t*)acts_img + (int64_t)(p.n_steps - 1) * step_bytes, d_rgbs, grad + la.w_off, grad + lr.w_off, n_rows, a.n_tiles);
+    NTX_LAUNCH_CHECK();
+    return NTX_OK;
+}
+
+NTX_API int ntx_mlp_backward_weights(const ntx_mlp_t* mlp, const void* acts_img, const void* dy_img, const void* enc_pos,
+                                     const void* enc_dir, const float* d_rgbs, float* grad, float* enc_scratch,
+                                     int64_t n_rows, int64_t n_tiles, void* stream) {
+    NTX_REQUIRE(acts_img, "mlp_backward_weights: null pointer");
+    return backward_weights_impl(mlp, acts_img, dy_img, enc_pos, enc_dir, d_rgbs, grad, enc_scratch, n_rows, n_tiles, stream,
+                                 nullptr, nullptr, nullptr, nullptr);
+}
+
+NTX_API int ntx_mlp_backward_weights_fp8(const ntx_mlp_t* mlp, const void* acts_img8, const void* dy_img8, const void* dy_img,
+                                         const float* x_scale8, const float* dy_scale8, const void* enc_pos, const void* enc_dir,
+                                         const float* d_rgbs, float* grad, float* enc_scratch, int64_t n_rows, int64_t n_tiles,
+                                         void* stream) {
+    NTX_REQUIRE(acts_img8, "mlp_backward_weights_fp8: null pointer");
+    return backward_weights_impl(mlp, nullptr, dy_img, enc_pos, enc_dir, d_rgbs, grad, enc_scratch, n_rows, n_tiles, stream, acts_img8,
+                                 dy_img8, x_scale8, dy_scale8);
+}
+
+NTX_API int ntx_fp8_update_scales(void* amax, float* scale, float* inv_scale, int n, float margin, void* stream) {
+    NTX_REQUIRE(amax && scale && inv_scale && n >= 0 && n <= 64 && margin > 0.0f, "fp8_update_scales: bad arguments");
+    if (n == 0) return NTX_OK;
+    fp8_update_scales_kernel<<<1, 64, 0, (cudaStream_t)stream>>>((uint32_t*)amax, scale, inv_scale, n, margin);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }

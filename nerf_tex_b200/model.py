@@ -106,6 +106,13 @@ class FusedNerfTexMLP:
         self.master.requires_grad_(flag)
         return self
 
+    def enable_fp8_saved_operands(self, enable: bool = True):
+        """Training: keep the saved tile images of the backward in fp8 e4m3 (half the bytes of the step's three big
+        kernels); see autograd.enable_fp8_saved_operands."""
+        from .autograd import enable_fp8_saved_operands
+        enable_fp8_saved_operands(self, enable)
+        return self
+
     def mark_dirty(self) -> None:
         """Call after changing ``master`` in place (optimizer step, checkpoint load)."""
         self._packed_version = -1

@@ -282,3 +282,43 @@ def test_tensorflow_checkpoint_restores_into_trainable_models(tmp_path):
     assert np.array_equal(m.master.detach().cpu().numpy(), flat)
     m.reset_parameters(seed=3)                                   # the other in-place writer
     assert m.master.requires_grad and m.master.is_leaf
+
+
+@pytest.mark.parametrize("npar,blur,noise_std,R,S", [((1, 4), None, 0.0, 300, 64), ((2, 3), 0, 0.1, 512, 256)])
+def test_fp8_saved_operands_keep_the_gradient_bars(npar, blur, noise_std, R, S):
+    """Training with the saved tile images in fp8 e4m3 (per-step scales delayed by one step; the first pass calibrates
+    with bf16 images): the gradient of the second pass meets the very bars of the bf16 path against float64 autograd."""
+    from nerf_tex_b200.renderer import Renderer
+    from nerf_tex_b200.loss import AlphaLoss
+    oms, gms, rays_o, rays_d, t, params, cone, ct, at = setup(npar, False, R)
+    gm, om = gms["model"].requires_grad_(True), oms["model"]
+    gm.enable_fp8_saved_operands()
+    rng = np.random.default_rng(5)
+    z_rand = rng.uniform(size=(R, S)).astype(np.float32)
+    noise = (rng.normal(size=(R, S)) * noise_std).astype(np.float32) if noise_std > 0 else None
+    r = Renderer(model=gm, n_samples=S, perturb=True, blur_idx=blur, raw_noise_std=noise_std)
+    loss_fn = AlphaLoss("network.loss.smape", "network.loss.mse")
+    grads = []
+    for step in range(2):
+        gm.master.grad = None
+        pred = r(dev(rays_o[None]), dev(rays_d[None]), dev(t[None]), dev(params), dev(cone[None]), composite_bkgd=True,
+                 bkgd_color=(1., 1., 1.), training=True, z_rand=dev(z_rand), noise=None if noise is None else dev(noise))
+        loss = loss_fn(color_true=dev(ct), alpha_true=dev(at), **pred)
+        loss.backward()
+        grads.append(gm.master.grad.detach().cpu().clone())
+        assert gm._fp8["calibrated"]
+    assert not torch.equal(grads[0], grads[1])                     # the second pass really took the 8-bit path
+    sx, sy = gm._fp8["scale_x"].cpu(), gm._fp8["scale_y"].cpu()
+    n_steps = gm.schedule().n_steps
+    assert bool((sx[:n_steps] > 0).all()) and bool((sy[:n_steps] > 0).all()) and float(sx[:n_steps].max()) < 1.0
+    P = T.make_params(om)
+    z = t64(O.stratified_z(t, S, True, z_rand))
+    C, A, _ = T.network_pass(om, P, t64(rays_o), t64(rays_d), z, t64(np.repeat(params, R, 0)), t64(cone), blur,
+                             composite_bkgd=True, noise=None if noise is None else t64(noise))
+    T.alpha_loss(t64(ct[0]), t64(at[0]), C, A).backward()
+    want = T.flat_grads(om, P)
+    check_grads(grads[1], want, om, "fp8 saved operands")
+    rel16 = float((grads[0].double() - want).norm() / want.norm())
+    rel8 = float((grads[1].double() - want).norm() / want.norm())
+    print(f"flat gradient rel error vs float64: bf16 images {rel16:.3e}, e4m3 images {rel8:.3e}")
+    assert rel8 < 2e-2

@@ -22,13 +22,19 @@ if __name__ == "__main__":
             "parameters": torch.rand((1, 5), device=dev, generator=g), "cone_scale": torch.rand((1, R, 1), device=dev, generator=g) * .01,
             "color": torch.rand((1, R, 3), device=dev, generator=g), "alpha": torch.rand((1, R), device=dev, generator=g)}
     models = {"model": FusedNerfTexMLP(2, 3, seed=1)}
+    if os.environ.get("NTX_FP8_SAVED") == "1":
+        models["model"].enable_fp8_saved_operands()
     r = Renderer(n_samples=256, n_importance=0, perturb=True, blur_idx=0, raw_noise_std=0.1, seed=0, **models)
     tr = Trainer(models, r, AlphaLoss("network.loss.smape", "network.loss.mse"))
     n = int(sys.argv[1]) if len(sys.argv) > 1 else 4
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for i in range(n):
+        if i == 2:
+            e0.record()
         if i == n - 1:
             torch.cuda.synchronize()
             torch.cuda.nvtx.range_push("last_step")
         loss = tr.train_step(data)
+    e1.record()
     torch.cuda.synchronize()
-    print("loss", float(loss))
+    print("loss", float(loss), "ms/step", e0.elapsed_time(e1) / max(n - 2, 1))
