@@ -722,7 +722,10 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
 // Pass 2, one thread per sample: every store of a warp is contiguous.  The sample finds its ray (binary search in
 // ray_ptr) and the hit interval it was emitted in (binary search in the ray's step_at row), replays the hits before it
 // to get the set of patches it is inside, and writes its record.
-__global__ void __launch_bounds__(256)
+// EXTRAS: shadow rays and parameter textures compiled in (their any-hit walks and parameter vectors cost registers:
+// the plain variant runs at twice the occupancy)
+template <bool EXTRAS>
+__global__ void __launch_bounds__(256, EXTRAS ? 2 : 4)
 instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const int32_t* __restrict__ ray_ids,
                       const float* __restrict__ params,
                       int n_param, int R, const SceneDev sc, float step_size, uint32_t seed, int light_idx, int strength_idx,
@@ -854,7 +857,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         out.dirs[3 * k + a] = dot3(Dt + 3 * a, dn);                           // getDir :561-563
     }
     const float* prm = params + (size_t)ray * n_param;
-    if (sc.sh.n_param_tex > 0 && sc.sh.n_base_faces > 0) {                    // :864, :916-926, :985-991
+    if (EXTRAS && sc.sh.n_param_tex > 0 && sc.sh.n_base_faces > 0) {          // :864, :916-926, :985-991
         const uint32_t n_tex = max((uint32_t)sc.sh.min_samples, (uint32_t)__fmul_rn((float)sc.sh.n_samples, ri.total));
         float pv[16];
         if (n_tex < (uint32_t)sh.n_pts) {
@@ -890,7 +893,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         // the direction becomes (position - sample) and the strength parameter the received radiance (:572-590)
         const float raw[3] = {__ldg(prm + light_idx), __ldg(prm + light_idx + 1), __ldg(prm + light_idx + 2)};
         bool shadowed = false;
-        if (sh.enabled) {                                                     // :863, :936-951
+        if (EXTRAS && sh.enabled) {                                           // :863, :936-951
             const uint32_t n_shadow = max((uint32_t)sh.min_samples, (uint32_t)__fmul_rn((float)sh.n_samples, ri.total));
             float q[3] = {pt[0], pt[1], pt[2]};
             if (n_shadow < (uint32_t)sh.n_pts) {
@@ -1034,10 +1037,17 @@ NTX_API int ntx_instancer_march(const float* rays_o, const float* rays_d, const 
         for (int a = 0; a < 3; ++a) { sh.box.b0[a] = b_0[a]; sh.box.b1[a] = b_1[a]; }
     }
     MarchOut out = {pts, dirs, params_out, dists, t, alpha_weight, instance_id};
-    instancer_emit_kernel<<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        rays_o, rays_d, ray_ids, parameters, n_param, R, sc, step_size, seed, light_dir_idx,
-        light_strength_idx, method, blend_range, use_mean_distance, carve_workspace(const_cast<void*>(workspace), R), ray_ptr,
-        T, out, sh);
+    const bool extras = sh.enabled || (sc.sh.n_param_tex > 0 && sc.sh.n_base_faces > 0);
+    if (extras)
+        instancer_emit_kernel<true><<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+            rays_o, rays_d, ray_ids, parameters, n_param, R, sc, step_size, seed, light_dir_idx,
+            light_strength_idx, method, blend_range, use_mean_distance, carve_workspace(const_cast<void*>(workspace), R), ray_ptr,
+            T, out, sh);
+    else
+        instancer_emit_kernel<false><<<(unsigned)((T + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+            rays_o, rays_d, ray_ids, parameters, n_param, R, sc, step_size, seed, light_dir_idx,
+            light_strength_idx, method, blend_range, use_mean_distance, carve_workspace(const_cast<void*>(workspace), R), ray_ptr,
+            T, out, sh);
     NTX_LAUNCH_CHECK();
     return NTX_OK;
 }
