@@ -85,7 +85,9 @@ def mlp_forward_train(model, *, n_rows, dir, params, rows_per_group, pos=None, r
         check(lib.ntx_mlp_forward_train_fp8(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
                                             ptr(acts_img8), ptr(f8["inv_x"]), ptr(f8["amax_x"]), ptr(masks), n_tiles, stream_ptr()))
         return rgbs, (enc_pos, enc_dir, acts_img8, masks, None, n_rows)
-    acts_img = torch.empty((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=dev)
+    # (the calibration pass of the 8-bit mode takes maxima over whole images: parts no kernel writes must read as zero)
+    alloc = torch.zeros if (f8 is not None and not f8["calibrated"]) else torch.empty
+    acts_img = alloc((sched.n_steps, n_tiles, 128 * 256), dtype=torch.bfloat16, device=dev)
     acts = torch.empty((sched.n_steps, n_rows, 256), dtype=torch.bfloat16, device=dev) if row_major_acts else None
     check(lib.ntx_mlp_forward_train(model._h, ptr(packed), C.byref(inp), ptr(rgbs), ptr(enc_pos), ptr(enc_dir),
                                     ptr(acts), ptr(acts_img), ptr(masks), n_tiles, stream_ptr()))
@@ -164,7 +166,7 @@ def mlp_backward_native(model, saved, d_rgbs: torch.Tensor, return_dy: bool = Fa
                                                ptr(f8["scale_y"]), ptr(enc_pos), ptr(enc_dir), ptr(d_rgbs), ptr(grad),
                                                ptr(enc_scratch), n_rows, n_tiles, stream_ptr()))
     else:
-        dy_img = torch.empty_like(acts_img)
+        dy_img = torch.zeros_like(acts_img) if (f8 is not None and not f8["calibrated"]) else torch.empty_like(acts_img)
         check(lib.ntx_mlp_backward_data(model._h, ptr(model._packed_t), ptr(d_rgbs), ptr(masks), ptr(dy_img), n_rows, n_tiles,
                                         stream_ptr()))
         check(lib.ntx_mlp_backward_weights(model._h, ptr(acts_img), ptr(dy_img), ptr(enc_pos), ptr(enc_dir), ptr(d_rgbs),

@@ -3,7 +3,10 @@
 // One persistent CTA per SM (320 threads) walks 256-row batches of samples:
 //
 //   warp 0      weight producer: streams the packed bf16 weight image, one [N x 32] K-slice per
-//               bulk-TMA copy (cp.async.bulk -> UBLKCP), into a 3-deep shared-memory ring.
+//               bulk-TMA copy (cp.async.bulk -> UBLKCP), into a 3-deep shared-memory ring.  In a CTA
+//               pair each CTA copies its N/2 rows of every slice as a tensor-map box
+//               (cp.async.bulk.tensor ... cta_group::2) whose bytes are credited straight to the
+//               issuing CTA's barrier: the ring's turnaround has no hop through the peer.
 //   warp 1      MMA issuer: one elected lane issues tcgen05.mma (M=128, N=256|128, K=16, bf16 in,
 //               fp32 accumulate in TMEM).  The CTA's two 128-row tiles alternate layer by layer:
 //               while the tensor core runs tile 1's layer, tile 0's epilogue warps turn their
@@ -19,9 +22,11 @@
 // heads (density 256->1, colour 128->3) run on CUDA cores in fp32 inside the epilogues.
 //
 // Reference: network/layer.py:11-23, network/model.py:58-125, network/renderer.py:145-168.
+#include <cuda.h>
 #include <cuda_bf16.h>
 
 #include <stdlib.h>
+#include <string.h>
 
 #include <new>
 
@@ -40,8 +45,15 @@ using namespace ntxmlp;
 // ----------------------------------------------------------------------------------------------
 constexpr uint32_t kEncBytes = kEncBlocks * kBlockBytes;                   // 24576
 constexpr uint32_t kTileBytes = kMainBytes + kEncBytes;                    // 90112
+#ifdef NTX_EXP_STAGES
+constexpr int kStagesX = NTX_EXP_STAGES;      // timing experiment only: a 4th stage overlaps tile 1's encoding buffer
+constexpr uint32_t kOffStages = kTilesPerCta * kTileBytes - (kStagesX > 3 ? (kStagesX - 3) * kStageBytes : 0);
+constexpr uint32_t kRingBytes = kStagesX * kStageBytes;
+#define kStages kStagesX
+#else
 constexpr uint32_t kOffStages = kTilesPerCta * kTileBytes;                 // 180224
 constexpr uint32_t kRingBytes = kStages * kStageBytes;                     // 49152: 3 x 16 KB, or 6 x 8 KB per CTA of a pair
+#endif
 constexpr uint32_t kOffHeads = kOffStages + kRingBytes;                    // 229376
 constexpr uint32_t kOffBars = kOffHeads + kHeadFloats * 4;                 // +2592
 constexpr uint32_t kMaxStages = 2 * kStages;
@@ -58,6 +70,9 @@ constexpr int kThreads = 320;
 constexpr int kEpiWarp0 = 2;
 
 struct KernelArgs {
+    // CTA pairs only: the packed weight image as rows of 2 KB; one box = this CTA's half of a K-slice
+    // (8 KB for N = 256, 4 KB for N = 128)
+    CUtensorMap w_map128, w_map64;
     ntx_mlp_inputs in;
     const uint8_t* packed;
     float* rgbs;
@@ -180,7 +195,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
     if (threadIdx.x == 0) {
         for (uint32_t i = 0; i < NSTAGE; ++i) {
             // pair: the issuing CTA's "landed" barrier also collects the peer's relay arrive
-            mbar_init(bar_full + 8 * i, (CTAS == 2 && rank == 0) ? 2 : 1);
+            // pair: only the issuing CTA's "landed" barrier is used; both CTAs' copies credit their bytes to it
+            mbar_init(bar_full + 8 * i, 1);
             mbar_init(bar_empty + 8 * i, 1);
         }
         for (int t = 0; t < kTilesPerCta; ++t) {
@@ -209,24 +225,38 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         // vice versa), so every layer's slices are streamed once per tile, in MMA issue order.
         if (lane == 0) {
             uint32_t stage = 0, parity = 1;      // a fresh barrier passes a wait on parity 1
+            const uint32_t leader_full = CTAS == 2 ? mapa_shared(bar_full, 0) : bar_full;
+            if (CTAS == 2) { prefetch_tensormap(&args.w_map128); prefetch_tensormap(&args.w_map64); }
             for (int64_t b = batch0; b < n_batches; b += batch_stride) {
                 for (int st = 0; st < prog.n_steps; ++st) {
                     const int n_main = prog.steps[st].n_main, enc_n = prog.steps[st].enc_n;
                     const uint32_t slice_bytes = (uint32_t)prog.steps[st].n_out * 64u;
                     const uint32_t bytes = slice_bytes / CTAS;               // pair: this CTA's N/2 rows of a slice
                     const uint8_t* src0 = args.packed + prog.slice_off[prog.steps[st].slice_begin] + rank * bytes;
+                    // pair: box coordinates in rows of 2 KB of the packed image
+                    const int32_t wrow0 = (int32_t)((prog.slice_off[prog.steps[st].slice_begin] + rank * bytes) >> 11);
+                    const int32_t wrows = (int32_t)(slice_bytes >> 11);
+                    const void* w_map = bytes == 8192u ? (const void*)&args.w_map128 : (const void*)&args.w_map64;
                     for (int t = 0; t < kTilesPerCta; ++t) {
                         const uint8_t* src = src0;
+                        int32_t wrow = wrow0;
                         // stage groups: main slices first, then encoding slices, SPS slices per stage
                         for (int part = 0; part < 2; ++part) {
                             int left = part == 0 ? n_main : enc_n;
                             while (left > 0) {
                                 const int n = left < SPS ? left : SPS;
                                 mbar_wait(bar_empty + 8 * stage, parity);
-                                mbar_arrive_expect_tx(bar_full + 8 * stage, bytes * n);
-                                for (int j = 0; j < n; ++j, src += slice_bytes)
-                                    tma_bulk_g2s(sbase + kOffStages + stage * STAGE_BYTES + j * bytes, src, bytes,
-                                                 bar_full + 8 * stage);
+                                if (CTAS == 2) {
+                                    if (rank == 0) mbar_arrive_expect_tx(bar_full + 8 * stage, 2 * bytes * n);
+                                    for (int j = 0; j < n; ++j, wrow += wrows)
+                                        tma_tile2d_g2s_pair(sbase + kOffStages + stage * STAGE_BYTES + j * bytes, w_map, 0, wrow,
+                                                            leader_full + 8 * stage);
+                                } else {
+                                    mbar_arrive_expect_tx(bar_full + 8 * stage, bytes * n);
+                                    for (int j = 0; j < n; ++j, src += slice_bytes)
+                                        tma_bulk_g2s(sbase + kOffStages + stage * STAGE_BYTES + j * bytes, src, bytes,
+                                                     bar_full + 8 * stage);
+                                }
                                 if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
                                 left -= n;
                             }
@@ -240,23 +270,8 @@ mlp_forward_kernel(const __grid_constant__ Program prog, const __grid_constant__
         // The whole warp walks the schedule (so every operand is warp-uniform); one elected lane
         // issues tcgen05.mma / tcgen05.commit.
         if (CTAS == 2 && rank != 0) {
-            // peer CTA of a pair: this warp only relays "my half of the slice has landed" to the
-            // issuing CTA (bulk copies can only signal a barrier in their own CTA)
-            if (lane == 0) {
-                uint32_t stage = 0, parity = 0;
-                const uint32_t remote_full = mapa_shared(bar_full, 0);
-                for (int64_t b = batch0; b < n_batches; b += batch_stride) {
-                    for (int st = 0; st < prog.n_steps; ++st) {
-                        const int n_sl = ((prog.steps[st].n_main + SPS - 1) / SPS + (prog.steps[st].enc_n + SPS - 1) / SPS) *
-                                         kTilesPerCta;
-                        for (int s = 0; s < n_sl; ++s) {
-                            mbar_wait(bar_full + 8 * stage, parity);
-                            mbar_arrive_remote(remote_full + 8 * stage);
-                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
-                        }
-                    }
-                }
-            }
+            // peer CTA of a pair: nothing to issue.  Its weight copies credit the issuing CTA's barriers themselves
+            // (cp.async.bulk.tensor ... cta_group::2), its stages are freed by the issuer's multicast commits.
         } else {
         uint32_t stage = 0, parity = 0, act_phase0 = 0, act_phase1 = 0;
         uint32_t b16 = (sbase + kOffStages) >> 4;         // ring stage base >> 4
@@ -805,6 +820,39 @@ NTX_API int64_t ntx_mlp_train_tiles(int64_t n_rows) {
     return ((n_rows + 511) / 512) * 4;
 }
 
+// The packed weight image as a 2-D tensor map over rows of 2 KB (256 eight-byte elements, the widest row a box can
+// have; every K-slice is stored pre-swizzled by the packer and starts on a 2 KB boundary), box = `box_rows` consecutive
+// rows = one CTA's half of a slice (4 rows = 8 KB for N = 256, 2 rows for N = 128).  No swizzle, no interleave: the
+// box lands in shared memory exactly as a linear copy of the same bytes would.
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+static int weight_map(CUtensorMap* map, const void* packed, int64_t packed_bytes, uint32_t box_rows) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    NTX_REQUIRE(enc, "mlp_forward: cuTensorMapEncodeTiled is not available from this driver");
+    const cuuint64_t dims[2] = {256, (cuuint64_t)(packed_bytes / 2048)};
+    const cuuint64_t strides[1] = {2048};
+    const cuuint32_t box[2] = {256, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void*>(packed), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    NTX_REQUIRE(r == CUDA_SUCCESS, "mlp_forward: cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return NTX_OK;
+}
+
 static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
                           void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks, int64_t n_tiles,
                           bool dump, void* stream, void* acts_img8 = nullptr, const float* inv_scale8 = nullptr,
@@ -846,6 +894,14 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
         attr_set[dev][mode][ctas - 1] = true;
     }
     KernelArgs ka;
+    if (ctas == 2) {
+        NTX_REQUIRE((mlp->packed_bytes & 2047) == 0, "mlp_forward: packed image is not a multiple of 2 KB");
+        if (int rc = weight_map(&ka.w_map128, packed, mlp->packed_bytes, 4)) return rc;
+        if (int rc = weight_map(&ka.w_map64, packed, mlp->packed_bytes, 2)) return rc;
+    } else {
+        memset(&ka.w_map128, 0, sizeof(CUtensorMap));
+        memset(&ka.w_map64, 0, sizeof(CUtensorMap));
+    }
     ka.in = *in;
     ka.packed = (const uint8_t*)packed;
     ka.rgbs = rgbs;

@@ -78,6 +78,18 @@ __device__ __forceinline__ void tma_bulk_g2s(uint32_t dst_smem, const void* src_
                  ::"r"(dst_smem), "l"(src_gmem), "r"(bytes), "r"(bar) : "memory");
 }
 
+// One box of a 2-D tensor map -> this CTA's shared memory, issued inside a CTA pair: the transaction bytes are
+// credited to `bar_cluster`, a barrier that may live in EITHER CTA of the pair (shared::cluster address).  This is what
+// lets the peer's weight copies signal the MMA-issuing CTA's barrier directly; a plain cp.async.bulk can only signal
+// a barrier of the CTA that receives the data.  The map always covers this GPU's own memory (the packed weights).
+__device__ __forceinline__ void tma_tile2d_g2s_pair(uint32_t dst_smem, const void* tmap, int32_t c0, int32_t c1, uint32_t bar_cluster) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                 ::"r"(dst_smem), "l"(tmap), "r"(c0), "r"(c1), "r"(bar_cluster) : "memory");
+}
+__device__ __forceinline__ void prefetch_tensormap(const void* tmap) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
 // shared -> global bulk store (TMA store), tracked by bulk async-groups of the issuing thread
 __device__ __forceinline__ void tma_bulk_s2g(void* dst_gmem, uint32_t src_smem, uint32_t bytes) {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(src_smem), "r"(bytes)

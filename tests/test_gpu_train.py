@@ -293,6 +293,8 @@ def test_fp8_saved_operands_keep_the_gradient_bars(npar, blur, noise_std, R, S):
     oms, gms, rays_o, rays_d, t, params, cone, ct, at = setup(npar, False, R)
     gm, om = gms["model"].requires_grad_(True), oms["model"]
     gm.enable_fp8_saved_operands()
+    junk = torch.full((96 << 20,), float("inf"), dtype=torch.bfloat16, device="cuda")   # what a recycled block may hold:
+    del junk                                                       # the calibration must not read unwritten image parts
     rng = np.random.default_rng(5)
     z_rand = rng.uniform(size=(R, S)).astype(np.float32)
     noise = (rng.normal(size=(R, S)) * noise_std).astype(np.float32) if noise_std > 0 else None
@@ -310,7 +312,9 @@ def test_fp8_saved_operands_keep_the_gradient_bars(npar, blur, noise_std, R, S):
     assert not torch.equal(grads[0], grads[1])                     # the second pass really took the 8-bit path
     sx, sy = gm._fp8["scale_x"].cpu(), gm._fp8["scale_y"].cpu()
     n_steps = gm.schedule().n_steps
-    assert bool((sx[:n_steps] > 0).all()) and bool((sy[:n_steps] > 0).all()) and float(sx[:n_steps].max()) < 1.0
+    assert bool((sx[:n_steps] > 0).all()) and bool((sy[:n_steps] > 0).all())
+    # the kernels' maxima replaced the initial 1.0
+    assert int((sx[:n_steps] < 1.0).sum()) >= n_steps - 1 and int((sy[:n_steps] != 1.0).sum()) >= n_steps - 1
     P = T.make_params(om)
     z = t64(O.stratified_z(t, S, True, z_rand))
     C, A, _ = T.network_pass(om, P, t64(rays_o), t64(rays_d), z, t64(np.repeat(params, R, 0)), t64(cone), blur,
