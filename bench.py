@@ -729,8 +729,10 @@ def run_gpu(args):
     time.sleep(0.3)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    torch.cuda.nvtx.range_push("ntx_value_timed")        # ncu --nvtx --nvtx-include "ntx_value_timed/": the timed region only
     for _ in range(args.steps):
         out = one_step()
+    torch.cuda.nvtx.range_pop()
     e1.record()
     sync_all()
     ms = e0.elapsed_time(e1)
@@ -772,8 +774,10 @@ def run_gpu(args):
     e_steps = max(1, args.steps)
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
+    torch.cuda.nvtx.range_push("ntx_e2e_timed")
     for i in range(e_steps):
         pipe.frame(i)
+    torch.cuda.nvtx.range_pop()
     e3.record()
     sync_all()
     ms_e2e = e2.elapsed_time(e3)
