@@ -17,6 +17,7 @@
 namespace {
 
 constexpr int kMaxHits = 200;        // MAX_TOTAL_HITS, instancer.cpp:22
+constexpr int kFirstOpenStride = 208; // kMaxHits bytes per ray, rounded up to 16
 constexpr int kInstTile = 128;
 constexpr int kTraceThreads = 128;   // rays per block of the trace pass
 constexpr int kSmemHits = 56;        // hit-list entries per ray kept in shared memory; the rest lives in the ray's workspace row
@@ -68,6 +69,7 @@ struct Workspace {
     float* segoff;       // [R][kMaxHits]
     RayInfo* info;       // [R]
     int32_t* n_hits;     // [R]
+    uint8_t* first_open; // [R][kFirstOpenStride]: oldest hit still open behind hit j (j + 1 if none): where pass 2's scans start
     float2* seg;         // [R][kMaxHits] (only with shadow rays): (entry t, length) of the segment open after hit j
 };
 __host__ __device__ inline Workspace carve_workspace(void* base, int64_t R) {
@@ -78,6 +80,7 @@ __host__ __device__ inline Workspace carve_workspace(void* base, int64_t R) {
     w.segoff = (float*)p;    p += R * kMaxHits * 4;
     w.info = (RayInfo*)p;    p += R * 16;
     w.n_hits = (int32_t*)p;  p += ((R * 4 + 15) / 16) * 16;
+    w.first_open = p;        p += R * kFirstOpenStride;
     w.seg = (float2*)p;
     return w;
 }
@@ -124,7 +127,7 @@ struct OpenList {
 template <class Hits>
 __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint32_t seed, uint32_t ray, int use_mean,
                         float t_mesh, int32_t* __restrict__ step_at, float* __restrict__ segoff,
-                        RayInfo* __restrict__ info, float2* __restrict__ seg) {
+                        RayInfo* __restrict__ info, float2* __restrict__ seg, uint8_t* __restrict__ first_open) {
     OpenList act;
     // :801-827 total in-shell length
     float total = 0.0f, t_entry = 0.0f;
@@ -150,6 +153,9 @@ __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint
             hits(j) = hj | ((uint64_t)kNoPartner << 24);
             if (was_empty) { t_entry = tt; seg_begin = j; }
         }
+        int fo = j + 1;                                   // a sample behind hit j is inside no patch entered before hit fo
+        for (int k = 0; k < act.n; ++k) fo = min(fo, (int)act.from[k]);
+        first_open[j] = (uint8_t)fo;
     }
     if (t_mesh < CUDART_INF_F && act.n > 0) {
         const float len = __fsub_rn(t_mesh, t_entry);
@@ -602,6 +608,27 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     // per cell the ray crosses; the same ray and box give the same t, so a repeat shows up as an equal key)
     auto insert = [&](float t, uint32_t inst) {
         const uint64_t key = ((uint64_t)__float_as_uint(t + 0.0f) << 32) | inst;
+        if (n_hits < kSmemHits) {
+            // the whole list is in shared memory (most rays): find the slot and open it in one backward pass (an exit
+            // lands ~30 places before the end of the list).  Longer lists take the two-pass form below: fusing it as well
+            // was measured slower (the shared / global split of every access costs more than the second pass).
+            uint64_t* __restrict__ mine = s_hits + threadIdx.x;
+            int q = n_hits;
+            bool dup = false;
+            while (q > 0) {
+                const uint64_t h = mine[(q - 1) * kTraceThreads];
+                if (h <= key) { dup = h == key; break; }
+                mine[q * kTraceThreads] = h;
+                --q;
+            }
+            if (dup) {                                   // met before in another cell (rare): close the gap again
+                for (int r = q; r < n_hits; ++r) mine[r * kTraceThreads] = mine[(r + 1) * kTraceThreads];
+                return;
+            }
+            mine[q * kTraceThreads] = key;
+            ++n_hits;
+            return;
+        }
         int k = n_hits;
         while (k > 0 && H(k - 1) > key) --k;            // slot of the new key (hits arrive nearly in order: short scan)
         if (k > 0 && H(k - 1) == key) return;
@@ -715,7 +742,7 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
     const uint32_t rid = ray_ids ? (uint32_t)ray_ids[ray] : (uint32_t)ray;
     n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, rid, use_mean, t_mesh,
                               ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray,
-                              ws.seg ? ws.seg + (size_t)ray * kMaxHits : nullptr);
+                              ws.seg ? ws.seg + (size_t)ray * kMaxHits : nullptr, ws.first_open + (size_t)ray * kFirstOpenStride);
     for (int k = 0; k < min(n_hits, kSmemHits); ++k) row[k] = H(k);     // with the partner indices walk_ray added
 }
 
@@ -734,14 +761,22 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
     const float* __restrict__ minv = sc.minv;
     const float* __restrict__ dirt = sc.dirt;
     const float* __restrict__ origins = sc.origins;
-    const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t k0 = (int64_t)blockIdx.x * blockDim.x;
+    const int64_t k = k0 + threadIdx.x;
+    auto ray_of = [&](int64_t kk, int lo, int hi) {       // last ray in [lo, hi) with ray_ptr[ray] <= kk
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (__ldg(ray_ptr + mid) <= kk) lo = mid; else hi = mid;
+        }
+        return lo;
+    };
+    // the rays of the block's first and last sample bound every thread's search
+    __shared__ int s_win[2];
+    if (threadIdx.x == 0) s_win[0] = ray_of(k0, 0, R);
+    if (threadIdx.x == 32) s_win[1] = ray_of(min(k0 + (int64_t)blockDim.x, T) - 1, 0, R);
+    __syncthreads();
     if (k >= T) return;
-    int lo = 0, hi = R;                                   // last ray with ray_ptr[ray] <= k
-    while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (__ldg(ray_ptr + mid) <= k) lo = mid; else hi = mid;
-    }
-    const int ray = lo;
+    const int ray = ray_of(k, s_win[0], s_win[1] + 1);
     const uint32_t rid = ray_ids ? (uint32_t)__ldg(ray_ids + ray) : (uint32_t)ray;     // the ray's name for the draws
     const int step = (int)(k - __ldg(ray_ptr + ray));
     const RayInfo ri = ws.info[ray];
@@ -754,6 +789,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         if (__ldg(step_at + mid) <= step) j = mid + 1; else jh = mid;
     }
     const float segment_offset = j > 0 ? ws.segoff[(size_t)ray * kMaxHits + j - 1] : 0.0f;
+    const int q0 = j > 0 ? (int)ws.first_open[(size_t)ray * kFirstOpenStride + j - 1] : 0;   // no open patch before hit q0
     float o[3], d[3];
 #pragma unroll
     for (int a = 0; a < 3; ++a) { o[a] = __ldg(rays_o + 3 * ray + a); d[a] = __ldg(rays_d + 3 * ray + a); }
@@ -768,19 +804,19 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
     float w = 1.0f;
     if (method == 0) {                                                        // random, :671-677
         int n_act = 0;
-        for (int q = 0; q < j; ++q) {
+        for (int q = q0; q < j; ++q) {
             const uint64_t h = __ldg(hits + q);
             if (inside(h)) { ++n_act; sel = hit_inst(h); }
         }
         if (n_act > 1) {                                                      // the idx-th smallest id of the set
             const int idx = (int)pick(seed, rid, (uint32_t)step, (uint32_t)n_act);
             w = (float)n_act;
-            for (int q = 0; q < j; ++q) {
+            for (int q = q0; q < j; ++q) {
                 const uint64_t h = __ldg(hits + q);
                 if (!inside(h)) continue;
                 const uint32_t id = hit_inst(h);
                 int rank = 0;
-                for (int r = 0; r < j; ++r) {
+                for (int r = q0; r < j; ++r) {
                     const uint64_t g = __ldg(hits + r);
                     rank += inside(g) && hit_inst(g) < id;
                 }
@@ -797,7 +833,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         };
         auto next_id = [&](int64_t cur) {                                     // smallest member id above cur, or -1
             int64_t best = -1;
-            for (int q = 0; q < j; ++q) {
+            for (int q = q0; q < j; ++q) {
                 const uint64_t h = __ldg(hits + q);
                 const int64_t id = hit_inst(h);
                 if (inside(h) && id > cur && (best < 0 || id < best)) best = id;
@@ -805,7 +841,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
             return best;
         };
         float min_dist = CUDART_INF_F;
-        for (int q = 0; q < j; ++q) {
+        for (int q = q0; q < j; ++q) {
             const uint64_t h = __ldg(hits + q);
             if (inside(h)) min_dist = fminf(min_dist, dist_to(hit_inst(h)));
         }
@@ -830,7 +866,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
         // keeps the first strict minimum); sqrt is monotone, so it is only taken for candidates that can win
         float best = CUDART_INF_F, best_sq = CUDART_INF_F;
         int n_act = 0;
-        for (int q = 0; q < j; ++q) {
+        for (int q = q0; q < j; ++q) {
             const uint64_t h = __ldg(hits + q);
             if (!inside(h)) continue;
             const uint32_t id = hit_inst(h);
@@ -944,7 +980,7 @@ instancer_emit_kernel(const float* __restrict__ rays_o, const float* __restrict_
 
 NTX_API int64_t ntx_instancer_workspace_bytes(int R, int cast_shadow_rays) {
     if (R < 0) return -1;
-    return (int64_t)R * (kMaxHits * 16 + 16 + 4) + 16 + (cast_shadow_rays ? (int64_t)R * kMaxHits * 8 : 0);
+    return (int64_t)R * (kMaxHits * 16 + 16 + 4 + kFirstOpenStride) + 16 + (cast_shadow_rays ? (int64_t)R * kMaxHits * 8 : 0);
 }
 
 static int check_scene(const ntx_instancer_scene* s, SceneDev* out) {

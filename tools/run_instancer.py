@@ -26,7 +26,7 @@ if __name__ == "__main__":
     mid = int(hit.sum()) // 2
     ro, rd = rays_o[hit][mid - n // 2:mid + n // 2].contiguous(), rays_d[hit][mid - n // 2:mid + n // 2].contiguous()
     pf = torch.tensor([[1, 1, 1, .1, 0, 0, 1.]], device=dev).repeat(ro.shape[0], 1)
-    for _ in range(3):
+    for _ in range(int(os.environ.get('NTX_ITERS', '3'))):
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         csr = inst.get_model_input_csr(ro, rd, pf, 1024, 0.002, seed=0)
