@@ -19,7 +19,10 @@ namespace {
 constexpr int kMaxHits = 200;        // MAX_TOTAL_HITS, instancer.cpp:22
 constexpr int kFirstOpenStride = 208; // kMaxHits bytes per ray, rounded up to 16
 constexpr int kInstTile = 128;
-constexpr int kTraceThreads = 128;   // rays per block of the trace pass
+#ifndef NTX_TRACE_THREADS
+#define NTX_TRACE_THREADS 128
+#endif
+constexpr int kTraceThreads = NTX_TRACE_THREADS;   // rays per block of the trace pass
 constexpr int kSmemHits = 56;        // hit-list entries per ray kept in shared memory; the rest lives in the ray's workspace row
 constexpr int kMailbox = 16;         // per-ray direct-mapped cache of instances already tested (grid walk)
 constexpr float kTFar = 100.0f;

@@ -62,21 +62,30 @@ _PLAN_CACHE: dict = {}
 
 
 def shard_plan(n_rays: int, world: int, block: int, interleave: bool, device):
-    """(per, [index tensor of every rank], gather) for one way of splitting a frame, built once per shape: `per` is the
-    padded share length, `gather[i]` the row of the [world * per] gathered buffer that holds ray i."""
+    """(per, [index tensor of every rank], restore) for one way of splitting a frame, built once per shape: `per` is the
+    padded share length, `restore(gathered[world * per, ...])` puts the gathered rows back into the frame's ray order.
+    Both splits are regular, so restoring is a reshape (blocks) or a permuted copy (stripes: the row of local stripe
+    l of rank r is global stripe l * world + r), never an index gather."""
     key = (n_rays, world, block, bool(interleave), str(device))
     plan = _PLAN_CACHE.get(key)
     if plan is None:
         idx = [shard_index(n_rays, r, world, block, interleave, device) for r in range(world)]
-        per = max(int(i.shape[0]) for i in idx)
-        if not interleave:
-            per = max(per, shard_rays(n_rays, 0, world, block).stop)
-        gather = torch.empty(n_rays, dtype=torch.int64, device=device)
-        for r, i in enumerate(idx):
-            gather[i] = r * per + torch.arange(i.shape[0], device=device)
+        if interleave:
+            n_stripes = (n_rays + block - 1) // block
+            per = ((n_stripes + world - 1) // world) * block
+
+            def restore(g, per=per):
+                g = g.reshape(world, per // block, block, *g.shape[1:])
+                return g.transpose(0, 1).reshape(world * per, *g.shape[3:])[:n_rays]
+        else:
+            per = shard_rays(n_rays, 0, world, block).stop
+
+            def restore(g):
+                return g[:n_rays]
+        assert all(int(i.shape[0]) <= per for i in idx)
         if len(_PLAN_CACHE) > 16:
             _PLAN_CACHE.clear()
-        plan = _PLAN_CACHE[key] = (per, idx, gather)
+        plan = _PLAN_CACHE[key] = (per, idx, restore)
     return plan
 
 
@@ -95,7 +104,7 @@ def render_sharded(renderer, rays_o, rays_d, t, parameters, cone_scale, *, group
     if interleave is None:
         from .renderer import InstanceRenderer
         interleave = isinstance(renderer, InstanceRenderer)
-    per, all_idx, gather_rows = shard_plan(Nr, world, block, interleave, dev)
+    per, all_idx, restore = shard_plan(Nr, world, block, interleave, dev)
     idx = all_idx[rank]
     n_mine = int(idx.shape[0])
     out: Dict[str, torch.Tensor] = {}
@@ -131,7 +140,7 @@ def render_sharded(renderer, rays_o, rays_d, t, parameters, cone_scale, *, group
     dist.all_gather_into_tensor(gathered.view(-1), rec, group=group)
     if not bool((gathered[:, -1] > 0).any()):                                   # no ray of the frame hit: renderer.py returns {}
         return {}
-    full = gathered[:, :-1].reshape(world * per, B, C)[gather_rows]             # ray order of the frame, one gather
+    full = restore(gathered[:, :-1].reshape(world * per, B, C))                 # ray order of the frame
     res: Dict[str, torch.Tensor] = {}
     col = 0
     for k, w in zip(keys, widths):

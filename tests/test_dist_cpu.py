@@ -139,3 +139,24 @@ def test_stripe_indices_partition_the_frame():
         seen = torch.cat([stripe_indices(n, r, w, b) for r in range(w)])
         assert sorted(seen.tolist()) == list(range(n))
         assert [stripe_count(n, r, w, b) for r in range(w)] == [int(stripe_indices(n, r, w, b).numel()) for r in range(w)]
+
+
+def test_shard_plan_restore_is_the_inverse_of_the_split():
+    """Every ray lands on exactly one rank and `restore` puts the gathered, padded shares back in frame order — for
+    stripes and blocks, frames that are no multiple of the stripe, more ranks than stripes, a short last stripe."""
+    import torch
+    from nerf_tex_b200.sharded import shard_plan
+    for n_rays, world, block, interleave in [(1000, 3, 16, True), (1000, 3, 16, False), (640000, 8, 256, True), (257, 8, 256, True),
+                                             (256, 2, 256, True), (5, 4, 1, True), (5, 4, 2, False), (4096, 8, 16, True),
+                                             (1023, 2, 64, True), (1023, 2, 64, False), (7, 8, 16, False)]:
+        per, idx, restore = shard_plan(n_rays, world, block, interleave, torch.device("cpu"))
+        seen = torch.cat(idx).sort().values
+        assert torch.equal(seen, torch.arange(n_rays)), (n_rays, world, block, interleave)
+        gathered = torch.full((world * per, 1, 2), -1.0)
+        for r, i in enumerate(idx):
+            assert i.shape[0] <= per
+            gathered[r * per:r * per + i.shape[0], 0, 0] = i.float()
+            gathered[r * per:r * per + i.shape[0], 0, 1] = 2.0 * i.float()
+        full = restore(gathered)
+        assert full.shape == (n_rays, 1, 2)
+        assert torch.equal(full[:, 0, 0], torch.arange(n_rays).float()) and torch.equal(full[:, 0, 1], 2.0 * torch.arange(n_rays).float())

@@ -18,7 +18,7 @@ if __name__ == "__main__":
     dev = torch.device("cuda:0")
     pipe = bench.DeviceFramePipeline(dev, 1)
     H, W = bench.H, bench.W
-    per, idx_all, gather_rows = shard_plan(H * W, world, pipe.STRIPE, True, dev)
+    per, idx_all, restore = shard_plan(H * W, world, pipe.STRIPE, True, dev)
     idx = idx_all[0]
     params = pipe.params_host.to(dev)
     ids = idx.to(torch.int32)
@@ -40,7 +40,7 @@ if __name__ == "__main__":
         body[:idx.shape[0], :, :3] = out["color_pred"].reshape(1, -1, 3).transpose(0, 1)
         body[:idx.shape[0], :, 3:] = out["alpha_pred"].reshape(1, -1, 1).transpose(0, 1)
         gathered = rec[:-1].repeat(world).view(world * per, 1, 4)                 # stands in for the all-gather
-        full = gathered[gather_rows]
+        full = restore(gathered)
         color, alpha = full[:, :, :3].transpose(0, 1).contiguous(), full[:, :, 3].transpose(0, 1).contiguous()
         mark("pack/unpack")
         _, u8 = finish_image(color, alpha, H, W, 1, straight_alpha=True, want_u8=True)
