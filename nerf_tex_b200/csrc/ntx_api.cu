@@ -27,3 +27,35 @@ int ntx_sm_count() {
     }
     return cached[dev];
 }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// cuTensorMapEncodeTiled through the runtime (the library does not link libcuda)
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return (EncodeTiledFn)p;
+    }();
+    return fn;
+}
+
+int ntx_weight_map(CUtensorMap* map, const void* packed, int64_t packed_bytes, uint32_t box_rows) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    NTX_REQUIRE(enc, "cuTensorMapEncodeTiled is not available from this driver");
+    NTX_REQUIRE(packed_bytes > 0 && (packed_bytes & 2047) == 0 && ((uintptr_t)packed & 15) == 0,
+                "weight image must be 16-byte aligned and a multiple of 2 KB (%lld bytes)", (long long)packed_bytes);
+    const cuuint64_t dims[2] = {256, (cuuint64_t)(packed_bytes / 2048)};
+    const cuuint64_t strides[1] = {2048};
+    const cuuint32_t box[2] = {256, box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void*>(packed), dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    NTX_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d)", (int)r);
+    return NTX_OK;
+}

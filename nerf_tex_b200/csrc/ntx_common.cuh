@@ -1,6 +1,7 @@
 // Shared host/device helpers for libnerftex_b200.so (sm_100a only).
 #pragma once
 
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -41,6 +42,12 @@ void ntx_set_error(const char* fmt, ...);
 
 // Number of SMs of the current device (cached per device id).
 int ntx_sm_count();
+
+// A packed weight image (this GPU's memory) as a 2-D tensor map over rows of 2 KB (256 eight-byte elements, the widest
+// row a box can have; every K-slice is stored pre-swizzled by its packer and starts on a 2 KB boundary), box =
+// `box_rows` consecutive rows = one CTA's half of a slice (4 rows = 8 KB for N = 256, 2 rows for N = 128).  No swizzle,
+// no interleave: the box lands in shared memory exactly as a linear copy of the same bytes would.  Defined in ntx_api.cu.
+int ntx_weight_map(CUtensorMap* map, const void* packed, int64_t packed_bytes, uint32_t box_rows);
 
 // tf.linspace(0, 1, n)[i]: exact endpoints, interior fl(1/(n-1)) * i  (no FMA involved).
 __host__ __device__ __forceinline__ float ntx_linspace01(int i, int n) {

@@ -820,39 +820,6 @@ NTX_API int64_t ntx_mlp_train_tiles(int64_t n_rows) {
     return ((n_rows + 511) / 512) * 4;
 }
 
-// The packed weight image as a 2-D tensor map over rows of 2 KB (256 eight-byte elements, the widest row a box can
-// have; every K-slice is stored pre-swizzled by the packer and starts on a 2 KB boundary), box = `box_rows` consecutive
-// rows = one CTA's half of a slice (4 rows = 8 KB for N = 256, 2 rows for N = 128).  No swizzle, no interleave: the
-// box lands in shared memory exactly as a linear copy of the same bytes would.
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn encode_tiled_fn() {
-    static EncodeTiledFn fn = [] {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess)
-            p = nullptr;
-        return (EncodeTiledFn)p;
-    }();
-    return fn;
-}
-
-static int weight_map(CUtensorMap* map, const void* packed, int64_t packed_bytes, uint32_t box_rows) {
-    EncodeTiledFn enc = encode_tiled_fn();
-    NTX_REQUIRE(enc, "mlp_forward: cuTensorMapEncodeTiled is not available from this driver");
-    const cuuint64_t dims[2] = {256, (cuuint64_t)(packed_bytes / 2048)};
-    const cuuint64_t strides[1] = {2048};
-    const cuuint32_t box[2] = {256, box_rows};
-    const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_UINT64, 2, const_cast<void*>(packed), dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    NTX_REQUIRE(r == CUDA_SUCCESS, "mlp_forward: cuTensorMapEncodeTiled failed (%d)", (int)r);
-    return NTX_OK;
-}
-
 static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_mlp_inputs* in, float* rgbs,
                           void* enc_pos, void* enc_dir, void* acts, void* acts_img, void* masks, int64_t n_tiles,
                           bool dump, void* stream, void* acts_img8 = nullptr, const float* inv_scale8 = nullptr,
@@ -896,8 +863,8 @@ static int launch_forward(const ntx_mlp_t* mlp, const void* packed, const ntx_ml
     KernelArgs ka;
     if (ctas == 2) {
         NTX_REQUIRE((mlp->packed_bytes & 2047) == 0, "mlp_forward: packed image is not a multiple of 2 KB");
-        if (int rc = weight_map(&ka.w_map128, packed, mlp->packed_bytes, 4)) return rc;
-        if (int rc = weight_map(&ka.w_map64, packed, mlp->packed_bytes, 2)) return rc;
+        if (int rc = ntx_weight_map(&ka.w_map128, packed, mlp->packed_bytes, 4)) return rc;
+        if (int rc = ntx_weight_map(&ka.w_map64, packed, mlp->packed_bytes, 2)) return rc;
     } else {
         memset(&ka.w_map128, 0, sizeof(CUtensorMap));
         memset(&ka.w_map64, 0, sizeof(CUtensorMap));

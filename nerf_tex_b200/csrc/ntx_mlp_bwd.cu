@@ -63,6 +63,7 @@ constexpr uint32_t kDgOffAmax = kDgOffTmemSlot + 16;                          //
 constexpr uint32_t kDgSmemBytes = kDgOffAmax + 64;
 
 struct DgradArgs {
+    CUtensorMap w_map;           // CTA pairs: packed_t as rows of 2 KB, box = this CTA's 8 KB half of a slice
     const uint8_t* packed_t;     // head block + transposed weight slices
     const float* d_rgbs;         // [N,4]
     const uint4* masks;          // [n_steps][n_tiles*128][2 x uint4]
@@ -101,7 +102,7 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
 
     if (threadIdx.x == 0) {
         for (uint32_t i = 0; i < NSTAGE; ++i) {
-            mbar_init(bar_full + 8 * i, (CTAS == 2 && rank == 0) ? 2 : 1);
+            mbar_init(bar_full + 8 * i, 1);             // pair: both CTAs' copies credit the issuing CTA's barrier
             mbar_init(bar_empty + 8 * i, 1);
         }
         for (int t = 0; t < kTilesPerCta; ++t) {
@@ -128,19 +129,31 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
         if (lane == 0) {
             uint32_t stage = 0, parity = 1;
             const uint32_t bytes = kStageBytes / CTAS;                         // this CTA's rows of one [256 x 32] slice
+            const uint32_t leader_full = CTAS == 2 ? mapa_shared(bar_full, 0) : bar_full;
+            if (CTAS == 2) prefetch_tensormap(&args.w_map);
             for (int64_t b = batch0; b < n_batches; b += batch_stride) {
                 for (int bs = 0; bs < prog.n_bwd; ++bs) {
                     const int n_k = prog.steps[bs].n_k;
                     const uint8_t* src0 = args.packed_t + prog.steps[bs].slice_off + rank * bytes;
+                    const int32_t wrow0 = (int32_t)((prog.steps[bs].slice_off + rank * bytes) >> 11);   // rows of 2 KB
                     for (int t = 0; t < kTilesPerCta; ++t) {
                         const uint8_t* src = src0;
+                        int32_t wrow = wrow0;
                         for (int left = n_k; left > 0;) {
                             const int n = left < SPS ? left : SPS;
                             mbar_wait(bar_empty + 8 * stage, parity);
+                            if (CTAS == 2) {
+                                // (see the forward kernel: the bytes of both CTAs' copies go to the issuer's barrier)
+                                if (rank == 0) mbar_arrive_expect_tx(bar_full + 8 * stage, 2 * bytes * n);
+                                for (int j = 0; j < n; ++j, wrow += (int32_t)(kStageBytes >> 11))
+                                    tma_tile2d_g2s_pair(sbase + kDgOffStages + stage * STAGE_BYTES + j * bytes, &args.w_map, 0, wrow,
+                                                        leader_full + 8 * stage);
+                            } else {
                             mbar_arrive_expect_tx(bar_full + 8 * stage, bytes * n);
                             for (int j = 0; j < n; ++j, src += kStageBytes)
                                 tma_bulk_g2s(sbase + kDgOffStages + stage * STAGE_BYTES + j * bytes, src, bytes,
                                              bar_full + 8 * stage);
+                            }
                             if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
                             left -= n;
                         }
@@ -150,19 +163,7 @@ mlp_dgrad_kernel(const __grid_constant__ BwdProgram prog, const __grid_constant_
         }
     } else if (warp == 1) {
         if (CTAS == 2 && rank != 0) {
-            if (lane == 0) {                                                    // relay (see forward kernel)
-                uint32_t stage = 0, parity = 0;
-                const uint32_t remote_full = mapa_shared(bar_full, 0);
-                for (int64_t b = batch0; b < n_batches; b += batch_stride)
-                    for (int bs = 0; bs < prog.n_bwd; ++bs) {
-                        const int n_st = ((prog.steps[bs].n_k + SPS - 1) / SPS) * kTilesPerCta;
-                        for (int s = 0; s < n_st; ++s) {
-                            mbar_wait(bar_full + 8 * stage, parity);
-                            mbar_arrive_remote(remote_full + 8 * stage);
-                            if (++stage == NSTAGE) { stage = 0; parity ^= 1; }
-                        }
-                    }
-            }
+            // peer CTA of a pair: nothing to issue (its copies credit the issuing CTA's barriers themselves)
         } else {
             // ================================================================= MMA issuer
             uint32_t stage = 0, parity = 0, act_phase0 = 0, act_phase1 = 0;
@@ -809,6 +810,11 @@ static int backward_data_impl(const ntx_mlp_t* mlp, const void* packed_t, const 
     BwdProgram bp;
     build_bwd_program(mlp, &bp);
     DgradArgs a;
+    if (ctas == 2) {
+        if (int rc = ntx_weight_map(&a.w_map, packed_t, build_bwd_program(mlp, &bp), 4)) return rc;
+    } else {
+        memset(&a.w_map, 0, sizeof(a.w_map));
+    }
     a.packed_t = (const uint8_t*)packed_t;
     a.d_rgbs = d_rgbs;
     a.masks = (const uint4*)masks;
