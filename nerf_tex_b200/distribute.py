@@ -26,10 +26,16 @@ def mt19937_uniform_float(seed: int, n: int, a: float, b: float) -> np.ndarray:
 
 
 def avg_edge_length(V: np.ndarray, F: np.ndarray) -> float:
-    """igl::avg_edge_length: mean over the three edges of every face."""
-    P = np.asarray(V, np.float64)[np.asarray(F, np.int64)]
-    e = [np.linalg.norm(P[:, (k + 1) % 3] - P[:, k], axis=-1) for k in range(3)]
-    return float(np.sum(e) / (3 * P.shape[0]))
+    """igl::avg_edge_length: mean over the mesh's UNIQUE undirected edges (igl::edges), every length taken in the
+    vertices' own precision (fp32 in the reference, instancer.cpp:244) and summed in double.  (Checked against the
+    reference's own code in tests/test_ref_instancer.py.)"""
+    F = np.asarray(F, np.int64)
+    E = np.concatenate([F[:, [0, 1]], F[:, [1, 2]], F[:, [2, 0]]], 0)
+    E = np.unique(np.sort(E, axis=1), axis=0)
+    d = (np.asarray(V, F32)[E[:, 0]] - np.asarray(V, F32)[E[:, 1]]).astype(F32)
+    sq = ((d[:, 0] * d[:, 0]).astype(F32) + (d[:, 1] * d[:, 1]).astype(F32)).astype(F32)
+    sq = (sq + (d[:, 2] * d[:, 2]).astype(F32)).astype(F32)
+    return float(np.sqrt(sq).astype(F32).astype(np.float64).sum() / E.shape[0])
 
 
 def _unit(v):

@@ -107,10 +107,13 @@ def write_ply(path: str, V, F=None, N=None, UV=None, binary: bool = True) -> Non
     if UV is not None:
         cols.append(np.asarray(UV, np.float32)); names += ["s", "t"]
     table = np.ascontiguousarray(np.concatenate(cols, 1), dtype="<f4")
-    F = np.zeros((0, 3), np.int32) if F is None else np.asarray(F, np.int32)
+    points_only = F is None          # an anchor point set has no face element at all (libigl's reader, which the
+    F = np.zeros((0, 3), np.int32) if F is None else np.asarray(F, np.int32)      # reference uses, divides by the face count)
     head = ["ply", "format binary_little_endian 1.0" if binary else "format ascii 1.0", f"element vertex {V.shape[0]}"]
     head += [f"property float {n}" for n in names]
-    head += [f"element face {F.shape[0]}", "property list uchar int vertex_indices", "end_header"]
+    if not points_only:
+        head += [f"element face {F.shape[0]}", "property list uchar int vertex_indices"]
+    head += ["end_header"]
     with open(path, "wb") as f:
         f.write(("\n".join(head) + "\n").encode("ascii"))
         if binary:

@@ -353,14 +353,16 @@ def mean_distance(mu, hw):
 def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformations, b_0, b_1, *, seed=0,
                     light_dir_idx=-1, method="random", use_mean_distance=False, light_strength_idx=-1, patch_scale=1.0,
                     mesh=None, ray_ids=None, cast_shadow_rays=False, min_shadow_samples=4, n_shadow_samples=512,
-                    texture=None, aux_meshes=None):
+                    texture=None, aux_meshes=None, ray_u=None):
     """Returns the CSR form over ALL rays: n_samples[R], hit[R], alpha_last[R], color_last[R,3] and per-sample
     records.  `mesh` = (V[n,3], F[m,3]): the base mesh the patches sit on (a ray ends at its first hit).  `ray_ids`:
     the identity of every ray for the random draws (default: its index in this call), so that a frame cut into chunks
     or spread over GPUs draws the same numbers.  `texture` = dict(UV=[n,2] of the base mesh, textures=[channel
     matrices], idxs=[parameter index per texture file], radius, min_samples, n_samples): parameter textures
     (:640-667, :916-926, :985-991).  `aux_meshes` = [dict(V, F, N, UV or None, textures=[channel matrices])]: meshes
-    added with AddMesh (:393-418) — they end rays like the base mesh and colour the last sample with shadeMesh (:716-744)."""
+    added with AddMesh (:393-418) — they end rays like the base mesh and colour the last sample with shadeMesh (:716-744).
+    `ray_u` = [R] per-ray offsets in [0, 1) to use instead of the counter hash (tests/test_ref_instancer.py feeds the
+    std::mt19937 stream the reference draws, :849/:858)."""
     rays_o, rays_d, parameters = np.asarray(rays_o, F), np.asarray(rays_d, F), np.asarray(parameters, F)
     base = None
     if mesh is not None:
@@ -425,7 +427,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
             continue
         necessary = int(F(total / step_size))                       # :845
         n_steps = min(necessary, n_pts)
-        u = ray_uniform(seed, rid)
+        u = ray_uniform(seed, rid) if ray_u is None else F(ray_u[i])
         dists = []
         if n_steps == 0:                                            # :848-851
             dists = [total]
@@ -656,11 +658,16 @@ def distribute_instances_on_mesh(V, Fc, N, UV, patch_origins=None, scale=1.0, ji
     """instancer.cpp:233-372: list of 4x4 patch matrices (what AddInstance receives) and the patch scale."""
     V, N, UV, Fc = np.asarray(V, F), np.asarray(N, F).copy(), np.asarray(UV, F), np.asarray(Fc, np.int64)
     nv, nf = V.shape[0], Fc.shape[0]
-    ael = 0.0                                                          # igl::avg_edge_length
-    for f in Fc:
+    ael, edges = 0.0, set()                                            # igl::avg_edge_length: every undirected edge ONCE
+    for f in Fc:                                                       # (igl::edges), lengths in fp32, sum in double
         for k in range(3):
-            ael += float(np.linalg.norm(V[f[(k + 1) % 3]].astype(np.float64) - V[f[k]].astype(np.float64)))
-    ael /= 3 * nf
+            e = (min(int(f[k]), int(f[(k + 1) % 3])), max(int(f[k]), int(f[(k + 1) % 3])))
+            if e in edges:
+                continue
+            edges.add(e)
+            dv = [F(V[e[0]][c] - V[e[1]][c]) for c in range(3)]
+            ael += float(np.sqrt(F(F(F(dv[0] * dv[0]) + F(dv[1] * dv[1])) + F(dv[2] * dv[2]))))
+    ael /= len(edges)
     if scale <= 0:
         scale = ael
     T = np.zeros((nv, 3), F)

@@ -1,0 +1,171 @@
+"""The oracle of the shell instancer (oracle/instancer_oracle.py) against the REFERENCE'S OWN C++ (instancer/src/
+instancer.cpp), compiled from where it lies under /root/reference by oracle/ref_instancer.py.  Embree — the one dependency
+that is absent — is replaced by a brute-force stand-in (oracle/embree_shim: our code, no BVH, Moeller-Trumbore in double),
+so what is pinned here is everything the reference does with the hits: sorting and duplicate removal, patch toggling,
+in-shell length, step count, the std::mt19937 offset, the walk over concatenated segments, 'nearest' patch choice, the
+mapping into the patch frame, light mapping, mesh termination, shadow and texture sampling along segments, shadeMesh,
+DistributeInstancesOnMesh (libigl PLY reader, tangent frames, closest points, jitter stream) — not the ray / box and
+ray / triangle arithmetic itself (the oracle uses fp32 slab and watertight tests, the stand-in double precision: hit
+distances agree to a few ulps, which is why the bars below are tolerances and not bit equality).
+
+CPU only.  The library is built on demand when /root/reference exists; the prebuilt oracle/_ref/libref_instancer.so
+is used otherwise (it travels to the GPU box); with neither the tests skip."""
+
+import json
+
+import numpy as np
+import pytest
+
+from oracle import instancer_oracle as IO
+from oracle import ref_instancer as RI
+
+F = np.float32
+pytestmark = pytest.mark.skipif(not RI.available(), reason="neither /root/reference nor a prebuilt oracle/_ref library")
+
+B0, B1 = [-1.0, -1.0, -0.1], [1.0, 1.0, 1.8]
+
+
+def mt_stream(seed, n):
+    """What std::uniform_real_distribution<float>(0, 1) draws from std::mt19937(seed) (instancer.cpp:767, :849, :858)."""
+    g = IO.MT19937(seed)
+    return [IO.uniform_real_float(g, 0.0, 1.0) for _ in range(n)]
+
+
+def rotations(n, rng):
+    q = rng.normal(size=(n, 4))
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    w, x, y, z = q.T
+    return np.stack([np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)], -1),
+                     np.stack([2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)], -1),
+                     np.stack([2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], -1)], 1)
+
+
+def patches(n, seed, scale=0.2, spread=1.0):
+    rng = np.random.default_rng(seed)
+    T = np.tile(np.eye(4), (n, 1, 1))
+    T[:, :3, :3] = rotations(n, rng) * scale
+    T[:, :3, 3] = rng.uniform(-spread, spread, (n, 3))
+    return T.astype(F)
+
+
+def camera_rays(R, seed, eye=(0.0, 0.3, 5.0), spread=1.0):
+    rng = np.random.default_rng(seed)
+    o = np.tile(np.asarray([eye], F), (R, 1))
+    d = rng.uniform(-spread, spread, (R, 3)).astype(F) - o
+    return o, (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(F)
+
+
+def run_both(ref_kwargs, ora_kwargs, o, d, prm, S, step, T):
+    inst = RI.RefInstancer(B0, B1, **ref_kwargs)
+    ref = inst.get_model_input(o, d, prm, S, step)
+    drew = ref["dist"][:, 0] > 0                                   # rays with in-shell length draw one offset, in ray order
+    u = np.zeros(o.shape[0], F)
+    u[drew] = mt_stream(0, int(drew.sum()))
+    ora = IO.get_model_input(o, d, prm, S, step, T, B0, B1, ray_u=u, **ora_kwargs)
+    return inst, ref, ora
+
+
+def compare(ref, ora, S, *, tol_t=2e-5, tol_pts=2e-4, max_count_mismatch=0.01, max_id_mismatch=0.005, params_tol=1e-5):
+    R = ref["hit"].shape[0]
+    assert np.array_equal(ref["hit"], ora["hit"])
+    n_ref = np.minimum((ref["dist"] > 0).sum(1), (ref["t"] != 0).sum(1))   # samples the reference really emitted
+    n_ora = ora["n_samples"]
+    same = n_ref == n_ora
+    assert (~same).mean() <= max_count_mismatch, (int((~same).sum()), R)
+    ptr = np.concatenate([[0], np.cumsum(n_ora)])
+    n_cmp = n_id_bad = 0
+    for i in np.nonzero(same & (n_ora > 0))[0]:
+        a, b = ptr[i], ptr[i + 1]
+        n = b - a
+        assert np.abs(ref["t"][i, :n] - ora["t"][a:b]).max() <= tol_t
+        assert np.abs(ref["dist"][i, :n] - ora["dists"][a:b]).max() <= tol_t
+        ok = ref["instance_id"][i, :n] == ora["instance_id"][a:b]
+        n_cmp, n_id_bad = n_cmp + n, n_id_bad + int((~ok).sum())
+        if ok.any():
+            assert np.abs(ref["pts"][i, :n] - ora["pts"][a:b])[ok].max() <= tol_pts
+            assert np.abs(ref["rays_d"][i, :n] - ora["dirs"][a:b])[ok].max() <= 1e-5
+            assert np.abs(ref["density_weight"][i, :n] - ora["alpha_weight"][a:b])[ok].max() <= 1e-6
+            assert np.abs(ref["parameters"][i, :n] - ora["params"][a:b])[ok].max() <= params_tol, i
+        assert not ref["t"][i, n:].any()                            # nothing behind the last sample
+    assert n_cmp > 0 and n_id_bad <= max_id_mismatch * n_cmp, (n_id_bad, n_cmp)
+    assert np.array_equal(ref["density"][:, 0], ora["alpha_last"])
+    return n_cmp
+
+
+@pytest.mark.parametrize("mean", [False, True])
+@pytest.mark.parametrize("light", ["light", "point"])
+def test_explicit_patches_nearest(mean, light):
+    """Rotated patches given as matrices (instancer.pyx:17-18), 'nearest' choice, directional and point light."""
+    T = patches(60, 1)
+    R, S, step = 300, 96, 0.01
+    o, d = camera_rays(R, 2)
+    if light == "light":
+        prm = np.tile(np.asarray([[0.5, 0.7, 0.3, 0.2, 1.0]], F), (R, 1))
+        kw = dict(light_dir_idx=2)
+    else:
+        prm = np.tile(np.asarray([[0.5, 0.7, 40.0, 0.3, 0.2, 3.0]], F), (R, 1))
+        kw = dict(light_dir_idx=3, light_strength_idx=2)
+    _, ref, ora = run_both(dict(textures=["", "", light], transformations=T.tolist(), instance_sampling_method="nearest",
+                                use_mean_distance=mean),
+                           dict(method="nearest", use_mean_distance=mean, **kw), o, d, prm, S, step, T)
+    n = compare(ref, ora, S)
+    assert n > 5000 and ora["hit"].sum() > 100 and not ora["alpha_last"].any()
+    assert (ora["n_samples"] == S).any() and (ora["n_samples"][ora["hit"]] < S).any()      # clipped and unclipped rays
+
+
+def test_short_crossings_take_the_single_sample_branch():
+    """Steps longer than most crossings: n_steps == 0 -> one sample with the whole length as its distance (:848-851)."""
+    T = patches(40, 3, scale=0.05)
+    R, S = 400, 16
+    o, d = camera_rays(R, 4)
+    prm = np.tile(np.asarray([[1.0, 0.0, 0.0, 1.0]], F), (R, 1))
+    _, ref, ora = run_both(dict(textures=["", "light"], transformations=T.tolist(), instance_sampling_method="nearest"),
+                           dict(method="nearest", light_dir_idx=1), o, d, prm, S, 0.25, T)
+    compare(ref, ora, S)
+    assert (ora["n_samples"][ora["hit"]] == 1).mean() > 0.5
+
+
+def plane_mesh(n, extent, wobble, z=0.0):
+    xs = np.linspace(-extent, extent, n + 1)
+    X, Y = np.meshgrid(xs, xs, indexing="ij")
+    Z = z + wobble * np.sin(2.1 * X) * np.cos(1.7 * Y)
+    V = np.stack([X, Y, Z], -1).reshape(-1, 3).astype(F)
+    dzdx, dzdy = wobble * 2.1 * np.cos(2.1 * X) * np.cos(1.7 * Y), -wobble * 1.7 * np.sin(2.1 * X) * np.sin(1.7 * Y)
+    N = np.stack([-dzdx, -dzdy, np.ones_like(X)], -1).reshape(-1, 3)
+    N = (N / np.linalg.norm(N, axis=-1, keepdims=True)).astype(F)
+    UV = np.stack([(X + extent) / (2 * extent), (Y + extent) / (2 * extent)], -1).reshape(-1, 2).astype(F)
+    idx = lambda i, j: i * (n + 1) + j
+    Fc = [[idx(i, j), idx(i + 1, j), idx(i + 1, j + 1)] for i in range(n) for j in range(n)]
+    Fc += [[idx(i, j), idx(i + 1, j + 1), idx(i, j + 1)] for i in range(n) for j in range(n)]
+    return {"V": V, "F": np.asarray(Fc, np.int32), "N": N, "UV": UV}
+
+
+def anchors_on(mesh_fn, n, seed, lim, lift=0.0):
+    rng = np.random.default_rng(seed)
+    xy = rng.uniform(-lim, lim, (n, 2))
+    return np.concatenate([xy, mesh_fn(xy[:, :1], xy[:, 1:]) + lift], 1).astype(F)
+
+
+@pytest.mark.parametrize("jitter,with_anchors", [(0.0, True), (1.0, True), (0.5, False)])
+def test_distribute_instances_on_mesh(jitter, with_anchors, tmp_path):
+    """DistributeInstancesOnMesh (:233-391) run by the reference on PLY files our writer produced (read back by libigl's
+    reader), exported with ExportTransformations (:1040-1061): placement, frames and the mt19937 jitter stream of
+    oracle.distribute_instances_on_mesh and of the product's nerf_tex_b200.distribute agree with it."""
+    from nerf_tex_b200 import distribute, ply
+    mesh = plane_mesh(6, 1.0, 0.1)
+    anchors = anchors_on(lambda x, y: 0.1 * np.sin(2.1 * x) * np.cos(1.7 * y), 40, 2, 0.9, lift=0.01)
+    ply.write_ply(str(tmp_path / "mesh.ply"), mesh["V"], mesh["F"], mesh["N"], mesh["UV"], binary=True)
+    ply.write_ply(str(tmp_path / "anchors.ply"), anchors, binary=False)
+    origins = str(tmp_path / "anchors.ply") if with_anchors else ""
+    scale = 0.09 if with_anchors else 0.0                            # <= 0: the average edge length (:244)
+    inst = RI.RefInstancer(B0, B1, mesh_path=str(tmp_path / "mesh.ply"), patch_origins_path=origins, patch_scale=scale,
+                           jitter_amount=jitter, transformation_export_path=str(tmp_path / "t.json"))
+    got = np.asarray(json.loads((tmp_path / "t.json").read_text()), np.float64)
+    want, used_scale = IO.distribute_instances_on_mesh(mesh["V"], mesh["F"], mesh["N"], mesh["UV"], anchors if with_anchors else None,
+                                                       scale, jitter, seed=0)
+    assert inst.n_instances() == want.shape[0] == (40 if with_anchors else 49)
+    np.testing.assert_allclose(got, want, atol=3e-6)                 # (the export inverts the stored inverse: two roundings)
+    prod, prod_scale = distribute.distribute_instances_on_mesh(mesh["V"], mesh["F"], mesh["N"], mesh["UV"],
+                                                               anchors if with_anchors else None, scale, jitter, seed=0)
+    np.testing.assert_allclose(got, prod, atol=3e-6)
+    assert abs(prod_scale - used_scale) < 1e-7
