@@ -60,7 +60,11 @@ def run_both(ref_kwargs, ora_kwargs, o, d, prm, S, step, T):
     ref = inst.get_model_input(o, d, prm, S, step)
     drew = ref["dist"][:, 0] > 0                                   # rays with in-shell length draw one offset, in ray order
     u = np.zeros(o.shape[0], F)
-    u[drew] = mt_stream(0, int(drew.sum()))
+    # the one generator of the instance has already served the placement: one jitter angle per patch (:329, :354)
+    skip = 0
+    if ref_kwargs.get("jitter_amount", 0) > 0 and ref_kwargs.get("mesh_path"):
+        skip = inst.n_instances() - len(ref_kwargs.get("transformations", ()))
+    u[drew] = mt_stream(0, skip + int(drew.sum()))[skip:]
     ora = IO.get_model_input(o, d, prm, S, step, T, B0, B1, ray_u=u, **ora_kwargs)
     return inst, ref, ora
 
@@ -169,3 +173,151 @@ def test_distribute_instances_on_mesh(jitter, with_anchors, tmp_path):
                                                                anchors if with_anchors else None, scale, jitter, seed=0)
     np.testing.assert_allclose(got, prod, atol=3e-6)
     assert abs(prod_scale - used_scale) < 1e-7
+
+
+def checker_texture(n=32, cells=4, seed=0):
+    rng = np.random.default_rng(seed)
+    yy, xx = np.meshgrid(np.arange(n), np.arange(n), indexing="ij")
+    return ((((xx * cells // n) + (yy * cells // n)) % 2) * 200 + rng.integers(0, 50, (n, n))).astype(np.uint8)
+
+
+def mesh_scene(tmp_path, seed, n_anchor=150, jitter=1.0, scale=0.09):
+    """A hilly plane as base mesh + anchors on it, written as PLY files for the reference; the oracle gets the arrays and
+    the patch matrices of its own DistributeInstancesOnMesh (pinned to the reference's in the test above)."""
+    from nerf_tex_b200 import ply
+    hill = lambda x, y: 0.15 * np.sin(2.1 * x) * np.cos(1.7 * y)
+    mesh = plane_mesh(12, 1.2, 0.15)
+    anchors = anchors_on(hill, n_anchor, seed, 1.0)
+    ply.write_ply(str(tmp_path / "mesh.ply"), mesh["V"], mesh["F"], mesh["N"], mesh["UV"], binary=True)
+    ply.write_ply(str(tmp_path / "anchors.ply"), anchors, binary=True)
+    T, _ = IO.distribute_instances_on_mesh(mesh["V"], mesh["F"], mesh["N"], mesh["UV"], anchors, scale, jitter, seed=0)
+    ref_kw = dict(mesh_path=str(tmp_path / "mesh.ply"), patch_origins_path=str(tmp_path / "anchors.ply"), patch_scale=scale,
+                  jitter_amount=jitter, instance_sampling_method="nearest")
+    return mesh, T.astype(F), ref_kw
+
+
+def rays_from_above(R, seed, lim=1.3):
+    rng = np.random.default_rng(seed)
+    o = np.stack([rng.uniform(-lim, lim, R), rng.uniform(-lim, lim, R), rng.uniform(0.7, 2.0, R)], 1).astype(F)
+    d = np.stack([rng.uniform(-1, 1, R), rng.uniform(-1, 1, R), np.full(R, -1.0)], 1).astype(F)
+    return o, d
+
+
+def test_base_mesh_ends_rays(tmp_path):
+    """Patches distributed by the reference on a PLY mesh; rays from above, from below and grazing: the first mesh hit
+    closes the open segment and ends the ray with density 1 and a black last sample (:804-814, :1019-1029)."""
+    mesh, T, ref_kw = mesh_scene(tmp_path, 5)
+    R, S, step = 400, 128, 0.004
+    o, d = rays_from_above(R, 6)
+    o[::5, 2] *= -1                                                  # from below
+    d[::5, 2] = 1.0
+    d[1::9, 2] = -0.05                                               # grazing
+    prm = np.tile(np.asarray([[0.7, 0.0, 0.0, 1.0]], F), (R, 1))
+    _, ref, ora = run_both(dict(textures=["", "light"], **ref_kw),
+                           dict(method="nearest", light_dir_idx=1, patch_scale=0.09, mesh=(mesh["V"], mesh["F"])), o, d, prm, S, step, T)
+    compare(ref, ora, S, tol_pts=5e-4)
+    assert 0.3 < ora["alpha_last"].mean() < 1.0 and (ora["alpha_last"][ora["hit"]] == 0).any()
+    assert not ref["color"].any() and not ora["color_last"].any()
+
+
+@pytest.mark.parametrize("n_tex", [64, 4000])
+def test_parameter_textures(n_tex, tmp_path):
+    """getParameters (:640-667): a PNG decoded by the reference's stb_image against the product's decoder + the oracle's
+    orientation / bilinear lookup; looked up per sample (n_tex >= n_pts) or along the segments and interpolated."""
+    from nerf_tex_b200.image import encode_png
+    mesh, T, ref_kw = mesh_scene(tmp_path, 7)
+    img0, img1 = checker_texture(32, 4, 1), checker_texture(17, 3, 2)
+    for name, img in (("a.png", img0), ("b.png", img1)):
+        (tmp_path / name).write_bytes(encode_png(img[:, :, None]))
+    R, S, step = 200, 96, 0.004
+    o, d = rays_from_above(R, 8)
+    prm = np.tile(np.asarray([[0.9, 0.4, 0.7, 0.2, 0.1, 1.0]], F), (R, 1))
+    radius = F(np.linalg.norm(np.maximum(np.asarray(B0, F), np.asarray(B1, F))) * F(0.09))
+    tex = dict(UV=mesh["UV"], textures=IO.texture_channels(img0) + IO.texture_channels(img1), idxs=[0, 2], radius=radius,
+               min_samples=8, n_samples=n_tex)
+    _, ref, ora = run_both(dict(textures=[str(tmp_path / "a.png"), "", str(tmp_path / "b.png"), "light"], min_texture_samples=8,
+                                n_texture_samples=n_tex, **ref_kw),
+                           dict(method="nearest", light_dir_idx=3, patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), texture=tex),
+                           o, d, prm, S, step, T)
+    # a texel edge crossed within the hit-distance rounding moves a looked-up value by a texel difference: rare, bounded
+    compare(ref, ora, S, tol_pts=5e-4, params_tol=2e-3)
+    p = ora["params"]
+    assert p[:, 0].min() < 0.2 < 0.6 < p[:, 0].max() and len(np.unique(p[:, 2])) > 50
+
+
+@pytest.mark.parametrize("light,n_shadow", [("light", 64), ("light", 4000), ("point", 64)])
+def test_shadow_rays(light, n_shadow, tmp_path):
+    """isShadowed / getShadowedLightDir (:572-603) with the occlusion filter of :544-551, sampled along the segments
+    (:992-1000, the nearer neighbour counts) or per sample; a low sun so that hills and boxes cast shadows."""
+    mesh, T, ref_kw = mesh_scene(tmp_path, 9)
+    # a few patches floating above the carpet, given as matrices: they come first (instancer.pyx:17-21); their bottom
+    # faces and the hills' slopes are what blocks the light
+    floating = np.tile(np.eye(4), (25, 1, 1))
+    floating[:, :3, :3] *= 0.09
+    floating[:, :3, 3] = np.concatenate([np.random.default_rng(3).uniform(-1.0, 1.0, (25, 2)),
+                                         np.random.default_rng(4).uniform(0.3, 0.5, (25, 1))], 1)
+    T = np.concatenate([floating.astype(F), T], 0)
+    ref_kw = dict(ref_kw, transformations=floating.astype(F).tolist())
+    R, S, step = 250, 96, 0.004
+    o, d = rays_from_above(R, 10)
+    if light == "light":
+        prm = np.tile(np.asarray([[0.7, 1.0, 0.2, 0.3]], F), (R, 1))
+        kw = dict(light_dir_idx=1)
+        tex = ["", "light"]
+    else:
+        prm = np.tile(np.asarray([[0.7, 30.0, 2.5, 0.3, 0.7]], F), (R, 1))
+        kw = dict(light_dir_idx=2, light_strength_idx=1)
+        tex = ["", "point"]
+    _, ref, ora = run_both(dict(textures=tex, cast_shadow_rays=True, min_shadow_samples=8, n_shadow_samples=n_shadow, **ref_kw),
+                           dict(method="nearest", patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), cast_shadow_rays=True,
+                                min_shadow_samples=8, n_shadow_samples=n_shadow, **kw), o, d, prm, S, step, T)
+    li = kw["light_dir_idx"]
+    # a shadow edge crossed within the hit-distance rounding flips a sample between lit and ambient: count those apart
+    n_ora = ora["n_samples"]
+    ptr = np.concatenate([[0], np.cumsum(n_ora)])
+    flips = total = 0
+    for i in np.nonzero(n_ora > 0)[0]:
+        a, b = ptr[i], ptr[i + 1]
+        if (ref["dist"][i] > 0).sum() != b - a:
+            continue
+        amb_r = (ref["parameters"][i, :b - a, li:li + 3] == np.asarray([0, 0, -1], F)).all(-1)
+        amb_o = (ora["params"][a:b, li:li + 3] == np.asarray([0, 0, -1], F)).all(-1)
+        flips, total = flips + int((amb_r != amb_o).sum()), total + (b - a)
+        ora["params"][a:b][amb_r != amb_o] = ref["parameters"][i, :b - a][amb_r != amb_o]
+    assert flips <= 0.01 * total, (flips, total)
+    compare(ref, ora, S, tol_pts=5e-4, params_tol=1e-4)
+    shadowed = (ora["params"][:, li:li + 3] == np.asarray([0, 0, -1], F)).all(-1)
+    assert 0.02 < shadowed.mean() < 0.98, float(shadowed.mean())
+
+
+def test_auxiliary_meshes_are_shaded(tmp_path):
+    """AddMesh / shadeMesh (:393-418, :716-744): a textured table top above the carpet and an untextured wall beside it;
+    rays that end on them carry the shaded colour (texture x diffuse / ambient term, shadowed or not)."""
+    from nerf_tex_b200 import ply
+    from nerf_tex_b200.image import encode_png
+    mesh, T, ref_kw = mesh_scene(tmp_path, 11)
+    table = plane_mesh(4, 0.5, 0.0, z=0.45)
+    table["V"][:, 0] += 0.3
+    wall = plane_mesh(3, 0.8, 0.0)
+    wall["V"] = np.stack([np.full(16, -1.15), wall["V"][:, 0], wall["V"][:, 1] + 0.6], 1).astype(F)
+    wall["N"] = np.tile(np.asarray([[1, 0, 0]], F), (16, 1))
+    rgb = np.stack([checker_texture(16, 2, 3), checker_texture(16, 2, 4), checker_texture(16, 2, 5)], -1)
+    ply.write_ply(str(tmp_path / "table.ply"), table["V"], table["F"], table["N"], table["UV"])
+    ply.write_ply(str(tmp_path / "wall.ply"), wall["V"], wall["F"], wall["N"], wall["UV"])
+    (tmp_path / "table.png").write_bytes(encode_png(rgb))
+    R, S, step = 300, 96, 0.004
+    o, d = rays_from_above(R, 12)
+    d[::4] = np.asarray([-1.0, 0.1, -0.2], F) + np.random.default_rng(13).uniform(-.1, .1, (len(d[::4]), 3)).astype(F)
+    prm = np.tile(np.asarray([[0.7, 0.3, 0.2, 0.9]], F), (R, 1))
+    aux_o = [dict(V=table["V"], F=table["F"], N=table["N"], UV=table["UV"], textures=IO.texture_channels(rgb)),
+             dict(V=wall["V"], F=wall["F"], N=wall["N"], UV=wall["UV"], textures=[])]
+    _, ref, ora = run_both(dict(textures=["", "light"], cast_shadow_rays=True, min_shadow_samples=8, n_shadow_samples=4000,
+                                auxiliary_meshes=[(str(tmp_path / "table.ply"), str(tmp_path / "table.png")),
+                                                  (str(tmp_path / "wall.ply"), "")], **ref_kw),
+                           dict(method="nearest", light_dir_idx=1, patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), cast_shadow_rays=True,
+                                min_shadow_samples=8, n_shadow_samples=4000, aux_meshes=aux_o), o, d, prm, S, step, T)
+    compare(ref, ora, S, tol_pts=5e-4, params_tol=2.1, max_id_mismatch=0.01)      # (lit / ambient flips are checked above)
+    rc, oc = ref["color"][:, 0], ora["color_last"]
+    close = np.abs(rc - oc).max(-1) < 2e-3
+    assert close.mean() > 0.98, float(close.mean())                  # texel / shadow edges within the rounding aside
+    assert (oc.max(-1) > 0.05).sum() > 20
