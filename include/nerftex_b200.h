@@ -313,8 +313,9 @@ int ntx_image_finish(const float* color, const float* alpha, int H, int W, int f
 /* Replace C_Instancer::GetModelInput (instancer/src/instancer.cpp:751-1037, bound in instancer/instancer.pyx:38-54):
  * patch instances (explicit, or distributed on a base mesh by the host side), optional base mesh whose first hit ends a
  * ray (:804-814,:983,:1019-1023), optional shadow rays (isShadowed :593-603 with the filter of :539-551: a sample whose
- * ray towards the light enters a patch box through its top face, crosses a box's bottom face or hits a mesh triangle on
- * its front side gets the ambient light direction (0, 0, -1), :572-575; looked up at min_shadow_samples /
+ * ray towards the light enters a patch box through its top face, crosses a box's bottom face, hits a mesh triangle on
+ * its front side — or the SECOND triangle of any mesh from either side, the filter's `primID == 1` clause at :550 does
+ * not look at the geometry — gets the ambient light direction (0, 0, -1), :572-575; looked up at min_shadow_samples /
  * n_shadow_samples points per ray as in :863,:936-951,:992-1000; cast_shadow_rays != 0 adds 1600 B per ray to the
  * workspace), optional parameter textures and auxiliary meshes (ntx_instancer_shading below).  The trace takes the rays'
  * parameters[R,n_param] and light_dir_idx for the shading of auxiliary-mesh hits (NULL / -1 without them) and writes
@@ -399,7 +400,10 @@ typedef struct ntx_instancer_scene {
     const ntx_instancer_shading* shading;   /* NULL: no parameter textures, no auxiliary meshes */
 } ntx_instancer_scene;
 int64_t ntx_instancer_workspace_bytes(int R, int cast_shadow_rays);
-int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
+/* ray_offsets [R] (may be NULL): the per-ray offset u in [0, 1) the reference draws from its std::mt19937
+ * (instancer.cpp:849,858); NULL: a counter hash of (seed, ray name).  A caller that must reproduce a reference run
+ * passes the stream (tests/test_gpu_ref_instancer.py does). */
+int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* ray_offsets, int R,
                         const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size, int n_pts,
                         uint32_t seed, int use_mean_distance, int cast_shadow_rays, const float* parameters, int n_param,
                         int light_dir_idx, void* workspace, int32_t* n_samples, int32_t* hit, float* alpha_last,

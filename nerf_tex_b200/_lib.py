@@ -111,7 +111,7 @@ SIGNATURES = {
     "ntx_composite_edges_backward": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
     "ntx_image_finish": (_I, [_P, _P, _I, _I, _I, _P, _I, _I, _P, _P, _P]),
     "ntx_instancer_workspace_bytes": (_I64, [_I, _I]),
-    "ntx_instancer_trace": (_I, [_P, _P, _P, _I, C.POINTER(InstancerScene), _P, _P, _F, _I, _U32, _I, _I, _P, _I, _I,
+    "ntx_instancer_trace": (_I, [_P, _P, _P, _P, _I, C.POINTER(InstancerScene), _P, _P, _F, _I, _U32, _I, _I, _P, _I, _I,
                                  _P, _P, _P, _P, _P, _P]),
     "ntx_instancer_march": (_I, [_P, _P, _P, _P, _I, _I, C.POINTER(InstancerScene), _F, _I, _U32, _I, _I, _I, _F, _I,
                                  _I, _I, _I, _P, _P, _P, _P, _I64] + [_P] * 7 + [_P]),

@@ -128,7 +128,7 @@ struct OpenList {
 // `t_mesh` < +inf: the ray ends on the base mesh there (the list holds no box hit behind it): the mesh closes an open
 // segment (:805-810) and samples go on behind the last box hit up to the mesh (:983).
 template <class Hits>
-__device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint32_t seed, uint32_t ray, int use_mean,
+__device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint32_t seed, uint32_t ray, const float* u_given, int use_mean,
                         float t_mesh, int32_t* __restrict__ step_at, float* __restrict__ segoff,
                         RayInfo* __restrict__ info, float2* __restrict__ seg, uint8_t* __restrict__ first_open) {
     OpenList act;
@@ -170,7 +170,7 @@ __device__ int walk_ray(Hits& hits, int n_hits, int n_pts, float step_size, uint
     if (!(total > 0.0f)) { *info = ri; return 0; }
     const uint32_t necessary = (uint32_t)__fdiv_rn(total, step_size);             // :845
     int n_steps = (int)min(necessary, (uint32_t)n_pts);
-    const float u = ray_uniform(seed, ray);
+    const float u = u_given ? *u_given : ray_uniform(seed, ray);
     if (n_steps == 0) {                                                           // :848-851
         ri.last_dist = total; ri.t_offset = __fmul_rn(u, total); n_steps = 1;
         ri.n_steps = -1;
@@ -484,7 +484,8 @@ __device__ void get_parameters(const SceneDev& sc, const float p[3], const float
 // isShadowed (instancer.cpp:593-603) with shadow_ray_filter_function (:539-551), in the operation order of
 // oracle/instancer_oracle.py::is_shadowed: a ray from `pt` along `dir` (not normalised), t in [0, 100], is blocked by the
 // top face of a patch box entered from above (patch frame), by the bottom face of a patch box from either side, or by a
-// mesh triangle hit on its front side.  Any-hit: the walk stops at the first blocker.
+// mesh triangle hit on its front side (or, like the reference, by the second triangle of any mesh from either side).
+// Any-hit: the walk stops at the first blocker.
 struct ShadowBox { float b0[3], b1[3]; };
 __device__ bool shadow_blocked(const SceneDev& sc, const ShadowBox& bx, const float pt[3], const float dir[3]) {
     bool blocked = false;
@@ -542,6 +543,11 @@ __device__ bool shadow_blocked(const SceneDev& sc, const ShadowBox& bx, const fl
                              __fsub_rn(__fmul_rn(e1[2], e2[0]), __fmul_rn(e1[0], e2[2])),
                              __fsub_rn(__fmul_rn(e1[0], e2[1]), __fmul_rn(e1[1], e2[0]))};
         if (dot3(ng, dir) < 0.0f) blocked = true;
+        // the reference's filter ends in `|| hit->primID == 1` without looking at the geometry (:550): the SECOND triangle of
+        // the base mesh and of every auxiliary mesh blocks from either side (seen by running the reference's own code)
+        if (face == 1 && sc.sh.n_base_faces >= 2) blocked = true;
+        for (int m = 0; m < sc.sh.n_aux; ++m)
+            if (face == sc.sh.aux_face_begin[m] + 1 && face < sc.sh.aux_face_begin[m + 1]) blocked = true;
     };
     if (sc.tg.start) {
         grid_walk(sc.tg, pt, dir, 0.0f, kTFar, [&](int cell, float) {
@@ -562,7 +568,7 @@ struct ShadowArgs {
 
 __global__ void __launch_bounds__(kTraceThreads)
 instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict__ rays_d, const int32_t* __restrict__ ray_ids,
-                       int R, SceneDev sc, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
+                       const float* __restrict__ ray_offsets, int R, SceneDev sc, float b00, float b01, float b02, float b10, float b11, float b12, float step_size,
                        int n_pts, uint32_t seed, int use_mean, Workspace ws, int32_t* __restrict__ n_samples,
                        int32_t* __restrict__ hit_flag, float* __restrict__ alpha_last, const float* __restrict__ params,
                        int n_param, int light_idx, float* __restrict__ color_last) {
@@ -743,7 +749,7 @@ instancer_trace_kernel(const float* __restrict__ rays_o, const float* __restrict
         color_last[3 * (size_t)ray] = col[0]; color_last[3 * (size_t)ray + 1] = col[1]; color_last[3 * (size_t)ray + 2] = col[2];
     }
     const uint32_t rid = ray_ids ? (uint32_t)ray_ids[ray] : (uint32_t)ray;
-    n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, rid, use_mean, t_mesh,
+    n_samples[ray] = walk_ray(H, n_hits, n_pts, step_size, seed, rid, ray_offsets ? ray_offsets + ray : nullptr, use_mean, t_mesh,
                               ws.step_at + (size_t)ray * kMaxHits, ws.segoff + (size_t)ray * kMaxHits, ws.info + ray,
                               ws.seg ? ws.seg + (size_t)ray * kMaxHits : nullptr, ws.first_open + (size_t)ray * kFirstOpenStride);
     for (int k = 0; k < min(n_hits, kSmemHits); ++k) row[k] = H(k);     // with the partner indices walk_ray added
@@ -1023,7 +1029,7 @@ static int check_scene(const ntx_instancer_scene* s, SceneDev* out) {
     return NTX_OK;
 }
 
-NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, int R,
+NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const int32_t* ray_ids, const float* ray_offsets, int R,
                                 const ntx_instancer_scene* scene, const float* b_0, const float* b_1, float step_size,
                                 int n_pts, uint32_t seed, int use_mean_distance, int cast_shadow_rays, const float* parameters,
                                 int n_param, int light_dir_idx, void* workspace, int32_t* n_samples, int32_t* hit,
@@ -1042,7 +1048,7 @@ NTX_API int ntx_instancer_trace(const float* rays_o, const float* rays_d, const 
     Workspace wsp = carve_workspace(workspace, R);
     if (!cast_shadow_rays) wsp.seg = nullptr;            // that part of the workspace is not there
     instancer_trace_kernel<<<(R + kTraceThreads - 1) / kTraceThreads, kTraceThreads, smem, (cudaStream_t)stream>>>(
-        rays_o, rays_d, ray_ids, R, sc, b_0[0], b_0[1], b_0[2], b_1[0], b_1[1], b_1[2], step_size, n_pts, seed,
+        rays_o, rays_d, ray_ids, ray_offsets, R, sc, b_0[0], b_0[1], b_0[2], b_1[0], b_1[1], b_1[2], step_size, n_pts, seed,
         use_mean_distance, wsp, n_samples, hit, alpha_last, parameters, n_param, light_dir_idx, color_last);
     NTX_LAUNCH_CHECK();
     return NTX_OK;

@@ -324,7 +324,8 @@ class Instancer:
         self._frame += 1
 
     def get_model_input_csr(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None,
-                            ray_ids=None):
+                            ray_ids=None, ray_offsets=None):
+        """`ray_offsets` [R]: per-ray offsets in [0, 1) instead of the counter hash (reproducing a reference run)."""
         from . import ops
         if seed is None:
             if ray_ids is not None:
@@ -338,7 +339,7 @@ class Instancer:
                                              blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)),   # fp32 product, instancer.cpp:696
                                              ray_ids=ray_ids, cast_shadow_rays=self.cast_shadow_rays,
                                              min_shadow_samples=self.min_shadow_samples, n_shadow_samples=self.n_shadow_samples,
-                                             param_textures=self.param_textures)
+                                             param_textures=self.param_textures, ray_offsets=ray_offsets)
 
     def get_model_input(self, rays_o, rays_d, parameters, n_samples: int, step_size: float, seed: Optional[int] = None):
         """Dense 10-tuple of instancer.pyx:54."""

@@ -232,10 +232,11 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
                               seed: int = 0, light_dir_idx: int = -1, method: int = 0, use_mean_distance: bool = False,
                               light_strength_idx: int = -1, blend_range: float = 0.0, ray_ids=None,
                               cast_shadow_rays: bool = False, min_shadow_samples: int = 4, n_shadow_samples: int = 512,
-                              param_textures: bool = False):
+                              param_textures: bool = False, ray_offsets=None):
     """Two-pass shell instancer (instancer/src/instancer.cpp:751-1037): trace + count, prefix sum, march.
     `scene`: _lib.InstancerScene (device pointers kept alive by the caller).  `ray_ids` [R] int32: the rays' names for
-    the random draws.  Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box or
+    the random draws.  `ray_offsets` [R] float32 (optional): the per-ray offsets u in [0, 1) to use instead of the
+    counter hash (to reproduce a run of the reference, whose std::mt19937 stream the caller then supplies).  Returns the CSR dict the instanced compositor consumes (rows = rays that touched a patch box or
     the base mesh)."""
     rays_o, rays_d, parameters = as_cuda(rays_o), as_cuda(rays_d), as_cuda(parameters)
     dev = rays_o.device
@@ -243,6 +244,9 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     if ray_ids is not None:
         ray_ids = as_cuda(ray_ids, torch.int32, device=dev).reshape(-1)
         assert ray_ids.shape[0] == R
+    if ray_offsets is not None:
+        ray_offsets = as_cuda(ray_offsets, torch.float32, device=dev).reshape(-1)
+        assert ray_offsets.shape[0] == R
     lib = _lib.load()
     b0 = (C.c_float * 3)(*[float(v) for v in b_0])
     b1 = (C.c_float * 3)(*[float(v) for v in b_1])
@@ -254,7 +258,7 @@ def instancer_get_model_input(rays_o, rays_d, parameters, n_pts: int, step_size:
     ws = torch.empty(max(int(lib.ntx_instancer_workspace_bytes(R, segments)), 16), dtype=torch.uint8, device=dev)
     color_last_all = torch.empty((R, 3), dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), ptr(ray_ids), R, C.byref(scene), b0, b1,
+        check(lib.ntx_instancer_trace(ptr(rays_o), ptr(rays_d), ptr(ray_ids), ptr(ray_offsets), R, C.byref(scene), b0, b1,
                                       float(step_size), int(n_pts), int(seed) & 0xFFFFFFFF, int(bool(use_mean_distance)), segments,
                                       ptr(parameters) if p > 0 else None, p, int(light_dir_idx),
                                       ptr(ws), ptr(n_samples), ptr(hit), ptr(alpha_last_all), ptr(color_last_all), stream_ptr()))

@@ -183,13 +183,16 @@ def _mesh_test(o, d, V, Fc):
     return ~miss, t, u, v
 
 
-def is_shadowed(pt, direction, minv, b0, b1, mesh=None):
+def is_shadowed(pt, direction, minv, b0, b1, mesh=None, prim1=()):
     """isShadowed (instancer.cpp:593-603) with shadow_ray_filter_function (:539-551): a ray from `pt` along `direction`
     (not normalised), t in [0, 100], is blocked by
       * the TOP face of a patch box (quad 4 of createAABB, :117: z = b_1[2]) entered from outside, i.e. travelling
         towards -z in the patch frame,
       * the BOTTOM face of a patch box (quad 1: z = b_0[2]) from either side,
-      * a mesh triangle hit on its front side (direction . Ng < 0, Ng = (v1 - v0) x (v2 - v0)).
+      * a mesh triangle hit on its front side (direction . Ng < 0, Ng = (v1 - v0) x (v2 - v0)),
+      * and — because the filter's last clause `hit->primID == 1` (:550) does not look at the geometry — the SECOND
+        triangle of the base mesh and of every auxiliary mesh from either side (`prim1`: their indices in the merged
+        face list).  Found by running the reference's own code (tests/test_ref_instancer.py).
     Side faces and top faces left from inside let the ray pass."""
     pt, direction = np.asarray(pt, F), np.asarray(direction, F)
     ol = _vdot3(minv[:, :, :3], pt, minv[:, :, 3])
@@ -214,6 +217,8 @@ def is_shadowed(pt, direction, minv, b0, b1, mesh=None):
                            ((e1[:, 2] * e2[:, 0]).astype(F) - (e1[:, 0] * e2[:, 2]).astype(F)).astype(F),
                            ((e1[:, 0] * e2[:, 1]).astype(F) - (e1[:, 1] * e2[:, 0]).astype(F)).astype(F)], -1)
             if (_vdot3(ng, direction) < 0).any():
+                return True
+            if any(hit[f] for f in prim1 if f < hit.shape[0]):
                 return True
     return False
 
@@ -313,7 +318,7 @@ def get_parameters(pt, parameters, V, Fc, UV, textures, texture_idxs, radius):
     return out
 
 
-def shade_mesh(pt, am, prim, uvw, light_raw, minv, b0, b1, mesh, diffuse=F(1.0), ambient=F(0.2)):
+def shade_mesh(pt, am, prim, uvw, light_raw, minv, b0, b1, mesh, diffuse=F(1.0), ambient=F(0.2), prim1=()):
     """shadeMesh (instancer.cpp:716-744): albedo (texture at the hit's UV, or 0.8) times min(diffuse + ambient, 1);
     diffuse = max(n . l, 0) unless the point, lifted 1e-6 along the normal, is shadowed.  Without a light parameter the
     reference reads an uninitialised vector; here that case is ambient only."""
@@ -334,7 +339,7 @@ def shade_mesh(pt, am, prim, uvw, light_raw, minv, b0, b1, mesh, diffuse=F(1.0),
         diffuse = F(0)
     else:
         lifted = [F(F(pt[k]) + F(n[k] * F(1e-6))) for k in range(3)]
-        if not is_shadowed(lifted, light_raw, minv, b0, b1, mesh):
+        if not is_shadowed(lifted, light_raw, minv, b0, b1, mesh, prim1):
             ln = _norm3(light_raw)
             ld = [F(light_raw[k] / ln) for k in range(3)]
             diffuse = F(diffuse * max(_dot3(n, ld), F(0)))
@@ -380,6 +385,8 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         mesh = (np.concatenate(Vs), np.concatenate(Fs))
     else:
         mesh = base
+    # the second triangle of every mesh, in the merged face list (the shadow filter's `primID == 1` clause, :550)
+    prim1 = ([1] if n_base_faces >= 2 else []) + [f0 + 1 for f0, f1 in aux_ranges if f1 - f0 >= 2]
     minv, dirt, origins = prepare_instances(transformations)
     b0, b1 = np.asarray(b_0, F), np.asarray(b_1, F)
     step_size = F(step_size)
@@ -405,7 +412,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                 if f0 <= mh[1] < f1:
                     raw = parameters[i, light_dir_idx:light_dir_idx + 3] if light_dir_idx >= 0 else None
                     color_last[i] = shade_mesh([F(o[a] + F(mh[0] * d[a])) for a in range(3)], am, mh[1] - f0,
-                                               [F(F(F(1) - mh[2]) - mh[3]), mh[2], mh[3]], raw, minv, b0, b1, mesh)
+                                               [F(F(F(1) - mh[2]) - mh[3]), mh[2], mh[3]], raw, minv, b0, b1, mesh, prim1=prim1)
         # :801-827 total in-shell length
         active, total, t_entry = set(), F(0), F(0)
         segment_lengths = []
@@ -462,7 +469,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
         tx_step, tx_entry = F(0), F(0)
         textured = lambda tq: get_parameters([F(o[a] + F(F(tq) * d[a])) for a in range(3)], parameters[i], base[0], base[1],
                                              texture["UV"], texture["textures"], texture["idxs"], texture["radius"])
-        occluded = lambda tq: is_shadowed([F(o[a] + F(F(tq) * d[a])) for a in range(3)], raw_light, minv, b0, b1, mesh)
+        occluded = lambda tq: is_shadowed([F(o[a] + F(F(tq) * d[a])) for a in range(3)], raw_light, minv, b0, b1, mesh, prim1)
         for tt, inst in hits + ([(float(mh[0]), -1)] if mh is not None else []):
             tt = F(tt)
             if step >= n_steps:
@@ -528,7 +535,7 @@ def get_model_input(rays_o, rays_d, parameters, n_pts, step_size, transformation
                     t1 = F(sh_entry + F(F(k) * sh_step))
                     shadowed = occluded(t1 if F(F(t_pt - t0) / sh_step) >= F(0.5) else t0)
                 elif shadow_on:                                     # :949-951 at the sample itself
-                    shadowed = is_shadowed(pt, raw_light, minv, b0, b1, mesh)
+                    shadowed = is_shadowed(pt, raw_light, minv, b0, b1, mesh, prim1)
                 if shadowed:                                        # :572-575 ambient only
                     prm[light_dir_idx:light_dir_idx + 3] = [F(0), F(0), F(-1)]
                     if light_strength_idx >= 0:                     # :954-956 the strength is mapped regardless

@@ -96,6 +96,24 @@ def compare(ref, ora, S, *, tol_t=2e-5, tol_pts=2e-4, max_count_mismatch=0.01, m
     return n_cmp
 
 
+def reconcile_flips(ref, rec, li, max_frac=0.01):
+    """A shadow edge crossed within the hit-distance rounding flips a sample between lit and ambient light: such samples
+    are counted (<= max_frac of all) and then taken out of the value comparison.  Returns (flips, samples looked at)."""
+    amb = np.asarray([0, 0, -1], F)
+    ptr = np.concatenate([[0], np.cumsum(rec["n_samples"])])
+    flips = total = 0
+    for i in np.nonzero(rec["n_samples"] > 0)[0]:
+        a, b = ptr[i], ptr[i + 1]
+        if (ref["dist"][i] > 0).sum() != b - a:
+            continue
+        amb_r = (ref["parameters"][i, :b - a, li:li + 3] == amb).all(-1)
+        amb_o = (rec["params"][a:b, li:li + 3] == amb).all(-1)
+        flips, total = flips + int((amb_r != amb_o).sum()), total + (b - a)
+        rec["params"][a:b][amb_r != amb_o] = ref["parameters"][i, :b - a][amb_r != amb_o]
+    assert total > 0 and flips <= max_frac * total, (flips, total)
+    return flips, total
+
+
 @pytest.mark.parametrize("mean", [False, True])
 @pytest.mark.parametrize("light", ["light", "point"])
 def test_explicit_patches_nearest(mean, light):
@@ -272,19 +290,7 @@ def test_shadow_rays(light, n_shadow, tmp_path):
                            dict(method="nearest", patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), cast_shadow_rays=True,
                                 min_shadow_samples=8, n_shadow_samples=n_shadow, **kw), o, d, prm, S, step, T)
     li = kw["light_dir_idx"]
-    # a shadow edge crossed within the hit-distance rounding flips a sample between lit and ambient: count those apart
-    n_ora = ora["n_samples"]
-    ptr = np.concatenate([[0], np.cumsum(n_ora)])
-    flips = total = 0
-    for i in np.nonzero(n_ora > 0)[0]:
-        a, b = ptr[i], ptr[i + 1]
-        if (ref["dist"][i] > 0).sum() != b - a:
-            continue
-        amb_r = (ref["parameters"][i, :b - a, li:li + 3] == np.asarray([0, 0, -1], F)).all(-1)
-        amb_o = (ora["params"][a:b, li:li + 3] == np.asarray([0, 0, -1], F)).all(-1)
-        flips, total = flips + int((amb_r != amb_o).sum()), total + (b - a)
-        ora["params"][a:b][amb_r != amb_o] = ref["parameters"][i, :b - a][amb_r != amb_o]
-    assert flips <= 0.01 * total, (flips, total)
+    reconcile_flips(ref, ora, li)
     compare(ref, ora, S, tol_pts=5e-4, params_tol=1e-4)
     shadowed = (ora["params"][:, li:li + 3] == np.asarray([0, 0, -1], F)).all(-1)
     assert 0.02 < shadowed.mean() < 0.98, float(shadowed.mean())
@@ -316,7 +322,9 @@ def test_auxiliary_meshes_are_shaded(tmp_path):
                                                   (str(tmp_path / "wall.ply"), "")], **ref_kw),
                            dict(method="nearest", light_dir_idx=1, patch_scale=0.09, mesh=(mesh["V"], mesh["F"]), cast_shadow_rays=True,
                                 min_shadow_samples=8, n_shadow_samples=4000, aux_meshes=aux_o), o, d, prm, S, step, T)
-    compare(ref, ora, S, tol_pts=5e-4, params_tol=2.1, max_id_mismatch=0.01)      # (lit / ambient flips are checked above)
+    # (the table's and the wall's second triangles block light from either side: the `primID == 1` clause of :550)
+    flips, _ = reconcile_flips(ref, ora, 1, max_frac=0.002)
+    compare(ref, ora, S, tol_pts=5e-4, params_tol=1e-4, max_id_mismatch=0.01)
     rc, oc = ref["color"][:, 0], ora["color_last"]
     close = np.abs(rc - oc).max(-1) < 2e-3
     assert close.mean() > 0.98, float(close.mean())                  # texel / shadow edges within the rounding aside
