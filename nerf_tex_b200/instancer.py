@@ -336,7 +336,9 @@ class Instancer:
         return ops.instancer_get_model_input(rays_o, rays_d, parameters, n_samples, step_size, self.scene, self.b_0, self.b_1,
                                              seed=seed, light_dir_idx=self.light_dir_idx, method=self.method,
                                              use_mean_distance=self.use_mean_distance, light_strength_idx=self.light_strength_idx,
-                                             blend_range=float(np.float32(0.2) * np.float32(self.patch_scale)),   # fp32 product, instancer.cpp:696
+                                             # fp32 product, instancer.cpp:696; the reference's patch_scale member is only
+                                             # set by DistributeInstancesOnMesh (:245) and stays 1 for explicit patches
+                                             blend_range=float(np.float32(0.2) * np.float32(self.patch_scale if self.mesh is not None else 1.0)),
                                              ray_ids=ray_ids, cast_shadow_rays=self.cast_shadow_rays,
                                              min_shadow_samples=self.min_shadow_samples, n_shadow_samples=self.n_shadow_samples,
                                              param_textures=self.param_textures, ray_offsets=ray_offsets)

@@ -102,8 +102,10 @@ def test_nearest_blend():
     R = 500
     o, d = rays_over(5, R, seed=9)
     prm = np.zeros((R, 2), np.float32)
+    # explicit patches: the reference's patch_scale member is only set by DistributeInstancesOnMesh (instancer.cpp:245) and
+    # stays 1 whatever the keyword says (checked on the reference's own code, tests/test_ref_instancer.py)
     inst = Instancer(B0, B1, transformations=Ts.tolist(), instance_sampling_method="nearest_blend", patch_scale=1.5)
-    want = IO.get_model_input(o, d, prm, 40, 0.02, Ts, B0, B1, seed=6, method="nearest_blend", patch_scale=1.5)
+    want = IO.get_model_input(o, d, prm, 40, 0.02, Ts, B0, B1, seed=6, method="nearest_blend", patch_scale=1.0)
     got = inst.get_model_input_csr(torch.as_tensor(o), torch.as_tensor(d), torch.as_tensor(prm), 40, 0.02, seed=6)
     check_records(got, want, R)
     w = want["alpha_weight"]

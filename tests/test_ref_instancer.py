@@ -329,3 +329,46 @@ def test_auxiliary_meshes_are_shaded(tmp_path):
     close = np.abs(rc - oc).max(-1) < 2e-3
     assert close.mean() > 0.98, float(close.mean())                  # texel / shadow edges within the rounding aside
     assert (oc.max(-1) > 0.05).sum() > 20
+
+
+@pytest.mark.parametrize("method", ["random", "nearest_blend"])
+def test_drawn_choices_carry_the_weights_the_restatement_gives(method):
+    """'random' and 'nearest_blend' draw per sample from the reference's std::mt19937 through std::uniform_int_distribution /
+    std::discrete_distribution; those streams are not reproduced.  What is checked instead, sample by sample on the
+    reference's own output: the chosen patch contains the sample, and the density weight it carries is what the
+    restated rule gives for THAT choice — the number of patches containing the point ('random', :670-675), or
+    sum(w) / w_chosen with w_i = max(0.2 * patch_scale + min_dist - dist_i, 0) ('nearest_blend', :694-713) — with the
+    containing set found independently of any hit logic (point-in-box in every patch frame)."""
+    Tm = patches(80, 21, scale=0.3, spread=0.8)                     # heavy overlap
+    R, S, step = 150, 64, 0.01
+    o, d = camera_rays(R, 22, spread=0.8)
+    prm = np.tile(np.asarray([[0.5, 0.0, 0.0, 1.0]], F), (R, 1))
+    inst = RI.RefInstancer(B0, B1, textures=["", "light"], transformations=Tm.tolist(), instance_sampling_method=method)
+    ref = inst.get_model_input(o, d, prm, S, step)
+    minv, _, origins = IO.prepare_instances(Tm)
+    b0, b1 = np.asarray(B0, np.float64), np.asarray(B1, np.float64)
+    checked = multi = 0
+    for i in range(R):
+        n = int((ref["dist"][i] > 0).sum())
+        for k in range(n):
+            p = o[i].astype(np.float64) + float(ref["t"][i, k]) * d[i].astype(np.float64)
+            loc = np.einsum("iab,b->ia", minv[:, :, :3].astype(np.float64), p) + minv[:, :, 3]
+            margin = np.minimum(loc - b0, b1 - loc).min(-1)
+            if (np.abs(margin) < 1e-4).any():                        # too close to a face to call
+                continue
+            inside = np.nonzero(margin > 0)[0]
+            sel = int(ref["instance_id"][i, k])
+            assert sel in inside, (i, k, sel, inside)
+            w_ref = float(ref["density_weight"][i, k])
+            if method == "random":
+                assert w_ref == len(inside)
+            else:
+                dist = np.linalg.norm(p[None, :] - origins[inside].astype(np.float64), axis=-1)
+                w = np.maximum(0.2 * 1.0 + dist.min() - dist, 0.0)   # patch_scale stays 1 without DistributeInstancesOnMesh
+                assert w[list(inside).index(sel)] > 0
+                assert abs(w_ref - w.sum() / w[list(inside).index(sel)]) <= 2e-3 * w_ref, (i, k)
+            checked += 1
+            multi += len(inside) > 1
+            # the sample is mapped into the chosen patch's frame
+            assert np.abs(ref["pts"][i, k] - loc[sel]).max() < 1e-4
+    assert checked > 2000 and multi > 0.3 * checked
