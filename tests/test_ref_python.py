@@ -171,3 +171,163 @@ def test_renderer_call(ref, case, composite_bkgd):
         assert np.abs(g - want[k]).max() <= tol, (k, float(np.abs(g - want[k]).max()))
     miss = ~hit.reshape(B, R)
     assert (got["alpha_pred"].numpy()[miss] == 0).all()
+
+
+# ------------------------------------------------------------------------------------------------ rays, proxy, losses
+def test_rays_from_camera_frustum_and_proxy(ref):
+    """network/ray_sampler.py:6-48, network/proxy.py:6-35: directions, origins, cone scale, Frustum t, AABB t (misses = inf)."""
+    tf, renderer, model, loss, ray_sampler, proxy, util = ref
+    H, W, focal = 37, 53, 60.0
+    ii, jj = np.meshgrid(np.arange(H), np.arange(W), indexing="ij")
+    loc = np.stack([ii.reshape(-1), jj.reshape(-1)], -1).astype(F)
+    th = 0.4
+    c2w = np.asarray([[np.cos(th), 0, np.sin(th), 2.0], [0, 1, 0, 0.3], [-np.sin(th), 0, np.cos(th), 4.0], [0, 0, 0, 1]], F)
+    o_r, d_r, c_r = ray_sampler.rays_from_camera(tf.constant(loc), H, W, focal, tf.constant(c2w))
+    o, d, c = O.rays_from_camera(loc, H, W, focal, c2w)
+    assert np.array_equal(o_r.numpy(), o) and np.array_equal(d_r.numpy(), d) and np.abs(c_r.numpy() - c).max() <= 4e-9   # (1 ulp: atan rounded before cos)
+    fo, fd, ft, fc = ray_sampler.Frustum(H, W, focal, 2.0, 6.0)(tf.constant(loc), tf.constant(c2w))
+    assert np.array_equal(ft.numpy(), np.tile(np.asarray([[2.0, 6.0]], F), (H * W, 1))) and np.array_equal(fd.numpy(), d)
+    b0, b1 = [-1.0, -1.2, -0.5], [1.0, 0.8, 0.7]
+    po, pd, pt, pc = ray_sampler.Proxy(H, W, focal, proxy.AABB(b0, b1))(tf.constant(loc), tf.constant(c2w))
+    wo, wd, wt, wc = O.proxy_rays(loc, H, W, focal, c2w, b0, b1)
+    assert np.array_equal(pd.numpy(), wd) and np.array_equal(pt.numpy(), wt)
+    assert 0.05 < np.isinf(wt[:, 0]).mean() < 0.95
+
+
+@pytest.mark.parametrize("coarse", [False, True])
+@pytest.mark.parametrize("hard", [True, False])
+def test_losses(ref, coarse, hard):
+    """network/loss.py: mse, smape, NerfLoss, AlphaLoss (hard / soft mask, with and without the coarse pair)."""
+    tf, renderer, model, loss, *_ = ref
+    rng = np.random.default_rng(21)
+    ct, cp, cc = (rng.uniform(0, 1, (2, 50, 3)).astype(F) for _ in range(3))
+    at, ap, ac = (rng.uniform(0, 1, (2, 50)).astype(F) for _ in range(3))
+    at[0, ::3] = 0
+    c = tf.constant
+    got = loss.AlphaLoss("network.loss.smape", "network.loss.mse", gamma=0.7, use_hard_mask=hard)(
+        color_true=c(ct), alpha_true=c(at), color_pred=c(cp), alpha_pred=c(ap), color_pred_coarse=c(cc) if coarse else None,
+        alpha_pred_coarse=c(ac) if coarse else None)
+    want = O.alpha_loss(ct, at, cp, ap, cc if coarse else None, ac if coarse else None, gamma=0.7, use_hard_mask=hard)
+    assert abs(float(got) - float(want)) <= 2e-6 * abs(float(want))
+    assert abs(float(loss.mse(c(ct), c(cp))) - float(O.mse(ct, cp))) <= 1e-7
+    got_n = loss.NerfLoss()(color_true=c(ct), color_pred=c(cp), color_pred_coarse=c(cc) if coarse else None)
+    assert abs(float(got_n) - float(O.mse(ct, cp) + (O.mse(ct, cc) if coarse else 0))) <= 1e-6
+
+
+# ------------------------------------------------------------------------------------------------ mip renderer
+@pytest.mark.parametrize("perturb,noise_std", [(True, 0.0), (False, 0.3)])
+def test_mip_renderer(ref, perturb, noise_std):
+    """MipRenderer (renderer.py:356-473) with IntegratedPositionalEncoding (layer.py:25-41): S + 1 edges, the blur parameter
+    spliced out, cone-segment gaussians, edge compositing."""
+    tf, renderer, model, loss, ray_sampler, proxy, util = ref
+    npar = (2, 2)                                                      # after the blur parameter is spliced out
+    om = O.ParamNerfOracle(n_parameters=npar, n_pos=6, seed=31)
+    om.randomize_biases(32, 0.2)
+    ipe = util.EasyDict({"module": "network.layer.IntegratedPositionalEncoding", "n_freq_bands": 10})
+    km = model.ParamNerf(ipe, RP.ff(util, 4), RP.ff(util, 4), n_parameters=list(npar), n_pos=6)["model"]
+    RP.set_weights(km, om)
+    R, S = 60, 24
+    o, d, t, cone = rays(R, 33)
+    prm = np.random.default_rng(34).uniform(0.2, 1.0, (1, 5)).astype(F)
+    r = renderer.MipRenderer(model=km, n_samples=S, perturb=perturb, raw_noise_std=noise_std, blur_idx=1, render_chunk=25)
+    tf.random.seed(35)
+    got = r(tf.constant(o), tf.constant(d), tf.constant(t), tf.constant(prm), tf.constant(cone), composite_bkgd=True, training=True)
+    log = list(tf.random.log)
+    outs = {"color_pred": [], "alpha_pred": []}
+    for i in range(0, R, 25):
+        zr = log.pop(0)[1] if perturb else None
+        nz = log.pop(0)[1] * F(noise_std) if noise_std > 0 else None
+        w, _ = O.mip_render_rays(om, o[0, i:i + 25], d[0, i:i + 25], t[0, i:i + 25], np.repeat(prm, R, 0)[i:i + 25], cone[0, i:i + 25], S, 1,
+                                 perturb=perturb, z_rand=zr, noise=nz, composite_bkgd=True)
+        for k in outs:
+            outs[k].append(w[k])
+    assert not log
+    for k in outs:
+        assert np.abs(got[k].numpy()[0] - np.concatenate(outs[k], 0)).max() <= 2e-5, k
+
+
+# ------------------------------------------------------------------------------------------------ instanced renderers
+def instanced_setup(ref, tmp_path, mip):
+    """The reference's InstanceRenderer over the reference's own C++ instancer (oracle/tf_shim/instancer wraps
+    oracle/ref_instancer like instancer.pyx wraps the class) on a mesh scene with a base mesh that ends rays."""
+    import test_ref_instancer as TI
+    tf, renderer, model, loss, ray_sampler, proxy, util = ref
+    mesh, T, ref_kw = TI.mesh_scene(tmp_path, 41, n_anchor=120)
+    npar = (1, 3) if not mip else (1, 2)
+    om = O.ParamNerfOracle(n_parameters=npar, n_pos=6 if mip else 3, seed=42)
+    om.randomize_biases(43, 0.2)
+    if mip:
+        ipe = util.EasyDict({"module": "network.layer.IntegratedPositionalEncoding", "n_freq_bands": 10})
+        km = model.ParamNerf(ipe, RP.ff(util, 4), RP.ff(util, 4), n_parameters=list(npar), n_pos=6)["model"]
+        RP.set_weights(km, om)
+    else:
+        km = RP.build_param_nerf(model, util, om)
+    icfg = util.EasyDict(dict(module="instancer.instancer.Instancer", b_0=TI.B0, b_1=TI.B1, textures=["", "light"], **ref_kw))
+    R = 160
+    o, d = TI.rays_from_above(R, 44)
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(F)
+    t = np.tile(np.asarray([[0.1, 5.0]], F), (R, 1))
+    t[::13, 0] = np.inf
+    cone = np.random.default_rng(45).uniform(0.001, 0.01, (R, 1)).astype(F)
+    prm = np.asarray([[0.7, 0.2, 0.3, 0.9]], F)
+    return tf, renderer, km, om, icfg, o, d, t, cone, prm, R
+
+
+@pytest.mark.parametrize("variant", [dict(), dict(blur_idx=0), dict(density_reweighting=False, density_scale=2.5), dict(false_color=True),
+                                     dict(map_exr=True)])
+def test_instance_renderer(ref, variant, tmp_path):
+    """InstanceRenderer (renderer.py:215-354) end to end on the reference's side: its Python over its C++ instancer.  The
+    oracle gets the very records the C++ returned."""
+    tf, renderer, km, om, icfg, o, d, t, cone, prm, R = instanced_setup(ref, tmp_path, mip=False)
+    S, step = 64, 0.004
+    tf.random.seed(46)
+    r = renderer.InstanceRenderer(instancer_config=icfg, model=km, n_samples=S, step_size=step, render_chunk=70, net_chunk=900, **variant)
+    got = r(tf.constant(o[None]), tf.constant(d[None]), tf.constant(t[None]), tf.constant(prm), tf.constant(cone[None]),
+            composite_bkgd=True, bkgd_color=[1.0, 0.5, 0.25], training=False)
+    inst_color = tf.random.log[0][1] if variant.get("false_color") else None
+    # replay chunk by chunk with a second instancer of the same seed: the same draws in the same order
+    inst2 = icfg_instancer(icfg)
+    hit = t[:, 0] != np.inf
+    idx = np.nonzero(hit)[0]
+    cm, am = np.zeros((R, 3), F), np.zeros(R, F)
+    cm[~hit] = np.asarray([1.0, 0.5, 0.25], F)
+    for i in range(0, idx.shape[0], 70):
+        sl = idx[i:i + 70]
+        rec = inst2.get_model_input(o[sl], d[sl], np.repeat(prm, sl.shape[0], 0), S, step)
+        tup = (rec["rays_d"], rec["pts"], rec["t"], rec["dist"], rec["color"], rec["density"], rec["density_weight"], rec["instance_id"],
+               np.nonzero(rec["hit"])[0], rec["parameters"])
+        c, a = O.instance_evaluate_model(om, tup, sl.shape[0], cone_scale=cone[sl], blur_idx=variant.get("blur_idx"), patch_scale=0.09,
+                                         density_scale=variant.get("density_scale", 1.0), density_reweighting=variant.get("density_reweighting", True),
+                                         composite_bkgd=True, bkgd_color=(1.0, 0.5, 0.25), map_exr=variant.get("map_exr", False),
+                                         net_chunk=900, instance_color=inst_color)
+        cm[sl], am[sl] = c, a
+    assert np.abs(got["color_pred"].numpy()[0] - cm).max() <= 3e-5 and np.abs(got["alpha_pred"].numpy()[0] - am).max() <= 3e-5
+    assert (am[hit] > 0.5).any() and (am[hit] == 0).any()
+
+
+def icfg_instancer(icfg):
+    from oracle import ref_instancer as RI
+    kw = {k: v for k, v in icfg.items() if k != "module"}
+    return RI.RefInstancer(kw.pop("b_0"), kw.pop("b_1"), **kw)
+
+
+def test_mip_instance_renderer(ref, tmp_path):
+    """MipInstanceRenderer (renderer.py:475-587)."""
+    tf, renderer, km, om, icfg, o, d, t, cone, prm, R = instanced_setup(ref, tmp_path, mip=True)
+    S, step = 64, 0.004
+    r = renderer.MipInstanceRenderer(instancer_config=icfg, model=km, n_samples=S, step_size=step, render_chunk=70, net_chunk=900, blur_idx=1)
+    got = r(tf.constant(o[None]), tf.constant(d[None]), tf.constant(t[None]), tf.constant(prm), tf.constant(cone[None]),
+            composite_bkgd=False, training=False)
+    inst2 = icfg_instancer(icfg)
+    hit = t[:, 0] != np.inf
+    idx = np.nonzero(hit)[0]
+    cm, am = np.zeros((R, 3), F), np.zeros(R, F)
+    for i in range(0, idx.shape[0], 70):
+        sl = idx[i:i + 70]
+        rec = inst2.get_model_input(o[sl], d[sl], np.repeat(prm, sl.shape[0], 0), S, step)
+        tup = (rec["rays_d"], rec["pts"], rec["t"], rec["dist"], rec["color"], rec["density"], rec["density_weight"], rec["instance_id"],
+               np.nonzero(rec["hit"])[0], rec["parameters"])
+        c, a = O.mip_instance_evaluate_model(om, tup, sl.shape[0], cone[sl], 1, patch_scale=0.09, net_chunk=900)
+        cm[sl], am[sl] = c, a
+    assert np.abs(got["color_pred"].numpy()[0] - cm).max() <= 3e-5 and np.abs(got["alpha_pred"].numpy()[0] - am).max() <= 3e-5
+    assert (am[hit] > 0.5).any()
