@@ -1,9 +1,10 @@
 """CPU oracle for the shell instancer (instancer/src/instancer.cpp:751-1037, GetModelInput).
-TEST INFRASTRUCTURE ONLY.  PARITY UNPINNED: the reference instancer needs Embree 3 (absent) and its
-meshes/textures are git-LFS stubs, so it can neither be built nor fed here; this is a restatement of
-its algorithm: explicit patch instances (`transformations`) or patches distributed on a base mesh
-(DistributeInstancesOnMesh), termination of a ray at the first mesh hit; no parameter textures, no shadow
-rays, no auxiliary-mesh shading yet.
+TEST INFRASTRUCTURE ONLY.  PINNING: the reference's own instancer.cpp is compiled here against a brute-force
+stand-in for Embree's API and run on generated assets (oracle/ref_instancer.py, oracle/embree_shim); this restatement
+agrees with it (tests/test_ref_instancer.py: explicit patches, patches distributed on a mesh, mesh termination,
+parameter textures, shadow rays, auxiliary meshes; the device kernels are held to the same runs in
+tests/test_gpu_ref_instancer.py).  Not pinned: Embree's own intersection arithmetic and traversal order, and the
+`random` / `nearest_blend` draw streams.
 
 What is restated (file:line of instancer.cpp):
   * all hits of a ray with every instanced patch box, sorted by (t, instance)            :780-799
@@ -24,9 +25,9 @@ What is restated (file:line of instancer.cpp):
     the mesh for every anchor, interpolated frame, optional rotation about the normal by jitter_amount * U(0, pi)
     drawn from std::mt19937(seed = 0) exactly as libstdc++ draws it, patch matrix [T B N | anchor] * scale
 
-Not reproducible by construction: the reference draws offsets / instance choices from a member
-`std::mt19937`; here they come from a counter-based hash of (seed, ray[, step]) so that a GPU kernel can
-reproduce them.  All arithmetic is fp32 in a fixed order (the kernel mirrors it with round-to-nearest
+The reference draws offsets / instance choices from a member `std::mt19937`; here they come from a counter-based
+hash of (seed, ray[, step]) so that a GPU kernel can reproduce them — or, for the per-ray offsets, from `ray_u`, which
+lets a test feed the reference's stream (reproduced exactly by `MT19937` / `uniform_real_float` below).  All arithmetic is fp32 in a fixed order (the kernel mirrors it with round-to-nearest
 intrinsics), so the kernel is expected to match this oracle bit for bit.
 """
 

@@ -4,11 +4,20 @@ This file is a CPU restatement (NumPy fp32, every reduction in a *defined* order
 reference algorithm.  Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s CPU
 baseline legs may import it; the product path (``nerf_tex_b200``) never does.
 
-PARITY UNPINNED: the reference's arithmetic lives in tensorflow-gpu==2.4.1
-(``/root/reference/environment.yml:12``) which cannot be installed in this image, and the
-reference ships no tests, golden vectors or fixtures.  The oracle is
-therefore pinned only against closed-form known answers (tests/test_oracle_kat.py) and
-against an independent C restatement (oracle/ntx_oracle.c) that must agree bit for bit.
+PINNING.  The reference ships no tests, golden vectors or fixtures and its
+arithmetic lives in tensorflow-gpu==2.4.1 (``/root/reference/environment.yml:12``), which cannot be
+installed in this image.  What pins this file:
+  * the REFERENCE'S OWN PYTHON SOURCE (network/renderer.py, model.py, layer.py, loss.py,
+    ray_sampler.py, proxy.py), imported from /root/reference and run over a NumPy stand-in for the
+    TensorFlow ops it calls (oracle/tf_shim): tests/test_ref_python.py, and the vectors that run
+    produced (tests/golden/ref_python_small.npz, tests/golden/make_ref_python.py) for machines
+    without the reference tree.  That pins the reference's LOGIC as written — which tensors are
+    sliced, gathered, concatenated, scattered, in which order.
+  * NOT pinned: TensorFlow's own kernels (the stand-in restates each op's documented semantics, as
+    listed below), so reduction orders and transcendental round-off remain restated, not observed;
+  * closed-form known answers (tests/test_oracle_kat.py), an independent C restatement
+    (oracle/ntx_oracle.c) that must agree bit for bit, a torch transcription
+    (tests/test_oracle_vs_torch.py).
 
 Every function cites the reference file:line it follows (paths relative to
 ``/root/reference``).  TF semantics restated from documentation:
