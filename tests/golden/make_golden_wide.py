@@ -39,7 +39,7 @@ def main():
     d = np.stack([rng.uniform(-.3, .3, R), rng.uniform(-.3, .3, R), np.full(R, -1.0)], 1).astype(np.float32)
     prm = rng.normal(size=(R, 5)).astype(np.float32)
     for method in ("random", "nearest", "nearest_blend"):
-        rec = IO.get_model_input(o, d, prm, 24, 0.02, Ts, B0, B1, seed=9, light_dir_idx=2, method=method, patch_scale=1.2)
+        rec = IO.get_model_input(o, d, prm, 24, 0.02, Ts, B0, B1, seed=9, light_dir_idx=2, method=method, patch_scale=1.0)   # explicit patches: the reference keeps its patch_scale member at 1 (instancer.cpp:53,245)
         for k, v in rec.items():
             out[f"inst_{method}_{k}"] = v
     out.update(inst_T=Ts, inst_o=o, inst_d=d, inst_prm=prm)

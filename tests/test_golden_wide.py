@@ -24,7 +24,7 @@ def same_bits(a, b):
 def test_oracles_reproduce_golden_vectors():
     for method in ("random", "nearest", "nearest_blend"):
         rec = IO.get_model_input(G["inst_o"], G["inst_d"], G["inst_prm"], 24, 0.02, G["inst_T"], B0, B1, seed=9, light_dir_idx=2,
-                                 method=method, patch_scale=1.2)
+                                 method=method, patch_scale=1.0)
         for k in REC:
             assert same_bits(rec[k], G[f"inst_{method}_{k}"]), (method, k)
     mean, cov = O.mip_cone_gaussians(G["mip_o"], G["mip_d"], G["mip_z"], G["mip_radii"])
