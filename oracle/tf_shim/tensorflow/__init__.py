@@ -477,8 +477,23 @@ class nn:
             return _t(np.where(a > 0, a, np.expm1(a.astype(np.float64)).astype(a.dtype)))
 
     @staticmethod
-    def depthwise_conv2d(*args, **kwargs):
-        raise NotImplementedError("stand-in: depthwise_conv2d (image post-processing) is outside the pinned path")
+    def depthwise_conv2d(input, filter, strides, padding, **kwargs):  # noqa: A002
+        """NHWC input, [kh, kw, C, 1] filter, 'SAME' padding as TensorFlow documents it: out = ceil(in / stride),
+        pad_total = max((out - 1) * stride + k - in, 0), the smaller half in front.  Products accumulated in float64."""
+        x, f = _np(input).astype(np.float64), _np(filter).astype(np.float64)
+        assert padding == "SAME" and f.shape[3] == 1 and x.shape[3] == f.shape[2]
+        n, H, W, C = x.shape
+        kh, kw = f.shape[:2]
+        sh, sw = int(strides[1]), int(strides[2])
+        oh, ow = -(-H // sh), -(-W // sw)
+        ph, pw = max((oh - 1) * sh + kh - H, 0), max((ow - 1) * sw + kw - W, 0)
+        xp = np.zeros((n, H + ph, W + pw, C))
+        xp[:, ph // 2:ph // 2 + H, pw // 2:pw // 2 + W] = x
+        out = np.zeros((n, oh, ow, C))
+        for i in np.arange(kh):
+            for j in np.arange(kw):
+                out += xp[:, i:i + (oh - 1) * sh + 1:sh, j:j + (ow - 1) * sw + 1:sw] * f[i, j, :, 0]
+        return _t(out.astype(np.float32))
 
 
 class linalg:

@@ -331,3 +331,18 @@ def test_mip_instance_renderer(ref, tmp_path):
         cm[sl], am[sl] = c, a
     assert np.abs(got["color_pred"].numpy()[0] - cm).max() <= 3e-5 and np.abs(got["alpha_pred"].numpy()[0] - am).max() <= 3e-5
     assert (am[hit] > 0.5).any()
+
+
+@pytest.mark.parametrize("factor,H,W", [(2, 16, 20), (3, 17, 23), (4, 32, 32)])
+def test_filtered_downsample(ref, factor, H, W):
+    """util/interpolate.py:67-82 (what Logger.render_image applies, logger.py:126-131): gaussian kernel size and
+    normalisation, strided 'SAME' depthwise convolution."""
+    tf, *_ = ref
+    from util import interpolate
+    img = np.random.default_rng(51).uniform(0, 1, (H, W, 4)).astype(F)
+    got = interpolate.filtered_downsample(tf.constant(img), factor).numpy()
+    want = O.filtered_downsample(img, factor)
+    assert got.shape == want.shape and np.abs(got - want).max() <= 2e-6
+    k = int(factor * .5 * 6)
+    ker = interpolate.gaussian_kernel(k, factor * .5, 4).numpy()
+    assert ker.shape == (k, k, 4, 1) and np.abs(ker[:, :, 0, 0] - O.gaussian_kernel_2d(k, factor * .5)).max() <= 1e-7
