@@ -503,6 +503,18 @@ class linalg:
         sq = reduce_sum(_t(a * a), axis=axis, keepdims=keepdims)._a
         return _t(np.sqrt(sq).astype(a.dtype))
 
+    @staticmethod
+    def normalize(x, axis=None):
+        a = _np(x)
+        n = np.sqrt((a * a).sum(axis=axis, keepdims=True, dtype=a.dtype)).astype(a.dtype)
+        return _t((a / n).astype(a.dtype)), _t(n)
+
+    @staticmethod
+    def cross(a, b):
+        x, y = _pair(a, b)
+        x, y = np.asarray(x, np.float32), np.asarray(y, np.float32)
+        return _t(np.cross(x, y).astype(np.float32))
+
 
 class bitwise:
     @staticmethod
@@ -560,6 +572,15 @@ def name_scope(name):
 
 # the functional Keras API writes graphs with these on symbolic tensors (network/model.py:28,44,85,93,101,108,115)
 concat = keras.layers.symbolic_op(concat)
+
+
+class Variable(Tensor):
+    pass
+
+
+class data:
+    class Dataset:
+        pass
 
 
 def function(fn=None, **kwargs):

@@ -346,3 +346,13 @@ def test_filtered_downsample(ref, factor, H, W):
     k = int(factor * .5 * 6)
     ker = interpolate.gaussian_kernel(k, factor * .5, 4).numpy()
     assert ker.shape == (k, k, 4, 1) and np.abs(ker[:, :, 0, 0] - O.gaussian_kernel_2d(k, factor * .5)).max() <= 1e-7
+
+
+def test_look_at(ref):
+    """network/dataset.py:231-238 against the product's dataset.look_at (the bench's camera poses)."""
+    tf, *_ = ref
+    from network import dataset as ref_dataset
+    from nerf_tex_b200.dataset import look_at
+    for pos in ([5.0, 0.3, 2.0], [0.1, -4.0, 3.0], [-2.0, 2.0, 0.5], [0.0, 0.0, 6.0]):
+        got = ref_dataset.look_at(tf.constant(pos)).numpy()
+        assert np.abs(got - look_at(pos)).max() <= 1e-6, pos
