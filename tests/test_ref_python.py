@@ -356,3 +356,83 @@ def test_look_at(ref):
     for pos in ([5.0, 0.3, 2.0], [0.1, -4.0, 3.0], [-2.0, 2.0, 0.5], [0.0, 0.0, 6.0]):
         got = ref_dataset.look_at(tf.constant(pos)).numpy()
         assert np.abs(got - look_at(pos)).max() <= 1e-6, pos
+
+
+# ------------------------------------------------------------------------------------------------ the shipped configs
+def _config_names():
+    return sorted(p.stem for p in (RP.REF / "configs").glob("config_*_*.py")) if RP.available() else []
+
+
+@pytest.mark.parametrize("name", _config_names())
+def test_shipped_config_through_the_references_own_classes(ref, name, tmp_path, monkeypatch):
+    """Every configs/config_*_{train,render}.py, imported as the reference's main.py imports it, its `model_config` and
+    `renderer_config` instantiated by the REFERENCE'S util.instantiate into the reference's own classes exactly as
+    network/render.py:21-25 and network/train.py:30-43 do (render configs: the reference's C++ instancer on generated
+    assets under the configs' file names) — against the oracle with the same keyword values."""
+    import copy
+    import importlib
+    tf, renderer, model, loss, ray_sampler, proxy, util = ref
+    cfg = copy.deepcopy(importlib.import_module("configs." + name).config)
+    mc, rc = util.EasyDict(cfg["model_config"]), util.EasyDict(cfg["renderer_config"])
+    npar = tuple(mc["n_parameters"]) if "n_parameters" in mc else tuple(mc["model_config"]["n_parameters"])
+    is_render = "instancer_config" in rc
+    if is_render:
+        from test_reference_configs import procedural_assets
+        procedural_assets(str(tmp_path), rc["instancer_config"])
+        monkeypatch.chdir(tmp_path)                                   # the configs name their assets relative to the run directory
+    models = util.instantiate(mc)                                    # the reference's ParamNerf / CoarseFine
+    oracles = {}
+    for i, (mname, km) in enumerate(models.items()):
+        om = O.ParamNerfOracle(n_parameters=npar, seed=70 + i)
+        om.randomize_biases(80 + i, 0.1)
+        RP.set_weights(km, om)
+        oracles[mname] = om
+    rc.update(models)
+    r = util.instantiate(rc)                                         # the reference's Renderer / InstanceRenderer
+    p = sum(npar)
+    rng = np.random.default_rng(90)
+    if not is_render:
+        R = 24
+        o, d, t, cone = rays(R, 91)
+        t[0, ::5, 0] = np.inf
+        prm = rng.uniform(0.2, 1.0, (1, p)).astype(F)
+        tf.random.seed(92)
+        got = r(tf.constant(o), tf.constant(d), tf.constant(t), tf.constant(prm), tf.constant(cone), composite_bkgd=True, training=True)
+        hit = t[0, :, 0] != np.inf
+        S, N = rc["n_samples"], rc.get("n_importance", 0)
+        log = list(tf.random.log)
+        z_rand = np.zeros((R, S), F)
+        if rc.get("perturb", True):
+            z_rand[hit] = log.pop(0)[1]
+        noise = None
+        if rc.get("raw_noise_std", 0) > 0:
+            noise = np.zeros((R, S), F)
+            noise[hit] = log.pop(0)[1] * F(rc["raw_noise_std"])
+        assert not log and N == 0
+        out = O.render_rays(oracles["model"], None, o[0][hit], d[0][hit], t[0][hit], np.repeat(prm, R, 0)[hit], cone[0][hit], S, 0,
+                            rc.get("perturb", True), z_rand=z_rand[hit], noise=None if noise is None else noise[hit],
+                            blur_idx=rc.get("blur_idx"), composite_bkgd=True)
+        assert np.abs(got["color_pred"].numpy()[0][hit] - out["color_pred"]).max() <= 3e-5
+        assert np.abs(got["alpha_pred"].numpy()[0][hit] - out["alpha_pred"]).max() <= 3e-5
+        assert (got["color_pred"].numpy()[0][~hit] == 1).all()
+        return
+    ic = rc["instancer_config"]
+    R = 40
+    o = np.stack([rng.uniform(-1.3, 1.3, R), rng.uniform(-1.3, 1.3, R), rng.uniform(0.8, 1.6, R)], 1).astype(F)
+    d = np.stack([rng.uniform(-.6, .6, R), rng.uniform(-.6, .6, R), np.full(R, -1.0)], 1).astype(F)
+    d = (d / np.linalg.norm(d, axis=-1, keepdims=True)).astype(F)
+    light = [3.0, 1.0, 0.4, 0.8] if "point" in ic["textures"] else [0.9, 0.1, 0.12]
+    prm = np.asarray([list(rng.uniform(0.3, 1.0, p - len(light))) + light], F)
+    t = np.tile(np.asarray([[0.1, 5.0]], F), (R, 1))
+    cone = rng.uniform(0.01, 0.05, (R, 1)).astype(F)
+    r.density_scale = 3.0
+    got = r(tf.constant(o[None]), tf.constant(d[None]), tf.constant(t[None]), tf.constant(prm), tf.constant(cone[None]),
+            composite_bkgd=True, training=False)
+    rec = r.instancer.last                                            # the C++ instancer's records of the one chunk
+    tup = (rec["rays_d"], rec["pts"], rec["t"], rec["dist"], rec["color"], rec["density"], rec["density_weight"], rec["instance_id"],
+           np.nonzero(rec["hit"])[0], rec["parameters"])
+    c, a = O.instance_evaluate_model(oracles["model"], tup, R, cone_scale=cone, blur_idx=rc.get("blur_idx"), patch_scale=ic["patch_scale"],
+                                     density_scale=3.0, density_reweighting=rc.get("density_reweighting", True), composite_bkgd=True,
+                                     net_chunk=rc["net_chunk"])
+    assert np.abs(got["color_pred"].numpy()[0] - c).max() <= 3e-5 and np.abs(got["alpha_pred"].numpy()[0] - a).max() <= 3e-5
+    assert rec["hit"].sum() > R // 2 and (a > 0.2).any()
