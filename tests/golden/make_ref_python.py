@@ -94,6 +94,42 @@ def main():
     po, pd, pt, pc = ray_sampler.Proxy(H, W, focal, proxy.AABB([-1.0, -1.2, -0.5], [1.0, 0.8, 0.7]))(tf.constant(loc), tf.constant(c2w))
     out.update(d_loc=loc, d_c2w=c2w, d_o=po.numpy(), d_d=pd.numpy(), d_t=pt.numpy(), d_cone=pc.numpy())
 
+    # ---- (e) MipRenderer [2,2] (n_pos = 6, IntegratedPositionalEncoding), perturb, blur parameter 1, background
+    ome = oracle_model((2, 2), 141, n_pos=6)
+    ipe = util.EasyDict({"module": "network.layer.IntegratedPositionalEncoding", "n_freq_bands": 10})
+    ke = model.ParamNerf(ipe, RP.ff(util, 4), RP.ff(util, 4), n_parameters=[2, 2], n_pos=6)["model"]
+    RP.set_weights(ke, ome)
+    Re, Se = 40, 24
+    oe = np.tile(np.asarray([[0.0, 0.3, 5.0]], F), (Re, 1))
+    de = rng.uniform(-1, 1, (Re, 3)).astype(F) - oe
+    de = (de / np.linalg.norm(de, axis=1, keepdims=True)).astype(F)
+    te = np.stack([rng.uniform(3.0, 4.0, Re), rng.uniform(5.5, 7.0, Re)], -1).astype(F)
+    conee = rng.uniform(0.001, 0.01, (Re, 1)).astype(F)
+    prm_e = rng.uniform(0.2, 1.0, (1, 5)).astype(F)
+    re_ = renderer.MipRenderer(model=ke, n_samples=Se, perturb=True, blur_idx=1)
+    tf.random.seed(142)
+    gote = re_(tf.constant(oe[None]), tf.constant(de[None]), tf.constant(te[None]), tf.constant(prm_e), tf.constant(conee[None]),
+               composite_bkgd=True, training=True)
+    out.update(e_o=oe, e_d=de, e_t=te, e_cone=conee, e_params=prm_e, e_z_rand=tf.random.log[0][1],
+               e_color_pred=gote["color_pred"].numpy()[0], e_alpha_pred=gote["alpha_pred"].numpy()[0])
+
+    # ---- (f) the grass_filtered training renderer (config values: S = 256, blur_idx 0, raw_noise_std 0.1), single net [2,3]
+    omg = oracle_model((2, 3), 151)
+    kg = RP.build_param_nerf(model, util, omg)
+    Rg, Sg = 24, 256
+    og = np.tile(np.asarray([[0.0, 0.3, 5.0]], F), (Rg, 1))
+    dg = rng.uniform(-1, 1, (Rg, 3)).astype(F) - og
+    dg = (dg / np.linalg.norm(dg, axis=1, keepdims=True)).astype(F)
+    tg = np.stack([rng.uniform(3.0, 4.0, Rg), rng.uniform(5.5, 7.0, Rg)], -1).astype(F)
+    coneg = rng.uniform(0.001, 0.01, (Rg, 1)).astype(F)
+    prm_g = rng.uniform(0.2, 1.0, (1, 5)).astype(F)
+    rg = renderer.Renderer(model=kg, n_samples=Sg, perturb=True, raw_noise_std=0.1, blur_idx=0, render_chunk=32768, net_chunk=65536)
+    tf.random.seed(152)
+    gotg = rg(tf.constant(og[None]), tf.constant(dg[None]), tf.constant(tg[None]), tf.constant(prm_g), tf.constant(coneg[None]),
+              composite_bkgd=True, training=True)
+    out.update(f_o=og, f_d=dg, f_t=tg, f_cone=coneg, f_params=prm_g, f_z_rand=tf.random.log[0][1], f_noise=tf.random.log[1][1] * F(0.1),
+               f_color_pred=gotg["color_pred"].numpy()[0], f_alpha_pred=gotg["alpha_pred"].numpy()[0])
+
     path = HERE / "ref_python_small.npz"
     np.savez_compressed(path, **out)
     print(path, path.stat().st_size, "bytes;", ", ".join(f"{k}{tuple(v.shape)}" for k, v in sorted(out.items())))

@@ -73,3 +73,17 @@ def test_proxy_rays():
     o, d, t, cone = O.proxy_rays(G["d_loc"], 13, 17, 21.0, G["d_c2w"], [-1.0, -1.2, -0.5], [1.0, 0.8, 0.7])
     assert np.array_equal(o, G["d_o"]) and np.array_equal(d, G["d_d"]) and np.array_equal(t, G["d_t"])
     assert np.abs(cone - G["d_cone"]).max() <= 4e-9
+
+
+def test_mip_renderer():
+    om = oracle_model((2, 2), 141, n_pos=6)
+    out, _ = O.mip_render_rays(om, G["e_o"], G["e_d"], G["e_t"], np.repeat(G["e_params"], 40, 0), G["e_cone"], 24, 1, perturb=True,
+                               z_rand=G["e_z_rand"], composite_bkgd=True)
+    assert np.abs(out["color_pred"] - G["e_color_pred"]).max() <= 2e-5 and np.abs(out["alpha_pred"] - G["e_alpha_pred"]).max() <= 2e-5
+
+
+def test_training_renderer_with_blur_and_noise():
+    om = oracle_model((2, 3), 151)
+    out = O.render_rays(om, None, G["f_o"], G["f_d"], G["f_t"], np.repeat(G["f_params"], 24, 0), G["f_cone"], 256, 0, True,
+                        z_rand=G["f_z_rand"], noise=G["f_noise"], blur_idx=0, composite_bkgd=True)
+    assert np.abs(out["color_pred"] - G["f_color_pred"]).max() <= 3e-5 and np.abs(out["alpha_pred"] - G["f_alpha_pred"]).max() <= 3e-5

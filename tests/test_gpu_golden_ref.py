@@ -128,3 +128,28 @@ def test_proxy_ray_sampler():
     assert np.array_equal(o.cpu().numpy(), G["d_o"]) and np.array_equal(d.cpu().numpy(), G["d_d"])
     assert np.array_equal(t.cpu().numpy(), G["d_t"])
     assert np.abs(cone.cpu().numpy() - G["d_cone"]).max() <= 1e-8
+
+
+def test_mip_renderer():
+    from nerf_tex_b200.model import FusedNerfTexMLP
+    from nerf_tex_b200.renderer import MipRenderer
+    om = O.ParamNerfOracle(n_parameters=(2, 2), n_pos=6, seed=141)
+    om.randomize_biases(142, 0.2)
+    gm = FusedNerfTexMLP(n_geo=2, n_app=2, n_pos=6)
+    gm.load_named_weights(om.named_weights())
+    r = MipRenderer(model=gm, n_samples=24, perturb=True, blur_idx=1)
+    got = r(cu(G["e_o"][None]), cu(G["e_d"][None]), cu(G["e_t"][None]), cu(G["e_params"]), cu(G["e_cone"][None]), composite_bkgd=True,
+            training=False, z_rand=cu(G["e_z_rand"]))
+    gc, ga = got["color_pred"][0].cpu().numpy(), got["alpha_pred"][0].cpu().numpy()
+    assert np.abs(gc - G["e_color_pred"]).max() <= 2e-3 and np.abs(ga - G["e_alpha_pred"]).max() <= 2e-3
+    assert psnr(gc, G["e_color_pred"]) >= 50 and psnr(ga, G["e_alpha_pred"]) >= 50
+
+
+def test_training_renderer_with_blur_and_noise():
+    from nerf_tex_b200.renderer import Renderer
+    r = Renderer(model=models((2, 3), 151), n_samples=256, perturb=True, raw_noise_std=0.1, blur_idx=0)
+    got = r(cu(G["f_o"][None]), cu(G["f_d"][None]), cu(G["f_t"][None]), cu(G["f_params"]), cu(G["f_cone"][None]), composite_bkgd=True,
+            training=False, z_rand=cu(G["f_z_rand"]), noise=cu(G["f_noise"]))
+    gc, ga = got["color_pred"][0].cpu().numpy(), got["alpha_pred"][0].cpu().numpy()
+    assert np.abs(gc - G["f_color_pred"]).max() <= 2e-3 and np.abs(ga - G["f_alpha_pred"]).max() <= 2e-3
+    assert psnr(gc, G["f_color_pred"]) >= 50 and psnr(ga, G["f_alpha_pred"]) >= 50
