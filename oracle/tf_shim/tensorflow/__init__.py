@@ -20,7 +20,9 @@ import contextlib
 
 import numpy as np
 
+from . import _autodiff as _ad
 from . import keras  # noqa: F401  (tensorflow.keras)
+from ._autodiff import GradientTape  # noqa: F401
 
 __version__ = "2.4.1-numpy-stand-in"
 
@@ -88,6 +90,8 @@ def _pair(a, b):
 class Tensor:
     __array_priority__ = 100
 
+    _node = None                                   # set by _autodiff.attach while a GradientTape records
+
     def __init__(self, a):
         self._a = np.asarray(a)
 
@@ -141,13 +145,40 @@ class Tensor:
         idx = tuple(int(i._a) if isinstance(i, Tensor) and i._a.ndim == 0 else (i._a if isinstance(i, Tensor) else i) for i in idx)
         idx = tuple(slice(*[None if v is None else int(_np(v)) for v in (i.start, i.stop, i.step)]) if isinstance(i, slice) else i
                     for i in idx)
-        return Tensor(self._a[idx])
+        out = Tensor(self._a[idx])
+        if _ad.recording(self):
+            shp, dt = self._a.shape, self._a.dtype
+
+            def vjp(g, idx=idx):
+                z = np.zeros(shp, dt)
+                np.add.at(z, idx, g)
+                return (z,)
+            _ad.attach(out, (self,), vjp)
+        return out
 
     # --- arithmetic (float32 stays float32; Python scalars adopt the tensor's dtype)
     def _bin(self, other, fn, swap=False):
-        x, y = _pair(other, self) if swap else _pair(self, other)
+        a_, b_ = (other, self) if swap else (self, other)
+        x, y = _pair(a_, b_)
         with np.errstate(all="ignore"):
-            return Tensor(fn(x, y))
+            out = Tensor(fn(x, y))
+        if _ad.recording(a_, b_):
+            xs, ys = np.shape(x), np.shape(y)
+            if fn is np.add:
+                vjp = lambda g: (_ad.unbroadcast(g, xs), _ad.unbroadcast(g, ys))
+            elif fn is np.subtract:
+                vjp = lambda g: (_ad.unbroadcast(g, xs), _ad.unbroadcast(-g, ys))
+            elif fn is np.multiply:
+                vjp = lambda g: (_ad.unbroadcast(g * y, xs), _ad.unbroadcast(g * x, ys))
+            elif fn is np.divide:
+                vjp = lambda g: (_ad.unbroadcast(g / y, xs), _ad.unbroadcast(-g * x / (y * y), ys))
+            elif fn is np.power and not _ad.tracked(b_):
+                vjp = lambda g: (_ad.unbroadcast(g * y * np.power(x, y - 1), xs), None)
+            else:
+                _ad.DROPPED.add(getattr(fn, "__name__", str(fn)))
+                return out
+            _ad.attach(out, (a_ if isinstance(a_, Tensor) else None, b_ if isinstance(b_, Tensor) else None), vjp)
+        return out
 
     def __add__(self, o): return self._bin(o, np.add)
     def __radd__(self, o): return self._bin(o, np.add, True)
@@ -160,7 +191,9 @@ class Tensor:
     def __pow__(self, o): return self._bin(o, np.power)
     def __rpow__(self, o): return self._bin(o, np.power, True)
     def __mod__(self, o): return self._bin(o, np.mod)
-    def __neg__(self): return Tensor(-self._a)
+    def __neg__(self):
+        out = Tensor(-self._a)
+        return _ad.attach(out, (self,), lambda g: (-g,)) if _ad.recording(self) else out
     def __abs__(self): return Tensor(np.abs(self._a))
     def __lt__(self, o): return self._bin(o, np.less)
     def __le__(self, o): return self._bin(o, np.less_equal)
@@ -190,7 +223,10 @@ convert_to_tensor = constant
 
 
 def cast(x, dtype):
-    return _t(_np(x).astype(dtype))
+    out = _t(_np(x).astype(dtype))
+    if _ad.recording(x) and np.issubdtype(dtype, np.floating):
+        _ad.attach(out, (x,), lambda g: (g,))
+    return out
 
 
 def zeros(shape, dtype=np.float32):
@@ -243,34 +279,54 @@ def rank(x):
 
 def reshape(x, shp):
     shp = [shp] if isinstance(shp, (int, np.integer)) else [int(_np(s)) for s in shp]
-    return _t(_np(x).reshape(shp))
+    out = _t(_np(x).reshape(shp))
+    if _ad.recording(x):
+        old = _np(x).shape
+        _ad.attach(out, (x,), lambda g: (g.reshape(old),))
+    return out
 
 
 def expand_dims(x, axis):
-    return _t(np.expand_dims(_np(x), axis))
+    out = _t(np.expand_dims(_np(x), axis))
+    if _ad.recording(x):
+        old = _np(x).shape
+        _ad.attach(out, (x,), lambda g: (g.reshape(old),))
+    return out
 
 
 def concat(values, axis):
-    return _t(np.concatenate([_np(v) for v in values], axis))
+    arrs = [_np(v) for v in values]
+    out = _t(np.concatenate(arrs, axis))
+    if _ad.recording(*values):
+        cuts = np.cumsum([a.shape[axis] for a in arrs])[:-1]
+        _ad.attach(out, tuple(v if isinstance(v, Tensor) else None for v in values), lambda g: tuple(np.split(g, cuts, axis)))
+    return out
 
 
 def stack(values, axis=0):
+    _ad.dropped("stack", *values)
     return _t(np.stack([_np(v) for v in values], axis))
 
 
 def repeat(x, repeats, axis=None):
+    _ad.dropped("repeat", x)
     return _t(np.repeat(_np(x), int(_np(repeats)), axis))
 
 
 def broadcast_to(x, shp):
-    return _t(np.broadcast_to(_np(x), [int(_np(s)) for s in shp]).copy())
+    out = _t(np.broadcast_to(_np(x), [int(_np(s)) for s in shp]).copy())
+    if _ad.recording(x):
+        old = _np(x).shape
+        _ad.attach(out, (x,), lambda g: (_ad.unbroadcast(g, old),))
+    return out
 
 
 def stop_gradient(x):
-    return x
+    return _t(_np(x)) if isinstance(x, Tensor) else x
 
 
 def sort(x, axis=-1, direction="ASCENDING"):
+    _ad.dropped("sort", x)
     a = np.sort(_np(x), axis=axis, kind="stable")
     return _t(a if direction == "ASCENDING" else np.flip(a, axis))
 
@@ -280,23 +336,37 @@ def where(condition, x=None, y=None):
     c = _np(condition)
     if x is None and y is None:
         return _t(np.argwhere(c).astype(np.int64))                 # [n, rank] coordinates, row-major order
+    _ad.dropped("where", x, y)
     a, b = _pair(x, y)
     return _t(np.where(c, a, b))
 
 
 def gather_nd(params, indices):
     p, i = _np(params), _np(indices)
-    return _t(p[tuple(i[..., k] for k in np.arange(i.shape[-1]))])
+    key = tuple(i[..., k] for k in np.arange(i.shape[-1]))
+    out = _t(p[key])
+    if _ad.recording(params):
+        def vjp(g):
+            z = np.zeros(p.shape, p.dtype)
+            np.add.at(z, key, g)
+            return (z,)
+        _ad.attach(out, (params,), vjp)
+    return out
 
 
 def scatter_nd(indices, updates, shape):  # noqa: A002
     i, u = _np(indices), _np(updates)
     out = np.zeros([int(_np(s)) for s in shape], u.dtype)
-    np.add.at(out, tuple(i[..., k] for k in np.arange(i.shape[-1])), u)     # duplicates add up, like tf.scatter_nd
-    return _t(out)
+    key = tuple(i[..., k] for k in np.arange(i.shape[-1]))
+    np.add.at(out, key, u)                                             # duplicates add up, like tf.scatter_nd
+    out = _t(out)
+    if _ad.recording(updates):
+        _ad.attach(out, (updates,), lambda g: (g[key],))
+    return out
 
 
 def gather(params, indices, axis=None, batch_dims=0):
+    _ad.dropped("gather", params)
     p, i = _np(params), _np(indices)
     if batch_dims == 0:
         return _t(np.take(p, i, axis=0 if axis is None else axis))
@@ -309,6 +379,7 @@ def gather(params, indices, axis=None, batch_dims=0):
 
 
 def searchsorted(sorted_sequence, values, side="left"):
+    _ad.dropped("searchsorted", sorted_sequence, values)
     s, v = _np(sorted_sequence), _np(values)
     fs, fv = s.reshape(-1, s.shape[-1]), v.reshape(-1, v.shape[-1])
     out = np.stack([np.searchsorted(fs[r], fv[r], side=side) for r in np.arange(fs.shape[0])]) if fs.shape[0] else np.zeros(fv.shape, np.int64)
@@ -328,10 +399,14 @@ def _seq_reduce(a, axis, fn):
 def reduce_sum(x, axis=None, keepdims=False):
     a = _np(x)
     if axis is None:
-        return _t(a.sum(dtype=a.dtype))
+        out = _t(a.sum(dtype=a.dtype))
+        return _ad.attach(out, (x,), lambda g: (np.broadcast_to(g, a.shape),)) if _ad.recording(x) else out
     axis = axis % a.ndim
     r = _seq_reduce(a, axis, np.add) if a.shape[axis] > 0 else np.zeros(np.delete(a.shape, axis), a.dtype)
-    return _t(np.expand_dims(r, axis) if keepdims else r)
+    out = _t(np.expand_dims(r, axis) if keepdims else r)
+    if _ad.recording(x):
+        _ad.attach(out, (x,), lambda g: (np.broadcast_to(g if keepdims else np.expand_dims(g, axis), a.shape),))
+    return out
 
 
 def reduce_prod(x, axis=None, keepdims=False):
@@ -340,7 +415,11 @@ def reduce_prod(x, axis=None, keepdims=False):
 
 def reduce_mean(x, axis=None, keepdims=False):
     a = _np(x)
-    return _t(a.mean(axis=axis, keepdims=keepdims, dtype=a.dtype))
+    out = _t(a.mean(axis=axis, keepdims=keepdims, dtype=a.dtype))
+    if _ad.recording(x):
+        assert axis is None, "stand-in: gradient of reduce_mean over all axes only"
+        _ad.attach(out, (x,), lambda g: (np.broadcast_to(g / a.dtype.type(a.size), a.shape),))
+    return out
 
 
 def reduce_max(x, axis=None, keepdims=False):
@@ -356,6 +435,7 @@ def reduce_any(x, axis=None, keepdims=False):
 
 
 def cumsum(x, axis=0, exclusive=False, reverse=False):
+    _ad.dropped("cumsum", x)
     a = _np(x)
     assert not reverse
     a = np.moveaxis(a, axis, 0)
@@ -384,7 +464,18 @@ def _cumprod(x, axis=0, exclusive=False, reverse=False):
         else:
             acc = (acc * a[k]).astype(a.dtype)
             out[k] = acc
-    return _t(np.moveaxis(out, 0, axis))
+    res = _t(np.moveaxis(out, 0, axis))
+    if _ad.recording(x):
+        assert exclusive, "stand-in: gradient of the exclusive cumprod only"
+
+        def vjp(g):
+            # y_k = prod_{j<k} x_j  =>  dL/dx_j = sum_{k>j} g_k y_k / x_j   (x = 1 - alpha + 1e-10 > 0 on this path)
+            gy = np.moveaxis(g, axis, 0) * out
+            suffix = np.cumsum(gy[::-1], axis=0)[::-1]
+            excl = np.concatenate([suffix[1:], np.zeros_like(suffix[:1])], 0)
+            return (np.moveaxis((excl / a).astype(a.dtype), 0, axis),)
+        _ad.attach(res, (x,), vjp)
+    return res
 
 
 def tensordot(a, b, axes):
@@ -421,11 +512,23 @@ def _unary64(fn):
     return op
 
 
-exp = _unary64(np.exp)
+def exp(x, name=None):
+    a = _np(x)
+    with np.errstate(all="ignore"):
+        y = np.exp(a.astype(np.float64)).astype(a.dtype if a.dtype.kind == "f" else np.float32)
+    out = _t(y)
+    return _ad.attach(out, (x,), lambda g: (g * y,)) if _ad.recording(x) else out
+
+
 sin = _unary64(np.sin)
 cos = _unary64(np.cos)
 atan = _unary64(np.arctan)
-abs = _unary(np.abs)  # noqa: A001
+def abs(x, name=None):  # noqa: A001
+    a = _np(x)
+    out = _t(np.abs(a))
+    return _ad.attach(out, (x,), lambda g: (g * np.sign(a),)) if _ad.recording(x) else out
+
+
 sqrt = _unary(np.sqrt)
 floor = _unary(np.floor)
 
@@ -433,14 +536,18 @@ floor = _unary(np.floor)
 def _sigmoid(x):
     a = _np(x)
     with np.errstate(all="ignore"):
-        return _t((1.0 / (1.0 + np.exp(-a.astype(np.float64)))).astype(a.dtype))
+        y = (1.0 / (1.0 + np.exp(-a.astype(np.float64)))).astype(a.dtype)
+    out = _t(y)
+    return _ad.attach(out, (x,), lambda g: (g * y * (1 - y),)) if _ad.recording(x) else out
 
 
 def maximum(x, y):
+    _ad.dropped("maximum", x, y)
     return _t(np.maximum(*_pair(x, y)))
 
 
 def minimum(x, y):
+    _ad.dropped("minimum", x, y)
     return _t(np.minimum(*_pair(x, y)))
 
 
@@ -457,7 +564,11 @@ class math:
     def squared_difference(x, y):
         a, b = _pair(x, y)
         d = a - b
-        return _t(d * d)
+        out = _t(d * d)
+        if _ad.recording(x, y):
+            _ad.attach(out, (x if isinstance(x, Tensor) else None, y if isinstance(y, Tensor) else None),
+                       lambda g: (_ad.unbroadcast(2 * g * d, np.shape(a)), _ad.unbroadcast(-2 * g * d, np.shape(b))))
+        return out
 
     @staticmethod
     def mod(x, y):
@@ -468,13 +579,16 @@ class nn:
     @staticmethod
     def relu(x):
         a = _np(x)
-        return _t(np.maximum(a, a.dtype.type(0)))
+        out = _t(np.maximum(a, a.dtype.type(0)))
+        return _ad.attach(out, (x,), lambda g: (g * (a > 0),)) if _ad.recording(x) else out
 
     @staticmethod
     def elu(x):
         a = _np(x)
         with np.errstate(all="ignore"):
-            return _t(np.where(a > 0, a, np.expm1(a.astype(np.float64)).astype(a.dtype)))
+            e = np.expm1(a.astype(np.float64)).astype(a.dtype)
+        out = _t(np.where(a > 0, a, e))
+        return _ad.attach(out, (x,), lambda g: (g * np.where(a > 0, a.dtype.type(1), e + 1),)) if _ad.recording(x) else out
 
     @staticmethod
     def depthwise_conv2d(input, filter, strides, padding, **kwargs):  # noqa: A002
@@ -499,6 +613,7 @@ class nn:
 class linalg:
     @staticmethod
     def norm(x, axis=None, keepdims=False):
+        _ad.dropped("norm", x)
         a = _np(x)
         sq = reduce_sum(_t(a * a), axis=axis, keepdims=keepdims)._a
         return _t(np.sqrt(sq).astype(a.dtype))
@@ -575,7 +690,24 @@ concat = keras.layers.symbolic_op(concat)
 
 
 class Variable(Tensor):
-    pass
+    """A trainable leaf: always tracked while a tape records."""
+    _node = _ad.LEAF
+
+    def __init__(self, initial_value, dtype=None, trainable=True, name=None):
+        super().__init__(np.array(_np(initial_value), dtype=dtype))
+        self.name = name
+
+    def assign(self, value):
+        self._a = np.array(_np(value), dtype=self._a.dtype).reshape(self._a.shape)
+        return self
+
+    def assign_sub(self, value):
+        self._a = (self._a - _np(value)).astype(self._a.dtype)
+        return self
+
+    def assign_add(self, value):
+        self._a = (self._a + _np(value)).astype(self._a.dtype)
+        return self
 
 
 class data:

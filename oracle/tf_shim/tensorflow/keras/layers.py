@@ -8,13 +8,28 @@ _ALL_LAYERS = []          # creation order
 
 
 class KerasTensor:
-    """A symbolic tensor of the functional API: a thunk over the Input placeholders."""
+    """A symbolic tensor of the functional API: a thunk over the Input placeholders.  `dummy` is the op applied to one
+    all-zero row (shape inference the way Keras builds layers when the graph is written: Dense creates its variables
+    here, so that model.trainable_variables exists before the first real call, network/train.py:33-34)."""
 
-    def __init__(self, fn, name=None, shape=None, parents=(), layer=None):
+    def __init__(self, fn, name=None, shape=None, parents=(), layer=None, dummy=None):
         self.fn, self.name, self._shape, self.parents, self.layer = fn, name, shape, tuple(parents), layer
+        if dummy is None and fn is None:                              # an Input placeholder
+            import tensorflow as tf
+            last = 0 if (shape is None or shape[-1] is None) else int(shape[-1])
+            dummy = tf.Tensor(np.zeros((1, last), np.float32))
+        self.dummy = dummy
 
     def __getitem__(self, idx):
-        return KerasTensor(lambda env, cache: resolve(self, env, cache)[idx], parents=[self])
+        return KerasTensor(lambda env, cache: resolve(self, env, cache)[idx], parents=[self], dummy=self.dummy[idx])
+
+
+def dummies(x):
+    if isinstance(x, KerasTensor):
+        return x.dummy
+    if isinstance(x, (list, tuple)):
+        return type(x)(dummies(v) for v in x)
+    return x
 
 
 def is_symbolic(x):
@@ -62,7 +77,7 @@ def symbolic_op(fn):
         if is_symbolic(args) or is_symbolic(list(kwargs.values())):
             parents = [a for a in _flatten(args) if isinstance(a, KerasTensor)]
             return KerasTensor(lambda env, cache: fn(*resolve(list(args), env, cache), **{k: resolve(v, env, cache) for k, v in kwargs.items()}),
-                               parents=parents)
+                               parents=parents, dummy=fn(*dummies(list(args)), **{k: dummies(v) for k, v in kwargs.items()}))
         return fn(*args, **kwargs)
     return op
 
@@ -91,7 +106,8 @@ class Layer:
     def __call__(self, inputs, *args, **kwargs):
         if is_symbolic(inputs):
             parents = [a for a in _flatten([inputs]) if isinstance(a, KerasTensor)]
-            return KerasTensor(lambda env, cache: self.call(resolve(inputs, env, cache)), parents=parents, layer=self)
+            return KerasTensor(lambda env, cache: self.call(resolve(inputs, env, cache)), parents=parents, layer=self,
+                               dummy=self.call(dummies(inputs)))
         return self.call(inputs)
 
 
@@ -104,10 +120,16 @@ class Dense(Layer):
         self.kernel = self.bias = None
 
     def set_weights(self, weights):
-        self.kernel, self.bias = np.asarray(weights[0], np.float32), np.asarray(weights[1], np.float32)
+        import tensorflow as tf
+        if self.kernel is not None:                                   # in place: optimizers and checkpoints hold the objects
+            self.kernel.assign(weights[0])
+            self.bias.assign(weights[1])
+            return
+        self.kernel = tf.Variable(np.asarray(weights[0], np.float32), name=f"{self.name}/kernel")
+        self.bias = tf.Variable(np.asarray(weights[1], np.float32), name=f"{self.name}/bias")
 
     def get_weights(self):
-        return [self.kernel, self.bias]
+        return [self.kernel.numpy(), self.bias.numpy()]
 
     @property
     def trainable_variables(self):
@@ -115,20 +137,32 @@ class Dense(Layer):
 
     def call(self, inputs):
         import tensorflow as tf
+        from tensorflow import _autodiff as ad
         x = np.asarray(inputs.numpy(), np.float32)
         if self.kernel is None:
             lim = np.sqrt(6.0 / (x.shape[-1] + self.units))
-            self.kernel = np.random.default_rng(self._creation_index).uniform(-lim, lim, (x.shape[-1], self.units)).astype(np.float32)
-            self.bias = np.zeros(self.units, np.float32)
-        assert self.kernel.shape[0] == x.shape[-1], (self.kernel.shape, x.shape)
+            self.set_weights([np.random.default_rng(self._creation_index).uniform(-lim, lim, (x.shape[-1], self.units)),
+                              np.zeros(self.units)])
+        W, b = self.kernel.numpy(), self.bias.numpy()
+        assert W.shape[0] == x.shape[-1], (W.shape, x.shape)
         # fp32 inputs and weights, products accumulated in float64 and rounded once: the reference arithmetic the parity
         # bars are written against is "fp32 Dense", whose summation order inside the GEMM is TensorFlow's own business
-        y = (x.astype(np.float64) @ self.kernel.astype(np.float64) + self.bias.astype(np.float64)).astype(np.float32)
+        y = (x.astype(np.float64) @ W.astype(np.float64) + b.astype(np.float64)).astype(np.float32)
         if self.activation == "relu":
             y = np.maximum(y, np.float32(0))
         elif self.activation is not None:
             raise NotImplementedError(self.activation)
-        return tf.Tensor(y)
+        out = tf.Tensor(y)
+        if ad.recording(inputs, self.kernel, self.bias):
+            relu = self.activation == "relu"
+
+            def vjp(g):
+                g = (g * (y > 0)) if relu else g
+                g64 = g.astype(np.float64)
+                gx = (g64 @ W.astype(np.float64).T).astype(np.float32) if ad.tracked(inputs) else None
+                return gx, (x.astype(np.float64).T @ g64).astype(np.float32), g64.sum(0).astype(np.float32)
+            ad.attach(out, (inputs, self.kernel, self.bias), vjp)
+        return out
 
 
 class LeakyReLU(Layer):

@@ -3,8 +3,10 @@ renderer.py, model.py, layer.py, loss.py, ray_sampler.py, proxy.py imported from
 NumPy stand-in for the TensorFlow ops they call (oracle/tf_shim: our code; it restates the documented semantics of each
 op in fp32).  What this pins is the reference's LOGIC as written — which tensors are sliced, concatenated, gathered,
 scattered, in which order; chunking; culling of rays with t = inf; the `det=self.perturb` inversion; `weights[..., 1:-1]`;
-the blur scaling; the instanced renderer's masking and last-sample handling; the mip cone gaussians — not TensorFlow's
-kernels (TensorFlow 2.4 cannot run here).  Random draws are taken from the stand-in's log and handed to the oracle.
+the blur scaling; the instanced renderer's masking and last-sample handling; the mip cone gaussians; the training
+loop of network/train.py (tape, AlphaLoss, Adam with its decayed rate); every shipped config through the reference's own
+util.instantiate — not TensorFlow's kernels (TensorFlow 2.4 cannot run here).  Random draws are taken from the
+stand-in's log and handed to the oracle.
 
 CPU only; needs /root/reference (skipped elsewhere; tests/golden/ref_python_small.npz carries vectors made by the same
 runs for machines without it, see tests/golden/make_ref_python.py)."""
@@ -436,3 +438,110 @@ def test_shipped_config_through_the_references_own_classes(ref, name, tmp_path, 
                                      net_chunk=rc["net_chunk"])
     assert np.abs(got["color_pred"].numpy()[0] - c).max() <= 3e-5 and np.abs(got["alpha_pred"].numpy()[0] - a).max() <= 3e-5
     assert rec["hit"].sum() > R // 2 and (a > 0.2).any()
+
+
+# ------------------------------------------------------------------------------------------------ the training step
+@pytest.mark.parametrize("cfg", ["grass_filtered", "coarse_fine"])
+def test_train_loop(ref, cfg, tmp_path, monkeypatch):
+    """network/train.py::Train, UNMODIFIED, for three iterations — its GradientTape over the renderer and AlphaLoss, its
+    Adam with its ExponentialDecay — with stand-ins only for the tf.data dataset and the logger (tests/ref_train_stubs.py).
+    Replica on our side: float64 autograd of the oracle graph (tests/torch_ref.py) + oracle.adam_step with
+    oracle.exponential_decay_lr.  (The stand-in differentiates in fp32 with rules of its own, oracle/tf_shim/
+    tensorflow/_autodiff.py, and implements Keras' documented Adam: what is pinned is the reference's use of them.)"""
+    import torch
+    import torch_ref as T
+    import ref_train_stubs as stubs
+    tf, renderer, model, loss, ray_sampler, proxy, util = ref
+    from network import train as ref_train
+    npar = (2, 3)
+    fine = cfg == "coarse_fine"
+    names = ["model", "model_fine"] if fine else ["model"]
+    oms = {n: O.ParamNerfOracle(n_parameters=npar, seed=201 + i) for i, n in enumerate(names)}
+    for i, om in enumerate(oms.values()):
+        om.randomize_biases(211 + i, 0.1)
+    R, S, N, iters, lrate, decay = 20, 16, (24 if fine else 0), 3, 5e-4, 0.002      # decay_steps = 2: the schedule moves in 3 steps
+    rng = np.random.default_rng(221)
+    batches = []
+    for _ in range(iters):
+        o, d, t, cone = rays(R, int(rng.integers(1 << 30)))
+        batches.append(dict(rays_o=o, rays_d=d, t=t, cone_scale=cone, parameters=rng.uniform(0.2, 1.0, (1, 5)).astype(F),
+                            color=rng.uniform(0, 1, (1, R, 3)).astype(F), alpha=(rng.uniform(0, 1, (1, R)) * (rng.uniform(size=(1, R)) > .3)).astype(F)))
+    ffc = lambda n: {"module": "network.layer.FourierFeatures", "n_freq_bands": n}
+    pn = {"module": "network.model.ParamNerf", "pos_embedding": ffc(10), "dir_embedding": ffc(4), "param_embedding": ffc(4),
+          "n_parameters": list(npar)}
+    model_config = {"module": "network.model.CoarseFine", "model_config": pn} if fine else pn
+    renderer_config = {"module": "network.renderer.Renderer", "n_samples": S, "n_importance": N, "perturb": True,
+                       "raw_noise_std": 0.0 if fine else 0.1, "blur_idx": None if fine else 0}
+    tf.random.seed(231)
+    tf._autodiff.DROPPED.clear()
+    # listen at the optimizer (the stand-in's class, not the reference's code): gradients and weights of every step
+    steps = []
+    Adam = tf.keras.optimizers.Adam
+    orig_apply = Adam.apply_gradients
+
+    def spy(self, grads_and_vars):
+        gv = list(grads_and_vars)
+        steps.append({"lr": self._lr(), "grads": [None if g is None else g.numpy().copy() for g, _ in gv],
+                      "before": [v.numpy().copy() for _, v in gv]})
+        orig_apply(self, gv)
+        steps[-1]["after"] = [v.numpy().copy() for _, v in gv]
+    monkeypatch.setattr(Adam, "apply_gradients", spy)
+    ref_train.Train(target_path=str(tmp_path),
+                    train_dataset_config=util.EasyDict({"module": "ref_train_stubs.Batches", "n_parameters": list(npar), "composite_bkgd": True,
+                                                        "bkgd_color": [1., 1., 1.],
+                                                        "batches": [{k: tf.constant(v) for k, v in b.items()} for b in batches]}),
+                    val_dataset_config=util.EasyDict({"module": "ref_train_stubs.Batches"}),
+                    model_config=util.EasyDict(model_config),
+                    loss_config=util.EasyDict({"module": "network.loss.AlphaLoss", "loss_fn": "network.loss.smape", "alpha_loss_fn": "network.loss.mse"}),
+                    n_iters=iters, lrate=lrate, lrate_decay=decay, renderer_config=util.EasyDict(renderer_config),
+                    logger_config=util.EasyDict({"module": "ref_train_stubs.Logger",
+                                                 "initial": {n: [(W, b) for _, W, b in om.layers] for n, om in oms.items()}}))
+    logger = stubs.LAST["logger"]
+    assert len(logger.losses) == iters == len(steps)
+    # operations that saw a tracked tensor without a differentiation rule: only what lies behind tf.stop_gradient
+    assert tf._autodiff.DROPPED <= {"cumsum", "stack", "gather", "searchsorted", "where", "maximum", "minimum", "sort"}, tf._autodiff.DROPPED
+    # one optimizer over the variables of all models, in model order, kernel before bias (train.py:33-34)
+    n_vars = sum(2 * len(om.layers) for om in oms.values())
+    assert all(len(st["grads"]) == n_vars for st in steps)
+    log = list(tf.random.log)
+    t64 = lambda a: torch.as_tensor(np.asarray(a), dtype=torch.float64)
+    mom = [(np.zeros_like(w), np.zeros_like(w)) for w in steps[0]["before"]]
+    for step, (b, st) in enumerate(zip(batches, steps)):
+        # ---- the reference's weights of this step into the float64 twin, its draws, the same graph
+        for n, om in oms.items():
+            k0 = sum(2 * len(oms[m].layers) for m in names[:names.index(n)])
+            om.layers = [(name, st["before"][k0 + 2 * j], st["before"][k0 + 2 * j + 1]) for j, (name, _, _) in enumerate(om.layers)]
+        P = {n: T.make_params(om) for n, om in oms.items()}
+        z_rand = log.pop(0)[1]
+        noise = None if fine else log.pop(0)[1] * F(0.1)
+        o, d, t, cone = b["rays_o"][0], b["rays_d"][0], b["t"][0], b["cone_scale"][0]
+        prm = np.repeat(b["parameters"], R, 0)
+        z = t64(O.stratified_z(t, S, True, z_rand))
+        C, A, W_c = T.network_pass(oms["model"], P["model"], t64(o), t64(d), z, t64(prm), t64(cone), None if fine else 0,
+                                   composite_bkgd=True, noise=None if noise is None else t64(noise))
+        if fine:                                                      # det=self.perturb=True: deterministic resampling of the coarse weights
+            z_all, _ = O.hierarchical_z(z.numpy().astype(F), W_c.detach().numpy().astype(F), N, True)
+            Cf, Af, _ = T.network_pass(oms["model_fine"], P["model_fine"], t64(o), t64(d), t64(z_all), t64(prm), t64(cone), None, composite_bkgd=True)
+            L = T.alpha_loss(t64(b["color"][0]), t64(b["alpha"][0]), Cf, Af, C, A)
+        else:
+            L = T.alpha_loss(t64(b["color"][0]), t64(b["alpha"][0]), C, A)
+        assert abs(logger.losses[step] - float(L.detach())) <= 2e-4 * max(abs(float(L.detach())), 1e-3)
+        leaves = [x for n in names for pair in P[n].values() for x in pair]
+        want = torch.autograd.grad(L, leaves, allow_unused=True)
+        # ---- the tape's gradients (fp32, the stand-in's rules) against float64 autograd of the oracle graph
+        flat_g = np.concatenate([np.zeros(w.size) if g is None else g.astype(np.float64).ravel() for g, w in zip(st["grads"], st["before"])])
+        flat_w = np.concatenate([np.zeros(x.numel()) if g is None else g.numpy().ravel() for g, x in zip(want, leaves)])
+        cos = float(flat_g @ flat_w / (np.linalg.norm(flat_g) * np.linalg.norm(flat_w)))
+        rel = float(np.linalg.norm(flat_g - flat_w) / np.linalg.norm(flat_w))
+        # (coarse + fine: the fine samples sit behind the resampling of fp32 against float64 coarse weights, which moves
+        # a few of them: the bars of the GPU gradient tests apply there)
+        assert (cos >= 0.9999 and rel <= 2e-2) if fine else (cos >= 0.99999 and rel <= 2e-3), (step, cos, rel)
+        # ---- the update: Adam as Keras documents it with the decayed rate, from the gradients the tape produced
+        assert abs(st["lr"] - O.exponential_decay_lr(lrate, decay, step)) <= 1e-9
+        for j, (g, w0, w1) in enumerate(zip(st["grads"], st["before"], st["after"])):
+            p_new, m_new, v_new = O.adam_step(w0, g, mom[j][0], mom[j][1], step + 1, st["lr"])
+            mom[j] = (m_new, v_new)
+            assert np.abs(p_new - w1).max() <= 2e-8 + 1e-6 * lrate, (step, j, np.abs(p_new - w1).max())
+            if step == 0:                                             # Adam's first step moves every weight by ~lr
+                assert np.abs(w1 - w0).max() > 0.5 * st["lr"], j
+    assert not log
