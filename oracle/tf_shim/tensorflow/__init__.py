@@ -191,6 +191,8 @@ class Tensor:
     def __pow__(self, o): return self._bin(o, np.power)
     def __rpow__(self, o): return self._bin(o, np.power, True)
     def __mod__(self, o): return self._bin(o, np.mod)
+    def __floordiv__(self, o): return self._bin(o, np.floor_divide)
+    def __rfloordiv__(self, o): return self._bin(o, np.floor_divide, True)
     def __neg__(self):
         out = Tensor(-self._a)
         return _ad.attach(out, (self,), lambda g: (-g,)) if _ad.recording(self) else out
@@ -631,6 +633,19 @@ class linalg:
         return _t(np.cross(x, y).astype(np.float32))
 
 
+class image:
+    @staticmethod
+    def resize(images, size, method="bilinear", **kwargs):
+        """'nearest' only, as TF 2 documents it (half-pixel centres): source = min(floor((i + 0.5) * in / out), in - 1)."""
+        assert method == "nearest"
+        a = _np(images)
+        n, H, W, C = a.shape
+        oh, ow = int(size[0]), int(size[1])
+        ys = np.minimum(np.floor((np.arange(oh) + 0.5) * (H / oh)).astype(np.int64), H - 1)
+        xs = np.minimum(np.floor((np.arange(ow) + 0.5) * (W / ow)).astype(np.int64), W - 1)
+        return _t(a[:, ys][:, :, xs])
+
+
 class bitwise:
     @staticmethod
     def right_shift(x, y):
@@ -670,6 +685,12 @@ class _Random:
             a = (self.rng.random(size=shape, dtype=np.float32) * np.float32(hi - minval) + np.float32(minval)).astype(np.float32)
         self.log.append(("uniform", a))
         return _t(a)
+
+    def shuffle(self, value):
+        a = _np(value)
+        perm = self.rng.permutation(a.shape[0])
+        self.log.append(("shuffle", perm))
+        return _t(a[perm])
 
     def normal(self, shape, mean=0.0, stddev=1.0, dtype=np.float32):  # noqa: A002
         a = (self.rng.standard_normal(size=[int(_np(s)) for s in shape], dtype=np.float32) * np.float32(stddev) + np.float32(mean)).astype(np.float32)

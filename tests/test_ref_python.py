@@ -545,3 +545,30 @@ def test_train_loop(ref, cfg, tmp_path, monkeypatch):
             if step == 0:                                             # Adam's first step moves every weight by ~lr
                 assert np.abs(w1 - w0).max() > 0.5 * st["lr"], j
     assert not log
+
+
+def test_pixel_samplers(ref):
+    """network/pixel_sampler.py: Full (every pixel, row-major), Independent (iid, in range), Proxy (pixels whose rays hit
+    the proxy on a grid `downsample_factor` coarser — focal // factor as written — upsampled with 'nearest', shuffled)."""
+    tf, renderer, model, loss, ray_sampler, proxy, util = ref
+    from network import pixel_sampler as ps
+    H, W, focal, factor = 48, 64, 70.0, 8
+    full = ps.Full(H, W)().numpy()
+    assert np.array_equal(full, np.stack(np.meshgrid(np.arange(H), np.arange(W), indexing="ij"), -1).reshape(-1, 2))
+    ind = ps.Independent(H, W, 500)().numpy()
+    assert ind.shape == (500, 2) and ind[:, 0].max() < H and ind[:, 1].max() < W and ind.min() >= 0
+    b0, b1 = [-0.6, -0.5, -0.4], [0.5, 0.6, 0.4]
+    c2w = np.asarray([[np.cos(.4), 0, np.sin(.4), 1.2], [0, 1, 0, 0.1], [-np.sin(.4), 0, np.cos(.4), 2.6], [0, 0, 0, 1]], F)
+    # the oracle's mask: coarse grid through rays_from_camera + AABB, half-pixel-centre nearest upsampling
+    hd, wd = H // factor, W // factor
+    ii, jj = np.meshgrid(np.arange(hd), np.arange(wd), indexing="ij")
+    o, d, _ = O.rays_from_camera(np.stack([ii.reshape(-1), jj.reshape(-1)], -1).astype(F), hd, wd, focal // factor, c2w)
+    hit = (O.aabb_intersect(b0, b1, o, d)[:, 0] != np.inf).reshape(hd, wd)
+    ys = np.minimum(np.floor((np.arange(H) + 0.5) * (hd / H)).astype(int), hd - 1)
+    xs = np.minimum(np.floor((np.arange(W) + 0.5) * (wd / W)).astype(int), wd - 1)
+    want = np.argwhere(hit[ys][:, xs])
+    assert 0.05 < hit.mean() < 0.95
+    tf.random.seed(61)
+    got = ps.Proxy(H, W, want.shape[0], proxy.AABB(b0, b1), focal, downsample_factor=factor)(tf.constant(c2w)).numpy()
+    perm = tf.random.log[-1][1]
+    assert np.array_equal(got, want[perm])                            # all hit pixels, in the drawn order
