@@ -8,16 +8,20 @@ configs/config_carpet_render.py:76-99 (n_samples 1024, step 0.002, patch_scale 0
 hit ray ~ LogNormal(ln 120, 0.6)).  A "step" is one frame: per render chunk one fused
 encoding+MLP launch (K1) and one compositing launch (K2).
 
-  value : rays/s, whole job, instancer records resident in HBM when the timed region starts.
-  e2e   : rays/s through the same plugin call (InstanceRenderer.__call__) with HOST buffers:
-          rays and per-chunk instancer records are copied from pinned host memory inside the timed
-          region and the rendered colour/alpha are read back.
+  value : rays/s, whole job, instancer records resident in HBM when the timed region starts.  For N > 1 the SAME
+          frame is split over the ranks (round-robin stripes of 256 rays, sharded.render_sharded) with the final
+          all-gather of the per-ray outputs inside the timed region ("scaling": "strong").
+  e2e   : rays/s through the call a user makes for a render with the device instancer: camera pose + parameter vector
+          in from the host (92 B), Proxy ray sampler -> InstanceRenderer(Instancer(1 500-patch carpet)) -> finish_image,
+          finished 8-bit RGBA frame out to pinned host memory (2.56 MB), every frame; sharded the same way for N > 1.
+          (Round 1's arm — host-side instancer records copied per chunk — is kept at N = 1 as `e2e_host_records`.)
   --impl reference : the reference's CPU implementation of the same path.  The reference's
-          TensorFlow cannot be installed here, so this arm times the oracle port
-          (oracle/nerftex_oracle.py, NumPy + multithreaded BLAS) on a bounded ray subset.
+          TensorFlow cannot be installed here (and /root/reference is not on the GPU box), so this arm times the
+          oracle port (oracle/torch_port.py, torch-CPU fp32, all host threads) on a bounded ray subset.
 
-One process per GPU; for N > 1 launch with torch.distributed.run (weak scaling: every rank renders
-its own frame, no data-path collective).  Rank 0 prints ONE JSON line.
+One process per GPU; for N > 1 launch with torch.distributed.run.  Rank 0 prints ONE JSON line; N > 1 lines carry
+`checks` (sharded frame == single-GPU frame, all-reduced gradient == mean, replicas identical).  Both timed regions are
+bracketed by NVTX ranges (ntx_value_timed, ntx_e2e_timed) for `ncu --nvtx --nvtx-include`.
 """
 
 from __future__ import annotations
